@@ -1,0 +1,532 @@
+/* libhutoken_b200.so -- C-ABI implementation (include/hutoken_b200.h) and host orchestration.
+ *
+ * Replaces, for the encode path, hutoken's p_initialize / p_encode / p_batch_encode plumbing (lib.c) and its
+ * pthread task queue (taskqueue.c, lib.c:779-794): documents are sharded by bytes over the context's devices,
+ * each shard runs prep_kernel + the fused tile_kernel on its own stream; there is no collective.
+ * No CPU fallback: every id is produced by the kernels in hut_tile_kernel.cuh.
+ */
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#include "../../include/hutoken_b200.h"
+#include "hut_model.h"
+#include "hut_tile_kernel.cuh"
+
+using namespace hut;
+
+#define MAX_DEV 16
+
+struct hut_dev {
+    int device;
+    cudaStream_t stream;
+    DevModel dm;
+    void* allocs[24];
+    int nalloc;
+    CacheSlot* cache;
+    uint32_t cache_bits;
+    Counters* ctr;
+    Counters* h_ctr;  // pinned mirror
+    CutRanges* cut;
+    uint32_t* cta_scratch;
+    unsigned long long cta_scratch_words;
+    uint32_t med_cap, ovf_cap;
+    uint32_t* big_pool;
+    unsigned long long big_slot_words;
+    uint32_t big_cap, big_slots;
+    int grid;
+    // grow-only temporaries
+    unsigned long long* tile_state;
+    uint32_t* first_doc;
+    size_t tiles_cap, first_doc_cap;
+    Job job;  // the last launched shard
+    int32_t* cut_tmp;
+    size_t cut_tmp_cap;
+    // staging for the host-buffer API
+    uint8_t* d_text;
+    size_t d_text_cap;
+    unsigned long long* d_off;
+    size_t d_off_cap;
+    int32_t* d_ids;
+    size_t d_ids_cap;
+    unsigned long long* d_tok;
+    size_t d_tok_cap;
+    cudaEvent_t ev[3];
+    hut_stats stats;
+};
+
+struct hut_ctx {
+    hut_model* model;
+    int ndev;
+    hut_dev dev[MAX_DEV];
+    hut_options opt;
+    char err[512];
+    // pinned result of the host-buffer API
+    int32_t* h_ids;
+    size_t h_ids_cap;
+    unsigned long long* h_tok;
+    size_t h_tok_cap;
+    unsigned long long* h_off_stage;  // rebased doc offsets per shard
+    size_t h_off_cap;
+};
+
+static int set_err(hut_ctx* ctx, int status, const char* fmt, const char* a) {
+    if (ctx) snprintf(ctx->err, sizeof ctx->err, fmt, a);
+    return status;
+}
+
+#define CU(ctx, call)                                                                      \
+    do {                                                                                   \
+        cudaError_t e_ = (call);                                                           \
+        if (e_ != cudaSuccess) return set_err(ctx, HUT_STATUS_CUDA, "CUDA error: %s", cudaGetErrorString(e_)); \
+    } while (0)
+
+template <class T>
+static cudaError_t upload(hut_dev* d, const T* src, size_t n, const T** out) {
+    T* p = nullptr;
+    cudaError_t e = cudaMalloc(&p, (n ? n : 1) * sizeof(T));
+    if (e != cudaSuccess) return e;
+    if (n) e = cudaMemcpy(p, src, n * sizeof(T), cudaMemcpyHostToDevice);
+    d->allocs[d->nalloc++] = p;
+    *out = p;
+    return e;
+}
+
+static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
+    const hut_model* m = ctx->model;
+    memset(d, 0, sizeof *d);
+    d->device = device;
+    CU(ctx, cudaSetDevice(device));
+    CU(ctx, cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 3; ++i) CU(ctx, cudaEventCreate(&d->ev[i]));
+    DevModel& dm = d->dm;
+    CU(ctx, upload(d, (const unsigned long long*)m->pair_tab, m->pair_cap, &dm.pair_tab));
+    dm.pair_mask = m->pair_cap - 1;
+    CU(ctx, upload(d, m->out_id, m->n_units + 1, &dm.out_id));
+    CU(ctx, upload(d, m->rank_of, m->n_units + 1, &dm.rank_of));
+    dm.n_vocab = m->n_vocab;
+    dm.n_units = m->n_units;
+    dm.inert = m->inert;
+    dm.distinct_values = m->distinct_values;
+    dm.identity_ids = m->identity_ids;
+    dm.byte_mode = m->is_byte_encoder;
+    dm.multi_sym = m->max_sym_per_char > 1;
+    dm.has_prefix = m->has_prefix;
+    dm.cache_ok = ((long long)m->max_value + 2 < (1ll << 21)) ? 1 : 0;
+    dm.kmax = m->max_sym_per_char;
+    CU(ctx, upload(d, m->sym_off, 257, &dm.sym_off));
+    CU(ctx, upload(d, m->sym_pool, m->sym_off[256], &dm.sym_pool));
+    uint32_t byte1[256];
+    for (int b = 0; b < 256; ++b) {
+        uint32_t n = m->sym_off[b + 1] - m->sym_off[b];
+        if (n == 1) byte1[b] = m->sym_pool[m->sym_off[b]];
+        else if (n == 0) byte1[b] = m->is_byte_encoder ? m->inert : RAWCHAR;  // byte mode: only b == 0 has none
+        else byte1[b] = NONE;
+    }
+    CU(ctx, upload(d, byte1, 256, &dm.byte1));
+    CU(ctx, upload(d, m->ascii_unit, 128, &dm.ascii_unit));
+    if (m->char_cap) {
+        CU(ctx, upload(d, (const unsigned long long*)m->char_tab, m->char_cap, &dm.char_tab));
+        dm.char_mask = m->char_cap - 1;
+    } else {
+        dm.char_tab = nullptr;
+        dm.char_mask = 0;
+    }
+    CU(ctx, upload(d, m->prefix_syms, m->n_prefix_syms, &dm.prefix_syms));
+    dm.n_prefix_syms = m->n_prefix_syms;
+    CU(ctx, upload(d, m->prefix_alone_ids, m->n_prefix_alone, &dm.prefix_alone));
+    dm.n_prefix_alone = m->n_prefix_alone;
+    dm.compat_cut = ctx->opt.max_pretoken == 0;
+    dm.limit = ctx->opt.max_pretoken ? ctx->opt.max_pretoken : 262144ull;  // core.c:27-28
+
+    d->cache_bits = ctx->opt.cache_log2_slots ? ctx->opt.cache_log2_slots : 20;
+    if (d->cache_bits < 10) d->cache_bits = 10;
+    if (d->cache_bits > 26) d->cache_bits = 26;
+    CU(ctx, cudaMalloc(&d->cache, sizeof(CacheSlot) << d->cache_bits));
+    CU(ctx, cudaMemset(d->cache, 0, sizeof(CacheSlot) << d->cache_bits));
+    CU(ctx, cudaMalloc(&d->ctr, sizeof(Counters)));
+    CU(ctx, cudaMemset(d->ctr, 0, sizeof(Counters)));
+    CU(ctx, cudaMallocHost(&d->h_ctr, sizeof(Counters)));
+    CU(ctx, cudaMalloc(&d->cut, sizeof(CutRanges)));
+
+    int per_sm = 0, sms = 0;
+    CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile_kernel, NT, 0));
+    CU(ctx, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    if (per_sm < 1) per_sm = 1;
+    d->grid = per_sm * sms;
+
+    const uint32_t extra = m->n_prefix_syms + m->n_prefix_alone + 1;
+    d->med_cap = (uint32_t)SPAN * dm.kmax + m->n_prefix_syms + 64;
+    d->ovf_cap = (uint32_t)SPAN * (dm.kmax + extra) + 256;
+    d->cta_scratch_words = 4ull * d->med_cap + d->ovf_cap;
+    CU(ctx, cudaMalloc(&d->cta_scratch, d->cta_scratch_words * sizeof(uint32_t) * d->grid));
+    d->big_slots = ctx->opt.big_slots ? ctx->opt.big_slots : (ctx->opt.max_pretoken > (64ull << 20) ? 2 : 8);
+    if (d->big_slots > 32) d->big_slots = 32;
+    unsigned long long bc = dm.limit * dm.kmax + m->n_prefix_syms + 64;
+    if (bc > 0xFFFFFFF0ull) return set_err(ctx, HUT_STATUS_ARG, "%s", "max_pretoken too large");
+    d->big_cap = (uint32_t)bc;
+    d->big_slot_words = 4ull * d->big_cap;
+    CU(ctx, cudaMalloc(&d->big_pool, d->big_slot_words * sizeof(uint32_t) * d->big_slots));
+    return HUT_STATUS_OK;
+}
+
+static void dev_free(hut_dev* d) {
+    cudaSetDevice(d->device);
+    for (int i = 0; i < d->nalloc; ++i) cudaFree(d->allocs[i]);
+    cudaFree(d->cache);
+    cudaFree(d->ctr);
+    cudaFreeHost(d->h_ctr);
+    cudaFree(d->cut);
+    cudaFree(d->cta_scratch);
+    cudaFree(d->big_pool);
+    cudaFree(d->tile_state);
+    cudaFree(d->first_doc);
+    cudaFree(d->cut_tmp);
+    cudaFree(d->d_text);
+    cudaFree(d->d_off);
+    cudaFree(d->d_ids);
+    cudaFree(d->d_tok);
+    for (int i = 0; i < 3; ++i)
+        if (d->ev[i]) cudaEventDestroy(d->ev[i]);
+    if (d->stream) cudaStreamDestroy(d->stream);
+}
+
+extern "C" int hut_create(const hut_model_desc* desc, const hut_options* opt, const int* devices, int ndev,
+                          hut_ctx** out, char* err, size_t errlen) {
+    auto fail = [&](int st, const char* msg) {
+        if (err && errlen) snprintf(err, errlen, "%s", msg);
+        return st;
+    };
+    if (!desc || !out || !desc->vocab_file_path || !desc->special_file_path)
+        return fail(HUT_STATUS_ARG, "vocab_file_path and special_file_path are required");
+    if (desc->pattern) return fail(HUT_STATUS_UNSUPPORTED, "regex pattern pretokenisation is not supported by the B200 engine");
+    if (desc->merges_file_path) return fail(HUT_STATUS_UNSUPPORTED, "merges-file (id-keyed) encoding is not supported by the B200 engine");
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
+        return fail(HUT_STATUS_CUDA, "no CUDA device: the hutoken_b200 engine has no CPU fallback");
+    hut_ctx* ctx = (hut_ctx*)calloc(1, sizeof *ctx);
+    if (!ctx) return fail(HUT_STATUS_MEMORY, "out of memory");
+    if (opt) memcpy(&ctx->opt, opt, opt->struct_size < sizeof ctx->opt ? opt->struct_size : sizeof ctx->opt);
+    char msg[256] = "";
+    int rc = hut_model_load(&ctx->model, desc->vocab_file_path, desc->special_file_path, desc->prefix,
+                            desc->is_byte_encoder, msg, sizeof msg);
+    if (rc != HUT_OK) {
+        free(ctx);
+        return fail(rc, msg);
+    }
+    int devs[MAX_DEV];
+    if (!devices || ndev <= 0) {
+        const char* lr = getenv("LOCAL_RANK");
+        devs[0] = lr ? atoi(lr) % count : 0;
+        ndev = 1;
+    } else {
+        if (ndev > MAX_DEV) ndev = MAX_DEV;
+        for (int i = 0; i < ndev; ++i) devs[i] = devices[i];
+    }
+    for (int i = 0; i < ndev; ++i) {
+        if (devs[i] < 0 || devs[i] >= count) {
+            hut_destroy(ctx);
+            return fail(HUT_STATUS_ARG, "device index out of range");
+        }
+        rc = dev_init(ctx, &ctx->dev[i], devs[i]);
+        ctx->ndev = i + 1;
+        if (rc != HUT_STATUS_OK) {
+            fail(rc, ctx->err);
+            hut_destroy(ctx);
+            return rc;
+        }
+    }
+    *out = ctx;
+    return HUT_STATUS_OK;
+}
+
+extern "C" void hut_destroy(hut_ctx* ctx) {
+    if (!ctx) return;
+    for (int i = 0; i < ctx->ndev; ++i) dev_free(&ctx->dev[i]);
+    cudaFreeHost(ctx->h_ids);
+    cudaFreeHost(ctx->h_tok);
+    cudaFreeHost(ctx->h_off_stage);
+    hut_model_free(ctx->model);
+    free(ctx);
+}
+
+extern "C" const char* hut_last_error(const hut_ctx* ctx) { return ctx ? ctx->err : "no context"; }
+extern "C" uint32_t hut_vocab_lines(const hut_ctx* ctx) { return ctx ? ctx->model->vocab_lines : 0; }
+extern "C" int hut_device_count(const hut_ctx* ctx) { return ctx ? ctx->ndev : 0; }
+
+extern "C" void* hut_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) return nullptr;
+    return p;
+}
+extern "C" void hut_host_free(void* p) {
+    if (p) cudaFreeHost(p);
+}
+
+extern "C" int hut_cache_reset(hut_ctx* ctx) {
+    if (!ctx) return HUT_STATUS_STATE;
+    for (int i = 0; i < ctx->ndev; ++i) {
+        hut_dev* d = &ctx->dev[i];
+        CU(ctx, cudaSetDevice(d->device));
+        CU(ctx, cudaMemsetAsync(d->cache, 0, sizeof(CacheSlot) << d->cache_bits, d->stream));
+        CU(ctx, cudaStreamSynchronize(d->stream));
+    }
+    return HUT_STATUS_OK;
+}
+
+extern "C" int hut_get_stats(const hut_ctx* ctx, int dev_index, hut_stats* out) {
+    if (!ctx || dev_index < 0 || dev_index >= ctx->ndev || !out) return HUT_STATUS_ARG;
+    *out = ctx->dev[dev_index].stats;
+    return HUT_STATUS_OK;
+}
+
+template <class T>
+static cudaError_t grow(T** p, size_t* cap, size_t need) {
+    if (need <= *cap) return cudaSuccess;
+    if (*p) cudaFree(*p);
+    *p = nullptr;
+    *cap = 0;
+    size_t n = need + need / 8 + 1024;
+    cudaError_t e = cudaMalloc(p, n * sizeof(T));
+    if (e == cudaSuccess) *cap = n;
+    return e;
+}
+
+/* launches the kernels for one resident shard on `st`; the device must be current */
+static int launch_shard(hut_ctx* ctx, hut_dev* d, const uint8_t* d_bytes, uint64_t n_bytes, const uint64_t* d_doc_offsets,
+                        uint64_t n_docs, int32_t* d_ids, uint64_t ids_capacity, uint64_t* d_tok_offsets,
+                        cudaStream_t st) {
+    if (n_docs >= 0xFFFFFFF0ull) return set_err(ctx, HUT_STATUS_ARG, "%s", "too many documents in one shard");
+    if ((uintptr_t)d_bytes & 15) return set_err(ctx, HUT_STATUS_ARG, "%s", "device text buffer must be 16-byte aligned");
+    const uint64_t ntiles64 = (n_bytes + TILE - 1) / TILE;
+    if (ntiles64 >= 0xFFFFFFF0ull) return set_err(ctx, HUT_STATUS_ARG, "%s", "shard too large (max 16 TiB)");
+    const uint32_t ntiles = (uint32_t)ntiles64;
+    d->stats.kernel_launches = 0;
+    if (ntiles == 0) {
+        CU(ctx, cudaMemsetAsync(d_tok_offsets, 0, (n_docs + 1) * sizeof(uint64_t), st));
+        CU(ctx, cudaMemsetAsync(d->ctr, 0, offsetof(Counters, events), st));
+        CU(ctx, cudaEventRecord(d->ev[0], st));
+        CU(ctx, cudaEventRecord(d->ev[1], st));
+        CU(ctx, cudaEventRecord(d->ev[2], st));
+        return HUT_STATUS_OK;
+    }
+    CU(ctx, grow(&d->tile_state, &d->tiles_cap, (size_t)ntiles));
+    CU(ctx, grow(&d->first_doc, &d->first_doc_cap, (size_t)ntiles));
+    Job J;
+    memset(&J, 0, sizeof J);
+    J.text = d_bytes;
+    J.nbytes = n_bytes;
+    J.doc_off = (const unsigned long long*)d_doc_offsets;
+    J.ndocs = n_docs;
+    J.out = d_ids;
+    J.out_cap = ids_capacity;
+    J.tok_off = (unsigned long long*)d_tok_offsets;
+    J.ntiles = ntiles;
+    J.tile_state = d->tile_state;
+    J.first_doc = d->first_doc;
+    J.ctr = d->ctr;
+    J.cache = d->cache;
+    J.cache_bits = d->cache_bits;
+    J.cta_scratch = d->cta_scratch;
+    J.cta_scratch_words = d->cta_scratch_words;
+    J.med_cap = d->med_cap;
+    J.ovf_cap = d->ovf_cap;
+    J.big_pool = d->big_pool;
+    J.big_slot_words = d->big_slot_words;
+    J.big_cap = d->big_cap;
+    J.big_slots = d->big_slots;
+    CU(ctx, cudaEventRecord(d->ev[0], st));
+    prep_kernel<<<(ntiles + 255) / 256, 256, 0, st>>>(J);
+    CU(ctx, cudaEventRecord(d->ev[1], st));
+    int grid = d->grid < (int)ntiles ? d->grid : (int)ntiles;
+    tile_kernel<<<grid, NT, 0, st>>>(d->dm, J);
+    CU(ctx, cudaEventRecord(d->ev[2], st));
+    CU(ctx, cudaGetLastError());
+    d->stats.kernel_launches = 2;
+    d->job = J;
+    return HUT_STATUS_OK;
+}
+
+/* after the stream has been synchronised: read the counters, apply document cuts, fill stats */
+static int finish_shard(hut_ctx* ctx, hut_dev* d, uint64_t n_docs, int32_t* d_ids, uint64_t* d_tok_offsets,
+                        uint64_t* n_ids_out, cudaStream_t st) {
+    CU(ctx, cudaMemcpyAsync(d->h_ctr, d->ctr, offsetof(Counters, events), cudaMemcpyDeviceToHost, st));
+    CU(ctx, cudaStreamSynchronize(st));
+    const Counters* c = d->h_ctr;
+    float ms_all = 0, ms_main = 0;
+    cudaEventElapsedTime(&ms_all, d->ev[0], d->ev[2]);
+    cudaEventElapsedTime(&ms_main, d->ev[1], d->ev[2]);
+    d->stats.pretokens = c->st_pretokens;
+    d->stats.cache_hits = c->st_hits;
+    d->stats.warp_merges = c->st_warp;
+    d->stats.block_merges = c->st_block;
+    d->stats.big_merges = c->st_big;
+    d->stats.cut_documents = 0;
+    d->stats.kernel_ms = ms_all;
+    d->stats.main_kernel_ms = ms_main;
+    uint64_t total = c->total_ids;
+    if (c->flags & FLAG_OUT_CAP) return set_err(ctx, HUT_STATUS_CAPACITY, "%s", "output id buffer too small");
+    if (c->flags & FLAG_BIG_CAP)
+        return set_err(ctx, HUT_STATUS_UNSUPPORTED, "%s", "a pretoken exceeds the configured max_pretoken working area");
+    if (c->flags & FLAG_EVENTS)
+        return set_err(ctx, HUT_STATUS_UNSUPPORTED, "%s", "too many over-long pretokens in one call");
+    if (c->flags & FLAG_NUL)
+        return set_err(ctx, HUT_STATUS_VALUE, "%s", "document contains a 0x00 byte (cut documents at NUL before calling)");
+    if (c->n_events) {
+        // reference-compatible cut (core.c:402-407,503): drop the rest of each affected document
+        CU(ctx, grow(&d->cut_tmp, &d->cut_tmp_cap, (size_t)total));
+        CU(ctx, cudaMemcpyAsync(d->cut_tmp, d_ids, total * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+        cut_prepare_kernel<<<1, 1, 0, st>>>(d->job, d->cut);
+        cut_apply_ids_kernel<<<592, 256, 0, st>>>(d->cut_tmp, d_ids, total, d->cut);
+        cut_apply_offs_kernel<<<148, 256, 0, st>>>((unsigned long long*)d_tok_offsets, n_docs + 1, d->cut);
+        CU(ctx, cudaGetLastError());
+        CutRanges head;
+        CU(ctx, cudaMemcpyAsync(&head, d->cut, offsetof(CutRanges, x), cudaMemcpyDeviceToHost, st));
+        CU(ctx, cudaStreamSynchronize(st));
+        total = head.new_total;
+        d->stats.cut_documents = head.n;
+        d->stats.kernel_launches += 3;
+    }
+    *n_ids_out = total;
+    return HUT_STATUS_OK;
+}
+
+extern "C" int hut_encode_device(hut_ctx* ctx, int dev_index, const uint8_t* d_bytes, uint64_t n_bytes,
+                                 const uint64_t* d_doc_offsets, uint64_t n_docs, int32_t* d_ids,
+                                 uint64_t ids_capacity, uint64_t* d_tok_offsets, uint64_t* n_ids_out, void* stream) {
+    if (!ctx) return HUT_STATUS_STATE;
+    if (dev_index < 0 || dev_index >= ctx->ndev || !n_ids_out || !d_doc_offsets || !d_tok_offsets)
+        return set_err(ctx, HUT_STATUS_ARG, "%s", "bad argument");
+    hut_dev* d = &ctx->dev[dev_index];
+    CU(ctx, cudaSetDevice(d->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : d->stream;
+    int rc = launch_shard(ctx, d, d_bytes, n_bytes, d_doc_offsets, n_docs, d_ids, ids_capacity, d_tok_offsets, st);
+    if (rc != HUT_STATUS_OK) return rc;
+    return finish_shard(ctx, d, n_docs, d_ids, d_tok_offsets, n_ids_out, st);
+}
+
+template <class T>
+static cudaError_t grow_host(T** p, size_t* cap, size_t need, bool keep) {
+    if (need <= *cap) return cudaSuccess;
+    size_t n = need + need / 4 + 4096;
+    T* q = nullptr;
+    cudaError_t e = cudaMallocHost(&q, n * sizeof(T));
+    if (e != cudaSuccess) return e;
+    if (*p) {
+        if (keep) memcpy(q, *p, *cap * sizeof(T));
+        cudaFreeHost(*p);
+    }
+    *p = q;
+    *cap = n;
+    return cudaSuccess;
+}
+
+/* Shards [doc_lo, doc_hi) of the batch onto one device and leaves ids / offsets on the device. */
+struct shard_plan {
+    uint64_t doc_lo, doc_hi, byte_lo, byte_hi, n_ids;
+};
+
+extern "C" int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64_t* doc_offsets, uint64_t n_docs,
+                                hut_result* result) {
+    if (!ctx) return HUT_STATUS_STATE;
+    if (!result || !doc_offsets || (n_docs && !bytes && doc_offsets[n_docs] != doc_offsets[0]))
+        return set_err(ctx, HUT_STATUS_ARG, "%s", "bad argument");
+    memset(result, 0, sizeof *result);
+    const uint64_t b0 = doc_offsets[0], b1 = doc_offsets[n_docs];
+    const uint64_t total_bytes = b1 - b0;
+    // ---- plan: contiguous document ranges balanced by bytes, one per device ----
+    int nsh = ctx->ndev;
+    if ((uint64_t)nsh > n_docs) nsh = n_docs ? (int)n_docs : 1;
+    shard_plan plan[MAX_DEV];
+    {
+        uint64_t d = 0;
+        for (int s = 0; s < nsh; ++s) {
+            plan[s].doc_lo = d;
+            uint64_t target = b0 + (total_bytes * (uint64_t)(s + 1)) / (uint64_t)nsh;
+            if (s == nsh - 1) d = n_docs;
+            else {
+                uint64_t lo = d, hi = n_docs;  // first doc boundary >= target
+                while (lo < hi) {
+                    uint64_t mid = (lo + hi) >> 1;
+                    if (doc_offsets[mid] < target) lo = mid + 1;
+                    else hi = mid;
+                }
+                d = lo;
+            }
+            plan[s].doc_hi = d;
+            plan[s].byte_lo = doc_offsets[plan[s].doc_lo];
+            plan[s].byte_hi = doc_offsets[plan[s].doc_hi];
+            plan[s].n_ids = 0;
+        }
+    }
+    CU(ctx, grow_host(&ctx->h_tok, &ctx->h_tok_cap, (size_t)n_docs + 1, false));
+    CU(ctx, grow_host(&ctx->h_off_stage, &ctx->h_off_cap, (size_t)n_docs + (size_t)nsh + 1, false));
+    // ---- phase A: upload + kernels on every device ----
+    uint64_t stage_at = 0;
+    uint64_t stage_pos[MAX_DEV];
+    for (int s = 0; s < nsh; ++s) {
+        hut_dev* d = &ctx->dev[s];
+        const shard_plan& p = plan[s];
+        const uint64_t nb = p.byte_hi - p.byte_lo, nd = p.doc_hi - p.doc_lo;
+        CU(ctx, cudaSetDevice(d->device));
+        CU(ctx, grow(&d->d_text, &d->d_text_cap, (size_t)nb + 64));
+        CU(ctx, grow(&d->d_off, &d->d_off_cap, (size_t)nd + 1));
+        CU(ctx, grow(&d->d_tok, &d->d_tok_cap, (size_t)nd + 1));
+        // worst case: every symbol survives as its own id (+ prefix ids per document)
+        const uint64_t worst = nb * d->dm.kmax + nd * (uint64_t)(d->dm.n_prefix_syms + d->dm.n_prefix_alone) + 64;
+        CU(ctx, grow(&d->d_ids, &d->d_ids_cap, (size_t)worst));
+        unsigned long long* ho = ctx->h_off_stage + stage_at;
+        stage_pos[s] = stage_at;
+        for (uint64_t i = 0; i <= nd; ++i) ho[i] = doc_offsets[p.doc_lo + i] - p.byte_lo;
+        stage_at += nd + 1;
+        if (nb) CU(ctx, cudaMemcpyAsync(d->d_text, bytes + p.byte_lo, nb, cudaMemcpyHostToDevice, d->stream));
+        CU(ctx, cudaMemcpyAsync(d->d_off, ho, (nd + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, d->stream));
+        int rc = launch_shard(ctx, d, d->d_text, nb, (const uint64_t*)d->d_off, nd, d->d_ids, d->d_ids_cap,
+                              (uint64_t*)d->d_tok, d->stream);
+        if (rc != HUT_STATUS_OK) return rc;
+    }
+    // ---- phase B: counts, then ids straight into the final pinned buffer ----
+    uint64_t total_ids = 0;
+    for (int s = 0; s < nsh; ++s) {
+        hut_dev* d = &ctx->dev[s];
+        CU(ctx, cudaSetDevice(d->device));
+        int rc = finish_shard(ctx, d, plan[s].doc_hi - plan[s].doc_lo, d->d_ids, (uint64_t*)d->d_tok, &plan[s].n_ids,
+                              d->stream);
+        if (rc != HUT_STATUS_OK) return rc;
+        total_ids += plan[s].n_ids;
+    }
+    CU(ctx, grow_host(&ctx->h_ids, &ctx->h_ids_cap, (size_t)total_ids + 1, false));
+    uint64_t id_base = 0;
+    for (int s = 0; s < nsh; ++s) {
+        hut_dev* d = &ctx->dev[s];
+        const uint64_t nd = plan[s].doc_hi - plan[s].doc_lo;
+        CU(ctx, cudaSetDevice(d->device));
+        if (plan[s].n_ids)
+            CU(ctx, cudaMemcpyAsync(ctx->h_ids + id_base, d->d_ids, plan[s].n_ids * sizeof(int32_t),
+                                    cudaMemcpyDeviceToHost, d->stream));
+        CU(ctx, cudaMemcpyAsync(ctx->h_tok + plan[s].doc_lo, d->d_tok, (nd + 1) * sizeof(uint64_t),
+                                cudaMemcpyDeviceToHost, d->stream));
+        id_base += plan[s].n_ids;
+    }
+    id_base = 0;
+    for (int s = 0; s < nsh; ++s) {
+        hut_dev* d = &ctx->dev[s];
+        CU(ctx, cudaSetDevice(d->device));
+        CU(ctx, cudaStreamSynchronize(d->stream));
+    }
+    // per-shard offsets are local: add each shard's base (host side, one add per document -- 8(e))
+    for (int s = 0; s < nsh; ++s) {
+        if (id_base)
+            for (uint64_t i = plan[s].doc_lo; i < plan[s].doc_hi; ++i) ctx->h_tok[i] += id_base;
+        id_base += plan[s].n_ids;
+    }
+    ctx->h_tok[n_docs] = total_ids;
+    result->ids = ctx->h_ids;
+    result->tok_offsets = (const uint64_t*)ctx->h_tok;
+    result->n_ids = total_ids;
+    result->n_docs = n_docs;
+    (void)stage_pos;
+    return HUT_STATUS_OK;
+}

@@ -1,0 +1,264 @@
+/* `_hutoken` CPython extension for the B200 engine -- same module name, method table, argument formats,
+ * defaults and error strings as the reference extension (src/lib.c:185-232, 668-874, 1128-1153), so that
+ * hutoken.py's surface (initialize / encode / batch_encode) works unchanged on top of it.
+ * All tokenisation happens in libhutoken_b200.so (include/hutoken_b200.h); this file only converts
+ * between Python objects and packed buffers.
+ */
+#define PY_SSIZE_T_CLEAN
+#include <Python.h>
+#include <string.h>
+
+#include "../../include/hutoken_b200.h"
+
+static hut_ctx* g_ctx = NULL; /* one live model per process, like lib.c:73-74 */
+static uint8_t* g_pack = NULL; /* pinned packing buffer (grow-only) */
+static size_t g_pack_cap = 0;
+static uint64_t* g_offs = NULL;
+static size_t g_offs_cap = 0;
+
+static const char* NOT_INIT_ENC =
+    "Vocabulary is not initialized for encoding. Call 'initialize_encode' function first."; /* lib.c:671-676 */
+static const char* NOT_INIT_DEC =
+    "Vocabulary is not initialized for decoding. Call 'initialize_decode' function first.";
+
+static PyObject* raise_status(int status, const char* msg) {
+    PyObject* type = PyExc_RuntimeError;
+    switch (status) {
+        case HUT_STATUS_FILE_NOT_FOUND: type = PyExc_FileNotFoundError; break;
+        case HUT_STATUS_VALUE: type = PyExc_ValueError; break;
+        case HUT_STATUS_MEMORY: type = PyExc_MemoryError; break;
+        case HUT_STATUS_ARG: type = PyExc_ValueError; break;
+        default: break;
+    }
+    PyErr_SetString(type, msg && msg[0] ? msg : "hutoken_b200 engine error");
+    return NULL;
+}
+
+static int ensure_pack(size_t bytes, size_t ndocs) {
+    if (bytes + 64 > g_pack_cap) {
+        size_t cap = bytes + bytes / 4 + (1u << 16);
+        uint8_t* p = hut_host_alloc(cap);
+        if (!p) return 0;
+        hut_host_free(g_pack);
+        g_pack = p;
+        g_pack_cap = cap;
+    }
+    if (ndocs + 2 > g_offs_cap) {
+        size_t cap = ndocs + ndocs / 4 + 1024;
+        uint64_t* p = hut_host_alloc(cap * sizeof(uint64_t));
+        if (!p) return 0;
+        hut_host_free(g_offs);
+        g_offs = p;
+        g_offs_cap = cap;
+    }
+    return 1;
+}
+
+/* initialize(vocab_file_path, special_file_path, prefix=None, is_byte_encoder=False, special_token_id=-1,
+ *            pattern=None, merges_file_path=None)   -- lib.c:185-232, format "ss|zpizz" */
+static PyObject* p_initialize(PyObject* self, PyObject* args, PyObject* kwargs) {
+    static char* kwlist[] = {"vocab_file_path", "special_file_path", "prefix", "is_byte_encoder",
+                             "special_token_id", "pattern", "merges_file_path", NULL};
+    char *vocab = NULL, *special = NULL, *prefix = NULL, *pattern = NULL, *merges = NULL;
+    int is_byte_encoder = 0, special_token_id = -1;
+    if (!PyArg_ParseTupleAndKeywords(args, kwargs, "ss|zpizz", kwlist, &vocab, &special, &prefix, &is_byte_encoder,
+                                     &special_token_id, &pattern, &merges)) {
+        PyErr_SetString(PyExc_TypeError,
+                        "Invalid arguments. Expected a string "
+                        "(vocab_file_path), a string (special_file_path), "
+                        "a string or None (prefix) a bool an"
+                        "optional integer (special_token_id), "
+                        " an optional string (regex_pattern) and"
+                        "a string or None (merges_file_path)");
+        return NULL;
+    }
+    hut_model_desc desc = {vocab, special, prefix, is_byte_encoder, special_token_id, pattern, merges};
+    hut_options opt;
+    memset(&opt, 0, sizeof opt);
+    opt.struct_size = sizeof opt;
+    const char* nl = getenv("HUTOKEN_B200_MAX_PRETOKEN"); /* opt-in "no-limit" mode, SURVEY.md 8(c) */
+    if (nl) opt.max_pretoken = strtoull(nl, NULL, 10);
+    /* HUTOKEN_B200_DEVICES="0,1,2,3": shard batch_encode over several GPUs of the box */
+    int devs[16], nd = 0;
+    const char* dv = getenv("HUTOKEN_B200_DEVICES");
+    if (dv) {
+        const char* p = dv;
+        while (*p && nd < 16) {
+            char* e = NULL;
+            long v = strtol(p, &e, 10);
+            if (e == p) break;
+            devs[nd++] = (int)v;
+            p = (*e == ',') ? e + 1 : e;
+        }
+    }
+    char err[512] = "";
+    hut_ctx* ctx = NULL;
+    int rc;
+    Py_BEGIN_ALLOW_THREADS
+    rc = hut_create(&desc, &opt, nd ? devs : NULL, nd, &ctx, err, sizeof err);
+    Py_END_ALLOW_THREADS
+    if (rc != HUT_STATUS_OK) return raise_status(rc, err);
+    if (g_ctx) hut_destroy(g_ctx); /* re-initialise replaces the model (the reference leaks it, lib.c:129-145) */
+    g_ctx = ctx;
+    Py_RETURN_NONE;
+}
+
+static PyObject* ids_to_list(const int32_t* ids, uint64_t n) {
+    PyObject* list = PyList_New((Py_ssize_t)n);
+    if (!list) return PyErr_NoMemory();
+    for (uint64_t i = 0; i < n; ++i) {
+        PyObject* v = PyLong_FromLong(ids[i]);
+        if (!v) {
+            Py_DECREF(list);
+            return PyErr_NoMemory();
+        }
+        PyList_SET_ITEM(list, (Py_ssize_t)i, v);
+    }
+    return list;
+}
+
+/* encode(text) -- lib.c:668-720, format "s" (rejects embedded NUL like the reference) */
+static PyObject* p_encode(PyObject* self, PyObject* args) {
+    if (!g_ctx) {
+        PyErr_SetString(PyExc_RuntimeError, NOT_INIT_ENC);
+        return NULL;
+    }
+    char* text = NULL;
+    if (!PyArg_ParseTuple(args, "s", &text)) return NULL;
+    size_t len = strlen(text);
+    if (!ensure_pack(len, 1)) return PyErr_NoMemory();
+    memcpy(g_pack, text, len);
+    g_offs[0] = 0;
+    g_offs[1] = len;
+    hut_result res;
+    int rc;
+    Py_BEGIN_ALLOW_THREADS
+    rc = hut_encode_batch(g_ctx, g_pack, g_offs, 1, &res);
+    Py_END_ALLOW_THREADS
+    if (rc != HUT_STATUS_OK) return raise_status(rc, hut_last_error(g_ctx));
+    return ids_to_list(res.ids, res.n_ids);
+}
+
+/* batch_encode(texts, num_threads=1) -- lib.c:722-874, format "O|i".  num_threads only keeps its one
+ * observable effect: <= 0 workers encode nothing (lib.c:779-794). */
+static PyObject* p_batch_encode(PyObject* self, PyObject* args) {
+    if (!g_ctx) {
+        PyErr_SetString(PyExc_RuntimeError, NOT_INIT_ENC);
+        return NULL;
+    }
+    PyObject* texts = NULL;
+    int num_threads = 1;
+    if (!PyArg_ParseTuple(args, "O|i", &texts, &num_threads) || !PyList_Check(texts)) {
+        PyErr_SetString(PyExc_TypeError, "Invalid arguments. Expected a list of strings.");
+        return NULL;
+    }
+    Py_ssize_t n = PyList_GET_SIZE(texts);
+    if (num_threads <= 0) {
+        PyObject* result = PyList_New(n);
+        if (!result) return PyErr_NoMemory();
+        for (Py_ssize_t i = 0; i < n; ++i) PyList_SET_ITEM(result, i, PyList_New(0));
+        return result;
+    }
+    /* pass 1: sizes (each text is cut at its first NUL, like strdup at lib.c:772) */
+    size_t total = 0;
+    for (Py_ssize_t i = 0; i < n; ++i) {
+        const char* s = PyUnicode_AsUTF8(PyList_GET_ITEM(texts, i));
+        if (!s) {
+            PyErr_SetString(PyExc_TypeError, "Invalid arguments. Expected a list of strings.");
+            return NULL;
+        }
+        total += strlen(s);
+    }
+    if (!ensure_pack(total, (size_t)n)) return PyErr_NoMemory();
+    size_t at = 0;
+    for (Py_ssize_t i = 0; i < n; ++i) {
+        const char* s = PyUnicode_AsUTF8(PyList_GET_ITEM(texts, i));
+        size_t l = strlen(s);
+        g_offs[i] = at;
+        memcpy(g_pack + at, s, l);
+        at += l;
+    }
+    g_offs[n] = at;
+    hut_result res;
+    int rc;
+    Py_BEGIN_ALLOW_THREADS
+    rc = hut_encode_batch(g_ctx, g_pack, g_offs, (uint64_t)n, &res);
+    Py_END_ALLOW_THREADS
+    if (rc != HUT_STATUS_OK) return raise_status(rc, hut_last_error(g_ctx));
+    PyObject* result = PyList_New(n);
+    if (!result) return PyErr_NoMemory();
+    for (Py_ssize_t i = 0; i < n; ++i) {
+        PyObject* sub = ids_to_list(res.ids + res.tok_offsets[i], res.tok_offsets[i + 1] - res.tok_offsets[i]);
+        if (!sub) {
+            Py_DECREF(result);
+            return NULL;
+        }
+        PyList_SET_ITEM(result, i, sub);
+    }
+    return result;
+}
+
+/* batch_encode_packed(texts) -> (ids: bytes of int32, offsets: bytes of uint64): zero-object output for
+ * callers that do not want one PyLong per token. */
+static PyObject* p_batch_encode_packed(PyObject* self, PyObject* args) {
+    if (!g_ctx) {
+        PyErr_SetString(PyExc_RuntimeError, NOT_INIT_ENC);
+        return NULL;
+    }
+    Py_buffer data, offs;
+    if (!PyArg_ParseTuple(args, "y*y*", &data, &offs)) return NULL;
+    PyObject* out = NULL;
+    if (offs.len < 8 || (offs.len % 8) != 0) {
+        PyErr_SetString(PyExc_ValueError, "offsets must be a uint64 buffer with n_docs + 1 entries");
+    } else {
+        uint64_t nd = (uint64_t)offs.len / 8 - 1;
+        const uint64_t* o = (const uint64_t*)offs.buf;
+        if (o[nd] > (uint64_t)data.len) {
+            PyErr_SetString(PyExc_ValueError, "offsets exceed the data buffer");
+        } else {
+            hut_result res;
+            int rc;
+            Py_BEGIN_ALLOW_THREADS
+            rc = hut_encode_batch(g_ctx, (const uint8_t*)data.buf, o, nd, &res);
+            Py_END_ALLOW_THREADS
+            if (rc != HUT_STATUS_OK) raise_status(rc, hut_last_error(g_ctx));
+            else
+                out = Py_BuildValue("(y#y#)", (const char*)res.ids, (Py_ssize_t)(res.n_ids * 4),
+                                    (const char*)res.tok_offsets, (Py_ssize_t)((nd + 1) * 8));
+        }
+    }
+    PyBuffer_Release(&data);
+    PyBuffer_Release(&offs);
+    return out;
+}
+
+static PyObject* p_decode(PyObject* self, PyObject* args) {
+    if (!g_ctx) {
+        PyErr_SetString(PyExc_RuntimeError, NOT_INIT_DEC);
+        return NULL;
+    }
+    PyErr_SetString(PyExc_RuntimeError,
+                    "decode is outside the B200 encode engine's scope (SURVEY.md 8(f) N1: next row)");
+    return NULL;
+}
+
+static PyObject* p_out_of_scope(PyObject* self, PyObject* args) {
+    PyErr_SetString(PyExc_RuntimeError, "offline trainers are outside the B200 encode engine's scope (SURVEY.md 2)");
+    return NULL;
+}
+
+static PyMethodDef methods[] = {
+    {"bpe_train", p_out_of_scope, METH_VARARGS, "BPE training (not provided by the B200 engine)"},
+    {"bbpe_train", p_out_of_scope, METH_VARARGS, "BBPE training (not provided by the B200 engine)"},
+    {"initialize", (PyCFunction)p_initialize, METH_VARARGS | METH_KEYWORDS, "Initalize tokenizer"},
+    {"encode", p_encode, METH_VARARGS, "Encodes string"},
+    {"batch_encode", p_batch_encode, METH_VARARGS, "Encodes list of strings"},
+    {"batch_encode_packed", p_batch_encode_packed, METH_VARARGS, "Encodes packed documents into packed ids"},
+    {"decode", p_decode, METH_VARARGS, "Decodes list of ints"},
+    {"batch_decode", p_decode, METH_VARARGS, "Decodes list of lists of ints"},
+    {NULL, NULL, 0, NULL}};
+
+static struct PyModuleDef moduledef = {PyModuleDef_HEAD_INIT, "huToken", "B200-native hutoken encode engine", -1,
+                                       methods};
+
+PyMODINIT_FUNC PyInit__hutoken(void) { return PyModule_Create(&moduledef); }

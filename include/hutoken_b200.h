@@ -1,0 +1,113 @@
+/* hutoken_b200 -- C-ABI of the B200-native BPE encode engine (libhutoken_b200.so).
+ *
+ * Drop-in boundary: the seam between hutoken's CPython layer and its core,
+ *     void encode(struct EncodeTask*)            reference include/hutoken/core.h:11
+ *     struct EncodeTask / struct EncodeContext   reference include/hutoken/taskqueue.h:16-25,40-45
+ * called per document from p_encode (src/lib.c:692-697) and from the batch_encode worker threads
+ * (src/lib.c:48-57, 779-794).  The functions below are what a cgo/ctypes/CPython binding of that path
+ * binds instead; INTEGRATION.md shows the binding.  Plain C types only: no torch, no C++ in signatures.
+ *
+ * All work runs in sm_100a CUDA kernels.  There is NO CPU fallback: without a CUDA device hut_create fails.
+ */
+#ifndef HUTOKEN_B200_H
+#define HUTOKEN_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct hut_ctx hut_ctx;
+
+/* status / error classes (mapped to Python exception types by the _hutoken extension) */
+#define HUT_STATUS_OK 0
+#define HUT_STATUS_FILE_NOT_FOUND 1 /* FileNotFoundError  (lib.c:248, 466) */
+#define HUT_STATUS_VALUE 2          /* ValueError         (lib.c:277-355, 494-543) */
+#define HUT_STATUS_MEMORY 3         /* MemoryError */
+#define HUT_STATUS_CUDA 4           /* RuntimeError: CUDA failure / no device */
+#define HUT_STATUS_UNSUPPORTED 5    /* RuntimeError: accepted by the reference, outside this engine's scope */
+#define HUT_STATUS_ARG 6            /* bad argument */
+#define HUT_STATUS_STATE 7          /* not initialised */
+#define HUT_STATUS_CAPACITY 8       /* caller-provided output buffer too small */
+
+/* Mirrors the arguments of hutoken.initialize / _hutoken.initialize (lib.c:185-232, format "ss|zpizz"). */
+typedef struct hut_model_desc {
+    const char* vocab_file_path;   /* "(0xHH)+ == <id>" lines, reference README.md:260-319 */
+    const char* special_file_path; /* "<byte> == <replacement>" lines; mandatory like the reference (lib.c:203) */
+    const char* prefix;            /* NULL or e.g. U+2581 for sentencepiece-style vocabularies */
+    int is_byte_encoder;           /* GPT-2 byte-level mode (pretokenizer.c:138-146) */
+    int special_token_id;          /* parsed and unused by the reference (lib.c:197); ignored */
+    const char* pattern;           /* regex pretokenisation (core.c:352-399): must be NULL -> HUT_STATUS_UNSUPPORTED */
+    const char* merges_file_path;  /* id-keyed merge path (core.c:211-337): must be NULL -> HUT_STATUS_UNSUPPORTED */
+} hut_model_desc;
+
+typedef struct hut_options {
+    uint32_t struct_size;      /* sizeof(hut_options), for forward compatibility */
+    uint32_t cache_log2_slots; /* unique-pretoken cache size; 0 = default (2^20 slots of 32 B per device) */
+    uint64_t max_pretoken;     /* 0 = reference-compatible: a document is cut at its first pretoken longer than
+                                  262144 bytes (core.c:27-28,402-407,503).  Otherwise: no cut; pretokens up to this
+                                  many bytes are merged (block-cooperative path), longer ones are an error. */
+    uint32_t big_slots;        /* working areas for pretokens that outgrow a tile; 0 = default */
+    uint32_t reserved;
+} hut_options;
+
+/* Replaces p_initialize (lib.c:185-666) + initialize_context (lib.c:128-183): loads the files, derives the
+ * device tables and uploads them to every device in `devices` (NULL/0 = device 0 only, or the device named by
+ * LOCAL_RANK when set).  On failure returns a status and writes the reference's message text into err. */
+int hut_create(const hut_model_desc* desc, const hut_options* opt, const int* devices, int ndev, hut_ctx** out,
+               char* err, size_t errlen);
+void hut_destroy(hut_ctx* ctx);
+const char* hut_last_error(const hut_ctx* ctx);
+
+typedef struct hut_result {
+    const int32_t* ids;          /* n_ids token ids; may contain -1 (unknown symbol, core.c:207) */
+    const uint64_t* tok_offsets; /* n_docs + 1: ids of document d are ids[tok_offsets[d] .. tok_offsets[d+1]) */
+    uint64_t n_ids;
+    uint64_t n_docs;
+} hut_result;
+
+/* Replaces the per-document encode() loop of p_batch_encode (lib.c:722-874) / p_encode (lib.c:668-720).
+ * Host buffers: documents are bytes[doc_offsets[i] .. doc_offsets[i+1]) (UTF-8, packed, no separators).
+ * A document is cut at its first 0x00 byte like the reference's strdup (lib.c:772).  Documents are sharded
+ * by bytes over the context's devices; there is no inter-device communication.  The result lives in
+ * pinned host memory owned by the context and stays valid until the next call on this context. */
+int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64_t* doc_offsets, uint64_t n_docs,
+                     hut_result* result);
+
+/* Same path with every buffer already resident on device `dev_index` of the context (benchmark / pipeline use):
+ * d_bytes must be 16-byte aligned; d_ids holds ids_capacity entries, d_tok_offsets n_docs+1 entries.
+ * stream is a cudaStream_t (NULL = the context's own stream).  Returns after the ids are complete on device. */
+int hut_encode_device(hut_ctx* ctx, int dev_index, const uint8_t* d_bytes, uint64_t n_bytes,
+                      const uint64_t* d_doc_offsets, uint64_t n_docs, int32_t* d_ids, uint64_t ids_capacity,
+                      uint64_t* d_tok_offsets, uint64_t* n_ids_out, void* stream);
+
+/* Drops the unique-pretoken cache of every device (it otherwise persists across calls). */
+int hut_cache_reset(hut_ctx* ctx);
+
+/* pinned host memory helpers for callers that want zero-staging H2D copies */
+void* hut_host_alloc(size_t bytes);
+void hut_host_free(void* p);
+
+typedef struct hut_stats {
+    uint64_t pretokens;     /* pretokens seen by the last call */
+    uint64_t cache_hits;    /* answered by the unique-pretoken cache */
+    uint64_t warp_merges;   /* merged by the warp-per-pretoken path */
+    uint64_t block_merges;  /* merged by the block-cooperative path */
+    uint64_t big_merges;    /* ... of which outgrew a tile (global working area) */
+    uint64_t cut_documents; /* documents cut at an over-long pretoken (reference-compatible mode) */
+    uint64_t kernel_launches; /* kernels launched by the last call */
+    double kernel_ms;       /* device time of the last call's kernels (CUDA events on the launch stream) */
+    double main_kernel_ms;  /* ... of which the fused tile kernel */
+} hut_stats;
+int hut_get_stats(const hut_ctx* ctx, int dev_index, hut_stats* out);
+
+/* model introspection (used by decode-side callers and tests) */
+uint32_t hut_vocab_lines(const hut_ctx* ctx); /* vocab_size_decode of the reference (lib.c:378) */
+int hut_device_count(const hut_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,136 @@
+/* TEST-ONLY scalar driver for the engine's HOST-side pieces: hut_model.c (loaders + derived unit / pair /
+ * symbol tables) and hut_classify.h (local pretoken-start rule).  It walks one document with the same tables the
+ * CUDA kernels read, so `pytest -m "not gpu"` can check table construction and boundary
+ * classification against the oracle without a GPU.  It is NOT part of libhutoken_b200.so and is never a
+ * fallback: the shipped library has no CPU encode path.
+ */
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "../hutoken_b200/csrc/hut_classify.h"
+#include "../hutoken_b200/csrc/hut_model.h"
+
+#define NONE HUT_UNIT_MASK
+
+/* class codes + start flags of one document; returns number of pretokens, starts[] filled */
+size_t harness_pretokens(const uint8_t* t, size_t n, uint32_t* starts, size_t cap) {
+    uint8_t* code = calloc(n + 8, 1);
+    for (size_t i = 0; i < n; ++i) {
+        uint32_t b1 = i + 1 < n ? t[i + 1] : 0, b2 = i + 2 < n ? t[i + 2] : 0, b3 = i + 3 < n ? t[i + 3] : 0;
+        uint32_t r = hut_lead_class(t[i], b1, b2, b3);
+        code[i] = (uint8_t)((r & 15u) | (((r >> 4) - 1u) << 4));
+    }
+    for (size_t i = 0; i < n; ++i) {
+        uint32_t extra = (code[i] >> 4) & 3u;
+        if ((code[i] & 7u) == HC_CONT) continue;
+        for (uint32_t k = 1; k <= extra && i + k < n; ++k) code[i + k] = HC_CONT;
+    }
+    size_t cnt = 0;
+    for (size_t i = 0; i < n; ++i) {
+        uint32_t c = code[i] & 7u;
+        if (c == HC_END) break; /* NUL ends the document */
+        if (c == HC_CONT) continue;
+        uint32_t p1 = i ? (code[i - 1] & 7u) : HC_END;
+        uint32_t pc = p1;
+        for (int k = 2; pc == HC_CONT && k <= 4 && (size_t)k <= i; ++k) pc = code[i - k] & 7u;
+        int lone = (i == 1) || (i >= 2 && (code[i - 2] & 7u) != HC_SPACE);
+        if (hut_is_start(c, i == 0, p1, pc, lone)) {
+            if (cnt < cap) starts[cnt] = (uint32_t)i;
+            cnt++;
+        }
+    }
+    free(code);
+    return cnt;
+}
+
+static uint32_t rank_of(const hut_model* m, uint32_t mg) { return mg == NONE ? 0xFFFFFFFFu : (uint32_t)m->rank_of[mg]; }
+
+/* symbols of pretoken t[s..e) into u[]; returns count */
+static size_t symbols(const hut_model* m, const uint8_t* t, size_t s, size_t e, uint32_t* u) {
+    size_t cnt = 0;
+    for (size_t p = s; p < e; ++p) {
+        uint8_t b = t[p];
+        if (!m->is_byte_encoder && p != s && (b & 0xC0) == 0x80) continue;
+        uint32_t lo = m->sym_off[b], hi = m->sym_off[b + 1];
+        if (hi > lo) {
+            for (uint32_t k = lo; k < hi; ++k) u[cnt++] = m->sym_pool[k];
+        } else if (m->is_byte_encoder) {
+            u[cnt++] = m->inert;
+        } else {
+            size_t l = 1;
+            while (l < 4 && p + l < e && (t[p + l] & 0xC0) == 0x80) l++;
+            u[cnt++] = hut_model_char_lookup(m, t + p, (uint32_t)l);
+        }
+    }
+    return cnt;
+}
+
+static size_t merge(const hut_model* m, uint32_t* u, size_t n) {
+    for (;;) {
+        uint32_t best = 0xFFFFFFFFu, bm = NONE;
+        size_t bi = 0;
+        for (size_t i = 0; i + 1 < n; ++i) {
+            if (u[i] >= m->inert || u[i + 1] >= m->inert) continue;
+            uint32_t mg = hut_model_pair_lookup(m, u[i], u[i + 1]);
+            uint32_t rk = rank_of(m, mg);
+            if (rk < best) {
+                best = rk;
+                bi = i;
+                bm = mg;
+            }
+        }
+        if (bm == NONE) return n;
+        u[bi] = bm;
+        memmove(u + bi + 1, u + bi + 2, (n - bi - 2) * sizeof *u);
+        n--;
+    }
+}
+
+/* table-driven encode of one document; returns id count (ids truncated to cap) */
+size_t harness_encode(const hut_model* m, const uint8_t* t, size_t n, int32_t* out, size_t cap) {
+    const uint8_t* z = memchr(t, 0, n);
+    if (z) n = (size_t)(z - t);
+    uint32_t* starts = malloc((n + 1) * sizeof *starts);
+    size_t np = harness_pretokens(t, n, starts, n + 1);
+    uint32_t* u = malloc((n * m->max_sym_per_char + m->n_prefix_syms + 8) * sizeof *u);
+    size_t w = 0;
+    for (size_t k = 0; k < np; ++k) {
+        size_t s = starts[k], e = k + 1 < np ? starts[k + 1] : n;
+        if (e - s > 262144) break; /* core.c:402-407 */
+        size_t cnt = 0;
+        int first = m->has_prefix && k == 0;
+        if (first && t[s] == ' ')
+            for (uint32_t i = 0; i < m->n_prefix_alone; ++i, ++w)
+                if (w < cap) out[w] = m->prefix_alone_ids[i];
+        if (first && t[s] != ' ')
+            for (uint32_t i = 0; i < m->n_prefix_syms; ++i) u[cnt++] = m->prefix_syms[i];
+        cnt += symbols(m, t, s, e, u + cnt);
+        cnt = merge(m, u, cnt);
+        for (size_t i = 0; i < cnt; ++i, ++w)
+            if (w < cap) out[w] = m->out_id[u[i]];
+    }
+    free(u);
+    free(starts);
+    return w;
+}
+
+hut_model* harness_load(const char* vocab, const char* special, const char* prefix, int byte_mode, char* msg,
+                        size_t msglen, int* status) {
+    hut_model* m = NULL;
+    *status = hut_model_load(&m, vocab, special, prefix, byte_mode, msg, msglen);
+    return m;
+}
+
+void harness_free(hut_model* m) { hut_model_free(m); }
+
+void harness_info(const hut_model* m, uint32_t* out) {
+    out[0] = m->n_vocab;
+    out[1] = m->n_units;
+    out[2] = m->pair_count;
+    out[3] = m->pair_cap;
+    out[4] = (uint32_t)m->distinct_values;
+    out[5] = (uint32_t)m->identity_ids;
+    out[6] = m->max_sym_per_char;
+    out[7] = m->vocab_lines;
+}

@@ -1,0 +1,181 @@
+"""GPU parity: the CUDA engine (through the C-ABI) against the CPU oracle on the same inputs.
+Bit-exact: ids are integers, so every comparison is equality (no tolerance)."""
+import random
+import tempfile
+
+import numpy as np
+import pytest
+
+import fuzzmodels as F
+import synth
+from common import MODELS, assert_same, engine_for, oracle_for, pack
+
+pytestmark = pytest.mark.gpu
+
+BASIC = [
+    "hello world", "", " ", "  ", "a", " a", "a ", "a  b", "a   b    c", "aaa", "aaaa", " Hello", "Hello, World!",
+    "12345 abc!!", "árvíztűrő tükörfúrógép", "ÁRVÍZTŰRŐ TÜKÖRFÚRÓGÉP", "x\n\ny\t z", "señor ñ!", "€ 😂 日本",
+    "tab\there", "line1\nline2\r\nline3", "  leading", "trailing  ", "a \n b", "1a.b2 c", "don't stop", "<0x41>",
+    "<|endoftext|>", "\x01\x02\x7f", "mixed123abc456", "...!!!???", " . , ; ", "ő", "őő űű", "a" * 40, "ab" * 100,
+    "é" * 50, " " * 70, "\n" * 33, "word " * 300, "How can the net amount of entropy of the universe be massively decreased?",
+]
+
+
+@pytest.mark.parametrize("name", MODELS)
+def test_basic_strings(name):
+    eng, orc = engine_for(name), oracle_for(name)
+    got = eng.batch_encode(BASIC)
+    want = orc.batch_encode(BASIC)
+    for t, g, w in zip(BASIC, got, want):
+        assert g == w, (name, t[:40], g[:20], w[:20])
+    # one document at a time too (documents starting at offset 0, the prefix path)
+    for t in BASIC[:20]:
+        assert eng.encode(t) == orc.encode(t), (name, t)
+
+
+@pytest.mark.parametrize("name", MODELS)
+@pytest.mark.parametrize("seed,special_every", [(21, 0), (22, 200)])
+def test_synthetic_corpus(name, seed, special_every):
+    eng, orc = engine_for(name), oracle_for(name)
+    data, offs = synth.corpus(seed, 3 << 20, special_every=special_every)
+    ids, tok = eng.encode_packed(data, offs)
+    oids, otok = orc.encode_packed(data, offs)
+    assert_same(ids, tok, oids, otok, f"{name} seed {seed}")
+    st = eng.stats()
+    assert st["kernel_launches"] >= 2 and st["pretokens"] > 0
+
+
+def test_cache_is_transparent():
+    """Same answer with a cold cache, a warm cache and a tiny (thrashing) cache."""
+    name = "gpt2"
+    data, offs = synth.corpus(31, 2 << 20)
+    oids, otok = oracle_for(name).encode_packed(data, offs)
+    eng = engine_for(name)
+    eng.cache_reset()
+    a = eng.encode_packed(data, offs)
+    b = eng.encode_packed(data, offs)  # warm
+    assert eng.stats()["cache_hits"] > 0
+    tiny = engine_for(name, cache_log2_slots=10)
+    c = tiny.encode_packed(data, offs)
+    for got in (a, b, c):
+        assert_same(got[0], got[1], oids, otok, "cache variants")
+
+
+@pytest.mark.parametrize("byte_mode", [True, False])
+def test_fuzz_models(byte_mode):
+    """Adversarial random vocabularies: non-monotone ranks, virtual units, duplicate keys / ids, -1 symbols."""
+    from hutoken_b200 import capi
+    from oracle import oracle as O
+    tmp = tempfile.mkdtemp()
+    for seed in range(40):
+        rng = random.Random(1000 + seed)
+        v, s, kw = F.random_model(rng, tmp, byte_mode, f"g{seed}")
+        eng = capi.Engine(v, s, **kw)
+        orc = O.Oracle(v, s, **kw)
+        texts = [F.random_text(rng, rng.randint(0, 60)) for _ in range(80)]
+        if byte_mode:  # raw invalid UTF-8 is defined in byte mode only
+            texts += [bytes(rng.choice([0x80, 0xC3, 0xE2, 0xF0, 0x41, 0x20, 0xA9, 0xFF, 0xC0, 0x0A, 0x61])
+                            for _ in range(rng.randint(1, 40))) for _ in range(20)]
+        got, want = eng.batch_encode(texts), orc.batch_encode(texts)
+        for t, g, w in zip(texts, got, want):
+            assert g == w, (seed, kw, t, g, w)
+        eng.close()
+
+
+@pytest.mark.parametrize("name", ["gpt2_small", "llama_small"])
+def test_document_edges(name):
+    """Empty / one-byte / many tiny documents, documents ending inside a tile halo, tile-straddling words."""
+    eng, orc = engine_for(name), oracle_for(name)
+    rng = random.Random(5)
+    docs = ["", "", "a", "", " ", "é", "", "x" * 4095, "y" * 4096, "z" * 4097, "", ("w" * 17 + " ") * 500, ""]
+    docs += [F.random_text(rng, rng.randint(0, 3)) for _ in range(3000)]
+    docs += ["", ""]
+    data, offs = pack(docs)
+    ids, tok = eng.encode_packed(data, offs)
+    oids, otok = orc.encode_packed(data, offs)
+    assert_same(ids, tok, oids, otok, name)
+    # only empty documents / no documents
+    for d in ([], [""], ["", "", ""]):
+        data, offs = pack(d)
+        ids, tok = eng.encode_packed(data, offs)
+        assert len(ids) == 0 and tok.tolist() == [0] * (len(d) + 1)
+
+
+@pytest.mark.parametrize("name", ["gpt2_small", "llama_small"])
+def test_medium_and_long_pretokens(name):
+    """Pretokens beyond 32 symbols (block-cooperative path) and beyond a tile (big path), reference-compatible."""
+    eng, orc = engine_for(name), oracle_for(name)
+    rng = random.Random(9)
+    letters = "abcdeégőz"
+    docs = []
+    for n in (33, 64, 100, 129, 500, 4000, 4300, 9000, 16384, 65536):
+        docs.append("start " + "".join(rng.choice(letters) for _ in range(n)) + " end")
+        docs.append("".join(rng.choice("0123456789") for _ in range(n)))
+        docs.append(" " * n + "x")
+        docs.append("!?" * (n // 2))
+    data, offs = pack(docs)
+    ids, tok = eng.encode_packed(data, offs)
+    oids, otok = orc.encode_packed(data, offs)
+    assert_same(ids, tok, oids, otok, name)
+    st = eng.stats()
+    assert st["block_merges"] > 0 and st["big_merges"] > 0
+
+
+def test_reference_cut_at_overlong_pretoken():
+    """core.c:402-407,503: a pretoken > 262144 bytes ends its document silently; later documents are unaffected."""
+    name = "gpt2_small"
+    eng, orc = engine_for(name), oracle_for(name)
+    docs = ["before one", "keep this " + "a" * (262144 + 8) + " dropped tail", "after one",
+            "b" * 262145, "x " + "c" * 262144 + " kept"]
+    data, offs = pack(docs)
+    ids, tok = eng.encode_packed(data, offs)
+    oids, otok = orc.encode_packed(data, offs)
+    assert_same(ids, tok, oids, otok, name)
+    assert eng.stats()["cut_documents"] == 2
+
+
+def test_device_resident_api():
+    """hut_encode_device: text and ids stay on the GPU (the path bench.py times)."""
+    import torch
+    name = "gpt2"
+    eng, orc = engine_for(name), oracle_for(name)
+    data, offs = synth.corpus(41, 4 << 20)
+    oids, otok = orc.encode_packed(data, offs)
+    dev = torch.device("cuda:0")
+    d_text = torch.from_numpy(np.concatenate([data, np.zeros(64, np.uint8)])).to(dev)
+    d_offs = torch.from_numpy(offs.astype(np.int64)).to(dev)
+    d_ids = torch.empty(len(data) + 64, dtype=torch.int32, device=dev)
+    d_tok = torch.empty(len(offs), dtype=torch.int64, device=dev)
+    torch.cuda.synchronize()
+    n = eng.encode_device(0, d_text.data_ptr(), len(data), d_offs.data_ptr(), len(offs) - 1, d_ids.data_ptr(),
+                          d_ids.numel(), d_tok.data_ptr())
+    assert n == len(oids)
+    assert_same(d_ids[:n].cpu().numpy(), d_tok.cpu().numpy().astype(np.uint64), oids, otok, "device api")
+    # too small an id buffer is reported, not overrun
+    from hutoken_b200 import capi
+    with pytest.raises(capi.HutError):
+        eng.encode_device(0, d_text.data_ptr(), len(data), d_offs.data_ptr(), len(offs) - 1, d_ids.data_ptr(), 1000,
+                          d_tok.data_ptr())
+
+
+def test_python_surface():
+    """hutoken.initialize / encode / batch_encode drop-in (hutoken.py:22-139, lib.c:668-874)."""
+    import hutoken_b200 as hutoken
+    v, s = synth.PATHS["gpt2_small"]
+    hutoken.initialize(v, s, is_byte_encoder=True)
+    orc = oracle_for("gpt2_small")
+    assert hutoken.encode("hello world") == orc.encode("hello world")
+    texts = ["How can the net", " amount of entropy of", " the universe be massively decreased?", ""]
+    for nt in (1, 3, 8):
+        assert hutoken.batch_encode(texts, nt) == orc.batch_encode(texts)
+    assert hutoken.batch_encode(texts, 0) == [[], [], [], []]  # no workers => nothing encoded (lib.c:779-794)
+    assert hutoken.batch_encode(["ab\0cd"], 1) == [orc.encode("ab")]  # strdup cut (lib.c:772)
+    with pytest.raises(RuntimeError, match="embedded null"):
+        hutoken.encode("ab\0cd")
+    with pytest.raises(RuntimeError, match="Expected a list of strings"):
+        hutoken.batch_encode("not a list")
+    v, s = synth.PATHS["llama_small"]
+    hutoken.initialize(v, s, prefix="▁")
+    orc = oracle_for("llama_small")
+    for t in ("hello world", " hello", "x\ny"):
+        assert hutoken.encode(t) == orc.encode(t)
