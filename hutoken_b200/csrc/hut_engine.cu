@@ -465,7 +465,6 @@ extern "C" int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64
     CU(ctx, grow_host(&ctx->h_off_stage, &ctx->h_off_cap, (size_t)n_docs + (size_t)nsh + 1, false));
     // ---- phase A: upload + kernels on every device ----
     uint64_t stage_at = 0;
-    uint64_t stage_pos[MAX_DEV];
     for (int s = 0; s < nsh; ++s) {
         hut_dev* d = &ctx->dev[s];
         const shard_plan& p = plan[s];
@@ -478,7 +477,6 @@ extern "C" int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64
         const uint64_t worst = nb * d->dm.kmax + nd * (uint64_t)(d->dm.n_prefix_syms + d->dm.n_prefix_alone) + 64;
         CU(ctx, grow(&d->d_ids, &d->d_ids_cap, (size_t)worst));
         unsigned long long* ho = ctx->h_off_stage + stage_at;
-        stage_pos[s] = stage_at;
         for (uint64_t i = 0; i <= nd; ++i) ho[i] = doc_offsets[p.doc_lo + i] - p.byte_lo;
         stage_at += nd + 1;
         if (nb) CU(ctx, cudaMemcpyAsync(d->d_text, bytes + p.byte_lo, nb, cudaMemcpyHostToDevice, d->stream));
@@ -506,8 +504,10 @@ extern "C" int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64
         if (plan[s].n_ids)
             CU(ctx, cudaMemcpyAsync(ctx->h_ids + id_base, d->d_ids, plan[s].n_ids * sizeof(int32_t),
                                     cudaMemcpyDeviceToHost, d->stream));
-        CU(ctx, cudaMemcpyAsync(ctx->h_tok + plan[s].doc_lo, d->d_tok, (nd + 1) * sizeof(uint64_t),
-                                cudaMemcpyDeviceToHost, d->stream));
+        // nd entries, not nd + 1: entry doc_hi belongs to the next shard (two streams must not write one word)
+        if (nd)
+            CU(ctx, cudaMemcpyAsync(ctx->h_tok + plan[s].doc_lo, d->d_tok, nd * sizeof(uint64_t),
+                                    cudaMemcpyDeviceToHost, d->stream));
         id_base += plan[s].n_ids;
     }
     id_base = 0;
@@ -527,6 +527,5 @@ extern "C" int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64
     result->tok_offsets = (const uint64_t*)ctx->h_tok;
     result->n_ids = total_ids;
     result->n_docs = n_docs;
-    (void)stage_pos;
     return HUT_STATUS_OK;
 }
