@@ -2,8 +2,8 @@
  *
  * Replaces, for the encode path, hutoken's p_initialize / p_encode / p_batch_encode plumbing (lib.c) and its
  * pthread task queue (taskqueue.c, lib.c:779-794): documents are sharded by bytes over the context's devices,
- * each shard runs prep_kernel + the fused tile_kernel on its own stream; there is no collective.
- * No CPU fallback: every id is produced by the kernels in hut_tile_kernel.cuh.
+ * each shard runs the kernel pipeline of hut_pipeline.cuh on its own stream; there is no collective.
+ * No CPU fallback: every id is produced by those kernels.
  */
 #include <cuda_runtime.h>
 
@@ -13,7 +13,7 @@
 
 #include "../../include/hutoken_b200.h"
 #include "hut_model.h"
-#include "hut_tile_kernel.cuh"
+#include "hut_pipeline.cuh"
 
 using namespace hut;
 
@@ -32,15 +32,23 @@ struct hut_dev {
     CutRanges* cut;
     uint32_t* cta_scratch;
     unsigned long long cta_scratch_words;
-    uint32_t med_cap, ovf_cap;
+    uint32_t med_cap;
     uint32_t* big_pool;
     unsigned long long big_slot_words;
     uint32_t big_cap, big_slots;
-    int grid;
-    // grow-only temporaries
-    unsigned long long* tile_state;
-    uint32_t* first_doc;
-    size_t tiles_cap, first_doc_cap;
+    int grid, long_grid, sms;
+    uint32_t stride;
+    // grow-only temporaries of the pipeline
+    int32_t* stage;
+    size_t stage_cap;
+    uint32_t* tilebuf;  // cnt | tot | first_doc | def_first, ntiles + 1 entries each
+    size_t tilebuf_cap;
+    unsigned long long* bsum;
+    size_t bsum_cap;
+    DefEntry* def;
+    size_t def_cap;
+    int32_t* long_ids;
+    size_t long_cap;
     Job job;  // the last launched shard
     int32_t* cut_tmp;
     size_t cut_tmp_cap;
@@ -53,7 +61,7 @@ struct hut_dev {
     size_t d_ids_cap;
     unsigned long long* d_tok;
     size_t d_tok_cap;
-    cudaEvent_t ev[3];
+    cudaEvent_t ev[4];
     hut_stats stats;
 };
 
@@ -100,7 +108,7 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     d->device = device;
     CU(ctx, cudaSetDevice(device));
     CU(ctx, cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
-    for (int i = 0; i < 3; ++i) CU(ctx, cudaEventCreate(&d->ev[i]));
+    for (int i = 0; i < 4; ++i) CU(ctx, cudaEventCreate(&d->ev[i]));
     DevModel& dm = d->dm;
     CU(ctx, upload(d, (const unsigned long long*)m->pair_tab, m->pair_cap, &dm.pair_tab));
     dm.pair_mask = m->pair_cap - 1;
@@ -141,7 +149,7 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     dm.compat_cut = ctx->opt.max_pretoken == 0;
     dm.limit = ctx->opt.max_pretoken ? ctx->opt.max_pretoken : 262144ull;  // core.c:27-28
 
-    d->cache_bits = ctx->opt.cache_log2_slots ? ctx->opt.cache_log2_slots : 20;
+    d->cache_bits = ctx->opt.cache_log2_slots ? ctx->opt.cache_log2_slots : 21;
     if (d->cache_bits < 10) d->cache_bits = 10;
     if (d->cache_bits > 26) d->cache_bits = 26;
     CU(ctx, cudaMalloc(&d->cache, sizeof(CacheSlot) << d->cache_bits));
@@ -155,13 +163,16 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile_kernel, NT, 0));
     CU(ctx, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
     if (per_sm < 1) per_sm = 1;
+    d->sms = sms;
     d->grid = per_sm * sms;
+    d->long_grid = 2 * sms;
 
-    const uint32_t extra = m->n_prefix_syms + m->n_prefix_alone + 1;
-    d->med_cap = (uint32_t)SPAN * dm.kmax + m->n_prefix_syms + 64;
-    d->ovf_cap = (uint32_t)SPAN * (dm.kmax + extra) + 256;
-    d->cta_scratch_words = 4ull * d->med_cap + d->ovf_cap;
-    CU(ctx, cudaMalloc(&d->cta_scratch, d->cta_scratch_words * sizeof(uint32_t) * d->grid));
+    // ids a 960-byte tile can produce: one per symbol of the pretokens STARTING in it (the last one may run up to
+    // MAXW - 1 bytes past the tile) + the prefix ids of every document starting in it
+    d->stride = (uint32_t)(OWN + MAXW) * (dm.kmax + (m->has_prefix ? m->n_prefix_syms + m->n_prefix_alone : 0u));
+    d->med_cap = 4096u * dm.kmax + m->n_prefix_syms + 64;
+    d->cta_scratch_words = 4ull * d->med_cap;
+    CU(ctx, cudaMalloc(&d->cta_scratch, d->cta_scratch_words * sizeof(uint32_t) * d->long_grid));
     d->big_slots = ctx->opt.big_slots ? ctx->opt.big_slots : (ctx->opt.max_pretoken > (64ull << 20) ? 2 : 8);
     if (d->big_slots > 32) d->big_slots = 32;
     unsigned long long bc = dm.limit * dm.kmax + m->n_prefix_syms + 64;
@@ -181,14 +192,17 @@ static void dev_free(hut_dev* d) {
     cudaFree(d->cut);
     cudaFree(d->cta_scratch);
     cudaFree(d->big_pool);
-    cudaFree(d->tile_state);
-    cudaFree(d->first_doc);
+    cudaFree(d->stage);
+    cudaFree(d->tilebuf);
+    cudaFree(d->bsum);
+    cudaFree(d->def);
+    cudaFree(d->long_ids);
     cudaFree(d->cut_tmp);
     cudaFree(d->d_text);
     cudaFree(d->d_off);
     cudaFree(d->d_ids);
     cudaFree(d->d_tok);
-    for (int i = 0; i < 3; ++i)
+    for (int i = 0; i < 4; ++i)
         if (d->ev[i]) cudaEventDestroy(d->ev[i]);
     if (d->stream) cudaStreamDestroy(d->stream);
 }
@@ -294,26 +308,30 @@ static cudaError_t grow(T** p, size_t* cap, size_t need) {
     return e;
 }
 
-/* launches the kernels for one resident shard on `st`; the device must be current */
+/* launches the kernel pipeline for one resident shard on `st`; the device must be current */
 static int launch_shard(hut_ctx* ctx, hut_dev* d, const uint8_t* d_bytes, uint64_t n_bytes, const uint64_t* d_doc_offsets,
                         uint64_t n_docs, int32_t* d_ids, uint64_t ids_capacity, uint64_t* d_tok_offsets,
-                        cudaStream_t st) {
+                        cudaStream_t st, size_t def_want, size_t long_want) {
     if (n_docs >= 0xFFFFFFF0ull) return set_err(ctx, HUT_STATUS_ARG, "%s", "too many documents in one shard");
     if ((uintptr_t)d_bytes & 15) return set_err(ctx, HUT_STATUS_ARG, "%s", "device text buffer must be 16-byte aligned");
-    const uint64_t ntiles64 = (n_bytes + TILE - 1) / TILE;
-    if (ntiles64 >= 0xFFFFFFF0ull) return set_err(ctx, HUT_STATUS_ARG, "%s", "shard too large (max 16 TiB)");
+    const uint64_t ntiles64 = (n_bytes + OWN - 1) / OWN;
+    if (ntiles64 >= 0x7FFFFFF0ull) return set_err(ctx, HUT_STATUS_ARG, "%s", "shard too large (max 2 TB)");
     const uint32_t ntiles = (uint32_t)ntiles64;
     d->stats.kernel_launches = 0;
     if (ntiles == 0) {
         CU(ctx, cudaMemsetAsync(d_tok_offsets, 0, (n_docs + 1) * sizeof(uint64_t), st));
         CU(ctx, cudaMemsetAsync(d->ctr, 0, offsetof(Counters, events), st));
-        CU(ctx, cudaEventRecord(d->ev[0], st));
-        CU(ctx, cudaEventRecord(d->ev[1], st));
-        CU(ctx, cudaEventRecord(d->ev[2], st));
+        for (int i = 0; i < 4; ++i) CU(ctx, cudaEventRecord(d->ev[i], st));
         return HUT_STATUS_OK;
     }
-    CU(ctx, grow(&d->tile_state, &d->tiles_cap, (size_t)ntiles));
-    CU(ctx, grow(&d->first_doc, &d->first_doc_cap, (size_t)ntiles));
+    const uint32_t nblocks = (ntiles + SCAN_BLK - 1) / SCAN_BLK;
+    if (def_want < (size_t)ntiles / 8 + 65536) def_want = (size_t)ntiles / 8 + 65536;
+    if (long_want < (size_t)n_bytes / 16 + (1u << 20)) long_want = (size_t)n_bytes / 16 + (1u << 20);
+    CU(ctx, grow(&d->stage, &d->stage_cap, (size_t)ntiles * d->stride));
+    CU(ctx, grow(&d->tilebuf, &d->tilebuf_cap, 4 * ((size_t)ntiles + 1)));
+    CU(ctx, grow(&d->bsum, &d->bsum_cap, (size_t)nblocks));
+    CU(ctx, grow(&d->def, &d->def_cap, def_want));
+    CU(ctx, grow(&d->long_ids, &d->long_cap, long_want));
     Job J;
     memset(&J, 0, sizeof J);
     J.text = d_bytes;
@@ -324,39 +342,67 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, const uint8_t* d_bytes, uint64
     J.out_cap = ids_capacity;
     J.tok_off = (unsigned long long*)d_tok_offsets;
     J.ntiles = ntiles;
-    J.tile_state = d->tile_state;
-    J.first_doc = d->first_doc;
+    J.stride = d->stride;
+    J.stage = d->stage;
+    J.cnt = d->tilebuf;
+    J.tot = J.cnt + ((size_t)ntiles + 1);
+    J.first_doc = J.tot + ((size_t)ntiles + 1);
+    J.def_first = J.first_doc + ((size_t)ntiles + 1);
+    J.bsum = d->bsum;
+    J.nblocks = nblocks;
+    J.def = d->def;
+    J.def_cap = d->def_cap > 0xFFFFFFF0ull ? 0xFFFFFFF0u : (uint32_t)d->def_cap;
+    J.long_ids = d->long_ids;
+    J.long_cap = d->long_cap;
     J.ctr = d->ctr;
     J.cache = d->cache;
     J.cache_bits = d->cache_bits;
     J.cta_scratch = d->cta_scratch;
     J.cta_scratch_words = d->cta_scratch_words;
     J.med_cap = d->med_cap;
-    J.ovf_cap = d->ovf_cap;
     J.big_pool = d->big_pool;
     J.big_slot_words = d->big_slot_words;
     J.big_cap = d->big_cap;
     J.big_slots = d->big_slots;
     CU(ctx, cudaEventRecord(d->ev[0], st));
-    prep_kernel<<<(ntiles + 255) / 256, 256, 0, st>>>(J);
+    CU(ctx, cudaMemsetAsync(J.first_doc, 0xFF, ((size_t)ntiles + 1) * sizeof(uint32_t), st));
+    init_kernel<<<1, 32, 0, st>>>(J);
+    if (n_docs) doc_kernel<<<(unsigned)((n_docs + 255) / 256), 256, 0, st>>>(J);
     CU(ctx, cudaEventRecord(d->ev[1], st));
-    int grid = d->grid < (int)ntiles ? d->grid : (int)ntiles;
-    tile_kernel<<<grid, NT, 0, st>>>(d->dm, J);
+    const uint32_t want = (ntiles + WPB - 1) / WPB;
+    tile_kernel<<<want < (uint32_t)d->grid ? want : (uint32_t)d->grid, NT, 0, st>>>(d->dm, J);
     CU(ctx, cudaEventRecord(d->ev[2], st));
+    long_kernel<<<d->long_grid, LNT, 0, st>>>(d->dm, J);
+    scan1_kernel<<<nblocks, 1024, 0, st>>>(J);
+    scan2_kernel<<<1, 1024, 0, st>>>(J);
+    const uint32_t cgrid = (ntiles + 7) / 8;
+    compact_kernel<<<cgrid < (uint32_t)d->sms * 8u ? cgrid : (uint32_t)d->sms * 8u, 256, 0, st>>>(J);
+    fixdoc_kernel<<<(unsigned)((n_docs + 1 + 255) / 256), 256, 0, st>>>(J);
+    CU(ctx, cudaEventRecord(d->ev[3], st));
     CU(ctx, cudaGetLastError());
-    d->stats.kernel_launches = 2;
+    d->stats.kernel_launches = n_docs ? 8 : 7;
     d->job = J;
     return HUT_STATUS_OK;
 }
 
-/* after the stream has been synchronised: read the counters, apply document cuts, fill stats */
+/* synchronises the stream: reads the counters, re-runs with larger side buffers if they overflowed, applies
+ * document cuts, fills stats */
 static int finish_shard(hut_ctx* ctx, hut_dev* d, uint64_t n_docs, int32_t* d_ids, uint64_t* d_tok_offsets,
                         uint64_t* n_ids_out, cudaStream_t st) {
-    CU(ctx, cudaMemcpyAsync(d->h_ctr, d->ctr, offsetof(Counters, events), cudaMemcpyDeviceToHost, st));
-    CU(ctx, cudaStreamSynchronize(st));
     const Counters* c = d->h_ctr;
+    for (int attempt = 0;; ++attempt) {
+        CU(ctx, cudaMemcpyAsync(d->h_ctr, d->ctr, offsetof(Counters, events), cudaMemcpyDeviceToHost, st));
+        CU(ctx, cudaStreamSynchronize(st));
+        if (!(c->flags & (FLAG_DEF_CAP | FLAG_LONG_CAP)) || attempt == 4) break;
+        // rare: many / very long deferred pretokens.  The counters kept counting, so they state the need.
+        const Job& J = d->job;
+        const size_t def_want = (size_t)c->n_def + 1024, long_want = (size_t)c->long_used * 2 + 4096;
+        int rc = launch_shard(ctx, d, J.text, J.nbytes, (const uint64_t*)J.doc_off, J.ndocs, J.out, J.out_cap,
+                              (uint64_t*)J.tok_off, st, def_want, long_want);
+        if (rc != HUT_STATUS_OK) return rc;
+    }
     float ms_all = 0, ms_main = 0;
-    cudaEventElapsedTime(&ms_all, d->ev[0], d->ev[2]);
+    cudaEventElapsedTime(&ms_all, d->ev[0], d->ev[3]);
     cudaEventElapsedTime(&ms_main, d->ev[1], d->ev[2]);
     d->stats.pretokens = c->st_pretokens;
     d->stats.cache_hits = c->st_hits;
@@ -370,6 +416,8 @@ static int finish_shard(hut_ctx* ctx, hut_dev* d, uint64_t n_docs, int32_t* d_id
     if (c->flags & FLAG_OUT_CAP) return set_err(ctx, HUT_STATUS_CAPACITY, "%s", "output id buffer too small");
     if (c->flags & FLAG_BIG_CAP)
         return set_err(ctx, HUT_STATUS_UNSUPPORTED, "%s", "a pretoken exceeds the configured max_pretoken working area");
+    if (c->flags & (FLAG_DEF_CAP | FLAG_LONG_CAP))
+        return set_err(ctx, HUT_STATUS_MEMORY, "%s", "side buffers for long pretokens could not be sized");
     if (c->flags & FLAG_EVENTS)
         return set_err(ctx, HUT_STATUS_UNSUPPORTED, "%s", "too many over-long pretokens in one call");
     if (c->flags & FLAG_NUL)
@@ -402,7 +450,7 @@ extern "C" int hut_encode_device(hut_ctx* ctx, int dev_index, const uint8_t* d_b
     hut_dev* d = &ctx->dev[dev_index];
     CU(ctx, cudaSetDevice(d->device));
     cudaStream_t st = stream ? (cudaStream_t)stream : d->stream;
-    int rc = launch_shard(ctx, d, d_bytes, n_bytes, d_doc_offsets, n_docs, d_ids, ids_capacity, d_tok_offsets, st);
+    int rc = launch_shard(ctx, d, d_bytes, n_bytes, d_doc_offsets, n_docs, d_ids, ids_capacity, d_tok_offsets, st, 0, 0);
     if (rc != HUT_STATUS_OK) return rc;
     return finish_shard(ctx, d, n_docs, d_ids, d_tok_offsets, n_ids_out, st);
 }
@@ -482,7 +530,7 @@ extern "C" int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64
         if (nb) CU(ctx, cudaMemcpyAsync(d->d_text, bytes + p.byte_lo, nb, cudaMemcpyHostToDevice, d->stream));
         CU(ctx, cudaMemcpyAsync(d->d_off, ho, (nd + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, d->stream));
         int rc = launch_shard(ctx, d, d->d_text, nb, (const uint64_t*)d->d_off, nd, d->d_ids, d->d_ids_cap,
-                              (uint64_t*)d->d_tok, d->stream);
+                              (uint64_t*)d->d_tok, d->stream, 0, 0);
         if (rc != HUT_STATUS_OK) return rc;
     }
     // ---- phase B: counts, then ids straight into the final pinned buffer ----

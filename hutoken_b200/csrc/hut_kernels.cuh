@@ -1,58 +1,73 @@
-/* sm_100a kernels of the BPE encode engine.  Included only by hut_engine.cu.
+/* sm_100a device code of the BPE encode engine, part 1: data layout, PTX helpers, table probes, the
+ * unique-pretoken cache and the merge loops.  Included only by hut_engine.cu (through hut_pipeline.cuh).
  *
- * One fused, persistent "tile" kernel does the whole hot path:
+ * Pipeline per shard (hut_pipeline.cuh), all on one stream, no host round trip, no inter-CTA waiting:
  *
- *   TMA bulk copy of a 4 KiB text tile (+halo) into shared memory        <- parser.c / pretokenizer.c input scan
- *   per-byte class codes, local pretoken-start rule, ballot-free bitmaps <- parser_next_token (parser.c:24-88)
- *   unique-pretoken cache probe (32-byte slots, L2 resident)             <- (no equivalent: reference re-merges)
- *   warp-per-pretoken merge: redux argmin over pair ranks, shuffle compaction
- *                                                                        <- bpe_encode_arena_string (core.c:66-209),
- *                                                                           MinPQ (queue.c), hashmap_get (hashmap.c)
- *   block-cooperative merge for pretokens > 32 symbols / outgrowing the tile
- *   single-pass decoupled look-back scan for output offsets, coalesced int32 stores, per-document offsets
- *                                                                        <- IntVector (vector.c), list building (lib.c)
+ *   doc_kernel      one thread per document: first document starting in each 960-byte tile
+ *   tile_kernel     WARP per tile, no block barrier: TMA bulk copy of the tile (+ 32-byte halos) into the warp's
+ *                   shared-memory slice; bit-sliced class masks + local start rule (hut_bitslice.h)
+ *                                                       <- parser_next_token (parser.c:24-88)
+ *                   lane-per-pretoken probe of the unique-pretoken cache (32-byte slots, L2 resident)
+ *                                                       <- (no equivalent: the reference re-merges every occurrence)
+ *                   misses: warp-per-pretoken merge, redux argmin over pair ranks + shuffle compaction
+ *                                                       <- bpe_encode_arena_string (core.c:66-209), MinPQ (queue.c),
+ *                                                          get_pair_rank_from_strings (core.c:700-722), hashmap.c
+ *                   ids -> the tile's slot of the staging buffer, coalesced; per-tile counts
+ *   long_kernel     pretokens > 32 bytes / symbols: block-cooperative merge (rare)
+ *   scan kernels    exclusive scan of the per-tile id counts      <- IntVector growth (vector.c:41-55)
+ *   compact_kernel  staging slots -> dense int32 ids, coalesced   <- list building (lib.c:699-715, 810-860)
+ *   fixdoc_kernel   per-document id offsets
  *
- * Algorithmic HBM traffic: B_in + 4*T + 8*(N_docs+1) bytes -- the text is read once, ids written once.
+ * Algorithmic HBM traffic of the path: B_in + 4*T + 8*(N_docs+1) bytes.
  */
 #pragma once
 
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "hut_bitslice.h"
 #include "hut_classify.h"
 #include "hut_model.h"
 
 namespace hut {
 
-constexpr int TILE = 4096;            // text bytes owned by one tile
-constexpr int BACK = 16;              // look-back halo (needs 4; 16 keeps TMA alignment)
-constexpr int FWD = 176;              // look-ahead halo: pretokens ending inside it are handled from shared memory
-constexpr int SPAN = BACK + TILE + FWD;
-constexpr int LIM = SPAN - 4;         // class codes at/after LIM may lack their look-ahead bytes
-constexpr int NT = 128;               // threads per CTA
-constexpr int NW = NT / 32;
-constexpr int NSEG = SPAN / 32;       // 32-byte segments per span
-constexpr int PCAP = 2048;            // pretokens handled per pass over a tile
-constexpr int STAGE = 2048;           // ids staged in shared memory per coalesced flush
-constexpr int CACHE_KEY_MAX = 23;     // longest pretoken (bytes) the cache keys on
+constexpr int OWN = 960;              // text bytes owned by one tile = 30 chunks of 32 bytes
+constexpr int CHUNK = 32;
+constexpr int BACK = 32;              // chunk 0 of the span: look-back halo (its own results are discarded)
+constexpr int SPAN = 1024;            // chunks 0..31; chunk 31 is the look-ahead halo
+constexpr int LOADB = SPAN + 16;      // bytes staged per tile (16 more: look-ahead of the halo's last chars)
+constexpr int TEXTB = LOADB + 16;     // shared bytes reserved (unaligned 20-byte key reads stay inside)
+constexpr int TRUST = SPAN - 3;       // boundaries at span positions >= TRUST lack their look-ahead
+constexpr int WPB = 8;                // warps per CTA (they never synchronise with each other)
+constexpr int NT = WPB * 32;
+constexpr int MAXW = 32;              // longest pretoken (bytes) / most symbols handled inside tile_kernel
+constexpr int CACHE_KEY_MAX = 15;     // longest pretoken (bytes) the cache keys on
 constexpr int CACHE_PROBES = 8;
+constexpr int CACHE_IDS = 5;          // most ids a cache value holds
+constexpr int OVF = 96;               // ids of >5-token results staged per round and warp
+constexpr int DEFMAX = 32;            // deferred pretokens per tile
 constexpr int MAX_EVENTS = 1024;
+constexpr int SCAN_BLK = 4096;        // tiles per scan block
+constexpr int LNT = 128;              // threads per CTA of long_kernel
+constexpr int LNW = LNT / 32;
 constexpr uint32_t NONE = HUT_UNIT_MASK;
 constexpr uint32_t RAWCHAR = 0xFFFFFFFEu;
 constexpr uint32_t ENDLINK = 0xFFFFFFFFu;
-constexpr uint64_t ESC = 1ull << 63;
-
-static_assert(SPAN % 32 == 0 && (SPAN % 16) == 0, "span must be TMA / segment aligned");
+constexpr uint32_t NODOC = 0xFFFFFFFFu;
+constexpr uint32_t BEYOND = 0xFFFFu;  // pstart sentinel: the pretoken's end lies beyond the halo
 
 enum : uint32_t {
     FLAG_NUL = 1u,        // a 0x00 byte inside a document
     FLAG_OUT_CAP = 2u,    // caller's id buffer too small
     FLAG_BIG_CAP = 4u,    // pretoken longer than the configured working area (no-limit mode)
-    FLAG_EVENTS = 8u      // more over-long pretokens than MAX_EVENTS
+    FLAG_EVENTS = 8u,     // more over-long pretokens than MAX_EVENTS
+    FLAG_DEF_CAP = 16u,   // deferred-pretoken list full   (host retries with a larger one)
+    FLAG_LONG_CAP = 32u   // ids of deferred pretokens do not fit (host retries with a larger buffer)
 };
 
-struct CacheSlot {  // 32 bytes = one L2 sector
-    unsigned long long k0, k1, k2, val;
+struct __align__(16) CacheSlot {  // 32 bytes = one L2 sector
+    unsigned long long k0, k1;    // text bytes 0..14, meta (0x80 | first << 4 | len) in byte 15
+    unsigned long long v0, v1;    // ids 0..2 / ids 3..4 as (id + 2) in 21-bit fields; count in v1 bits 61..63
 };
 
 struct CutEvent {  // a document cut at an over-long pretoken (core.c:402-407, 503)
@@ -60,12 +75,24 @@ struct CutEvent {  // a document cut at an over-long pretoken (core.c:402-407, 5
     unsigned long long pos;        // byte position of the pretoken
 };
 
+struct DefEntry {  // a pretoken tile_kernel hands to long_kernel
+    unsigned long long pos;   // global byte position of its first byte
+    uint32_t tile;
+    uint32_t local_off;       // ids of its tile that precede it in the staging slot
+    uint32_t len;             // bytes, 0 = unknown (runs past the halo)
+    uint32_t flags;           // bit 0: first pretoken of its document, bit 1: cut (set by long_kernel)
+    uint32_t count;           // ids produced (long_kernel)
+    uint32_t pad;
+    unsigned long long ids_off;  // into long_ids
+};
+
 struct Counters {
-    unsigned int ticket;
     unsigned int flags;
     unsigned int n_events;
+    unsigned int n_def;
     unsigned int pad;
     unsigned long long total_ids;
+    unsigned long long long_used;  // bump pointer into long_ids
     unsigned long long st_pretokens, st_hits, st_warp, st_block, st_big, st_cut;
     unsigned int pool_lock[32];
     CutEvent events[MAX_EVENTS];
@@ -102,17 +129,25 @@ struct Job {
     unsigned long long out_cap;
     unsigned long long* tok_off;
     uint32_t ntiles;
-    unsigned long long* tile_state;
-    uint32_t* first_doc;
+    uint32_t stride;           // ids per staging slot
+    int32_t* stage;            // [ntiles * stride]
+    uint32_t* cnt;             // [ntiles] bits 0..23 ids in the slot, bits 24..31 deferred pretokens
+    uint32_t* tot;             // [ntiles] ids of the tile incl. deferred ones; after scan1: exclusive in-block prefix
+    unsigned long long* bsum;  // [nblocks] block sums; after scan2: exclusive prefix
+    uint32_t nblocks;
+    uint32_t* first_doc;       // [ntiles + 1]
+    uint32_t* def_first;       // [ntiles] index of the tile's first DefEntry
+    DefEntry* def;
+    uint32_t def_cap;
+    int32_t* long_ids;
+    unsigned long long long_cap;
     Counters* ctr;
     CacheSlot* cache;
     uint32_t cache_bits;
-    // per-CTA scratch in global memory (L2 resident): medium merge arrays + overflow ids
+    // long_kernel working areas (global memory, L2 resident)
     uint32_t* cta_scratch;
     unsigned long long cta_scratch_words;  // per CTA
     uint32_t med_cap;                      // symbols per medium array
-    uint32_t ovf_cap;                      // overflow ids per CTA
-    // pool of working areas for pretokens that outgrow the tile
     uint32_t* big_pool;
     unsigned long long big_slot_words;
     uint32_t big_cap;  // symbols per big array
@@ -154,13 +189,17 @@ __device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned lon
     asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ void st_volatile_u64(unsigned long long* p, unsigned long long v) {
-    asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-// streaming store for ids: written once, never re-read by this kernel
+// streaming accesses for data touched exactly once
 __device__ __forceinline__ void st_stream_s32(int32_t* p, int32_t v) {
     asm volatile("st.global.cs.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ int32_t ld_stream_s32(const int32_t* p) {
+    int32_t v;
+    asm volatile("ld.global.cs.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void set_flag(const Job& J, uint32_t f) { atomicOr(&J.ctr->flags, f); }
 
 // ------------------------------------------------------------------------------------------------
 // table probes
@@ -210,181 +249,86 @@ __device__ __forceinline__ uint32_t char_probe(const DevModel& M, uint32_t key) 
 }
 
 // ------------------------------------------------------------------------------------------------
-// packed values: up to three ids in 3 x 21 bits (id + 2; 0 = empty) -- both the cache value and the
-// per-pretoken record in shared memory.  ESC records point into the CTA's overflow ids instead.
+// unique-pretoken cache.  Key = the pretoken's bytes (<= 15) + meta byte; value = up to 5 ids.
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t val_count(unsigned long long v) {
-    if (v & ESC) return (uint32_t)((v >> 32) & 0x3FFFFFFFu);
-    return (uint32_t)((v & 0x1FFFFFull) != 0) + (uint32_t)(((v >> 21) & 0x1FFFFFull) != 0) +
-           (uint32_t)(((v >> 42) & 0x1FFFFFull) != 0);
-}
-__device__ __forceinline__ int32_t val_id(unsigned long long v, uint32_t i) {
-    return (int32_t)((v >> (21 * i)) & 0x1FFFFFull) - 2;
-}
-__device__ __forceinline__ unsigned long long esc_make(uint32_t cnt, uint32_t off) {
-    return ESC | ((unsigned long long)cnt << 32) | off;
-}
-
-__device__ __forceinline__ uint32_t cache_slot_of(unsigned long long k0, unsigned long long k1, unsigned long long k2,
-                                                  uint32_t bits) {
-    uint64_t h = k0 * 0x9E3779B97F4A7C15ull;
-    h ^= h >> 32;
-    h += k1 * 0xC2B2AE3D27D4EB4Full + k2 * 0x165667B19E3779F9ull;
-    h ^= h >> 29;
-    h *= 0xD6E8FEB86659FD93ull;
-    return (uint32_t)(h >> (64 - bits));
+// 16 key bytes of text[s .. s+len) read from shared memory (len <= 15), meta in byte 15
+__device__ __forceinline__ void build_key(const uint8_t* text, int s, int len, uint32_t first, uint32_t x[4]) {
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(text + (s & ~3));
+    const uint32_t sh = (uint32_t)(s & 3) * 8u;
+    uint32_t r0 = w[0], r1 = w[1], r2 = w[2], r3 = w[3], r4 = w[4];
+    x[0] = __funnelshift_r(r0, r1, sh);
+    x[1] = __funnelshift_r(r1, r2, sh);
+    x[2] = __funnelshift_r(r2, r3, sh);
+    x[3] = __funnelshift_r(r3, r4, sh);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int rem = len - 4 * i;
+        x[i] = rem >= 4 ? x[i] : (rem <= 0 ? 0u : (x[i] & ((1u << (8 * rem)) - 1u)));
+    }
+    x[3] |= (0x80u | (first << 4) | (uint32_t)len) << 24;
 }
 
-// 0 = miss (or entry still being written)
-__device__ __forceinline__ unsigned long long cache_lookup(const Job& J, unsigned long long k0, unsigned long long k1,
-                                                           unsigned long long k2) {
-    uint32_t mask = (1u << J.cache_bits) - 1;
-    uint32_t i = cache_slot_of(k0, k1, k2, J.cache_bits);
+__device__ __forceinline__ uint32_t cache_hash(const uint32_t x[4], uint32_t bits) {
+    uint32_t h = x[0] * 0x9E3779B1u;
+    h ^= x[1] * 0x85EBCA77u;
+    h ^= x[2] * 0xC2B2AE3Du;
+    h ^= x[3] * 0x27D4EB2Fu;
+    h ^= h >> 15;
+    h *= 0x2C1B3C6Du;
+    h ^= h >> 13;
+    return h >> (32 - bits);
+}
+
+// true on a hit; a slot whose value is still being written (count field 0) reads as a miss
+__device__ __forceinline__ bool cache_lookup(const Job& J, const uint32_t x[4], unsigned long long& v0,
+                                             unsigned long long& v1) {
+    const unsigned long long k0 = x[0] | ((unsigned long long)x[1] << 32);
+    const unsigned long long k1 = x[2] | ((unsigned long long)x[3] << 32);
+    const uint32_t mask = (1u << J.cache_bits) - 1;
+    uint32_t i = cache_hash(x, J.cache_bits);
 #pragma unroll 1
     for (int p = 0; p < CACHE_PROBES; ++p) {
         const ulonglong2* s = reinterpret_cast<const ulonglong2*>(J.cache + i);
-        ulonglong2 a = s[0], b = s[1];
-        if (a.x == 0) return 0;
-        if (a.x == k0 && a.y == k1 && b.x == k2) return b.y;
+        const ulonglong2 a = s[0], b = s[1];
+        if (a.x == 0) return false;
+        if (a.x == k0 && a.y == k1) {
+            v0 = b.x;
+            v1 = b.y;
+            return (b.y >> 61) != 0;
+        }
         i = (i + 1) & mask;
     }
-    return 0;
+    return false;
 }
 
-// Called by one thread.  Slots are claimed by CAS on k0 (never zero for a valid key), the value is
-// published last; readers treat val == 0 as a miss, so a half-written slot is harmless.
-__device__ __forceinline__ void cache_insert(const Job& J, unsigned long long k0, unsigned long long k1,
-                                             unsigned long long k2, unsigned long long val) {
-    uint32_t mask = (1u << J.cache_bits) - 1;
-    uint32_t i = cache_slot_of(k0, k1, k2, J.cache_bits);
+// Called by one thread.  Slots are claimed by CAS on k0 (never zero: the first text byte is not NUL); the value
+// word carrying the count is published last, so a half-written slot reads as a miss.
+__device__ __forceinline__ void cache_insert(const Job& J, const uint32_t x[4], unsigned long long v0,
+                                             unsigned long long v1) {
+    const unsigned long long k0 = x[0] | ((unsigned long long)x[1] << 32);
+    const unsigned long long k1 = x[2] | ((unsigned long long)x[3] << 32);
+    const uint32_t mask = (1u << J.cache_bits) - 1;
+    uint32_t i = cache_hash(x, J.cache_bits);
 #pragma unroll 1
     for (int p = 0; p < CACHE_PROBES; ++p) {
         CacheSlot* s = J.cache + i;
         unsigned long long old = atomicCAS(&s->k0, 0ull, k0);
         if (old == 0) {
             s->k1 = k1;
-            s->k2 = k2;
+            s->v0 = v0;
             __threadfence();
-            atomicExch(&s->val, val);
+            atomicExch(&s->v1, v1);
             return;
         }
-        if (old == k0) {
-            unsigned long long o1 = ld_volatile_u64(&s->k1), o2 = ld_volatile_u64(&s->k2);
-            if (o1 == k1 && o2 == k2) return;  // same key already there (or being written by another warp)
-        }
+        if (old == k0 && ld_volatile_u64(&s->k1) == k1) return;  // already there (or being written)
         i = (i + 1) & mask;
     }
 }
 
-// ------------------------------------------------------------------------------------------------
-// shared memory of one CTA
-// ------------------------------------------------------------------------------------------------
-struct __align__(16) Smem {
-    uint8_t text[SPAN];
-    uint8_t code[SPAN];
-    uint32_t docmask[NSEG + 2];
-    uint32_t startmask[NSEG + 2];  // pretoken starts
-    uint32_t bndmask[NSEG + 2];    // starts | END bytes
-    uint16_t wcount[NSEG + 2];
-    uint16_t wprefix[NSEG + 2];    // exclusive count of tile-proper starts before this word
-    uint16_t pstart[TILE + 4];
-    unsigned long long pval[PCAP];
-    int32_t stage[STAGE];          // ids staged for a coalesced flush; reused as the miss queue before that
-    uint32_t byte1[256];
-    uint32_t tbase[NT];
-    uint32_t wscratch[NW][32];     // per-warp symbol scatter
-    unsigned long long red64[NW];
-    uint32_t red32[NW];
-    unsigned long long mbar;
-    // scalars
-    uint32_t tile;
-    uint32_t np;
-    uint32_t nmiss;
-    uint32_t nmed;
-    uint32_t ovf_used;
-    uint32_t dfirst;
-    unsigned long long base;       // exclusive prefix of ids before this tile
-    unsigned long long found;      // find_run_end result
-    unsigned long long doc_end;
-    uint32_t slot;
-    uint32_t medq[160];            // pretokens for the block-cooperative path
-    uint32_t bigout[96];           // ESC records copied cooperatively: k
-    uint32_t nbigout;
-    unsigned long long st[6];      // stats accumulators
-};
-
-// block-wide exclusive scan of one uint32 per thread; returns exclusive prefix, *total = sum
-__device__ __forceinline__ uint32_t block_scan_excl(Smem& sm, uint32_t v, uint32_t* total) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t inc = v;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        uint32_t n = __shfl_up_sync(0xFFFFFFFFu, inc, d);
-        if (lane >= d) inc += n;
-    }
-    __syncthreads();  // protect red32 from a previous use
-    if (lane == 31) sm.red32[warp] = inc;
-    __syncthreads();
-    uint32_t wbase = 0, tot = 0;
-#pragma unroll
-    for (int w = 0; w < NW; ++w) {
-        uint32_t s = sm.red32[w];
-        if (w < warp) wbase += s;
-        tot += s;
-    }
-    *total = tot;
-    return wbase + inc - v;
-}
-
-// ------------------------------------------------------------------------------------------------
-// text access beyond the staged span (block-cooperative / big paths)
-// ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t gbyte(const Job& J, unsigned long long p, unsigned long long end) {
-    return p < end ? (uint32_t)__ldg(J.text + p) : 0u;
-}
-
-// class of the char starting at p (bytes at/after `end` read as 0); continuation bytes covered by a valid lead
-// come back as HC_CONT.  Same rule as the tile pass, evaluated from global memory.
-__device__ uint32_t gclass(const Job& J, unsigned long long p, unsigned long long lo, unsigned long long end) {
-    uint32_t b0 = gbyte(J, p, end);
-    if ((b0 & 0xC0u) == 0x80u) {
-        for (int k = 1; k <= 3; ++k) {
-            if (p < lo + k) break;
-            unsigned long long q = p - k;
-            uint32_t bq = gbyte(J, q, end);
-            if ((bq & 0xC0u) == 0x80u) continue;
-            uint32_t r = hut_lead_class(bq, gbyte(J, q + 1, end), gbyte(J, q + 2, end), gbyte(J, q + 3, end));
-            if ((r >> 4) > (uint32_t)k) return HC_CONT;
-            break;
-        }
-        return HC_BAD;
-    }
-    return hut_lead_class(b0, gbyte(J, p + 1, end), gbyte(J, p + 2, end), gbyte(J, p + 3, end)) & 15u;
-}
-
-// First position >= from where the run of class `cls` (HC_SPACE = run of spaces) ends; at most `end`.
-// Stops early (returns a value > stop) once the scan passes `stop`.  All threads call; result broadcast.
-__device__ unsigned long long find_run_end(const Job& J, Smem& sm, unsigned long long from, unsigned long long lo,
-                                           unsigned long long end, uint32_t cls, unsigned long long stop) {
-    unsigned long long p0 = from;
-    for (;;) {
-        __syncthreads();
-        if (threadIdx.x == 0) sm.found = ~0ull;
-        __syncthreads();
-        unsigned long long p = p0 + threadIdx.x;
-        if (p < end) {
-            uint32_t c = gclass(J, p, lo, end);
-            bool bnd = (cls == HC_SPACE) ? (c != HC_SPACE) : (c != HC_CONT && c != cls);
-            if (bnd) atomicMin(&sm.found, p);
-        } else {
-            atomicMin(&sm.found, end);
-        }
-        __syncthreads();
-        unsigned long long f = sm.found;
-        if (f != ~0ull) return f;
-        p0 += NT;
-        if (p0 > stop) return p0;
-    }
+__device__ __forceinline__ uint32_t val_count(unsigned long long v1) { return (uint32_t)(v1 >> 61); }
+__device__ __forceinline__ int32_t val_id(unsigned long long v0, unsigned long long v1, uint32_t i) {
+    const unsigned long long w = i < 3 ? (v0 >> (21 * i)) : (v1 >> (21 * (i - 3)));
+    return (int32_t)(w & 0x1FFFFFull) - 2;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -468,8 +412,44 @@ __device__ __forceinline__ uint32_t char_symbols(const DevModel& M, const uint32
     return hi - lo;
 }
 
+// ------------------------------------------------------------------------------------------------
+// long_kernel helpers: one CTA (LNT threads) per deferred pretoken
+// ------------------------------------------------------------------------------------------------
+struct LongSm {
+    uint32_t byte1[256];
+    unsigned long long red64[LNW];
+    uint32_t red32[LNW];
+    unsigned long long found;
+    unsigned long long doc_end;
+    unsigned long long ids_off;
+    uint32_t slot;
+};
+
+// block-wide exclusive scan of one uint32 per thread; returns exclusive prefix, *total = sum
+__device__ __forceinline__ uint32_t block_scan_excl(LongSm& sm, uint32_t v, uint32_t* total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t n = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+        if (lane >= d) inc += n;
+    }
+    __syncthreads();  // protect red32 from a previous use
+    if (lane == 31) sm.red32[warp] = inc;
+    __syncthreads();
+    uint32_t wbase = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < LNW; ++w) {
+        uint32_t s = sm.red32[w];
+        if (w < warp) wbase += s;
+        tot += s;
+    }
+    *total = tot;
+    return wbase + inc - v;
+}
+
 // 64-bit min across the block (all threads get the result)
-__device__ __forceinline__ unsigned long long block_min64(Smem& sm, unsigned long long v) {
+__device__ __forceinline__ unsigned long long block_min64(LongSm& sm, unsigned long long v) {
 #pragma unroll
     for (int d = 16; d; d >>= 1) {
         unsigned long long o = __shfl_xor_sync(0xFFFFFFFFu, v, d);
@@ -480,23 +460,72 @@ __device__ __forceinline__ unsigned long long block_min64(Smem& sm, unsigned lon
     __syncthreads();
     unsigned long long r = sm.red64[0];
 #pragma unroll
-    for (int w = 1; w < NW; ++w) r = sm.red64[w] < r ? sm.red64[w] : r;
+    for (int w = 1; w < LNW; ++w) r = sm.red64[w] < r ? sm.red64[w] : r;
     return r;
+}
+
+__device__ __forceinline__ uint32_t gbyte(const Job& J, unsigned long long p, unsigned long long end) {
+    return p < end ? (uint32_t)__ldg(J.text + p) : 0u;
+}
+
+// class of the char starting at p (bytes at/after `end` read as 0); continuation bytes covered by a valid lead
+// come back as HC_CONT.  The scalar rule of hut_classify.h, evaluated from global memory.
+__device__ uint32_t gclass(const Job& J, unsigned long long p, unsigned long long lo, unsigned long long end) {
+    uint32_t b0 = gbyte(J, p, end);
+    if ((b0 & 0xC0u) == 0x80u) {
+        for (int k = 1; k <= 3; ++k) {
+            if (p < lo + k) break;
+            unsigned long long q = p - k;
+            uint32_t bq = gbyte(J, q, end);
+            if ((bq & 0xC0u) == 0x80u) continue;
+            uint32_t r = hut_lead_class(bq, gbyte(J, q + 1, end), gbyte(J, q + 2, end), gbyte(J, q + 3, end));
+            if ((r >> 4) > (uint32_t)k) return HC_CONT;
+            break;
+        }
+        return HC_BAD;
+    }
+    return hut_lead_class(b0, gbyte(J, p + 1, end), gbyte(J, p + 2, end), gbyte(J, p + 3, end)) & 15u;
+}
+
+// First position >= from where the run of class `cls` (HC_SPACE = run of spaces) ends; at most `end`.
+// Stops early (returns a value > stop) once the scan passes `stop`.  All threads call; result broadcast.
+__device__ unsigned long long find_run_end(const Job& J, LongSm& sm, unsigned long long from, unsigned long long lo,
+                                           unsigned long long end, uint32_t cls, unsigned long long stop) {
+    unsigned long long p0 = from;
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) sm.found = ~0ull;
+        __syncthreads();
+        unsigned long long p = p0 + threadIdx.x;
+        if (p < end) {
+            uint32_t c = gclass(J, p, lo, end);
+            bool bnd = (cls == HC_SPACE) ? (c != HC_SPACE) : (c != HC_CONT && c != cls);
+            if (bnd) atomicMin(&sm.found, p);
+        } else {
+            atomicMin(&sm.found, end);
+        }
+        __syncthreads();
+        unsigned long long f = sm.found;
+        if (f != ~0ull) return f;
+        p0 += LNT;
+        if (p0 > stop) return p0;
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
 // block-cooperative merge of one pretoken [gs, ge) with its symbol arrays in global memory (L2):
 // U unit, MG merged unit of pair (i, next(i)), NX / PV linked list.  One merge per round, chosen by a
-// block-wide min over (rank, index) -- the same order as the reference heap.  Ids go to dst.
-// Returns the token count (0xFFFFFFFF if the symbol count exceeds cap).
+// block-wide min over (rank, index) -- the same order as the reference heap.
+// cta_merge_run leaves the survivors in U (dead = ENDLINK) and returns their number (+ the ids emitted alone
+// before the first pretoken); 0xFFFFFFFF if the symbol count exceeds cap.  cta_merge_emit writes the ids.
 // ------------------------------------------------------------------------------------------------
-__device__ uint32_t cta_merge(const DevModel& M, const Job& J, Smem& sm, unsigned long long gs,
-                              unsigned long long ge, bool with_prefix, bool alone_first, uint32_t* U, uint32_t* MG,
-                              uint32_t* NX, uint32_t* PV, uint32_t cap, int32_t* dst, unsigned long long dst_cap) {
+__device__ uint32_t cta_merge_run(const DevModel& M, const Job& J, LongSm& sm, unsigned long long gs,
+                                  unsigned long long ge, bool with_prefix, bool alone_first, uint32_t* U, uint32_t* MG,
+                                  uint32_t* NX, uint32_t* PV, uint32_t cap, uint32_t* m_out) {
     const uint32_t tid = threadIdx.x;
     auto at = [&](unsigned long long p) -> uint32_t { return (uint32_t)__ldg(J.text + p); };
     const unsigned long long len = ge - gs;
-    const unsigned long long chunk = (len + NT - 1) / NT;
+    const unsigned long long chunk = (len + LNT - 1) / LNT;
     unsigned long long a = gs + chunk * tid, b = a + chunk;
     if (a > ge) a = ge;
     if (b > ge) b = ge;
@@ -513,8 +542,7 @@ __device__ uint32_t cta_merge(const DevModel& M, const Job& J, Smem& sm, unsigne
     if (m64 > cap) return 0xFFFFFFFFu;
     const uint32_t m = (uint32_t)m64;
     // pass 2: write units
-    if (tid < npfx) U[tid] = M.prefix_syms[tid];
-    for (uint32_t i = tid + NT; i < npfx; i += NT) U[i] = M.prefix_syms[i];
+    for (uint32_t i = tid; i < npfx; i += LNT) U[i] = M.prefix_syms[i];
     uint32_t w = base + npfx;
     for (unsigned long long p = a; p < b; ++p) {
         uint32_t f = M.inert, pb = 0;
@@ -524,7 +552,7 @@ __device__ uint32_t cta_merge(const DevModel& M, const Job& J, Smem& sm, unsigne
             for (uint32_t k = 0; k < c; ++k) U[w++] = __ldg(M.sym_pool + pb + k);
     }
     __syncthreads();
-    for (uint32_t i = tid; i < m; i += NT) {
+    for (uint32_t i = tid; i < m; i += LNT) {
         MG[i] = (i + 1 < m) ? pair_probe(M, U[i], U[i + 1]) : NONE;
         NX[i] = (i + 1 < m) ? i + 1 : ENDLINK;
         PV[i] = i ? i - 1 : ENDLINK;
@@ -532,7 +560,7 @@ __device__ uint32_t cta_merge(const DevModel& M, const Job& J, Smem& sm, unsigne
     __syncthreads();
     for (;;) {
         unsigned long long best = ~0ull;
-        for (uint32_t i = tid; i < m; i += NT) {
+        for (uint32_t i = tid; i < m; i += LNT) {
             uint32_t mg = MG[i];
             if (mg != NONE) {
                 unsigned long long key = ((unsigned long long)rank_of_unit(M, mg) << 32) | i;
@@ -555,8 +583,18 @@ __device__ uint32_t cta_merge(const DevModel& M, const Job& J, Smem& sm, unsigne
         }
         __syncthreads();
     }
-    // survivors in order -> ids
-    const uint32_t chunk2 = (m + NT - 1) / NT;
+    uint32_t live = 0;
+    for (uint32_t i = tid; i < m; i += LNT) live += (U[i] != ENDLINK);
+    uint32_t tot2;
+    block_scan_excl(sm, live, &tot2);
+    *m_out = m;
+    return tot2 + (alone_first ? M.n_prefix_alone : 0u);
+}
+
+__device__ void cta_merge_emit(const DevModel& M, LongSm& sm, const uint32_t* U, uint32_t m, bool alone_first,
+                               int32_t* dst) {
+    const uint32_t tid = threadIdx.x;
+    const uint32_t chunk2 = (m + LNT - 1) / LNT;
     uint32_t i0 = chunk2 * tid, i1 = i0 + chunk2;
     if (i0 > m) i0 = m;
     if (i1 > m) i1 = m;
@@ -565,71 +603,13 @@ __device__ uint32_t cta_merge(const DevModel& M, const Job& J, Smem& sm, unsigne
     uint32_t tot2;
     uint32_t ob = block_scan_excl(sm, live, &tot2);
     const uint32_t nal = alone_first ? M.n_prefix_alone : 0;
-    if (tid < nal && tid < dst_cap) dst[tid] = M.prefix_alone[tid];
+    for (uint32_t i = tid; i < nal; i += LNT) dst[i] = M.prefix_alone[i];
     ob += nal;
     for (uint32_t i = i0; i < i1; ++i) {
         uint32_t u = U[i];
-        if (u != ENDLINK) {
-            if (ob < dst_cap) dst[ob] = id_of_unit(M, u);
-            ob++;
-        }
+        if (u != ENDLINK) dst[ob++] = id_of_unit(M, u);
     }
     __syncthreads();
-    return tot2 + nal;
-}
-
-// ------------------------------------------------------------------------------------------------
-// decoupled look-back over tile_state (status in bits 62-63: 1 aggregate, 2 inclusive prefix).
-// Called by warp 0.  publish_aggregate == false: wait-only variant for tiles that cannot know their
-// count early (they publish their inclusive prefix themselves when done).
-// ------------------------------------------------------------------------------------------------
-constexpr unsigned long long ST_AGG = 1ull << 62, ST_INC = 2ull << 62, ST_MASK = 3ull << 62;
-
-__device__ unsigned long long lookback(const Job& J, uint32_t tile, unsigned long long aggregate,
-                                       bool publish_aggregate) {
-    const uint32_t lane = threadIdx.x & 31;
-    if (tile == 0) {
-        if (publish_aggregate && lane == 0) {
-            __threadfence();
-            st_volatile_u64(J.tile_state, ST_INC | aggregate);
-        }
-        return 0;
-    }
-    if (publish_aggregate && lane == 0) {
-        __threadfence();
-        st_volatile_u64(J.tile_state + tile, ST_AGG | aggregate);
-    }
-    unsigned long long excl = 0;
-    long long top = (long long)tile - 1;
-    for (;;) {
-        long long j = top - lane;
-        unsigned long long s;
-        if (j >= 0) {
-            s = ld_volatile_u64(J.tile_state + j);
-            while ((s & ST_MASK) == 0) {
-                __nanosleep(40);
-                s = ld_volatile_u64(J.tile_state + j);
-            }
-        } else {
-            s = ST_INC;  // before tile 0: inclusive prefix 0
-        }
-        uint32_t inc_mask = __ballot_sync(0xFFFFFFFFu, (s & ST_MASK) == ST_INC);
-        unsigned long long v = s & ~ST_MASK;
-        if (inc_mask) {
-            uint32_t first = __ffs(inc_mask) - 1;
-            if (lane > first) v = 0;
-        }
-#pragma unroll
-        for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, d);
-        excl += v;
-        if (inc_mask) break;
-        top -= 32;
-    }
-    if (publish_aggregate && lane == 0) {
-        __threadfence();
-        st_volatile_u64(J.tile_state + tile, ST_INC | (excl + aggregate));
-    }
-    return excl;
 }
 
 }  // namespace hut

@@ -10,7 +10,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_HERE)
 _SO = os.path.join(_HERE, "_build", "libhost_harness.so")
 _SRCS = [os.path.join(_HERE, "host_harness.c"), os.path.join(_ROOT, "hutoken_b200", "csrc", "hut_model.c")]
-_DEPS = _SRCS + [os.path.join(_ROOT, "hutoken_b200", "csrc", f) for f in ("hut_model.h", "hut_classify.h")]
+_DEPS = _SRCS + [os.path.join(_ROOT, "hutoken_b200", "csrc", f)
+                 for f in ("hut_model.h", "hut_classify.h", "hut_bitslice.h")]
 
 _lib = None
 
@@ -31,6 +32,10 @@ def lib():
         L.harness_pretokens.restype = C.c_size_t
         L.harness_pretokens.argtypes = [C.c_char_p, C.c_size_t, C.c_void_p, C.c_size_t]
         L.harness_info.argtypes = [C.c_void_p, C.c_void_p]
+        L.harness_pretokens_bs.restype = C.c_size_t
+        L.harness_pretokens_bs.argtypes = [C.c_char_p, C.c_size_t, C.c_char_p, C.c_void_p, C.c_size_t,
+                                           C.POINTER(C.c_int)]
+        L.harness_bitslice_check.argtypes = [C.c_char_p]
         _lib = L
     return _lib
 
@@ -76,3 +81,21 @@ def pretoken_starts(data: bytes):
     out = np.empty(cap, dtype=np.uint32)
     n = lib().harness_pretokens(data, len(data), out.ctypes.data, cap)
     return out[:n].tolist()
+
+
+def pretoken_starts_bitsliced(data: bytes, doc_starts=(0,)):
+    """(starts, exotic) from the bit-sliced classifier; doc_starts = byte positions where documents begin."""
+    isds = bytearray(len(data) + 1)
+    for p in doc_starts:
+        if p < len(data):
+            isds[p] = 1
+    cap = len(data) + 1
+    out = np.empty(cap, dtype=np.uint32)
+    ex = C.c_int()
+    n = lib().harness_pretokens_bs(data, len(data), bytes(isds), out.ctypes.data, cap, C.byref(ex))
+    return out[:n].tolist(), bool(ex.value)
+
+
+def bitslice_ok(chunk32: bytes) -> bool:
+    assert len(chunk32) == 32
+    return lib().harness_bitslice_check(chunk32) == 0

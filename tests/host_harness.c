@@ -134,3 +134,57 @@ void harness_info(const hut_model* m, uint32_t* out) {
     out[6] = m->max_sym_per_char;
     out[7] = m->vocab_lines;
 }
+
+/* ---- bit-sliced classifier (hut_bitslice.h), chunk by chunk the way the warp lanes run it ---- */
+#include "../hutoken_b200/csrc/hut_bitslice.h"
+
+/* t[0..n): packed documents; isds[i] != 0 marks a document start.  Writes every pretoken start (over all
+ * documents) into starts[]; *exotic = 1 if an over-long form was seen (the kernel then uses the generic path).
+ * NUL bytes end nothing here: the caller passes NUL-free text. */
+size_t harness_pretokens_bs(const uint8_t* t, size_t n, const uint8_t* isds, uint32_t* starts, size_t cap,
+                            int* exotic) {
+    size_t nch = (n + 31) / 32 + 1;
+    uint8_t* buf = calloc(nch * 32 + 32, 1);
+    memcpy(buf, t, n);
+    hut_bs_local* loc = calloc(nch + 1, sizeof *loc);
+    hut_bs_mid* mid = calloc(nch + 1, sizeof *mid);
+    for (size_t c = 0; c < nch; ++c) {
+        uint32_t w[8], p[8], ds = 0;
+        memcpy(w, buf + c * 32, 32);
+        for (int i = 0; i < 32; ++i)
+            if (c * 32 + i < n && isds[c * 32 + i]) ds |= 1u << i;
+        hut_bitslice32(w, p);
+        hut_bs_classify_local(p, ds, &loc[c]);
+    }
+    memset(&loc[nch], 0, sizeof loc[nch]);
+    *exotic = 0;
+    size_t cnt = 0;
+    for (size_t c = 0; c < nch; ++c) {
+        hut_bs_lookahead(&loc[c], hut_bs_pack_next(&loc[c + 1]), &mid[c]);
+        if (mid[c].EX) *exotic = 1;
+    }
+    for (size_t c = 0; c < nch; ++c) {
+        uint32_t px = c ? hut_bs_pack_prev(&loc[c - 1], &mid[c - 1]) : 0u, st, nu;
+        hut_bs_starts(&loc[c], &mid[c], px, &st, &nu);
+        for (int i = 0; i < 32; ++i)
+            if (((st >> i) & 1u) && c * 32 + i < n) {
+                if (cnt < cap) starts[cnt] = (uint32_t)(c * 32 + i);
+                cnt++;
+            }
+    }
+    free(buf);
+    free(loc);
+    free(mid);
+    return cnt;
+}
+
+/* exhaustive check of hut_bitslice32 on caller-provided bytes: returns 0 if every plane bit is right */
+int harness_bitslice_check(const uint8_t* bytes32) {
+    uint32_t w[8], p[8];
+    memcpy(w, bytes32, 32);
+    hut_bitslice32(w, p);
+    for (int k = 0; k < 8; ++k)
+        for (int i = 0; i < 32; ++i)
+            if (((p[k] >> i) & 1u) != (uint32_t)((bytes32[i] >> k) & 1)) return 1;
+    return 0;
+}

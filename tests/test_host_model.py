@@ -120,3 +120,83 @@ def test_loader_errors_match_oracle():
     assert hm.status == 1
     hm = HostModel(good_v, os.path.join(tmp, "missing_s.txt"))
     assert hm.status == 1
+
+
+# ---- bit-sliced classifier (hut_bitslice.h): the fused tile kernel's fast path ----
+def _oracle_starts(data, doc_starts):
+    """pretoken starts of packed documents by the oracle's sequential parser, document by document"""
+    bounds = sorted(set(doc_starts)) + [len(data)]
+    out = []
+    for a, b in zip(bounds, bounds[1:]):
+        pos = 0
+        doc = data[a:b]
+        while True:
+            n = O.next_pretoken(doc, pos)
+            if n == 0:
+                break
+            out.append(a + pos)
+            pos += n
+    return out
+
+
+def test_bitslice_transpose():
+    from harness import bitslice_ok
+    rng = random.Random(1)
+    for _ in range(300):
+        assert bitslice_ok(bytes(rng.randrange(256) for _ in range(32)))
+
+
+def test_bitsliced_rule_matches_parser_on_golden():
+    from harness import pretoken_starts_bitsliced
+    with open(os.path.join(GOLDEN, "pretokens.json")) as f:
+        g = json.load(f)
+    for c in g["cases"]:
+        data = bytes.fromhex(c["text_hex"])
+        if b"\0" in data:
+            continue
+        want, pos = [], 0
+        for n in c["lengths"]:
+            want.append(pos)
+            pos += n
+        got, exotic = pretoken_starts_bitsliced(data)
+        if not exotic:
+            assert got == want, data
+
+
+def test_bitsliced_rule_random_bytes_and_documents():
+    """Byte soup with every class transition / malformed UTF-8 shape, packed as several documents whose
+    boundaries fall anywhere (also inside multi-byte characters), compared with the sequential parser.
+    Over-long forms must be FLAGGED (the kernel then switches to hut_classify.h); everything else must match."""
+    from harness import pretoken_starts_bitsliced
+    rng = random.Random(12)
+    alphabet = [0x20, 0x20, 0x41, 0x61, 0x7A, 0x31, 0x2E, 0x0A, 0x09, 0x7F, 0x01, 0xC3, 0xA9, 0xC5, 0x91, 0xB1, 0xE2,
+                0x82, 0xAC, 0xF0, 0x9F, 0x98, 0x82, 0x80, 0xFF, 0xC0, 0xC1, 0xE0, 0xF8, 0xED, 0xA0, 0xC2, 0xF4, 0x90,
+                0xBC, 0x96, 0x9C, 0x8D, 0xB6]
+    n_exotic = n_plain = 0
+    for it in range(6000):
+        n = rng.randint(1, 90)
+        if it % 3 == 0:  # valid text: never exotic
+            data = "".join(rng.choice("aábc őŰ1 2.€😂\n\tZé  ñ日") for _ in range(n // 2 + 1)).encode("utf-8")
+        else:
+            data = bytes(rng.choice(alphabet) for _ in range(n))
+        ds = sorted({0} | {rng.randrange(len(data)) for _ in range(rng.randint(0, 3))})
+        got, exotic = pretoken_starts_bitsliced(data, ds)
+        if it % 3 == 0:
+            valid_cut = all((data[p] & 0xC0) != 0x80 for p in ds)
+            assert not exotic or not valid_cut
+        if exotic:
+            n_exotic += 1
+            continue
+        n_plain += 1
+        assert got == _oracle_starts(data, ds), (data.hex(), ds)
+    assert n_plain > 3000 and n_exotic > 50
+
+
+def test_bitsliced_rule_on_corpus():
+    from harness import pretoken_starts_bitsliced
+    data, offs = synth.corpus(55, 1 << 18, special_every=150)
+    b = data.tobytes()
+    ds = [int(x) for x in offs[:-1]]
+    got, exotic = pretoken_starts_bitsliced(b, ds)
+    assert not exotic
+    assert got == _oracle_starts(b, ds)
