@@ -122,7 +122,7 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     dm.byte_mode = m->is_byte_encoder;
     dm.multi_sym = m->max_sym_per_char > 1;
     dm.has_prefix = m->has_prefix;
-    dm.cache_ok = ((long long)m->max_value + 2 < (1ll << 21)) ? 1 : 0;
+    dm.cache_ok = (m->max_value < (1 << 20)) ? 1 : 0;  // ids are packed as signed 21-bit fields
     dm.kmax = m->max_sym_per_char;
     CU(ctx, upload(d, m->sym_off, 257, &dm.sym_off));
     CU(ctx, upload(d, m->sym_pool, m->sym_off[256], &dm.sym_pool));

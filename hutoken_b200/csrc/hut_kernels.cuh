@@ -67,7 +67,8 @@ enum : uint32_t {
 
 struct __align__(16) CacheSlot {  // 32 bytes = one L2 sector
     unsigned long long k0, k1;    // text bytes 0..14, meta (0x80 | first << 4 | len) in byte 15
-    unsigned long long v0, v1;    // ids 0..2 / ids 3..4 as (id + 2) in 21-bit fields; count in v1 bits 61..63
+    uint32_t w[4];                // ids 0..3 as signed 21-bit fields in bits 0..20 of w[0..3]; count in w[0] bits
+                                  // 21..23; id 4 spread over w[0] bits 24..31, w[1] bits 21..31, w[2] bits 21..22
 };
 
 struct CutEvent {  // a document cut at an over-long pretoken (core.c:402-407, 503)
@@ -217,8 +218,8 @@ __device__ __forceinline__ uint64_t mix64(uint64_t x) {
 // get_pair_rank_from_strings (core.c:700-722) + hashmap_get (hashmap.c:232-257) + murmur (hash.c).
 __device__ __forceinline__ uint32_t pair_probe(const DevModel& M, uint32_t l, uint32_t r) {
     if (l >= M.inert || r >= M.inert) return NONE;
-    uint64_t key = ((uint64_t)l << 21) | r;
-    uint32_t i = (uint32_t)(mix64(key) >> 32) & M.pair_mask;
+    const uint64_t key = ((uint64_t)l << 21) | r;
+    uint32_t i = hut_pair_hash(l, r, M.pair_mask);
     for (;;) {
         unsigned long long s = __ldg(M.pair_tab + i);
         if (s == HUT_PAIR_EMPTY) return NONE;
@@ -249,52 +250,68 @@ __device__ __forceinline__ uint32_t char_probe(const DevModel& M, uint32_t key) 
 }
 
 // ------------------------------------------------------------------------------------------------
-// unique-pretoken cache.  Key = the pretoken's bytes (<= 15) + meta byte; value = up to 5 ids.
+// unique-pretoken cache.  Key = the pretoken's bytes (<= 15) + meta byte; value = up to 5 ids (CacheSlot).
 // ------------------------------------------------------------------------------------------------
-// 16 key bytes of text[s .. s+len) read from shared memory (len <= 15), meta in byte 15
-__device__ __forceinline__ void build_key(const uint8_t* text, int s, int len, uint32_t first, uint32_t x[4]) {
+// 16 key bytes of text[s .. s+len) read from shared memory (len <= 15), meta in byte 15.  kmask = the
+// per-length byte masks (kmask[len] = 4 words), also in shared memory.
+__device__ __forceinline__ uint32_t build_key(const uint8_t* text, const uint4* kmask, int s, int len, uint32_t first,
+                                              uint32_t x[4]) {
     const uint32_t* w = reinterpret_cast<const uint32_t*>(text + (s & ~3));
     const uint32_t sh = (uint32_t)(s & 3) * 8u;
-    uint32_t r0 = w[0], r1 = w[1], r2 = w[2], r3 = w[3], r4 = w[4];
-    x[0] = __funnelshift_r(r0, r1, sh);
-    x[1] = __funnelshift_r(r1, r2, sh);
-    x[2] = __funnelshift_r(r2, r3, sh);
-    x[3] = __funnelshift_r(r3, r4, sh);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int rem = len - 4 * i;
-        x[i] = rem >= 4 ? x[i] : (rem <= 0 ? 0u : (x[i] & ((1u << (8 * rem)) - 1u)));
-    }
-    x[3] |= (0x80u | (first << 4) | (uint32_t)len) << 24;
+    const uint32_t r0 = w[0], r1 = w[1], r2 = w[2], r3 = w[3], r4 = w[4];
+    const uint4 m = kmask[len];
+    const uint32_t x0 = __funnelshift_r(r0, r1, sh);
+    x[0] = x0 & m.x;
+    x[1] = __funnelshift_r(r1, r2, sh) & m.y;
+    x[2] = __funnelshift_r(r2, r3, sh) & m.z;
+    x[3] = (__funnelshift_r(r3, r4, sh) & m.w) | ((0x80u | (first << 4) | (uint32_t)len) << 24);
+    return x0 & 0xFFu;  // the first text byte
 }
 
 __device__ __forceinline__ uint32_t cache_hash(const uint32_t x[4], uint32_t bits) {
     uint32_t h = x[0] * 0x9E3779B1u;
-    h ^= x[1] * 0x85EBCA77u;
-    h ^= x[2] * 0xC2B2AE3Du;
-    h ^= x[3] * 0x27D4EB2Fu;
+    h += x[1] * 0x85EBCA77u;
+    h += x[2] * 0xC2B2AE3Du;
+    h += x[3] * 0x27D4EB2Fu;
     h ^= h >> 15;
     h *= 0x2C1B3C6Du;
-    h ^= h >> 13;
     return h >> (32 - bits);
 }
 
+__device__ __forceinline__ int32_t sext21(uint32_t w) {
+    int32_t r;
+    asm("bfe.s32 %0, %1, 0, 21;" : "=r"(r) : "r"(w));
+    return r;
+}
+__device__ __forceinline__ uint32_t val_count(uint32_t w0) { return (w0 >> 21) & 7u; }
+__device__ __forceinline__ int32_t val_id4(const uint32_t w[4]) {
+    return sext21((w[0] >> 24) | ((w[1] >> 21) << 8) | (((w[2] >> 21) & 3u) << 19));
+}
+// packs up to 5 ids (each in [-2^20, 2^20)) + their count into a slot value
+__device__ __forceinline__ void val_pack(const int32_t t[5], uint32_t total, uint32_t w[4]) {
+    const uint32_t F = 0x1FFFFFu;
+    const uint32_t f4 = total > 4 ? ((uint32_t)t[4] & F) : 0u;
+    w[0] = (total > 0 ? ((uint32_t)t[0] & F) : 0u) | (total << 21) | ((f4 & 0xFFu) << 24);
+    w[1] = (total > 1 ? ((uint32_t)t[1] & F) : 0u) | (((f4 >> 8) & 0x7FFu) << 21);
+    w[2] = (total > 2 ? ((uint32_t)t[2] & F) : 0u) | (((f4 >> 19) & 3u) << 21);
+    w[3] = (total > 3 ? ((uint32_t)t[3] & F) : 0u);
+}
+
 // true on a hit; a slot whose value is still being written (count field 0) reads as a miss
-__device__ __forceinline__ bool cache_lookup(const Job& J, const uint32_t x[4], unsigned long long& v0,
-                                             unsigned long long& v1) {
-    const unsigned long long k0 = x[0] | ((unsigned long long)x[1] << 32);
-    const unsigned long long k1 = x[2] | ((unsigned long long)x[3] << 32);
+__device__ __forceinline__ bool cache_lookup(const Job& J, const uint32_t x[4], uint32_t w[4]) {
     const uint32_t mask = (1u << J.cache_bits) - 1;
     uint32_t i = cache_hash(x, J.cache_bits);
 #pragma unroll 1
     for (int p = 0; p < CACHE_PROBES; ++p) {
-        const ulonglong2* s = reinterpret_cast<const ulonglong2*>(J.cache + i);
-        const ulonglong2 a = s[0], b = s[1];
-        if (a.x == 0) return false;
-        if (a.x == k0 && a.y == k1) {
-            v0 = b.x;
-            v1 = b.y;
-            return (b.y >> 61) != 0;
+        const uint4* s = reinterpret_cast<const uint4*>(J.cache + i);
+        const uint4 a = s[0], b = s[1];
+        if ((a.x | a.y) == 0) return false;
+        if (a.x == x[0] && a.y == x[1] && a.z == x[2] && a.w == x[3]) {
+            w[0] = b.x;
+            w[1] = b.y;
+            w[2] = b.z;
+            w[3] = b.w;
+            return val_count(b.x) != 0;
         }
         i = (i + 1) & mask;
     }
@@ -303,8 +320,7 @@ __device__ __forceinline__ bool cache_lookup(const Job& J, const uint32_t x[4], 
 
 // Called by one thread.  Slots are claimed by CAS on k0 (never zero: the first text byte is not NUL); the value
 // word carrying the count is published last, so a half-written slot reads as a miss.
-__device__ __forceinline__ void cache_insert(const Job& J, const uint32_t x[4], unsigned long long v0,
-                                             unsigned long long v1) {
+__device__ __forceinline__ void cache_insert(const Job& J, const uint32_t x[4], const uint32_t w[4]) {
     const unsigned long long k0 = x[0] | ((unsigned long long)x[1] << 32);
     const unsigned long long k1 = x[2] | ((unsigned long long)x[3] << 32);
     const uint32_t mask = (1u << J.cache_bits) - 1;
@@ -315,20 +331,16 @@ __device__ __forceinline__ void cache_insert(const Job& J, const uint32_t x[4], 
         unsigned long long old = atomicCAS(&s->k0, 0ull, k0);
         if (old == 0) {
             s->k1 = k1;
-            s->v0 = v0;
+            s->w[1] = w[1];
+            s->w[2] = w[2];
+            s->w[3] = w[3];
             __threadfence();
-            atomicExch(&s->v1, v1);
+            atomicExch(&s->w[0], w[0]);
             return;
         }
         if (old == k0 && ld_volatile_u64(&s->k1) == k1) return;  // already there (or being written)
         i = (i + 1) & mask;
     }
-}
-
-__device__ __forceinline__ uint32_t val_count(unsigned long long v1) { return (uint32_t)(v1 >> 61); }
-__device__ __forceinline__ int32_t val_id(unsigned long long v0, unsigned long long v1, uint32_t i) {
-    const unsigned long long w = i < 3 ? (v0 >> (21 * i)) : (v1 >> (21 * (i - 3)));
-    return (int32_t)(w & 0x1FFFFFull) - 2;
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -452,7 +452,7 @@ static int add_pair(builder* b, uint32_t l, uint32_t r, uint32_t mrg) {
 uint32_t hut_model_pair_lookup(const hut_model* m, uint32_t l, uint32_t r) {
     uint64_t key = ((uint64_t)l << 21) | r;
     uint32_t mask = m->pair_cap - 1;
-    uint32_t i = (uint32_t)(hut_mix64(key) >> 32) & mask;
+    uint32_t i = hut_pair_hash(l, r, mask);
     for (;;) {
         uint64_t s = m->pair_tab[i];
         if (s == HUT_PAIR_EMPTY) return HUT_UNIT_MASK;
@@ -725,7 +725,7 @@ int hut_model_load(hut_model** out, const char* vocab_path, const char* special_
     }
 
     m->pair_cap = 1024;
-    while (m->pair_cap < b.n_pairs * 2 + 16) m->pair_cap <<= 1;
+    while (m->pair_cap < b.n_pairs * 4 + 16) m->pair_cap <<= 1; /* load <= 0.25: ~1.2 probes per lookup */
     m->pair_tab = malloc((size_t)m->pair_cap * sizeof(uint64_t));
     if (!m->pair_tab) {
         rc = fail(msg, msglen, HUT_ERR_MEMORY, "out of memory");
@@ -734,7 +734,8 @@ int hut_model_load(hut_model** out, const char* vocab_path, const char* special_
     memset(m->pair_tab, 0xFF, (size_t)m->pair_cap * sizeof(uint64_t));
     for (size_t k = 0; k < b.n_pairs; ++k) {
         uint64_t e = b.pairs[k], key = e >> 21;
-        uint32_t mask = m->pair_cap - 1, i = (uint32_t)(hut_mix64(key) >> 32) & mask;
+        uint32_t mask = m->pair_cap - 1;
+        uint32_t i = hut_pair_hash((uint32_t)(key >> 21), (uint32_t)key & HUT_UNIT_MASK, mask);
         int dup = 0;
         while (m->pair_tab[i] != HUT_PAIR_EMPTY) {
             if ((m->pair_tab[i] >> 21) == key) { /* same (L,R) => same concatenation => same M */

@@ -95,6 +95,15 @@ static inline uint64_t hut_mix64(uint64_t x) {
     return x;
 }
 
+/* slot of the pair (l, r) in the pair table: cheap enough for the merge loop (2 multiply-adds, shift, xor-and) */
+#ifdef __CUDACC__
+__host__ __device__
+#endif
+static inline uint32_t hut_pair_hash(uint32_t l, uint32_t r, uint32_t mask) {
+    uint32_t h = l * 0x9E3779B1u + r * 0x85EBCA77u;
+    return (h ^ (h >> 15)) & mask;
+}
+
 /* host-side lookups (used by the builder itself and by tests/host_harness.c) */
 uint32_t hut_model_pair_lookup(const hut_model* m, uint32_t l, uint32_t r); /* unit or HUT_UNIT_MASK if none */
 uint32_t hut_model_char_lookup(const hut_model* m, const uint8_t* p, uint32_t len);

@@ -18,6 +18,7 @@ struct __align__(16) WarpSm {
 };
 
 struct TileSm {
+    uint4 kmask[16];            // kmask[len]: byte masks of a 16-byte key holding len text bytes
     uint32_t byte1[256];
     WarpSm w[WPB];
 };
@@ -120,6 +121,10 @@ __global__ void __launch_bounds__(NT, 3) tile_kernel(const DevModel M, const Job
     WarpSm& ws = sm.w[warp];
 
     for (int i = tid; i < 256; i += NT) sm.byte1[i] = M.byte1[i];
+    if (tid < 16) {
+        auto wm = [&](int rem) -> uint32_t { return rem >= 4 ? 0xFFFFFFFFu : (rem <= 0 ? 0u : ((1u << (8 * rem)) - 1u)); };
+        sm.kmask[tid] = make_uint4(wm(tid), wm(tid - 4), wm(tid - 8), wm(tid - 12));
+    }
     if (lane == 0) {
         mbar_init(&ws.mbar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -127,7 +132,8 @@ __global__ void __launch_bounds__(NT, 3) tile_kernel(const DevModel M, const Job
     __syncthreads();  // the only block-wide barrier: byte1 is read-only afterwards
 
     uint32_t parity = 0;
-    unsigned long long st_pre = 0, st_hit = 0, st_wm = 0, st_def = 0;
+    uint32_t st_pre = 0, st_hit = 0;  // per lane
+    unsigned long long st_wm = 0, st_def = 0;
     const uint32_t gw = blockIdx.x * WPB + warp, nw = gridDim.x * WPB;
 
     for (uint32_t tile = gw; tile < J.ntiles; tile += nw) {
@@ -177,6 +183,7 @@ __global__ void __launch_bounds__(NT, 3) tile_kernel(const DevModel M, const Job
 
         // ---- classify: bit planes -> class masks -> pretoken starts (hut_bitslice.h) ----
         uint32_t ST, NU;
+        bool tile_docs;
         {
             const uint4* tp = reinterpret_cast<const uint4*>(ws.text + lane * CHUNK);
             const uint4 a = tp[0], b = tp[1];
@@ -184,7 +191,9 @@ __global__ void __launch_bounds__(NT, 3) tile_kernel(const DevModel M, const Job
             uint32_t planes[8];
             hut_bitslice32(w, planes);
             hut_bs_local loc;
-            hut_bs_classify_local(planes, ws.dsm[lane], &loc);
+            const uint32_t mydsm = ws.dsm[lane];
+            tile_docs = __any_sync(FULL, mydsm != 0);
+            hut_bs_classify_local(planes, mydsm, &loc);
             uint32_t nx = __shfl_down_sync(FULL, hut_bs_pack_next(&loc), 1);
             if (lane == 31) nx = 0;  // positions >= TRUST of the halo chunk are not used
             hut_bs_mid mid;
@@ -233,91 +242,95 @@ __global__ void __launch_bounds__(NT, 3) tile_kernel(const DevModel M, const Job
             const bool active = q < n;
             const int s = active ? ws.pstart[q] : BACK;
             const int e = active ? ws.pstart[q + 1] : BACK;
-            const bool dummy = !active || ws.text[s] == 0;  // NUL boundary (zero fill past the end of the text)
-            const int len = e - s;
-            const uint32_t dsb = (ws.dsm[s >> 5] >> (s & 31)) & 1u;
-            const uint32_t first = (M.has_prefix && dsb) ? 1u : 0u;
+            const int len = e - s;                       // > MAXW when the end lies beyond the halo (BEYOND)
+            const bool keyed = len <= CACHE_KEY_MAX;
+            uint32_t dsb = 0;
+            if (tile_docs) dsb = (ws.dsm[s >> 5] >> (s & 31)) & 1u;
+            const uint32_t first = M.has_prefix ? dsb : 0u;
+            uint32_t key[4], w[4] = {0u, 0u, 0u, 0u};
+            const uint32_t b0 = build_key(ws.text, sm.kmask, s, keyed ? len : 0, first, key);
+            const bool dummy = !active || b0 == 0;       // NUL boundary (zero fill past the end of the text)
             // state: 0 nothing, 1 value ready, 2 needs a warp merge, 3 deferred to long_kernel
             uint32_t state = 0;
-            unsigned long long v0 = 0, v1 = 0;
-            uint32_t key[4] = {0, 0, 0, 0};
             bool was_hit = false;
             if (!dummy) {
-                if (e == (int)BEYOND || len > MAXW) state = 3;
-                else if (M.cache_ok && len <= CACHE_KEY_MAX) {
-                    build_key(ws.text, s, len, first, key);
-                    was_hit = cache_lookup(J, key, v0, v1);
+                if (keyed && M.cache_ok) {
+                    was_hit = cache_lookup(J, key, w);
                     state = was_hit ? 1u : 2u;
-                } else state = 2;
+                } else state = len > MAXW ? 3u : 2u;
             }
-            // ---- misses: the whole warp merges them one after the other ----
-            uint32_t nproc = 32, ovf_used = 0;
-            uint32_t mm = __ballot_sync(FULL, state == 2);
-            while (mm) {
-                const int src = __ffs(mm) - 1;
-                mm &= mm - 1;
-                const int ss = __shfl_sync(FULL, s, src), ll = __shfl_sync(FULL, len, src);
-                const uint32_t ff = __shfl_sync(FULL, first, src);
-                const bool with_prefix = ff && ws.text[ss] != ' ';
-                const bool alone_first = ff && ws.text[ss] == ' ';
-                const uint32_t npfx = with_prefix ? M.n_prefix_syms : 0u;
-                const uint32_t nal = alone_first ? M.n_prefix_alone : 0u;
-                uint32_t cnt = 0, unit = M.inert, pb = 0;
-                auto at = [&](unsigned long long p) -> uint32_t { return ws.text[p]; };
-                if (lane < ll)
-                    cnt = char_symbols(M, sm.byte1, at, (unsigned long long)(ss + lane), (unsigned long long)ss,
-                                       (unsigned long long)(ss + ll), &unit, &pb);
-                const uint32_t smask = __ballot_sync(FULL, cnt != 0);
-                const uint32_t m = npfx + __popc(smask);
-                if (__any_sync(FULL, cnt > 1) || m > 32 || npfx > 8 || nal > 2) {  // not a register-path pretoken
-                    if (lane == src) state = 3;
-                    continue;
-                }
-                __syncwarp();
-                if ((uint32_t)lane < npfx) ws.wscratch[lane] = M.prefix_syms[lane];
-                if (cnt) ws.wscratch[npfx + __popc(smask & lt_mask)] = unit;
-                __syncwarp();
-                uint32_t u = (uint32_t)lane < m ? ws.wscratch[lane] : NONE;
-                const uint32_t ntok = warp_merge(M, u, m);
-                const int32_t id = (uint32_t)lane < ntok ? id_of_unit(M, u) : -1;
-                const uint32_t total = ntok + nal;
-                st_wm++;
-                if (total >= 1 && total <= (uint32_t)CACHE_IDS) {
-                    unsigned long long p0 = 0, p1 = (unsigned long long)total << 61;
+            uint32_t nproc = 32;
+            if (__any_sync(FULL, state >= 2)) {
+                // ---- misses: the whole warp merges them one after the other ----
+                uint32_t ovf_used = 0;
+                uint32_t mm = __ballot_sync(FULL, state == 2);
+                while (mm) {
+                    const int src = __ffs(mm) - 1;
+                    mm &= mm - 1;
+                    const int ss = __shfl_sync(FULL, s, src), ll = __shfl_sync(FULL, len, src);
+                    const uint32_t ff = __shfl_sync(FULL, first, src);
+                    const bool with_prefix = ff && ws.text[ss] != ' ';
+                    const bool alone_first = ff && ws.text[ss] == ' ';
+                    const uint32_t npfx = with_prefix ? M.n_prefix_syms : 0u;
+                    const uint32_t nal = alone_first ? M.n_prefix_alone : 0u;
+                    uint32_t cnt = 0, unit = M.inert, pb = 0;
+                    auto at = [&](unsigned long long p) -> uint32_t { return ws.text[p]; };
+                    if (lane < ll)
+                        cnt = char_symbols(M, sm.byte1, at, (unsigned long long)(ss + lane), (unsigned long long)ss,
+                                           (unsigned long long)(ss + ll), &unit, &pb);
+                    const uint32_t smask = __ballot_sync(FULL, cnt != 0);
+                    const uint32_t m = npfx + __popc(smask);
+                    if (__any_sync(FULL, cnt > 1) || m > 32 || npfx > 8 || nal > 2) {  // not a register-path pretoken
+                        if (lane == src) state = 3;
+                        continue;
+                    }
+                    __syncwarp();
+                    if ((uint32_t)lane < npfx) ws.wscratch[lane] = M.prefix_syms[lane];
+                    if (cnt) ws.wscratch[npfx + __popc(smask & lt_mask)] = unit;
+                    __syncwarp();
+                    uint32_t u = (uint32_t)lane < m ? ws.wscratch[lane] : NONE;
+                    const uint32_t ntok = warp_merge(M, u, m);
+                    const int32_t id = (uint32_t)lane < ntok ? id_of_unit(M, u) : -1;
+                    const uint32_t total = ntok + nal;
+                    st_wm++;
+                    if (M.cache_ok && total >= 1 && total <= (uint32_t)CACHE_IDS) {
+                        int32_t t[CACHE_IDS];
 #pragma unroll
-                    for (uint32_t i = 0; i < (uint32_t)CACHE_IDS; ++i) {
-                        const int32_t got = __shfl_sync(FULL, id, i >= nal ? (int)(i - nal) : 0);
-                        const int32_t t = i < nal ? M.prefix_alone[i] : got;
-                        const unsigned long long f = i < total ? (unsigned long long)(uint32_t)(t + 2) : 0ull;
-                        if (i < 3) p0 |= f << (21 * i);
-                        else p1 |= f << (21 * (i - 3));
+                        for (uint32_t i = 0; i < (uint32_t)CACHE_IDS; ++i) {
+                            const int32_t got = __shfl_sync(FULL, id, i >= nal ? (int)(i - nal) : 0);
+                            t[i] = i < nal ? M.prefix_alone[i] : got;
+                        }
+                        uint32_t pw[4];
+                        val_pack(t, total, pw);
+                        if (lane == src) {
+                            w[0] = pw[0];
+                            w[1] = pw[1];
+                            w[2] = pw[2];
+                            w[3] = pw[3];
+                            state = 1;
+                            if (ll <= CACHE_KEY_MAX) cache_insert(J, key, pw);
+                        }
+                    } else {
+                        if (ovf_used + total > (uint32_t)OVF) {  // does not fit: this round ends before lane src
+                            nproc = (uint32_t)src;
+                            break;
+                        }
+                        if ((uint32_t)lane < nal) ws.ovf[ovf_used + lane] = M.prefix_alone[lane];
+                        if ((uint32_t)lane < ntok) ws.ovf[ovf_used + nal + lane] = id;
+                        if (lane == src) {
+                            w[0] = 7u << 21;
+                            w[1] = ovf_used | (total << 16);
+                            state = 1;
+                        }
+                        ovf_used += total;
                     }
-                    if (lane == src) {
-                        v0 = p0;
-                        v1 = p1;
-                        state = 1;
-                        if (M.cache_ok && ll <= CACHE_KEY_MAX) cache_insert(J, key, p0, p1);
-                    }
-                } else {
-                    if (ovf_used + total > (uint32_t)OVF) {  // does not fit: this round ends before lane src
-                        nproc = (uint32_t)src;
-                        break;
-                    }
-                    if ((uint32_t)lane < nal) ws.ovf[ovf_used + lane] = M.prefix_alone[lane];
-                    if ((uint32_t)lane < ntok) ws.ovf[ovf_used + nal + lane] = id;
-                    if (lane == src) {
-                        v0 = ovf_used | ((unsigned long long)total << 16);
-                        v1 = 7ull << 61;
-                        state = 1;
-                    }
-                    ovf_used += total;
                 }
+                __syncwarp();
             }
-            __syncwarp();
             const bool in_round = (uint32_t)lane < nproc;
             // ---- counts -> offsets inside the tile's slot ----
-            const uint32_t cf = (uint32_t)(v1 >> 61);
-            const uint32_t c = (in_round && state == 1) ? (cf == 7 ? (uint32_t)(v0 >> 16) & 0xFFFFu : cf) : 0u;
+            const uint32_t cf = val_count(w[0]);
+            const uint32_t c = (in_round && state == 1) ? (cf == 7 ? (w[1] >> 16) : cf) : 0u;
             uint32_t inc = c;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) {
@@ -328,16 +341,21 @@ __global__ void __launch_bounds__(NT, 3) tile_kernel(const DevModel M, const Job
             const uint32_t off = run + inc - c;
             // ---- ids -> staging slot ----
             {
+                int32_t* const p = slot + off;
                 const uint32_t cs = cf == 7 ? 0u : c;  // packed values; results parked in ovf follow below
-                const uint32_t cmax = __reduce_max_sync(FULL, cs);
-#pragma unroll
-                for (uint32_t i = 0; i < (uint32_t)CACHE_IDS; ++i) {
-                    if (i >= cmax) break;
-                    if (i < cs) slot[off + i] = val_id(v0, v1, i);
-                }
-                if (cf == 7 && c) {
-                    const int32_t* src = ws.ovf + (uint32_t)(v0 & 0xFFFFu);
-                    for (uint32_t i = 0; i < c; ++i) slot[off + i] = src[i];
+                if (cs > 0) p[0] = sext21(w[0]);
+                if (cs > 1) p[1] = sext21(w[1]);
+                if (cs > 2) p[2] = sext21(w[2]);
+                if (cs > 3) p[3] = sext21(w[3]);
+                if (__any_sync(FULL, c > 4)) {
+                    if (cs > 4) p[4] = val_id4(w);
+                    if (cf == 7 && c) {
+                        const int32_t* src = ws.ovf + (w[1] & 0xFFFFu);
+                        for (uint32_t i = 0; i < c; ++i) p[i] = src[i];
+                    }
+                } else if (cf == 7 && c) {
+                    const int32_t* src = ws.ovf + (w[1] & 0xFFFFu);
+                    for (uint32_t i = 0; i < c; ++i) p[i] = src[i];
                 }
             }
             // ---- deferred pretokens, per-document offsets (rare) ----
@@ -356,7 +374,7 @@ __global__ void __launch_bounds__(NT, 3) tile_kernel(const DevModel M, const Job
                 def_head = __shfl_sync(FULL, def_head, 0);
                 def_tail = __shfl_sync(FULL, def_tail, 0);
             }
-            if (in_round && !dummy && dsb) {  // documents starting at this pretoken: ids before it in the tile
+            if (tile_docs && in_round && !dummy && dsb) {  // documents starting at this pretoken: ids before it in the tile
                 const unsigned long long gpos = (unsigned long long)(g0 + s);
                 unsigned long long d = dfirst;
                 while (d < J.ndocs && J.doc_off[d] < gpos) ++d;
@@ -377,15 +395,16 @@ __global__ void __launch_bounds__(NT, 3) tile_kernel(const DevModel M, const Job
         }
     }
     // ---- statistics ----
+    unsigned long long sum_pre = st_pre, sum_hit = st_hit;
 #pragma unroll
     for (int d = 16; d; d >>= 1) {
-        st_pre += __shfl_xor_sync(FULL, st_pre, d);
-        st_hit += __shfl_xor_sync(FULL, st_hit, d);
+        sum_pre += __shfl_xor_sync(FULL, sum_pre, d);
+        sum_hit += __shfl_xor_sync(FULL, sum_hit, d);
     }
     if (lane == 0) {
         Counters* c = J.ctr;
-        if (st_pre) atomicAdd(&c->st_pretokens, st_pre);
-        if (st_hit) atomicAdd(&c->st_hits, st_hit);
+        if (sum_pre) atomicAdd(&c->st_pretokens, sum_pre);
+        if (sum_hit) atomicAdd(&c->st_hits, sum_hit);
         if (st_wm) atomicAdd(&c->st_warp, st_wm);
         if (st_def) atomicAdd(&c->st_block, st_def);
     }
