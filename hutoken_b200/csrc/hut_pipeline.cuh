@@ -113,7 +113,7 @@ __device__ __forceinline__ void defer_push(const Job& J, uint32_t tile, unsigned
     tail = idx;
 }
 
-__global__ void __launch_bounds__(NT, 3) tile_kernel(const DevModel M, const Job J) {
+__global__ void __launch_bounds__(NT, 5) tile_kernel(const DevModel M, const Job J) {
     __shared__ TileSm sm;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t FULL = 0xFFFFFFFFu;
