@@ -471,6 +471,28 @@ static cudaError_t grow_host(T** p, size_t* cap, size_t need, bool keep) {
     return cudaSuccess;
 }
 
+extern "C" int hut_plan_shards(const uint64_t* doc_offsets, uint64_t n_docs, int n_shards, uint64_t* bounds) {
+    if (!doc_offsets || !bounds || n_shards <= 0) return HUT_STATUS_ARG;
+    const uint64_t b0 = doc_offsets[0], total = doc_offsets[n_docs] - b0;
+    uint64_t d = 0;
+    bounds[0] = 0;
+    for (int s = 0; s < n_shards; ++s) {
+        if (s == n_shards - 1) d = n_docs;
+        else {
+            const uint64_t target = b0 + (uint64_t)(((unsigned __int128)total * (uint64_t)(s + 1)) / (uint64_t)n_shards);
+            uint64_t lo = d, hi = n_docs;  // first doc boundary >= target
+            while (lo < hi) {
+                const uint64_t mid = (lo + hi) >> 1;
+                if (doc_offsets[mid] < target) lo = mid + 1;
+                else hi = mid;
+            }
+            d = lo;
+        }
+        bounds[s + 1] = d;
+    }
+    return HUT_STATUS_OK;
+}
+
 /* Shards [doc_lo, doc_hi) of the batch onto one device and leaves ids / offsets on the device. */
 struct shard_plan {
     uint64_t doc_lo, doc_hi, byte_lo, byte_hi, n_ids;
@@ -482,28 +504,16 @@ extern "C" int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64
     if (!result || !doc_offsets || (n_docs && !bytes && doc_offsets[n_docs] != doc_offsets[0]))
         return set_err(ctx, HUT_STATUS_ARG, "%s", "bad argument");
     memset(result, 0, sizeof *result);
-    const uint64_t b0 = doc_offsets[0], b1 = doc_offsets[n_docs];
-    const uint64_t total_bytes = b1 - b0;
     // ---- plan: contiguous document ranges balanced by bytes, one per device ----
     int nsh = ctx->ndev;
     if ((uint64_t)nsh > n_docs) nsh = n_docs ? (int)n_docs : 1;
     shard_plan plan[MAX_DEV];
     {
-        uint64_t d = 0;
+        uint64_t bounds[MAX_DEV + 1];
+        hut_plan_shards(doc_offsets, n_docs, nsh, bounds);
         for (int s = 0; s < nsh; ++s) {
-            plan[s].doc_lo = d;
-            uint64_t target = b0 + (total_bytes * (uint64_t)(s + 1)) / (uint64_t)nsh;
-            if (s == nsh - 1) d = n_docs;
-            else {
-                uint64_t lo = d, hi = n_docs;  // first doc boundary >= target
-                while (lo < hi) {
-                    uint64_t mid = (lo + hi) >> 1;
-                    if (doc_offsets[mid] < target) lo = mid + 1;
-                    else hi = mid;
-                }
-                d = lo;
-            }
-            plan[s].doc_hi = d;
+            plan[s].doc_lo = bounds[s];
+            plan[s].doc_hi = bounds[s + 1];
             plan[s].byte_lo = doc_offsets[plan[s].doc_lo];
             plan[s].byte_hi = doc_offsets[plan[s].doc_hi];
             plan[s].n_ids = 0;

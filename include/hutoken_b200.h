@@ -76,6 +76,12 @@ typedef struct hut_result {
 int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64_t* doc_offsets, uint64_t n_docs,
                      hut_result* result);
 
+/* The sharding rule of hut_encode_batch as a pure host function (no CUDA call): cuts documents [0, n_docs) into
+ * n_shards contiguous ranges balanced by bytes; shard s gets documents [bounds[s], bounds[s+1]).  bounds holds
+ * n_shards + 1 entries.  Replaces the dynamic doc->thread assignment of taskqueue_get (taskqueue.c:16-35): shards
+ * are independent, so ranks (or devices) only ever exchange their per-shard id counts. */
+int hut_plan_shards(const uint64_t* doc_offsets, uint64_t n_docs, int n_shards, uint64_t* bounds);
+
 /* Same path with every buffer already resident on device `dev_index` of the context (benchmark / pipeline use):
  * d_bytes must be 16-byte aligned; d_ids holds ids_capacity entries, d_tok_offsets n_docs+1 entries.
  * stream is a cudaStream_t (NULL = the context's own stream).  Returns after the ids are complete on device. */
