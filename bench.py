@@ -348,20 +348,14 @@ def run_ours(args):
         barrier()
         e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
 
-    # ---- max over ranks ----
+    # ---- max over ranks / whole-job sums (hutoken_b200/dist.py; covered on CPU by tests/test_dist_cpu.py) ----
+    from hutoken_b200 import dist as D
+
     def allmax(x):
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+        return D.all_reduce_scalar(x, "max", dev)
 
     def allsum(x):
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+        return D.all_reduce_scalar(x, "sum", dev)
 
     dev_ms_max = allmax(dev_ms)
     total_bytes = allsum(float(nbytes))
