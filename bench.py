@@ -47,6 +47,7 @@ def parse_args():
     ap.add_argument("--model", default="gpt2", choices=["gpt2", "llama", "gpt2_small", "llama_small"])
     ap.add_argument("--special-every", type=int, default=0)
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
+    ap.add_argument("--chunk-mb", type=int, default=0, help="hut_options.chunk_mb of the e2e leg (0 = library default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--check", action="store_true", help="also verify a sample of the output against the oracle")
@@ -283,7 +284,7 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     lib = capi.load_library()
     v, s = synth.PATHS[args.model]
-    eng = capi.Engine(v, s, devices=[local], **synth.MODEL_KW[args.model])
+    eng = capi.Engine(v, s, devices=[local], chunk_mb=args.chunk_mb, **synth.MODEL_KW[args.model])
 
     # ---- this rank's documents (pinned host memory: the e2e leg copies from it) ----
     t0 = time.time()

@@ -19,16 +19,41 @@ using namespace hut;
 
 #define MAX_DEV 16
 
+/* one launched shard whose counters have not been read yet */
+struct hut_flight {
+    Job job;
+    Counters* h_ctr;     // pinned mirror of the device counters, copied at the end of the launch
+    cudaEvent_t ev[4];   // start, before / after tile_kernel, end
+    cudaEvent_t done;    // counters are in h_ctr
+};
+
+/* device-side buffers of one chunk of the host-buffer API (two per device: chunk i+1 uploads while chunk i runs
+ * and chunk i-1 downloads) */
+struct hut_chunkbuf {
+    uint8_t* d_text;
+    size_t d_text_cap;
+    unsigned long long* d_off;
+    size_t d_off_cap;
+    int32_t* d_ids;
+    size_t d_ids_cap;
+    unsigned long long* d_tok;
+    size_t d_tok_cap;
+    unsigned long long* h_off;  // pinned: this chunk's rebased document offsets
+    size_t h_off_cap;
+    cudaEvent_t ev_in, ev_out;
+    int out_pending;
+};
+
 struct hut_dev {
     int device;
-    cudaStream_t stream;
+    cudaStream_t stream;        // kernels
+    cudaStream_t s_in, s_out;   // H2D / D2H copies of the host-buffer API
     DevModel dm;
     void* allocs[24];
     int nalloc;
     CacheSlot* cache;
     uint32_t cache_bits;
     Counters* ctr;
-    Counters* h_ctr;  // pinned mirror
     CutRanges* cut;
     uint32_t* cta_scratch;
     unsigned long long cta_scratch_words;
@@ -49,19 +74,11 @@ struct hut_dev {
     size_t def_cap;
     int32_t* long_ids;
     size_t long_cap;
-    Job job;  // the last launched shard
     int32_t* cut_tmp;
     size_t cut_tmp_cap;
-    // staging for the host-buffer API
-    uint8_t* d_text;
-    size_t d_text_cap;
-    unsigned long long* d_off;
-    size_t d_off_cap;
-    int32_t* d_ids;
-    size_t d_ids_cap;
-    unsigned long long* d_tok;
-    size_t d_tok_cap;
-    cudaEvent_t ev[4];
+    hut_flight fl[2];
+    hut_flight* ctr_owner;  // the flight whose launch last (re)set the device counters
+    hut_chunkbuf cb[2];
     hut_stats stats;
 };
 
@@ -76,8 +93,6 @@ struct hut_ctx {
     size_t h_ids_cap;
     unsigned long long* h_tok;
     size_t h_tok_cap;
-    unsigned long long* h_off_stage;  // rebased doc offsets per shard
-    size_t h_off_cap;
 };
 
 static int set_err(hut_ctx* ctx, int status, const char* fmt, const char* a) {
@@ -108,7 +123,15 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     d->device = device;
     CU(ctx, cudaSetDevice(device));
     CU(ctx, cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
-    for (int i = 0; i < 4; ++i) CU(ctx, cudaEventCreate(&d->ev[i]));
+    CU(ctx, cudaStreamCreateWithFlags(&d->s_in, cudaStreamNonBlocking));
+    CU(ctx, cudaStreamCreateWithFlags(&d->s_out, cudaStreamNonBlocking));
+    for (int b = 0; b < 2; ++b) {
+        for (int i = 0; i < 4; ++i) CU(ctx, cudaEventCreate(&d->fl[b].ev[i]));
+        CU(ctx, cudaEventCreateWithFlags(&d->fl[b].done, cudaEventDisableTiming));
+        CU(ctx, cudaMallocHost(&d->fl[b].h_ctr, sizeof(Counters)));
+        CU(ctx, cudaEventCreateWithFlags(&d->cb[b].ev_in, cudaEventDisableTiming));
+        CU(ctx, cudaEventCreateWithFlags(&d->cb[b].ev_out, cudaEventDisableTiming));
+    }
     DevModel& dm = d->dm;
     CU(ctx, upload(d, (const unsigned long long*)m->pair_tab, m->pair_cap, &dm.pair_tab));
     dm.pair_mask = m->pair_cap - 1;
@@ -156,7 +179,6 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     CU(ctx, cudaMemset(d->cache, 0, sizeof(CacheSlot) << d->cache_bits));
     CU(ctx, cudaMalloc(&d->ctr, sizeof(Counters)));
     CU(ctx, cudaMemset(d->ctr, 0, sizeof(Counters)));
-    CU(ctx, cudaMallocHost(&d->h_ctr, sizeof(Counters)));
     CU(ctx, cudaMalloc(&d->cut, sizeof(CutRanges)));
 
     int per_sm = 0, sms = 0;
@@ -185,10 +207,10 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
 
 static void dev_free(hut_dev* d) {
     cudaSetDevice(d->device);
+    cudaDeviceSynchronize();
     for (int i = 0; i < d->nalloc; ++i) cudaFree(d->allocs[i]);
     cudaFree(d->cache);
     cudaFree(d->ctr);
-    cudaFreeHost(d->h_ctr);
     cudaFree(d->cut);
     cudaFree(d->cta_scratch);
     cudaFree(d->big_pool);
@@ -198,13 +220,23 @@ static void dev_free(hut_dev* d) {
     cudaFree(d->def);
     cudaFree(d->long_ids);
     cudaFree(d->cut_tmp);
-    cudaFree(d->d_text);
-    cudaFree(d->d_off);
-    cudaFree(d->d_ids);
-    cudaFree(d->d_tok);
-    for (int i = 0; i < 4; ++i)
-        if (d->ev[i]) cudaEventDestroy(d->ev[i]);
+    for (int b = 0; b < 2; ++b) {
+        hut_chunkbuf* c = &d->cb[b];
+        cudaFree(c->d_text);
+        cudaFree(c->d_off);
+        cudaFree(c->d_ids);
+        cudaFree(c->d_tok);
+        cudaFreeHost(c->h_off);
+        if (c->ev_in) cudaEventDestroy(c->ev_in);
+        if (c->ev_out) cudaEventDestroy(c->ev_out);
+        cudaFreeHost(d->fl[b].h_ctr);
+        for (int i = 0; i < 4; ++i)
+            if (d->fl[b].ev[i]) cudaEventDestroy(d->fl[b].ev[i]);
+        if (d->fl[b].done) cudaEventDestroy(d->fl[b].done);
+    }
     if (d->stream) cudaStreamDestroy(d->stream);
+    if (d->s_in) cudaStreamDestroy(d->s_in);
+    if (d->s_out) cudaStreamDestroy(d->s_out);
 }
 
 extern "C" int hut_create(const hut_model_desc* desc, const hut_options* opt, const int* devices, int ndev,
@@ -261,7 +293,6 @@ extern "C" void hut_destroy(hut_ctx* ctx) {
     for (int i = 0; i < ctx->ndev; ++i) dev_free(&ctx->dev[i]);
     cudaFreeHost(ctx->h_ids);
     cudaFreeHost(ctx->h_tok);
-    cudaFreeHost(ctx->h_off_stage);
     hut_model_free(ctx->model);
     free(ctx);
 }
@@ -309,19 +340,21 @@ static cudaError_t grow(T** p, size_t* cap, size_t need) {
 }
 
 /* launches the kernel pipeline for one resident shard on `st`; the device must be current */
-static int launch_shard(hut_ctx* ctx, hut_dev* d, const uint8_t* d_bytes, uint64_t n_bytes, const uint64_t* d_doc_offsets,
-                        uint64_t n_docs, int32_t* d_ids, uint64_t ids_capacity, uint64_t* d_tok_offsets,
-                        cudaStream_t st, size_t def_want, size_t long_want) {
+static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* d_bytes, uint64_t n_bytes,
+                        const uint64_t* d_doc_offsets, uint64_t n_docs, int32_t* d_ids, uint64_t ids_capacity,
+                        uint64_t* d_tok_offsets, cudaStream_t st, size_t def_want, size_t long_want) {
     if (n_docs >= 0xFFFFFFF0ull) return set_err(ctx, HUT_STATUS_ARG, "%s", "too many documents in one shard");
     if ((uintptr_t)d_bytes & 15) return set_err(ctx, HUT_STATUS_ARG, "%s", "device text buffer must be 16-byte aligned");
     const uint64_t ntiles64 = (n_bytes + OWN - 1) / OWN;
     if (ntiles64 >= 0x7FFFFFF0ull) return set_err(ctx, HUT_STATUS_ARG, "%s", "shard too large (max 2 TB)");
     const uint32_t ntiles = (uint32_t)ntiles64;
-    d->stats.kernel_launches = 0;
     if (ntiles == 0) {
         CU(ctx, cudaMemsetAsync(d_tok_offsets, 0, (n_docs + 1) * sizeof(uint64_t), st));
         CU(ctx, cudaMemsetAsync(d->ctr, 0, offsetof(Counters, events), st));
-        for (int i = 0; i < 4; ++i) CU(ctx, cudaEventRecord(d->ev[i], st));
+        for (int i = 0; i < 4; ++i) CU(ctx, cudaEventRecord(f->ev[i], st));
+        memset(&f->job, 0, sizeof f->job);
+        CU(ctx, cudaMemcpyAsync(f->h_ctr, d->ctr, offsetof(Counters, events), cudaMemcpyDeviceToHost, st));
+        CU(ctx, cudaEventRecord(f->done, st));
         return HUT_STATUS_OK;
     }
     const uint32_t nblocks = (ntiles + SCAN_BLK - 1) / SCAN_BLK;
@@ -364,54 +397,58 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, const uint8_t* d_bytes, uint64
     J.big_slot_words = d->big_slot_words;
     J.big_cap = d->big_cap;
     J.big_slots = d->big_slots;
-    CU(ctx, cudaEventRecord(d->ev[0], st));
+    CU(ctx, cudaEventRecord(f->ev[0], st));
     CU(ctx, cudaMemsetAsync(J.first_doc, 0xFF, ((size_t)ntiles + 1) * sizeof(uint32_t), st));
     init_kernel<<<1, 32, 0, st>>>(J);
     if (n_docs) doc_kernel<<<(unsigned)((n_docs + 255) / 256), 256, 0, st>>>(J);
-    CU(ctx, cudaEventRecord(d->ev[1], st));
+    CU(ctx, cudaEventRecord(f->ev[1], st));
     const uint32_t want = (ntiles + WPB - 1) / WPB;
     tile_kernel<<<want < (uint32_t)d->grid ? want : (uint32_t)d->grid, NT, 0, st>>>(d->dm, J);
-    CU(ctx, cudaEventRecord(d->ev[2], st));
+    CU(ctx, cudaEventRecord(f->ev[2], st));
     long_kernel<<<d->long_grid, LNT, 0, st>>>(d->dm, J);
     scan1_kernel<<<nblocks, 1024, 0, st>>>(J);
     scan2_kernel<<<1, 1024, 0, st>>>(J);
     const uint32_t cgrid = (ntiles + 7) / 8;
     compact_kernel<<<cgrid < (uint32_t)d->sms * 8u ? cgrid : (uint32_t)d->sms * 8u, 256, 0, st>>>(J);
     fixdoc_kernel<<<(unsigned)((n_docs + 1 + 255) / 256), 256, 0, st>>>(J);
-    CU(ctx, cudaEventRecord(d->ev[3], st));
+    CU(ctx, cudaEventRecord(f->ev[3], st));
     CU(ctx, cudaGetLastError());
-    d->stats.kernel_launches = n_docs ? 8 : 7;
-    d->job = J;
+    d->stats.kernel_launches += n_docs ? 8 : 7;
+    f->job = J;
+    d->ctr_owner = f;
+    CU(ctx, cudaMemcpyAsync(f->h_ctr, d->ctr, offsetof(Counters, events), cudaMemcpyDeviceToHost, st));
+    CU(ctx, cudaEventRecord(f->done, st));
     return HUT_STATUS_OK;
 }
 
-/* synchronises the stream: reads the counters, re-runs with larger side buffers if they overflowed, applies
- * document cuts, fills stats */
-static int finish_shard(hut_ctx* ctx, hut_dev* d, uint64_t n_docs, int32_t* d_ids, uint64_t* d_tok_offsets,
-                        uint64_t* n_ids_out, cudaStream_t st) {
-    const Counters* c = d->h_ctr;
+static void stats_begin(hut_dev* d) { memset(&d->stats, 0, sizeof d->stats); }
+
+/* waits for the flight's counters: re-runs with larger side buffers if they overflowed, applies document cuts,
+ * accumulates stats */
+static int finish_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, uint64_t n_docs, int32_t* d_ids,
+                        uint64_t* d_tok_offsets, uint64_t* n_ids_out, cudaStream_t st) {
+    const Counters* c = f->h_ctr;
     for (int attempt = 0;; ++attempt) {
-        CU(ctx, cudaMemcpyAsync(d->h_ctr, d->ctr, offsetof(Counters, events), cudaMemcpyDeviceToHost, st));
-        CU(ctx, cudaStreamSynchronize(st));
+        CU(ctx, cudaEventSynchronize(f->done));
         if (!(c->flags & (FLAG_DEF_CAP | FLAG_LONG_CAP)) || attempt == 4) break;
         // rare: many / very long deferred pretokens.  The counters kept counting, so they state the need.
-        const Job& J = d->job;
+        CU(ctx, cudaStreamSynchronize(st));  // later chunks queued behind this one still use the side buffers
+        const Job J = f->job;
         const size_t def_want = (size_t)c->n_def + 1024, long_want = (size_t)c->long_used * 2 + 4096;
-        int rc = launch_shard(ctx, d, J.text, J.nbytes, (const uint64_t*)J.doc_off, J.ndocs, J.out, J.out_cap,
+        int rc = launch_shard(ctx, d, f, J.text, J.nbytes, (const uint64_t*)J.doc_off, J.ndocs, J.out, J.out_cap,
                               (uint64_t*)J.tok_off, st, def_want, long_want);
         if (rc != HUT_STATUS_OK) return rc;
     }
     float ms_all = 0, ms_main = 0;
-    cudaEventElapsedTime(&ms_all, d->ev[0], d->ev[3]);
-    cudaEventElapsedTime(&ms_main, d->ev[1], d->ev[2]);
-    d->stats.pretokens = c->st_pretokens;
-    d->stats.cache_hits = c->st_hits;
-    d->stats.warp_merges = c->st_warp;
-    d->stats.block_merges = c->st_block;
-    d->stats.big_merges = c->st_big;
-    d->stats.cut_documents = 0;
-    d->stats.kernel_ms = ms_all;
-    d->stats.main_kernel_ms = ms_main;
+    cudaEventElapsedTime(&ms_all, f->ev[0], f->ev[3]);
+    cudaEventElapsedTime(&ms_main, f->ev[1], f->ev[2]);
+    d->stats.pretokens += c->st_pretokens;
+    d->stats.cache_hits += c->st_hits;
+    d->stats.warp_merges += c->st_warp;
+    d->stats.block_merges += c->st_block;
+    d->stats.big_merges += c->st_big;
+    d->stats.kernel_ms += ms_all;
+    d->stats.main_kernel_ms += ms_main;
     uint64_t total = c->total_ids;
     if (c->flags & FLAG_OUT_CAP) return set_err(ctx, HUT_STATUS_CAPACITY, "%s", "output id buffer too small");
     if (c->flags & FLAG_BIG_CAP)
@@ -423,10 +460,20 @@ static int finish_shard(hut_ctx* ctx, hut_dev* d, uint64_t n_docs, int32_t* d_id
     if (c->flags & FLAG_NUL)
         return set_err(ctx, HUT_STATUS_VALUE, "%s", "document contains a 0x00 byte (cut documents at NUL before calling)");
     if (c->n_events) {
-        // reference-compatible cut (core.c:402-407,503): drop the rest of each affected document
+        // reference-compatible cut (core.c:402-407,503): drop the rest of each affected document.  The events are
+        // still in the device counters only if no later chunk has started: drain the stream and re-read them.
+        CU(ctx, cudaStreamSynchronize(st));
+        if (d->ctr_owner != f) {  // a later chunk reset the counters: run this one again, alone
+            const Job J = f->job;
+            int rc = launch_shard(ctx, d, f, J.text, J.nbytes, (const uint64_t*)J.doc_off, J.ndocs, J.out, J.out_cap,
+                                  (uint64_t*)J.tok_off, st, d->def_cap, d->long_cap);
+            if (rc != HUT_STATUS_OK) return rc;
+            CU(ctx, cudaEventSynchronize(f->done));
+            total = c->total_ids;
+        }
         CU(ctx, grow(&d->cut_tmp, &d->cut_tmp_cap, (size_t)total));
         CU(ctx, cudaMemcpyAsync(d->cut_tmp, d_ids, total * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
-        cut_prepare_kernel<<<1, 1, 0, st>>>(d->job, d->cut);
+        cut_prepare_kernel<<<1, 1, 0, st>>>(f->job, d->cut);
         cut_apply_ids_kernel<<<592, 256, 0, st>>>(d->cut_tmp, d_ids, total, d->cut);
         cut_apply_offs_kernel<<<148, 256, 0, st>>>((unsigned long long*)d_tok_offsets, n_docs + 1, d->cut);
         CU(ctx, cudaGetLastError());
@@ -434,7 +481,7 @@ static int finish_shard(hut_ctx* ctx, hut_dev* d, uint64_t n_docs, int32_t* d_id
         CU(ctx, cudaMemcpyAsync(&head, d->cut, offsetof(CutRanges, x), cudaMemcpyDeviceToHost, st));
         CU(ctx, cudaStreamSynchronize(st));
         total = head.new_total;
-        d->stats.cut_documents = head.n;
+        d->stats.cut_documents += head.n;
         d->stats.kernel_launches += 3;
     }
     *n_ids_out = total;
@@ -450,9 +497,11 @@ extern "C" int hut_encode_device(hut_ctx* ctx, int dev_index, const uint8_t* d_b
     hut_dev* d = &ctx->dev[dev_index];
     CU(ctx, cudaSetDevice(d->device));
     cudaStream_t st = stream ? (cudaStream_t)stream : d->stream;
-    int rc = launch_shard(ctx, d, d_bytes, n_bytes, d_doc_offsets, n_docs, d_ids, ids_capacity, d_tok_offsets, st, 0, 0);
+    stats_begin(d);
+    hut_flight* f = &d->fl[0];
+    int rc = launch_shard(ctx, d, f, d_bytes, n_bytes, d_doc_offsets, n_docs, d_ids, ids_capacity, d_tok_offsets, st, 0, 0);
     if (rc != HUT_STATUS_OK) return rc;
-    return finish_shard(ctx, d, n_docs, d_ids, d_tok_offsets, n_ids_out, st);
+    return finish_shard(ctx, d, f, n_docs, d_ids, d_tok_offsets, n_ids_out, st);
 }
 
 template <class T>
@@ -493,10 +542,93 @@ extern "C" int hut_plan_shards(const uint64_t* doc_offsets, uint64_t n_docs, int
     return HUT_STATUS_OK;
 }
 
-/* Shards [doc_lo, doc_hi) of the batch onto one device and leaves ids / offsets on the device. */
-struct shard_plan {
-    uint64_t doc_lo, doc_hi, byte_lo, byte_hi, n_ids;
+/* One chunk of a host-buffer batch: documents [doc_lo, doc_hi) on device `dev`, buffers cb[buf] / fl[buf]. */
+struct chunk_plan {
+    uint64_t doc_lo, doc_hi, byte_lo, byte_hi, n_ids, id_base;
+    int dev, buf;
 };
+
+static int drain_outputs(hut_ctx* ctx) {
+    for (int i = 0; i < ctx->ndev; ++i) {
+        CU(ctx, cudaSetDevice(ctx->dev[i].device));
+        CU(ctx, cudaStreamSynchronize(ctx->dev[i].s_out));
+    }
+    return HUT_STATUS_OK;
+}
+
+/* upload + kernels of one chunk (asynchronous) */
+static int chunk_issue(hut_ctx* ctx, const uint8_t* bytes, const uint64_t* doc_offsets, chunk_plan* p) {
+    hut_dev* d = &ctx->dev[p->dev];
+    hut_chunkbuf* c = &d->cb[p->buf];
+    const uint64_t nb = p->byte_hi - p->byte_lo, nd = p->doc_hi - p->doc_lo;
+    CU(ctx, cudaSetDevice(d->device));
+    if (c->out_pending) {  // the ids of the chunk that used these buffers before are still going to the host
+        CU(ctx, cudaStreamWaitEvent(d->stream, c->ev_out, 0));
+        c->out_pending = 0;
+    }
+    // worst case: every symbol survives as its own id (+ prefix ids per document)
+    const uint64_t worst = nb * d->dm.kmax + nd * (uint64_t)(d->dm.n_prefix_syms + d->dm.n_prefix_alone) + 64;
+    if (nb + 64 > c->d_text_cap || nd + 1 > c->d_off_cap || nd + 1 > c->d_tok_cap || worst > c->d_ids_cap) {
+        CU(ctx, cudaDeviceSynchronize());  // growing frees buffers that queued work may still use
+        CU(ctx, grow(&c->d_text, &c->d_text_cap, (size_t)nb + 64));
+        CU(ctx, grow(&c->d_off, &c->d_off_cap, (size_t)nd + 1));
+        CU(ctx, grow(&c->d_tok, &c->d_tok_cap, (size_t)nd + 1));
+        CU(ctx, grow(&c->d_ids, &c->d_ids_cap, (size_t)worst));
+    }
+    if (nd + 1 > c->h_off_cap) {
+        CU(ctx, cudaStreamSynchronize(d->s_in));
+        if (c->h_off) cudaFreeHost(c->h_off);
+        c->h_off = nullptr;
+        c->h_off_cap = 0;
+        const size_t n = (size_t)nd + 1 + nd / 4 + 1024;
+        CU(ctx, cudaMallocHost(&c->h_off, n * sizeof(uint64_t)));
+        c->h_off_cap = n;
+    }
+    for (uint64_t i = 0; i <= nd; ++i) c->h_off[i] = doc_offsets[p->doc_lo + i] - p->byte_lo;
+    if (nb) CU(ctx, cudaMemcpyAsync(c->d_text, bytes + p->byte_lo, nb, cudaMemcpyHostToDevice, d->s_in));
+    CU(ctx, cudaMemcpyAsync(c->d_off, c->h_off, (nd + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, d->s_in));
+    CU(ctx, cudaEventRecord(c->ev_in, d->s_in));
+    CU(ctx, cudaStreamWaitEvent(d->stream, c->ev_in, 0));
+    return launch_shard(ctx, d, &d->fl[p->buf], c->d_text, nb, (const uint64_t*)c->d_off, nd, c->d_ids, c->d_ids_cap,
+                        (uint64_t*)c->d_tok, d->stream, 0, 0);
+}
+
+/* waits for the chunk's kernels, then starts the download of its ids and offsets into the final pinned buffers */
+static int chunk_complete(hut_ctx* ctx, chunk_plan* p, uint64_t id_base, uint64_t bytes_done, uint64_t bytes_total) {
+    hut_dev* d = &ctx->dev[p->dev];
+    hut_chunkbuf* c = &d->cb[p->buf];
+    const uint64_t nd = p->doc_hi - p->doc_lo;
+    CU(ctx, cudaSetDevice(d->device));
+    int rc = finish_shard(ctx, d, &d->fl[p->buf], nd, c->d_ids, (uint64_t*)c->d_tok, &p->n_ids, d->stream);
+    if (rc != HUT_STATUS_OK) return rc;
+    p->id_base = id_base;
+    if (id_base + p->n_ids + 1 > ctx->h_ids_cap) {  // grow the pinned result, keeping what has arrived
+        rc = drain_outputs(ctx);
+        if (rc != HUT_STATUS_OK) return rc;
+        const double per_byte = (double)(id_base + p->n_ids) / (double)(bytes_done ? bytes_done : 1);
+        size_t need = (size_t)(per_byte * 1.05 * (double)bytes_total) + 4096;
+        if (need < id_base + p->n_ids + 1) need = id_base + p->n_ids + 1;
+        int32_t* q = nullptr;
+        CU(ctx, cudaMallocHost(&q, need * sizeof(int32_t)));
+        if (ctx->h_ids) {
+            if (id_base) memcpy(q, ctx->h_ids, id_base * sizeof(int32_t));
+            cudaFreeHost(ctx->h_ids);
+        }
+        ctx->h_ids = q;
+        ctx->h_ids_cap = need;
+        CU(ctx, cudaSetDevice(d->device));
+    }
+    if (p->n_ids)
+        CU(ctx, cudaMemcpyAsync(ctx->h_ids + id_base, c->d_ids, p->n_ids * sizeof(int32_t), cudaMemcpyDeviceToHost,
+                                d->s_out));
+    // nd entries, not nd + 1: entry doc_hi belongs to the next chunk (two streams must not write one word)
+    if (nd)
+        CU(ctx, cudaMemcpyAsync(ctx->h_tok + p->doc_lo, c->d_tok, nd * sizeof(uint64_t), cudaMemcpyDeviceToHost,
+                                d->s_out));
+    CU(ctx, cudaEventRecord(c->ev_out, d->s_out));
+    c->out_pending = 1;
+    return HUT_STATUS_OK;
+}
 
 extern "C" int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64_t* doc_offsets, uint64_t n_docs,
                                 hut_result* result) {
@@ -504,86 +636,80 @@ extern "C" int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64
     if (!result || !doc_offsets || (n_docs && !bytes && doc_offsets[n_docs] != doc_offsets[0]))
         return set_err(ctx, HUT_STATUS_ARG, "%s", "bad argument");
     memset(result, 0, sizeof *result);
-    // ---- plan: contiguous document ranges balanced by bytes, one per device ----
-    int nsh = ctx->ndev;
-    if ((uint64_t)nsh > n_docs) nsh = n_docs ? (int)n_docs : 1;
-    shard_plan plan[MAX_DEV];
+    const uint64_t total_bytes = doc_offsets[n_docs] - doc_offsets[0];
+    // ---- plan: contiguous document ranges balanced by bytes (hut_plan_shards), dealt round-robin to the devices;
+    //      every device works on two chunks at a time: upload of chunk k+1 | kernels of chunk k | download of k-1 ----
+    const int ndev = ctx->ndev;
+    uint64_t chunk_bytes = (uint64_t)(ctx->opt.chunk_mb ? ctx->opt.chunk_mb : 32u) << 20;
+    uint64_t nch64 = (total_bytes + chunk_bytes - 1) / chunk_bytes;
+    if (nch64 < (uint64_t)ndev) nch64 = (uint64_t)ndev;
+    if (nch64 > n_docs) nch64 = n_docs ? n_docs : 1;
+    if (nch64 > (1u << 20)) nch64 = 1u << 20;
+    const int nch = (int)nch64;
+    uint64_t* bounds = (uint64_t*)malloc(((size_t)nch + 1) * sizeof(uint64_t));
+    chunk_plan* plan = (chunk_plan*)calloc((size_t)nch, sizeof(chunk_plan));
+    if (!bounds || !plan) {
+        free(bounds);
+        free(plan);
+        return set_err(ctx, HUT_STATUS_MEMORY, "%s", "out of memory");
+    }
+    hut_plan_shards(doc_offsets, n_docs, nch, bounds);
+    for (int k = 0; k < nch; ++k) {
+        plan[k].doc_lo = bounds[k];
+        plan[k].doc_hi = bounds[k + 1];
+        plan[k].byte_lo = doc_offsets[plan[k].doc_lo];
+        plan[k].byte_hi = doc_offsets[plan[k].doc_hi];
+        plan[k].dev = k % ndev;
+        plan[k].buf = (k / ndev) & 1;
+    }
+    free(bounds);
+    int rc = HUT_STATUS_OK;
+    auto bail = [&](int st) {
+        for (int i = 0; i < ctx->ndev; ++i) {
+            cudaSetDevice(ctx->dev[i].device);
+            cudaDeviceSynchronize();
+            ctx->dev[i].cb[0].out_pending = ctx->dev[i].cb[1].out_pending = 0;
+        }
+        free(plan);
+        return st;
+    };
     {
-        uint64_t bounds[MAX_DEV + 1];
-        hut_plan_shards(doc_offsets, n_docs, nsh, bounds);
-        for (int s = 0; s < nsh; ++s) {
-            plan[s].doc_lo = bounds[s];
-            plan[s].doc_hi = bounds[s + 1];
-            plan[s].byte_lo = doc_offsets[plan[s].doc_lo];
-            plan[s].byte_hi = doc_offsets[plan[s].doc_hi];
-            plan[s].n_ids = 0;
+        cudaError_t e = grow_host(&ctx->h_tok, &ctx->h_tok_cap, (size_t)n_docs + 1, false);
+        if (e != cudaSuccess) return bail(set_err(ctx, HUT_STATUS_CUDA, "CUDA error: %s", cudaGetErrorString(e)));
+    }
+    for (int i = 0; i < ndev; ++i) stats_begin(&ctx->dev[i]);
+    const int depth = 2 * ndev;
+    uint64_t id_base = 0, bytes_done = 0;
+    for (int k = 0; k < nch + depth; ++k) {
+        if (k >= depth) {
+            chunk_plan* p = &plan[k - depth];
+            bytes_done += p->byte_hi - p->byte_lo;
+            rc = chunk_complete(ctx, p, id_base, bytes_done, total_bytes);
+            if (rc != HUT_STATUS_OK) return bail(rc);
+            id_base += p->n_ids;
+        }
+        if (k < nch) {
+            rc = chunk_issue(ctx, bytes, doc_offsets, &plan[k]);
+            if (rc != HUT_STATUS_OK) return bail(rc);
         }
     }
-    CU(ctx, grow_host(&ctx->h_tok, &ctx->h_tok_cap, (size_t)n_docs + 1, false));
-    CU(ctx, grow_host(&ctx->h_off_stage, &ctx->h_off_cap, (size_t)n_docs + (size_t)nsh + 1, false));
-    // ---- phase A: upload + kernels on every device ----
-    uint64_t stage_at = 0;
-    for (int s = 0; s < nsh; ++s) {
-        hut_dev* d = &ctx->dev[s];
-        const shard_plan& p = plan[s];
-        const uint64_t nb = p.byte_hi - p.byte_lo, nd = p.doc_hi - p.doc_lo;
-        CU(ctx, cudaSetDevice(d->device));
-        CU(ctx, grow(&d->d_text, &d->d_text_cap, (size_t)nb + 64));
-        CU(ctx, grow(&d->d_off, &d->d_off_cap, (size_t)nd + 1));
-        CU(ctx, grow(&d->d_tok, &d->d_tok_cap, (size_t)nd + 1));
-        // worst case: every symbol survives as its own id (+ prefix ids per document)
-        const uint64_t worst = nb * d->dm.kmax + nd * (uint64_t)(d->dm.n_prefix_syms + d->dm.n_prefix_alone) + 64;
-        CU(ctx, grow(&d->d_ids, &d->d_ids_cap, (size_t)worst));
-        unsigned long long* ho = ctx->h_off_stage + stage_at;
-        for (uint64_t i = 0; i <= nd; ++i) ho[i] = doc_offsets[p.doc_lo + i] - p.byte_lo;
-        stage_at += nd + 1;
-        if (nb) CU(ctx, cudaMemcpyAsync(d->d_text, bytes + p.byte_lo, nb, cudaMemcpyHostToDevice, d->stream));
-        CU(ctx, cudaMemcpyAsync(d->d_off, ho, (nd + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, d->stream));
-        int rc = launch_shard(ctx, d, d->d_text, nb, (const uint64_t*)d->d_off, nd, d->d_ids, d->d_ids_cap,
-                              (uint64_t*)d->d_tok, d->stream, 0, 0);
-        if (rc != HUT_STATUS_OK) return rc;
+    rc = drain_outputs(ctx);
+    if (rc != HUT_STATUS_OK) return bail(rc);
+    for (int i = 0; i < ndev; ++i) ctx->dev[i].cb[0].out_pending = ctx->dev[i].cb[1].out_pending = 0;
+    // per-chunk offsets are local: add each chunk's base (host side, one add per document -- 8(e))
+    for (int k = 0; k < nch; ++k)
+        if (plan[k].id_base)
+            for (uint64_t i = plan[k].doc_lo; i < plan[k].doc_hi; ++i) ctx->h_tok[i] += plan[k].id_base;
+    ctx->h_tok[n_docs] = id_base;
+    if (!ctx->h_ids) {  // nothing was produced: still hand out a valid pointer
+        cudaError_t e = cudaMallocHost(&ctx->h_ids, 64);
+        if (e != cudaSuccess) return bail(set_err(ctx, HUT_STATUS_CUDA, "CUDA error: %s", cudaGetErrorString(e)));
+        ctx->h_ids_cap = 16;
     }
-    // ---- phase B: counts, then ids straight into the final pinned buffer ----
-    uint64_t total_ids = 0;
-    for (int s = 0; s < nsh; ++s) {
-        hut_dev* d = &ctx->dev[s];
-        CU(ctx, cudaSetDevice(d->device));
-        int rc = finish_shard(ctx, d, plan[s].doc_hi - plan[s].doc_lo, d->d_ids, (uint64_t*)d->d_tok, &plan[s].n_ids,
-                              d->stream);
-        if (rc != HUT_STATUS_OK) return rc;
-        total_ids += plan[s].n_ids;
-    }
-    CU(ctx, grow_host(&ctx->h_ids, &ctx->h_ids_cap, (size_t)total_ids + 1, false));
-    uint64_t id_base = 0;
-    for (int s = 0; s < nsh; ++s) {
-        hut_dev* d = &ctx->dev[s];
-        const uint64_t nd = plan[s].doc_hi - plan[s].doc_lo;
-        CU(ctx, cudaSetDevice(d->device));
-        if (plan[s].n_ids)
-            CU(ctx, cudaMemcpyAsync(ctx->h_ids + id_base, d->d_ids, plan[s].n_ids * sizeof(int32_t),
-                                    cudaMemcpyDeviceToHost, d->stream));
-        // nd entries, not nd + 1: entry doc_hi belongs to the next shard (two streams must not write one word)
-        if (nd)
-            CU(ctx, cudaMemcpyAsync(ctx->h_tok + plan[s].doc_lo, d->d_tok, nd * sizeof(uint64_t),
-                                    cudaMemcpyDeviceToHost, d->stream));
-        id_base += plan[s].n_ids;
-    }
-    id_base = 0;
-    for (int s = 0; s < nsh; ++s) {
-        hut_dev* d = &ctx->dev[s];
-        CU(ctx, cudaSetDevice(d->device));
-        CU(ctx, cudaStreamSynchronize(d->stream));
-    }
-    // per-shard offsets are local: add each shard's base (host side, one add per document -- 8(e))
-    for (int s = 0; s < nsh; ++s) {
-        if (id_base)
-            for (uint64_t i = plan[s].doc_lo; i < plan[s].doc_hi; ++i) ctx->h_tok[i] += id_base;
-        id_base += plan[s].n_ids;
-    }
-    ctx->h_tok[n_docs] = total_ids;
+    free(plan);
     result->ids = ctx->h_ids;
     result->tok_offsets = (const uint64_t*)ctx->h_tok;
-    result->n_ids = total_ids;
+    result->n_ids = id_base;
     result->n_docs = n_docs;
     return HUT_STATUS_OK;
 }

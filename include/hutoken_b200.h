@@ -50,7 +50,8 @@ typedef struct hut_options {
                                   262144 bytes (core.c:27-28,402-407,503).  Otherwise: no cut; pretokens up to this
                                   many bytes are merged (block-cooperative path), longer ones are an error. */
     uint32_t big_slots;        /* working areas for pretokens that outgrow a tile; 0 = default */
-    uint32_t reserved;
+    uint32_t chunk_mb;         /* hut_encode_batch streams the batch through the devices in chunks of about this many
+                                  MiB so that upload, kernels and download overlap; 0 = default (32) */
 } hut_options;
 
 /* Replaces p_initialize (lib.c:185-666) + initialize_context (lib.c:128-183): loads the files, derives the
@@ -70,8 +71,11 @@ typedef struct hut_result {
 
 /* Replaces the per-document encode() loop of p_batch_encode (lib.c:722-874) / p_encode (lib.c:668-720).
  * Host buffers: documents are bytes[doc_offsets[i] .. doc_offsets[i+1]) (UTF-8, packed, no separators).
- * A document is cut at its first 0x00 byte like the reference's strdup (lib.c:772).  Documents are sharded
- * by bytes over the context's devices; there is no inter-device communication.  The result lives in
+ * A 0x00 byte inside a document is an error (HUT_STATUS_VALUE): the binding cuts documents at their first NUL
+ * like the reference's strdup (lib.c:772).  The batch is cut into contiguous document ranges balanced by bytes
+ * (hut_plan_shards) which are dealt round-robin to the context's devices and streamed through them (upload of one
+ * chunk overlaps the kernels of the previous and the download of the one before); there is no inter-device
+ * communication.  The result lives in
  * pinned host memory owned by the context and stays valid until the next call on this context. */
 int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64_t* doc_offsets, uint64_t n_docs,
                      hut_result* result);

@@ -179,3 +179,26 @@ def test_python_surface():
     orc = oracle_for("llama_small")
     for t in ("hello world", " hello", "x\ny"):
         assert hutoken.encode(t) == orc.encode(t)
+
+
+@pytest.mark.parametrize("devices,chunk_mb", [([0], 1), ([0, 0], 1), ([0, 0, 0], 2)])
+def test_host_api_streams_chunks(devices, chunk_mb):
+    """hut_encode_batch streams the batch through the devices in chunks (upload | kernels | download overlap) and
+    deals the chunks round-robin to the devices of the context; the result must not depend on either.  (The same
+    physical GPU listed several times stands in for several GPUs: each entry has its own streams, tables and cache.)"""
+    for name in ("gpt2", "llama_small"):
+        eng, orc = engine_for(name, devices=tuple(devices), chunk_mb=chunk_mb), oracle_for(name)
+        data, offs = synth.corpus(51, 9 << 20, special_every=300)
+        oids, otok = orc.encode_packed(data, offs)
+        for _ in range(2):  # second call: warm caches, reused buffers
+            ids, tok = eng.encode_packed(data, offs)
+            assert_same(ids, tok, oids, otok, f"{name} devices={devices}")
+        assert eng.device_count == len(devices)
+        # ragged batches: fewer documents than chunks / devices, empty documents, a document larger than a chunk
+        docs = ["", "x" * (3 << 20) + " tail", "", "short one", ""]
+        d2, o2 = pack(docs)
+        ids, tok = eng.encode_packed(d2, o2)
+        oids2, otok2 = orc.encode_packed(d2, o2)
+        assert_same(ids, tok, oids2, otok2, f"{name} ragged devices={devices}")
+        ids, tok = eng.encode_packed(*pack([]))
+        assert len(ids) == 0 and tok.tolist() == [0]
