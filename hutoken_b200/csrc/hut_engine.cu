@@ -72,6 +72,9 @@ struct hut_dev {
     size_t bsum_cap;
     DefEntry* def;
     size_t def_cap;
+    MissEntry* miss;
+    size_t miss_cap;
+    int miss_grid;
     int32_t* long_ids;
     size_t long_cap;
     int32_t* cut_tmp;
@@ -146,7 +149,15 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     dm.multi_sym = m->max_sym_per_char > 1;
     dm.has_prefix = m->has_prefix;
     dm.cache_ok = (m->max_value < (1 << 20)) ? 1 : 0;  // ids are packed as signed 21-bit fields
-    dm.kmax = m->max_sym_per_char;
+    dm.kmax = m->max_sym_per_char ? m->max_sym_per_char : 1;
+    {   // pretokens up to this many bytes are merged by one lane of miss_kernel (<= MISS_SYMS symbols incl. prefix)
+        const uint32_t pfx = m->has_prefix ? m->n_prefix_syms : 0u;
+        uint32_t lmax = pfx < (uint32_t)MISS_SYMS ? ((uint32_t)MISS_SYMS - pfx) / dm.kmax : 0u;
+        if (lmax > (uint32_t)MAXW) lmax = MAXW;
+        if (m->n_prefix_alone > 8) lmax = 0;
+        dm.miss_len_max = lmax;
+        dm.first_extra = m->has_prefix ? (m->n_prefix_syms > m->n_prefix_alone ? m->n_prefix_syms : m->n_prefix_alone) : 0u;
+    }
     CU(ctx, upload(d, m->sym_off, 257, &dm.sym_off));
     CU(ctx, upload(d, m->sym_pool, m->sym_off[256], &dm.sym_pool));
     uint32_t byte1[256];
@@ -188,6 +199,11 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     d->sms = sms;
     d->grid = per_sm * sms;
     d->long_grid = 2 * sms;
+    {
+        int per = 0;
+        CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, miss_kernel, MNT, 0));
+        d->miss_grid = (per < 1 ? 1 : per) * sms;
+    }
 
     // ids a 960-byte tile can produce: one per symbol of the pretokens STARTING in it (the last one may run up to
     // MAXW - 1 bytes past the tile) + the prefix ids of every document starting in it
@@ -218,6 +234,7 @@ static void dev_free(hut_dev* d) {
     cudaFree(d->tilebuf);
     cudaFree(d->bsum);
     cudaFree(d->def);
+    cudaFree(d->miss);
     cudaFree(d->long_ids);
     cudaFree(d->cut_tmp);
     for (int b = 0; b < 2; ++b) {
@@ -342,7 +359,8 @@ static cudaError_t grow(T** p, size_t* cap, size_t need) {
 /* launches the kernel pipeline for one resident shard on `st`; the device must be current */
 static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* d_bytes, uint64_t n_bytes,
                         const uint64_t* d_doc_offsets, uint64_t n_docs, int32_t* d_ids, uint64_t ids_capacity,
-                        uint64_t* d_tok_offsets, cudaStream_t st, size_t def_want, size_t long_want) {
+                        uint64_t* d_tok_offsets, cudaStream_t st, size_t def_want, size_t long_want,
+                        size_t miss_want = 0) {
     if (n_docs >= 0xFFFFFFF0ull) return set_err(ctx, HUT_STATUS_ARG, "%s", "too many documents in one shard");
     if ((uintptr_t)d_bytes & 15) return set_err(ctx, HUT_STATUS_ARG, "%s", "device text buffer must be 16-byte aligned");
     const uint64_t ntiles64 = (n_bytes + OWN - 1) / OWN;
@@ -365,6 +383,9 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     CU(ctx, grow(&d->bsum, &d->bsum_cap, (size_t)nblocks));
     CU(ctx, grow(&d->def, &d->def_cap, def_want));
     CU(ctx, grow(&d->long_ids, &d->long_cap, long_want));
+    if (miss_want < (size_t)n_bytes / 96 + 65536) miss_want = (size_t)n_bytes / 96 + 65536;
+    if (n_bytes > (1ull << 40) - 1) return set_err(ctx, HUT_STATUS_ARG, "%s", "shard too large (max 1 TB)");
+    CU(ctx, grow(&d->miss, &d->miss_cap, miss_want));
     Job J;
     memset(&J, 0, sizeof J);
     J.text = d_bytes;
@@ -385,6 +406,8 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     J.nblocks = nblocks;
     J.def = d->def;
     J.def_cap = d->def_cap > 0xFFFFFFF0ull ? 0xFFFFFFF0u : (uint32_t)d->def_cap;
+    J.miss = d->miss;
+    J.miss_cap = d->miss_cap > 0xFFFFFFF0ull ? 0xFFFFFFF0u : (uint32_t)d->miss_cap;
     J.long_ids = d->long_ids;
     J.long_cap = d->long_cap;
     J.ctr = d->ctr;
@@ -402,8 +425,18 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     init_kernel<<<1, 32, 0, st>>>(J);
     if (n_docs) doc_kernel<<<(unsigned)((n_docs + 255) / 256), 256, 0, st>>>(J);
     CU(ctx, cudaEventRecord(f->ev[1], st));
+    // tile_kernel merges the cache misses it can key itself (batches of 32, one per lane) and lists the rest, which
+    // miss_kernel merges afterwards
+    J.tile_lo = 0;
+    J.tile_hi = ntiles;
+    J.seg = 0;
     const uint32_t want = (ntiles + WPB - 1) / WPB;
     tile_kernel<<<want < (uint32_t)d->grid ? want : (uint32_t)d->grid, NT, 0, st>>>(d->dm, J);
+    {
+        const uint32_t mg = ntiles / 4 + 1;
+        miss_kernel<<<mg < (uint32_t)d->miss_grid ? mg : (uint32_t)d->miss_grid, MNT, 0, st>>>(d->dm, J);
+    }
+    const uint32_t nlaunch = 2;
     CU(ctx, cudaEventRecord(f->ev[2], st));
     long_kernel<<<d->long_grid, LNT, 0, st>>>(d->dm, J);
     scan1_kernel<<<nblocks, 1024, 0, st>>>(J);
@@ -413,7 +446,7 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     fixdoc_kernel<<<(unsigned)((n_docs + 1 + 255) / 256), 256, 0, st>>>(J);
     CU(ctx, cudaEventRecord(f->ev[3], st));
     CU(ctx, cudaGetLastError());
-    d->stats.kernel_launches += n_docs ? 8 : 7;
+    d->stats.kernel_launches += nlaunch + (n_docs ? 7 : 6);
     f->job = J;
     d->ctr_owner = f;
     CU(ctx, cudaMemcpyAsync(f->h_ctr, d->ctr, offsetof(Counters, events), cudaMemcpyDeviceToHost, st));
@@ -430,13 +463,15 @@ static int finish_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, uint64_t n_docs
     const Counters* c = f->h_ctr;
     for (int attempt = 0;; ++attempt) {
         CU(ctx, cudaEventSynchronize(f->done));
-        if (!(c->flags & (FLAG_DEF_CAP | FLAG_LONG_CAP)) || attempt == 4) break;
+        if (!(c->flags & (FLAG_DEF_CAP | FLAG_LONG_CAP | FLAG_MISS_CAP)) || attempt == 4) break;
         // rare: many / very long deferred pretokens.  The counters kept counting, so they state the need.
         CU(ctx, cudaStreamSynchronize(st));  // later chunks queued behind this one still use the side buffers
         const Job J = f->job;
         const size_t def_want = (size_t)c->n_def + 1024, long_want = (size_t)c->long_used * 2 + 4096;
+        // the miss count of a run that overflowed is only a lower bound (later segments saw a colder cache)
+        const size_t miss_want = (c->flags & FLAG_MISS_CAP) ? (size_t)c->n_miss * 2 + 65536 : 0;
         int rc = launch_shard(ctx, d, f, J.text, J.nbytes, (const uint64_t*)J.doc_off, J.ndocs, J.out, J.out_cap,
-                              (uint64_t*)J.tok_off, st, def_want, long_want);
+                              (uint64_t*)J.tok_off, st, def_want, long_want, miss_want);
         if (rc != HUT_STATUS_OK) return rc;
     }
     float ms_all = 0, ms_main = 0;
@@ -453,7 +488,7 @@ static int finish_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, uint64_t n_docs
     if (c->flags & FLAG_OUT_CAP) return set_err(ctx, HUT_STATUS_CAPACITY, "%s", "output id buffer too small");
     if (c->flags & FLAG_BIG_CAP)
         return set_err(ctx, HUT_STATUS_UNSUPPORTED, "%s", "a pretoken exceeds the configured max_pretoken working area");
-    if (c->flags & (FLAG_DEF_CAP | FLAG_LONG_CAP))
+    if (c->flags & (FLAG_DEF_CAP | FLAG_LONG_CAP | FLAG_MISS_CAP))
         return set_err(ctx, HUT_STATUS_MEMORY, "%s", "side buffers for long pretokens could not be sized");
     if (c->flags & FLAG_EVENTS)
         return set_err(ctx, HUT_STATUS_UNSUPPORTED, "%s", "too many over-long pretokens in one call");

@@ -44,7 +44,14 @@ constexpr int MAXW = 32;              // longest pretoken (bytes) / most symbols
 constexpr int CACHE_KEY_MAX = 15;     // longest pretoken (bytes) the cache keys on
 constexpr int CACHE_PROBES = 8;
 constexpr int CACHE_IDS = 5;          // most ids a cache value holds
-constexpr int OVF = 96;               // ids of >5-token results staged per round and warp
+constexpr int MISS_SMALL = 16;        // ... of the small instance of miss_kernel (most pretokens)
+constexpr int MISS_SYMS = 40;         // most initial symbols (incl. prefix symbols) miss_kernel merges in one lane
+constexpr int MAX_SEG = 64;           // segments of one launch (tile_kernel / miss_kernel pairs)
+constexpr int MNT = 128;              // threads per CTA of miss_kernel
+constexpr int32_t HOLE = (int32_t)0x80000000;  // staging filler behind the ids of a deferred cache miss
+constexpr uint32_t CNT_CHAIN = 0x80000000u;    // cnt[tile] flag: the tile has pretokens deferred to long_kernel
+constexpr uint32_t CNT_HOLES = 0x40000000u;    // cnt[tile] flag: the tile's slot holds holes (deferred misses)
+constexpr uint32_t CNT_MASK = 0x3FFFFFFFu;
 constexpr int DEFMAX = 32;            // deferred pretokens per tile
 constexpr int MAX_EVENTS = 1024;
 constexpr int SCAN_BLK = 4096;        // tiles per scan block
@@ -62,7 +69,8 @@ enum : uint32_t {
     FLAG_BIG_CAP = 4u,    // pretoken longer than the configured working area (no-limit mode)
     FLAG_EVENTS = 8u,     // more over-long pretokens than MAX_EVENTS
     FLAG_DEF_CAP = 16u,   // deferred-pretoken list full   (host retries with a larger one)
-    FLAG_LONG_CAP = 32u   // ids of deferred pretokens do not fit (host retries with a larger buffer)
+    FLAG_LONG_CAP = 32u,  // ids of deferred pretokens do not fit (host retries with a larger buffer)
+    FLAG_MISS_CAP = 64u   // list of cache misses full          (host retries with a larger one)
 };
 
 struct __align__(16) CacheSlot {  // 32 bytes = one L2 sector
@@ -87,15 +95,22 @@ struct DefEntry {  // a pretoken tile_kernel hands to long_kernel
     unsigned long long ids_off;  // into long_ids
 };
 
+struct MissEntry {  // a pretoken that missed the cache: merged later, 32 at a time, by miss_kernel
+    unsigned long long pos_off;  // global byte position (bits 0..39) | offset of its ids in the tile's slot (bits 40..63)
+    uint32_t meta;               // len (bits 0..7) | first-of-document (bit 8) | staging entries reserved (bits 16..31)
+    uint32_t pad;
+};
+
 struct Counters {
     unsigned int flags;
     unsigned int n_events;
     unsigned int n_def;
-    unsigned int pad;
+    unsigned int n_miss;
     unsigned long long total_ids;
     unsigned long long long_used;  // bump pointer into long_ids
     unsigned long long st_pretokens, st_hits, st_warp, st_block, st_big, st_cut;
     unsigned int pool_lock[32];
+    unsigned int seg_end[MAX_SEG];  // n_miss at the end of each segment's tile_kernel
     CutEvent events[MAX_EVENTS];
 };
 
@@ -117,6 +132,8 @@ struct DevModel {
     const int32_t* prefix_alone;
     uint32_t n_prefix_alone;
     uint32_t kmax;
+    uint32_t miss_len_max;     // longest pretoken (bytes) whose symbols fit one lane of miss_kernel
+    uint32_t first_extra;      // extra ids the first pretoken of a document can produce (prefix symbols / ids)
     unsigned long long limit;  // longest pretoken merged; beyond: cut (compat) or error (no-limit)
     int compat_cut;
 };
@@ -132,7 +149,11 @@ struct Job {
     uint32_t ntiles;
     uint32_t stride;           // ids per staging slot
     int32_t* stage;            // [ntiles * stride]
-    uint32_t* cnt;             // [ntiles] bits 0..23 ids in the slot, bits 24..31 deferred pretokens
+    uint32_t tile_lo, tile_hi; // tiles of the current segment
+    uint32_t seg;
+    MissEntry* miss;
+    uint32_t miss_cap;
+    uint32_t* cnt;             // [ntiles] entries used in the slot (CNT_MASK) | CNT_CHAIN | CNT_HOLES
     uint32_t* tot;             // [ntiles] ids of the tile incl. deferred ones; after scan1: exclusive in-block prefix
     unsigned long long* bsum;  // [nblocks] block sums; after scan2: exclusive prefix
     uint32_t nblocks;
@@ -226,6 +247,29 @@ __device__ __forceinline__ uint32_t pair_probe(const DevModel& M, uint32_t l, ui
         if ((s >> 21) == key) return (uint32_t)(s & HUT_UNIT_MASK);
         i = (i + 1) & M.pair_mask;
     }
+}
+
+// both new neighbour pairs of a merge, (l, c) and (c, r), with their first loads issued together; l / r == NONE
+// means there is no such neighbour
+__device__ __forceinline__ void pair_probe2(const DevModel& M, uint32_t l, uint32_t c, uint32_t r, uint32_t* ml,
+                                            uint32_t* mr) {
+    const bool okc = c < M.inert;
+    const bool ok1 = okc && l < M.inert, ok2 = okc && r < M.inert;
+    uint32_t i1 = hut_pair_hash(l, c, M.pair_mask), i2 = hut_pair_hash(c, r, M.pair_mask);
+    unsigned long long s1 = HUT_PAIR_EMPTY, s2 = HUT_PAIR_EMPTY;
+    if (ok1) s1 = __ldg(M.pair_tab + i1);
+    if (ok2) s2 = __ldg(M.pair_tab + i2);
+    const uint64_t key1 = ((uint64_t)l << 21) | c, key2 = ((uint64_t)c << 21) | r;
+    while (s1 != HUT_PAIR_EMPTY && (s1 >> 21) != key1) {
+        i1 = (i1 + 1) & M.pair_mask;
+        s1 = __ldg(M.pair_tab + i1);
+    }
+    while (s2 != HUT_PAIR_EMPTY && (s2 >> 21) != key2) {
+        i2 = (i2 + 1) & M.pair_mask;
+        s2 = __ldg(M.pair_tab + i2);
+    }
+    *ml = s1 == HUT_PAIR_EMPTY ? NONE : (uint32_t)(s1 & HUT_UNIT_MASK);
+    *mr = s2 == HUT_PAIR_EMPTY ? NONE : (uint32_t)(s2 & HUT_UNIT_MASK);
 }
 
 __device__ __forceinline__ uint32_t rank_of_unit(const DevModel& M, uint32_t mg) {
@@ -422,6 +466,96 @@ __device__ __forceinline__ uint32_t char_symbols(const DevModel& M, const uint32
     *pool_begin = lo;
     if (hi - lo == 1) *first = __ldg(M.sym_pool + lo);
     return hi - lo;
+}
+
+// ------------------------------------------------------------------------------------------------
+// lane-per-pretoken merge.  ONE LANE runs the whole merge loop of one pretoken of at most S symbols (arrays in
+// local memory, which the hardware interleaves by lane): per merge one scan for the leftmost minimal rank -- the
+// (rank, left index) order of the reference's heap (queue.c:162-164) -- one shift to close the gap and two pair-table
+// probes (issued together) for the new neighbours.  Replaces bpe_encode_arena_string (core.c:66-209) for the
+// pretokens the cache has not seen; 32 independent pretokens per warp keep the probe latency overlapped.
+// The ids go into the `room` entries tile_kernel reserved at dst (the rest of the room becomes HOLEs) and, when the
+// pretoken is cacheable, into the cache.  Returns room - ids written.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+
+template <int S>
+__device__ __forceinline__ uint32_t merge_entry(const DevModel& M, const Job& J, const uint32_t* byte1,
+                                                unsigned long long pos, uint32_t len, uint32_t first, uint32_t room,
+                                                int32_t* dst) {
+    uint32_t U[S], MG[S];
+    auto at = [&](unsigned long long p) -> uint32_t { return (uint32_t)__ldg(J.text + p); };
+    const uint32_t b0 = at(pos);
+    const bool with_prefix = first && b0 != ' ';
+    const bool alone_first = first && b0 == ' ';
+    const uint32_t npfx = with_prefix ? M.n_prefix_syms : 0u;
+    const uint32_t nal = alone_first ? M.n_prefix_alone : 0u;
+    // ---- initial symbols (A.3) + the cache key ----
+    uint32_t m = 0;
+    for (uint32_t k = 0; k < npfx; ++k) U[m++] = M.prefix_syms[k];
+    unsigned long long k0 = 0, k1 = 0;
+    for (uint32_t p = 0; p < len; ++p) {
+        uint32_t unit = M.inert, pb = 0;
+        const uint32_t cnt = char_symbols(M, byte1, at, pos + p, pos, pos + len, &unit, &pb);
+        if (cnt == 1) U[m++] = unit;
+        else
+            for (uint32_t k = 0; k < cnt; ++k) U[m++] = __ldg(M.sym_pool + pb + k);
+        const unsigned long long b = at(pos + p);
+        if (p < 8) k0 |= b << (8 * p);
+        else if (p < 15) k1 |= b << (8 * (p - 8));
+    }
+    // ---- merge loop (A.4).  The first slot of every initial pair is prefetched so that the probes overlap. ----
+    for (uint32_t k = 0; k + 1 < m; ++k) {
+        const uint32_t l = U[k], r = U[k + 1];
+        if (l < M.inert && r < M.inert) prefetch_l1(M.pair_tab + hut_pair_hash(l, r, M.pair_mask));
+    }
+    for (uint32_t k = 0; k + 1 < m; ++k) MG[k] = pair_probe(M, U[k], U[k + 1]);
+    for (;;) {
+        uint32_t best = 0xFFFFFFFFu, j = 0;
+        for (uint32_t k = 0; k + 1 < m; ++k) {
+            const uint32_t rk = rank_of_unit(M, MG[k]);
+            if (rk < best) {
+                best = rk;
+                j = k;
+            }
+        }
+        if (best == 0xFFFFFFFFu) break;
+        const uint32_t mu = MG[j];
+        U[j] = mu;
+        m--;
+        const uint32_t ul = j > 0 ? U[j - 1] : NONE;
+        const uint32_t ur = j + 1 < m ? U[j + 2] : NONE;  // not shifted yet
+        uint32_t ml, mr;
+        pair_probe2(M, ul, mu, ur, &ml, &mr);
+        for (uint32_t k = j + 1; k < m; ++k) {
+            U[k] = U[k + 1];
+            MG[k] = MG[k + 1];
+        }
+        if (j > 0) MG[j - 1] = ml;
+        MG[j] = mr;  // NONE when j is the last symbol now
+    }
+    // ---- ids into the reserved room, HOLEs behind them ----
+    const uint32_t total = nal + m;  // <= room by construction (tile_kernel reserves the worst case)
+    int32_t t5[CACHE_IDS] = {0, 0, 0, 0, 0};
+    for (uint32_t k = 0; k < room; ++k) {
+        int32_t id = HOLE;
+        if (k < nal) id = M.prefix_alone[k];
+        else if (k < total) id = id_of_unit(M, U[k - nal]);
+#pragma unroll
+        for (int z = 0; z < CACHE_IDS; ++z)
+            if (k == (uint32_t)z) t5[z] = id;
+        dst[k] = id;
+    }
+    if (M.cache_ok && len <= (uint32_t)CACHE_KEY_MAX && total >= 1 && total <= (uint32_t)CACHE_IDS) {
+        uint32_t key[4], pw[4];
+        key[0] = (uint32_t)k0;
+        key[1] = (uint32_t)(k0 >> 32);
+        key[2] = (uint32_t)k1;
+        key[3] = (uint32_t)(k1 >> 32) | ((0x80u | (first << 4) | len) << 24);
+        val_pack(t5, total, pw);
+        cache_insert(J, key, pw);
+    }
+    return room - total;
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -9,11 +9,9 @@ namespace hut {
 // shared memory of ONE WARP of tile_kernel
 struct __align__(16) WarpSm {
     uint8_t text[TEXTB];        // span bytes: [tile_start - 32, tile_start + 992 + 16), then zero padding
-    uint32_t bnd[CHUNK];        // per chunk: pretoken starts | NUL bytes
     uint32_t dsm[CHUNK + 4];    // per chunk: document starts
     uint16_t pstart[OWN + 8];   // span positions of the boundaries inside the owned chunks, then the end sentinel
-    uint32_t wscratch[32];      // symbol scatter of the warp merge
-    int32_t ovf[OVF];           // ids of results with more than 5 tokens, until the round is emitted
+    uint4 q[64];                // cache misses waiting for a full batch: pos_off (x, y), meta (z), tile (w)
     unsigned long long mbar;
 };
 
@@ -29,6 +27,7 @@ __global__ void init_kernel(Job J) {
         c->flags = 0;
         c->n_events = 0;
         c->n_def = 0;
+        c->n_miss = 0;
         c->total_ids = 0;
         c->long_used = 0;
         c->st_pretokens = c->st_hits = c->st_warp = c->st_block = c->st_big = c->st_cut = 0;
@@ -113,7 +112,32 @@ __device__ __forceinline__ void defer_push(const Job& J, uint32_t tile, unsigned
     tail = idx;
 }
 
-__global__ void __launch_bounds__(NT, 5) tile_kernel(const DevModel M, const Job J) {
+// merges the first n (<= 32) queued cache misses, one per lane (merge_entry).  The room a pretoken of another tile
+// did not use is subtracted from that tile's count here; for the tile in progress it is returned (warp sum).
+__device__ __forceinline__ uint32_t run_batch(const DevModel& M, const Job& J, const uint32_t* byte1, const uint4* q,
+                                           uint32_t n, uint32_t cur_tile) {
+    const uint32_t lane = threadIdx.x & 31;
+    uint32_t slack = 0;
+    if (lane < n) {
+        const uint4 E = q[lane];
+        const unsigned long long pos_off = E.x | ((unsigned long long)E.y << 32);
+        const unsigned long long pos = pos_off & ((1ull << 40) - 1);
+        const uint32_t loff = (uint32_t)(pos_off >> 40);
+        const uint32_t len = E.z & 0xFFu, first = (E.z >> 8) & 1u, room = E.z >> 16;
+        slack = merge_entry<MISS_SMALL>(M, J, byte1, pos, len, first, room,
+                                        J.stage + (unsigned long long)E.w * J.stride + loff);
+        if (slack && E.w != cur_tile) {
+            atomicSub(&J.tot[E.w], slack);
+            slack = 0;
+        }
+    }
+    __syncwarp();
+#pragma unroll
+    for (int d = 16; d; d >>= 1) slack += __shfl_xor_sync(0xFFFFFFFFu, slack, d);
+    return slack;
+}
+
+__global__ void __launch_bounds__(NT, 4) tile_kernel(const __grid_constant__ DevModel M, const __grid_constant__ Job J) {
     __shared__ TileSm sm;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t FULL = 0xFFFFFFFFu;
@@ -129,14 +153,15 @@ __global__ void __launch_bounds__(NT, 5) tile_kernel(const DevModel M, const Job
         mbar_init(&ws.mbar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    __syncthreads();  // the only block-wide barrier: byte1 is read-only afterwards
+    __syncthreads();  // the only block-wide barrier: kmask is read-only afterwards
 
     uint32_t parity = 0;
     uint32_t st_pre = 0, st_hit = 0;  // per lane
-    unsigned long long st_wm = 0, st_def = 0;
+    unsigned long long st_def = 0, st_wm = 0;
+    uint32_t qn = 0;                  // cache misses queued in ws.q
     const uint32_t gw = blockIdx.x * WPB + warp, nw = gridDim.x * WPB;
 
-    for (uint32_t tile = gw; tile < J.ntiles; tile += nw) {
+    for (uint32_t tile = J.tile_lo + gw; tile < J.tile_hi; tile += nw) {
         const long long g0 = (long long)tile * OWN - BACK;  // global position of span index 0
         const long long lo = g0 < 0 ? 0 : g0;
         const long long hi = (g0 + LOADB) < (long long)J.nbytes ? (g0 + LOADB) : (long long)J.nbytes;
@@ -233,11 +258,12 @@ __global__ void __launch_bounds__(NT, 5) tile_kernel(const DevModel M, const Job
         __syncwarp();
 
         // ---- rounds of up to 32 pretokens, one per lane ----
-        uint32_t run = 0;                       // ids of this tile already in its staging slot
+        uint32_t run = 0;                       // entries of this tile's staging slot used so far
         uint32_t def_head = NODOC, def_tail = NODOC;
+        bool holes = false;
+        uint32_t slack = 0;                     // room reserved for misses of this tile that stayed unused
         int32_t* const slot = J.stage + (unsigned long long)tile * J.stride;
-        uint32_t r0 = 0;
-        while (r0 < n) {
+        for (uint32_t r0 = 0; r0 < n; r0 += 32) {
             const uint32_t q = r0 + lane;
             const bool active = q < n;
             const int s = active ? ws.pstart[q] : BACK;
@@ -250,87 +276,19 @@ __global__ void __launch_bounds__(NT, 5) tile_kernel(const DevModel M, const Job
             uint32_t key[4], w[4] = {0u, 0u, 0u, 0u};
             const uint32_t b0 = build_key(ws.text, sm.kmask, s, keyed ? len : 0, first, key);
             const bool dummy = !active || b0 == 0;       // NUL boundary (zero fill past the end of the text)
-            // state: 0 nothing, 1 value ready, 2 needs a warp merge, 3 deferred to long_kernel
+            // state: 0 nothing, 1 ids ready, 2 cache miss merged by this warp (batches of 32), 3 long pretoken ->
+            // long_kernel, 4 miss too long for the cache / the small per-lane arrays -> miss_kernel
             uint32_t state = 0;
-            bool was_hit = false;
             if (!dummy) {
-                if (keyed && M.cache_ok) {
-                    was_hit = cache_lookup(J, key, w);
-                    state = was_hit ? 1u : 2u;
-                } else state = len > MAXW ? 3u : 2u;
+                if (keyed && M.cache_ok && cache_lookup(J, key, w)) state = 1;
+                else if ((uint32_t)len > M.miss_len_max) state = 3;
+                else state = (keyed && (uint32_t)len * M.kmax + (first ? M.n_prefix_syms : 0u) <= (uint32_t)MISS_SMALL)
+                                 ? 2u : 4u;
             }
-            uint32_t nproc = 32;
-            if (__any_sync(FULL, state >= 2)) {
-                // ---- misses: the whole warp merges them one after the other ----
-                uint32_t ovf_used = 0;
-                uint32_t mm = __ballot_sync(FULL, state == 2);
-                while (mm) {
-                    const int src = __ffs(mm) - 1;
-                    mm &= mm - 1;
-                    const int ss = __shfl_sync(FULL, s, src), ll = __shfl_sync(FULL, len, src);
-                    const uint32_t ff = __shfl_sync(FULL, first, src);
-                    const bool with_prefix = ff && ws.text[ss] != ' ';
-                    const bool alone_first = ff && ws.text[ss] == ' ';
-                    const uint32_t npfx = with_prefix ? M.n_prefix_syms : 0u;
-                    const uint32_t nal = alone_first ? M.n_prefix_alone : 0u;
-                    uint32_t cnt = 0, unit = M.inert, pb = 0;
-                    auto at = [&](unsigned long long p) -> uint32_t { return ws.text[p]; };
-                    if (lane < ll)
-                        cnt = char_symbols(M, sm.byte1, at, (unsigned long long)(ss + lane), (unsigned long long)ss,
-                                           (unsigned long long)(ss + ll), &unit, &pb);
-                    const uint32_t smask = __ballot_sync(FULL, cnt != 0);
-                    const uint32_t m = npfx + __popc(smask);
-                    if (__any_sync(FULL, cnt > 1) || m > 32 || npfx > 8 || nal > 2) {  // not a register-path pretoken
-                        if (lane == src) state = 3;
-                        continue;
-                    }
-                    __syncwarp();
-                    if ((uint32_t)lane < npfx) ws.wscratch[lane] = M.prefix_syms[lane];
-                    if (cnt) ws.wscratch[npfx + __popc(smask & lt_mask)] = unit;
-                    __syncwarp();
-                    uint32_t u = (uint32_t)lane < m ? ws.wscratch[lane] : NONE;
-                    const uint32_t ntok = warp_merge(M, u, m);
-                    const int32_t id = (uint32_t)lane < ntok ? id_of_unit(M, u) : -1;
-                    const uint32_t total = ntok + nal;
-                    st_wm++;
-                    if (M.cache_ok && total >= 1 && total <= (uint32_t)CACHE_IDS) {
-                        int32_t t[CACHE_IDS];
-#pragma unroll
-                        for (uint32_t i = 0; i < (uint32_t)CACHE_IDS; ++i) {
-                            const int32_t got = __shfl_sync(FULL, id, i >= nal ? (int)(i - nal) : 0);
-                            t[i] = i < nal ? M.prefix_alone[i] : got;
-                        }
-                        uint32_t pw[4];
-                        val_pack(t, total, pw);
-                        if (lane == src) {
-                            w[0] = pw[0];
-                            w[1] = pw[1];
-                            w[2] = pw[2];
-                            w[3] = pw[3];
-                            state = 1;
-                            if (ll <= CACHE_KEY_MAX) cache_insert(J, key, pw);
-                        }
-                    } else {
-                        if (ovf_used + total > (uint32_t)OVF) {  // does not fit: this round ends before lane src
-                            nproc = (uint32_t)src;
-                            break;
-                        }
-                        if ((uint32_t)lane < nal) ws.ovf[ovf_used + lane] = M.prefix_alone[lane];
-                        if ((uint32_t)lane < ntok) ws.ovf[ovf_used + nal + lane] = id;
-                        if (lane == src) {
-                            w[0] = 7u << 21;
-                            w[1] = ovf_used | (total << 16);
-                            state = 1;
-                        }
-                        ovf_used += total;
-                    }
-                }
-                __syncwarp();
-            }
-            const bool in_round = (uint32_t)lane < nproc;
-            // ---- counts -> offsets inside the tile's slot ----
-            const uint32_t cf = val_count(w[0]);
-            const uint32_t c = (in_round && state == 1) ? (cf == 7 ? (w[1] >> 16) : cf) : 0u;
+            // ---- counts -> offsets inside the tile's slot.  A miss reserves room for its worst case. ----
+            uint32_t c = 0;
+            if (state == 1) c = val_count(w[0]);
+            else if (state == 2 || state == 4) c = (uint32_t)len * M.kmax + (first ? M.first_extra : 0u);
             uint32_t inc = c;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) {
@@ -342,24 +300,56 @@ __global__ void __launch_bounds__(NT, 5) tile_kernel(const DevModel M, const Job
             // ---- ids -> staging slot ----
             {
                 int32_t* const p = slot + off;
-                const uint32_t cs = cf == 7 ? 0u : c;  // packed values; results parked in ovf follow below
+                const uint32_t cs = state == 1 ? c : 0u;
                 if (cs > 0) p[0] = sext21(w[0]);
                 if (cs > 1) p[1] = sext21(w[1]);
                 if (cs > 2) p[2] = sext21(w[2]);
                 if (cs > 3) p[3] = sext21(w[3]);
-                if (__any_sync(FULL, c > 4)) {
-                    if (cs > 4) p[4] = val_id4(w);
-                    if (cf == 7 && c) {
-                        const int32_t* src = ws.ovf + (w[1] & 0xFFFFu);
-                        for (uint32_t i = 0; i < c; ++i) p[i] = src[i];
-                    }
-                } else if (cf == 7 && c) {
-                    const int32_t* src = ws.ovf + (w[1] & 0xFFFFu);
-                    for (uint32_t i = 0; i < c; ++i) p[i] = src[i];
+                if (cs > 4) p[4] = val_id4(w);
+            }
+            // ---- cache misses -> this warp's queue; every 32 of them are merged at once, one per lane ----
+            const uint32_t m2 = __ballot_sync(FULL, state == 2);
+            if (m2) {
+                holes = true;
+                const unsigned long long po = (unsigned long long)(g0 + s) | ((unsigned long long)off << 40);
+                if (state == 2)
+                    ws.q[qn + __popc(m2 & lt_mask)] = make_uint4((uint32_t)po, (uint32_t)(po >> 32),
+                                                                 (uint32_t)len | (first << 8) | (c << 16), tile);
+                qn += __popc(m2);
+                __syncwarp();
+                while (qn >= 32) {
+                    slack += run_batch(M, J, sm.byte1, ws.q, 32, tile);
+                    st_wm += 32;
+                    uint4 t = make_uint4(0, 0, 0, 0);
+                    if (lane + 32 < qn) t = ws.q[lane + 32];
+                    __syncwarp();
+                    if (lane + 32 < qn) ws.q[lane] = t;
+                    qn -= 32;
+                    __syncwarp();
                 }
             }
-            // ---- deferred pretokens, per-document offsets (rare) ----
-            uint32_t dm = __ballot_sync(FULL, in_round && state == 3);
+            // ---- the other misses -> the global miss list (one atomic per round) ----
+            const uint32_t mm = __ballot_sync(FULL, state == 4);
+            if (mm) {
+                holes = true;
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(&J.ctr->n_miss, (unsigned)__popc(mm));
+                base = __shfl_sync(FULL, base, 0);
+                if (state == 4) {
+                    const uint32_t idx = base + __popc(mm & lt_mask);
+                    if (idx < J.miss_cap) {
+                        MissEntry E;
+                        E.pos_off = (unsigned long long)(g0 + s) | ((unsigned long long)off << 40);
+                        E.meta = (uint32_t)len | (first << 8) | (c << 16);
+                        E.pad = 0;
+                        J.miss[idx] = E;
+                    } else {
+                        set_flag(J, FLAG_MISS_CAP);
+                    }
+                }
+            }
+            // ---- long pretokens, per-document offsets (rare) ----
+            uint32_t dm = __ballot_sync(FULL, state == 3);
             while (dm) {
                 const int src = __ffs(dm) - 1;
                 dm &= dm - 1;
@@ -374,25 +364,27 @@ __global__ void __launch_bounds__(NT, 5) tile_kernel(const DevModel M, const Job
                 def_head = __shfl_sync(FULL, def_head, 0);
                 def_tail = __shfl_sync(FULL, def_tail, 0);
             }
-            if (tile_docs && in_round && !dummy && dsb) {  // documents starting at this pretoken: ids before it in the tile
+            if (tile_docs && !dummy && dsb) {  // documents starting at this pretoken: slot entries before it
                 const unsigned long long gpos = (unsigned long long)(g0 + s);
                 unsigned long long d = dfirst;
                 while (d < J.ndocs && J.doc_off[d] < gpos) ++d;
                 while (d < J.ndocs && J.doc_off[d] == gpos) J.tok_off[d++] = off;
             }
-            if (in_round && !dummy) {
-                st_pre++;
-                st_hit += was_hit ? 1u : 0u;
-            }
+            st_pre += dummy ? 0u : 1u;
+            st_hit += state == 1 ? 1u : 0u;
             run += round_total;
-            r0 += nproc;
-            __syncwarp();
         }
         if (lane == 0) {
-            J.cnt[tile] = run | (def_head != NODOC ? 0x80000000u : 0u);
-            J.tot[tile] = run;
+            J.cnt[tile] = run | (def_head != NODOC ? CNT_CHAIN : 0u) | (holes ? CNT_HOLES : 0u);
+            J.tot[tile] = run - slack;
             J.def_first[tile] = def_head;
         }
+    }
+    // ---- the misses still queued ----
+    __syncwarp();
+    if (qn) {
+        run_batch(M, J, sm.byte1, ws.q, qn, NODOC);
+        st_wm += qn;
     }
     // ---- statistics ----
     unsigned long long sum_pre = st_pre, sum_hit = st_hit;
@@ -405,11 +397,39 @@ __global__ void __launch_bounds__(NT, 5) tile_kernel(const DevModel M, const Job
         Counters* c = J.ctr;
         if (sum_pre) atomicAdd(&c->st_pretokens, sum_pre);
         if (sum_hit) atomicAdd(&c->st_hits, sum_hit);
-        if (st_wm) atomicAdd(&c->st_warp, st_wm);
         if (st_def) atomicAdd(&c->st_block, st_def);
+        if (st_wm) atomicAdd(&c->st_warp, st_wm);
     }
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// miss_kernel: LANE per entry of the global miss list = the cache misses tile_kernel did not merge itself
+// (pretokens too long for the cache key or for its small per-lane arrays).  See merge_entry.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(MNT) miss_kernel(const DevModel M, const Job J) {
+    __shared__ uint32_t byte1[256];
+    const uint32_t tid = threadIdx.x;
+    for (uint32_t i = tid; i < 256; i += MNT) byte1[i] = M.byte1[i];
+    __syncthreads();
+    uint32_t hi = J.ctr->n_miss;
+    if (hi > J.miss_cap) hi = J.miss_cap;
+    uint32_t n_done = 0;
+    for (uint32_t ei = blockIdx.x * MNT + tid; ei < hi; ei += gridDim.x * MNT) {
+        const MissEntry E = J.miss[ei];
+        const unsigned long long pos = E.pos_off & ((1ull << 40) - 1);
+        const uint32_t loff = (uint32_t)(E.pos_off >> 40);
+        const uint32_t len = E.meta & 0xFFu, first = (E.meta >> 8) & 1u, room = E.meta >> 16;
+        const unsigned long long tile = pos / OWN;
+        const uint32_t slack = merge_entry<MISS_SYMS>(M, J, byte1, pos, len, first, room,
+                                                      J.stage + tile * J.stride + loff);
+        if (slack) atomicSub(&J.tot[tile], slack);
+        n_done++;
+    }
+#pragma unroll
+    for (int d = 16; d; d >>= 1) n_done += __shfl_xor_sync(0xFFFFFFFFu, n_done, d);
+    if ((tid & 31) == 0 && n_done) atomicAdd(&J.ctr->st_warp, (unsigned long long)n_done);
+}
 
 // ------------------------------------------------------------------------------------------------
 // long_kernel: one CTA per deferred pretoken (longer than 32 bytes / symbols, or running past the tile's halo)
@@ -615,24 +635,48 @@ __device__ __forceinline__ void copy_ids(const Job& J, const int32_t* src, unsig
     for (uint32_t i = lane; i < n; i += 32) st_stream_s32(J.out + o + i, ld_stream_s32(src + i));
 }
 
-// staging slots -> dense ids (warp per tile); splices in the ids of deferred pretokens
+// warp copy of the non-HOLE entries of src[0 .. n) to the dense output at position o; returns how many there were
+__device__ __forceinline__ uint32_t copy_ids_filtered(const Job& J, const int32_t* src, unsigned long long o, uint32_t n) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t lt = (1u << lane) - 1u;
+    uint32_t kept = 0;
+    for (uint32_t base = 0; base < n; base += 32) {
+        const uint32_t i = base + lane;
+        const int32_t v = i < n ? ld_stream_s32(src + i) : HOLE;
+        const bool keep = v != HOLE;
+        const uint32_t mask = __ballot_sync(0xFFFFFFFFu, keep);
+        if (keep) {
+            const unsigned long long at = o + kept + __popc(mask & lt);
+            if (at < J.out_cap) st_stream_s32(J.out + at, v);
+            else set_flag(J, FLAG_OUT_CAP);
+        }
+        kept += __popc(mask);
+    }
+    return kept;
+}
+
+// staging slots -> dense ids (warp per tile); drops the HOLEs left by deferred cache misses and splices in the ids
+// of the pretokens long_kernel merged
 __global__ void __launch_bounds__(256) compact_kernel(const Job J) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t gw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), nw = gridDim.x * (blockDim.x >> 5);
     for (uint32_t tile = gw; tile < J.ntiles; tile += nw) {
         const uint32_t c = J.cnt[tile];
-        const uint32_t ns = c & 0x7FFFFFFFu;
+        const uint32_t ns = c & CNT_MASK;
         unsigned long long o = tile_base(J, tile);
         const int32_t* src = J.stage + (unsigned long long)tile * J.stride;
-        if (!(c >> 31)) {
+        if (!(c & (CNT_CHAIN | CNT_HOLES))) {
             copy_ids(J, src, o, ns);
+            continue;
+        }
+        if (!(c & CNT_CHAIN)) {
+            copy_ids_filtered(J, src, o, ns);
             continue;
         }
         uint32_t prev = 0;
         for (uint32_t idx = J.def_first[tile]; idx != NODOC;) {
             const DefEntry E = J.def[idx];
-            copy_ids(J, src + prev, o, E.local_off - prev);
-            o += E.local_off - prev;
+            o += copy_ids_filtered(J, src + prev, o, E.local_off - prev);
             prev = E.local_off;
             if (E.flags & 2u) {  // reference-compatible cut: everything from here to the end of the document goes
                 if (lane == 0) {
@@ -650,7 +694,7 @@ __global__ void __launch_bounds__(256) compact_kernel(const Job J) {
             }
             idx = E.pad;
         }
-        copy_ids(J, src + prev, o, ns - prev);
+        copy_ids_filtered(J, src + prev, o, ns - prev);
     }
 }
 
@@ -665,8 +709,16 @@ __global__ void fixdoc_kernel(const Job J) {
         return;
     }
     const unsigned long long t = pos / OWN;
-    unsigned long long v = J.tok_off[d] + tile_base(J, t);
-    if (J.cnt[t] >> 31)
+    const uint32_t c = J.cnt[t];
+    unsigned long long v = J.tok_off[d];  // entries of the tile's slot before the document
+    if (c & CNT_HOLES) {
+        const int32_t* src = J.stage + t * J.stride;
+        uint32_t h = 0;
+        for (uint32_t i = 0; i < (uint32_t)v; ++i) h += src[i] == HOLE;
+        v -= h;
+    }
+    v += tile_base(J, t);
+    if (c & CNT_CHAIN)
         for (uint32_t idx = J.def_first[t]; idx != NODOC; idx = J.def[idx].pad)
             if (J.def[idx].pos < pos) v += J.def[idx].count;
     J.tok_off[d] = v;
