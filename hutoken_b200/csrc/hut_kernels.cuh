@@ -504,47 +504,62 @@ __device__ __forceinline__ uint32_t merge_entry(const DevModel& M, const Job& J,
         if (p < 8) k0 |= b << (8 * p);
         else if (p < 15) k1 |= b << (8 * (p - 8));
     }
-    // ---- merge loop (A.4).  The first slot of every initial pair is prefetched so that the probes overlap. ----
-    for (uint32_t k = 0; k + 1 < m; ++k) {
+    // ---- merge loop (A.4).  The first slot of every initial pair is prefetched so that the probes overlap.
+    // Symbols never move: a merged-away symbol is cleared in `alive` and neighbours are found with bit scans, so the
+    // array index of the scans is the same in every lane (coalesced local memory) ----
+    const uint32_t m0 = m;
+    for (uint32_t k = 0; k + 1 < m0; ++k) {
         const uint32_t l = U[k], r = U[k + 1];
         if (l < M.inert && r < M.inert) prefetch_l1(M.pair_tab + hut_pair_hash(l, r, M.pair_mask));
     }
-    for (uint32_t k = 0; k + 1 < m; ++k) MG[k] = pair_probe(M, U[k], U[k + 1]);
+    for (uint32_t k = 0; k < m0; ++k) MG[k] = k + 1 < m0 ? pair_probe(M, U[k], U[k + 1]) : NONE;
+    unsigned long long alive = m0 >= 64 ? ~0ull : ((1ull << m0) - 1ull);
     for (;;) {
-        uint32_t best = 0xFFFFFFFFu, j = 0;
-        for (uint32_t k = 0; k + 1 < m; ++k) {
-            const uint32_t rk = rank_of_unit(M, MG[k]);
+        uint32_t best = 0xFFFFFFFFu, j = 0, mu = NONE;
+        for (uint32_t k = 0; k + 1 < m0; ++k) {
+            const uint32_t mg = MG[k];
+            const uint32_t rk = rank_of_unit(M, mg);
             if (rk < best) {
                 best = rk;
                 j = k;
+                mu = mg;
             }
         }
         if (best == 0xFFFFFFFFu) break;
-        const uint32_t mu = MG[j];
+        const uint32_t r = j + 1 + (uint32_t)(__ffsll((long long)(alive >> (j + 1))) - 1);  // right partner of j
+        alive &= ~(1ull << r);
         U[j] = mu;
-        m--;
-        const uint32_t ul = j > 0 ? U[j - 1] : NONE;
-        const uint32_t ur = j + 1 < m ? U[j + 2] : NONE;  // not shifted yet
+        MG[r] = NONE;
+        const unsigned long long below = alive & ((1ull << j) - 1ull), above = alive >> (r + 1);
+        const int l = below ? 63 - __clzll((long long)below) : -1;
+        const int r2 = above ? (int)(r + 1) + (__ffsll((long long)above) - 1) : -1;
+        const uint32_t ul = l >= 0 ? U[l] : NONE, ur = r2 >= 0 ? U[r2] : NONE;
         uint32_t ml, mr;
         pair_probe2(M, ul, mu, ur, &ml, &mr);
-        for (uint32_t k = j + 1; k < m; ++k) {
-            U[k] = U[k + 1];
-            MG[k] = MG[k + 1];
-        }
-        if (j > 0) MG[j - 1] = ml;
+        if (l >= 0) MG[l] = ml;
         MG[j] = mr;  // NONE when j is the last symbol now
     }
     // ---- ids into the reserved room, HOLEs behind them ----
-    const uint32_t total = nal + m;  // <= room by construction (tile_kernel reserves the worst case)
+    const uint32_t total = nal + (uint32_t)__popcll(alive);  // <= room by construction (tile_kernel reserves the worst case)
     int32_t t5[CACHE_IDS] = {0, 0, 0, 0, 0};
-    for (uint32_t k = 0; k < room; ++k) {
-        int32_t id = HOLE;
-        if (k < nal) id = M.prefix_alone[k];
-        else if (k < total) id = id_of_unit(M, U[k - nal]);
+    {
+        uint32_t k = 0;
+        for (; k < nal; ++k) {
+            const int32_t id = M.prefix_alone[k];
 #pragma unroll
-        for (int z = 0; z < CACHE_IDS; ++z)
-            if (k == (uint32_t)z) t5[z] = id;
-        dst[k] = id;
+            for (int z = 0; z < CACHE_IDS; ++z)
+                if (k == (uint32_t)z) t5[z] = id;
+            dst[k] = id;
+        }
+        for (uint32_t i = 0; i < m0; ++i) {
+            if (!((alive >> i) & 1ull)) continue;
+            const int32_t id = id_of_unit(M, U[i]);
+#pragma unroll
+            for (int z = 0; z < CACHE_IDS; ++z)
+                if (k == (uint32_t)z) t5[z] = id;
+            dst[k++] = id;
+        }
+        for (; k < room; ++k) dst[k] = HOLE;
     }
     if (M.cache_ok && len <= (uint32_t)CACHE_KEY_MAX && total >= 1 && total <= (uint32_t)CACHE_IDS) {
         uint32_t key[4], pw[4];
