@@ -632,27 +632,98 @@ __device__ __forceinline__ void copy_ids(const Job& J, const int32_t* src, unsig
         if (lane == 0) set_flag(J, FLAG_OUT_CAP);
         return;
     }
-    for (uint32_t i = lane; i < n; i += 32) st_stream_s32(J.out + o + i, ld_stream_s32(src + i));
+    for (uint32_t base = 0; base < n; base += 128) {
+        int32_t v[4];
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            const uint32_t i = base + 32 * g + lane;
+            v[g] = i < n ? ld_stream_s32(src + i) : 0;
+        }
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            const uint32_t i = base + 32 * g + lane;
+            if (i < n) st_stream_s32(J.out + o + i, v[g]);
+        }
+    }
 }
 
-// warp copy of the non-HOLE entries of src[0 .. n) to the dense output at position o; returns how many there were
+// warp copy of the non-HOLE entries of src[0 .. n) to the dense output at position o; returns how many there were.
+// Four 128-byte loads are in flight per step.
 __device__ __forceinline__ uint32_t copy_ids_filtered(const Job& J, const int32_t* src, unsigned long long o, uint32_t n) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t lt = (1u << lane) - 1u;
     uint32_t kept = 0;
-    for (uint32_t base = 0; base < n; base += 32) {
-        const uint32_t i = base + lane;
-        const int32_t v = i < n ? ld_stream_s32(src + i) : HOLE;
-        const bool keep = v != HOLE;
-        const uint32_t mask = __ballot_sync(0xFFFFFFFFu, keep);
-        if (keep) {
-            const unsigned long long at = o + kept + __popc(mask & lt);
-            if (at < J.out_cap) st_stream_s32(J.out + at, v);
-            else set_flag(J, FLAG_OUT_CAP);
+    for (uint32_t base = 0; base < n; base += 128) {
+        int32_t v[4];
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            const uint32_t i = base + 32 * g + lane;
+            v[g] = i < n ? ld_stream_s32(src + i) : HOLE;
         }
-        kept += __popc(mask);
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            const bool keep = v[g] != HOLE;
+            const uint32_t mask = __ballot_sync(0xFFFFFFFFu, keep);
+            if (keep) {
+                const unsigned long long at = o + kept + __popc(mask & lt);
+                if (at < J.out_cap) st_stream_s32(J.out + at, v[g]);
+                else set_flag(J, FLAG_OUT_CAP);
+            }
+            kept += __popc(mask);
+        }
     }
     return kept;
+}
+
+// The same for a whole tile whose slot holds HOLEs, and the documents starting in the tile get their final id offset
+// on the way: tile_kernel left the slot position of their first pretoken in tok_off, which is translated to the
+// number of ids kept before it.
+__device__ __forceinline__ void compact_tile_holes(const Job& J, uint32_t tile, const int32_t* src, unsigned long long o,
+                                                   uint32_t n) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t lt = (1u << lane) - 1u;
+    const unsigned long long tile_end = ((unsigned long long)tile + 1) * OWN;
+    unsigned long long d = J.first_doc[tile];
+    uint32_t so = 0xFFFFFFFFu;  // slot position of document d's first pretoken; none left: 0xFFFFFFFF
+    auto load_doc = [&]() {
+        so = 0xFFFFFFFFu;
+        if (d != NODOC && d < J.ndocs) {
+            const unsigned long long pos = J.doc_off[d];
+            if (pos < tile_end && pos < J.nbytes) so = (uint32_t)J.tok_off[d];
+        }
+    };
+    load_doc();
+    uint32_t kept = 0;
+    for (uint32_t base = 0; base < n; base += 128) {
+        int32_t v[4];
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            const uint32_t i = base + 32 * g + lane;
+            v[g] = i < n ? ld_stream_s32(src + i) : HOLE;
+        }
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            const uint32_t gbase = base + 32 * g;
+            const bool keep = v[g] != HOLE;
+            const uint32_t mask = __ballot_sync(0xFFFFFFFFu, keep);
+            while (so < gbase + 32) {  // warp-uniform
+                if (lane == 0) J.tok_off[d] = o + kept + __popc(mask & ((1u << (so - gbase)) - 1u));
+                ++d;
+                load_doc();
+            }
+            if (keep) {
+                const unsigned long long at = o + kept + __popc(mask & lt);
+                if (at < J.out_cap) st_stream_s32(J.out + at, v[g]);
+                else set_flag(J, FLAG_OUT_CAP);
+            }
+            kept += __popc(mask);
+        }
+    }
+    while (so != 0xFFFFFFFFu) {  // documents starting behind the last entry of the slot
+        if (lane == 0) J.tok_off[d] = o + kept;
+        ++d;
+        load_doc();
+    }
 }
 
 // staging slots -> dense ids (warp per tile); drops the HOLEs left by deferred cache misses and splices in the ids
@@ -670,7 +741,7 @@ __global__ void __launch_bounds__(256) compact_kernel(const Job J) {
             continue;
         }
         if (!(c & CNT_CHAIN)) {
-            copy_ids_filtered(J, src, o, ns);
+            compact_tile_holes(J, tile, src, o, ns);
             continue;
         }
         uint32_t prev = 0;
@@ -710,6 +781,7 @@ __global__ void fixdoc_kernel(const Job J) {
     }
     const unsigned long long t = pos / OWN;
     const uint32_t c = J.cnt[t];
+    if ((c & (CNT_HOLES | CNT_CHAIN)) == CNT_HOLES) return;  // compact_kernel has translated these already
     unsigned long long v = J.tok_off[d];  // entries of the tile's slot before the document
     if (c & CNT_HOLES) {
         const int32_t* src = J.stage + t * J.stride;
