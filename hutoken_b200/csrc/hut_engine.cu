@@ -53,6 +53,8 @@ struct hut_dev {
     int nalloc;
     CacheSlot* cache;
     uint32_t cache_bits;
+    CacheSlot2* cache2;
+    uint32_t cache2_bits;
     Counters* ctr;
     CutRanges* cut;
     uint32_t* cta_scratch;
@@ -188,6 +190,9 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     if (d->cache_bits > 26) d->cache_bits = 26;
     CU(ctx, cudaMalloc(&d->cache, sizeof(CacheSlot) << d->cache_bits));
     CU(ctx, cudaMemset(d->cache, 0, sizeof(CacheSlot) << d->cache_bits));
+    d->cache2_bits = d->cache_bits > 4 ? d->cache_bits - 4 : 6;  // long pretokens are rare
+    CU(ctx, cudaMalloc(&d->cache2, sizeof(CacheSlot2) << d->cache2_bits));
+    CU(ctx, cudaMemset(d->cache2, 0, sizeof(CacheSlot2) << d->cache2_bits));
     CU(ctx, cudaMalloc(&d->ctr, sizeof(Counters)));
     CU(ctx, cudaMemset(d->ctr, 0, sizeof(Counters)));
     CU(ctx, cudaMalloc(&d->cut, sizeof(CutRanges)));
@@ -226,6 +231,7 @@ static void dev_free(hut_dev* d) {
     cudaDeviceSynchronize();
     for (int i = 0; i < d->nalloc; ++i) cudaFree(d->allocs[i]);
     cudaFree(d->cache);
+    cudaFree(d->cache2);
     cudaFree(d->ctr);
     cudaFree(d->cut);
     cudaFree(d->cta_scratch);
@@ -333,6 +339,7 @@ extern "C" int hut_cache_reset(hut_ctx* ctx) {
         hut_dev* d = &ctx->dev[i];
         CU(ctx, cudaSetDevice(d->device));
         CU(ctx, cudaMemsetAsync(d->cache, 0, sizeof(CacheSlot) << d->cache_bits, d->stream));
+        CU(ctx, cudaMemsetAsync(d->cache2, 0, sizeof(CacheSlot2) << d->cache2_bits, d->stream));
         CU(ctx, cudaStreamSynchronize(d->stream));
     }
     return HUT_STATUS_OK;
@@ -413,6 +420,8 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     J.ctr = d->ctr;
     J.cache = d->cache;
     J.cache_bits = d->cache_bits;
+    J.cache2 = d->cache2;
+    J.cache2_bits = d->cache2_bits;
     J.cta_scratch = d->cta_scratch;
     J.cta_scratch_words = d->cta_scratch_words;
     J.med_cap = d->med_cap;

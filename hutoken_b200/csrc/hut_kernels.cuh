@@ -42,9 +42,10 @@ constexpr int WPB = 8;                // warps per CTA (they never synchronise w
 constexpr int NT = WPB * 32;
 constexpr int MAXW = 32;              // longest pretoken (bytes) / most symbols handled inside tile_kernel
 constexpr int CACHE_KEY_MAX = 15;     // longest pretoken (bytes) the cache keys on
+constexpr int CACHE2_KEY_MAX = 31;    // ... the second cache (64-byte slots) keys on
 constexpr int CACHE_PROBES = 8;
 constexpr int CACHE_IDS = 5;          // most ids a cache value holds
-constexpr int MISS_SMALL = 16;        // ... of the small instance of miss_kernel (most pretokens)
+constexpr int MISS_SMALL = 32;        // most initial symbols of a miss tile_kernel merges itself (one lane each)
 constexpr int MISS_SYMS = 40;         // most initial symbols (incl. prefix symbols) miss_kernel merges in one lane
 constexpr int MAX_SEG = 64;           // segments of one launch (tile_kernel / miss_kernel pairs)
 constexpr int MNT = 128;              // threads per CTA of miss_kernel
@@ -77,6 +78,12 @@ struct __align__(16) CacheSlot {  // 32 bytes = one L2 sector
     unsigned long long k0, k1;    // text bytes 0..14, meta (0x80 | first << 4 | len) in byte 15
     uint32_t w[4];                // ids 0..3 as signed 21-bit fields in bits 0..20 of w[0..3]; count in w[0] bits
                                   // 21..23; id 4 spread over w[0] bits 24..31, w[1] bits 21..31, w[2] bits 21..22
+};
+
+struct __align__(16) CacheSlot2 {  // 64 bytes: the same for pretokens of 16..31 bytes
+    uint32_t k[8];                 // text bytes 0..30, meta (0x80 | first << 5 | len) in byte 31
+    uint32_t w[4];                 // as CacheSlot::w
+    uint32_t pad[4];
 };
 
 struct CutEvent {  // a document cut at an over-long pretoken (core.c:402-407, 503)
@@ -166,6 +173,8 @@ struct Job {
     Counters* ctr;
     CacheSlot* cache;
     uint32_t cache_bits;
+    CacheSlot2* cache2;
+    uint32_t cache2_bits;
     // long_kernel working areas (global memory, L2 resident)
     uint32_t* cta_scratch;
     unsigned long long cta_scratch_words;  // per CTA
@@ -362,6 +371,86 @@ __device__ __forceinline__ bool cache_lookup(const Job& J, const uint32_t x[4], 
     return false;
 }
 
+// ---- second cache: keys of 16..31 text bytes ----
+__device__ __forceinline__ void build_key32(const uint8_t* text, const uint4* kmask32, int s, int len, uint32_t first,
+                                            uint32_t x[8]) {
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(text + (s & ~3));
+    const uint32_t sh = (uint32_t)(s & 3) * 8u;
+    uint32_t r[9];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) r[i] = w[i];
+    const uint4 m0 = kmask32[2 * len], m1 = kmask32[2 * len + 1];
+    const uint32_t m[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+#pragma unroll
+    for (int i = 0; i < 8; ++i) x[i] = __funnelshift_r(r[i], r[i + 1], sh) & m[i];
+    x[7] |= (0x80u | (first << 5) | (uint32_t)len) << 24;
+}
+
+__device__ __forceinline__ uint32_t cache2_hash(const uint32_t x[8], uint32_t bits) {
+    uint32_t h = x[0] * 0x9E3779B1u;
+    h += x[1] * 0x85EBCA77u;
+    h += x[2] * 0xC2B2AE3Du;
+    h += x[3] * 0x27D4EB2Fu;
+    h = (h ^ (h >> 15)) * 0x2C1B3C6Du;
+    h += x[4] * 0x9E3779B1u;
+    h += x[5] * 0x85EBCA77u;
+    h += x[6] * 0xC2B2AE3Du;
+    h += x[7] * 0x27D4EB2Fu;
+    h ^= h >> 15;
+    h *= 0x2C1B3C6Du;
+    return h >> (32 - bits);
+}
+
+__device__ __forceinline__ bool cache2_lookup(const Job& J, const uint32_t x[8], uint32_t w[4]) {
+    const uint32_t mask = (1u << J.cache2_bits) - 1;
+    uint32_t i = cache2_hash(x, J.cache2_bits);
+#pragma unroll 1
+    for (int p = 0; p < CACHE_PROBES; ++p) {
+        const uint4* s = reinterpret_cast<const uint4*>(J.cache2 + i);
+        const uint4 a = s[0], b = s[1];
+        if ((a.x | a.y) == 0) return false;
+        if (a.x == x[0] && a.y == x[1] && a.z == x[2] && a.w == x[3] && b.x == x[4] && b.y == x[5] && b.z == x[6] &&
+            b.w == x[7]) {
+            const uint4 v = s[2];
+            w[0] = v.x;
+            w[1] = v.y;
+            w[2] = v.z;
+            w[3] = v.w;
+            return val_count(v.x) != 0;
+        }
+        i = (i + 1) & mask;
+    }
+    return false;
+}
+
+__device__ __forceinline__ void cache2_insert(const Job& J, const uint32_t x[8], const uint32_t w[4]) {
+    const unsigned long long k0 = x[0] | ((unsigned long long)x[1] << 32);
+    const uint32_t mask = (1u << J.cache2_bits) - 1;
+    uint32_t i = cache2_hash(x, J.cache2_bits);
+#pragma unroll 1
+    for (int p = 0; p < CACHE_PROBES; ++p) {
+        CacheSlot2* s = J.cache2 + i;
+        unsigned long long old = atomicCAS(reinterpret_cast<unsigned long long*>(s->k), 0ull, k0);
+        if (old == 0) {
+#pragma unroll
+            for (int z = 2; z < 8; ++z) s->k[z] = x[z];
+            s->w[1] = w[1];
+            s->w[2] = w[2];
+            s->w[3] = w[3];
+            __threadfence();
+            atomicExch(&s->w[0], w[0]);
+            return;
+        }
+        if (old == k0) {  // the same key (inserted or being inserted by someone else)?  Otherwise keep probing.
+            bool same = true;
+#pragma unroll
+            for (int z = 2; z < 8; ++z) same = same && *reinterpret_cast<volatile uint32_t*>(&s->k[z]) == x[z];
+            if (same) return;
+        }
+        i = (i + 1) & mask;
+    }
+}
+
 // Called by one thread.  Slots are claimed by CAS on k0 (never zero: the first text byte is not NUL); the value
 // word carrying the count is published last, so a half-written slot reads as a miss.
 __device__ __forceinline__ void cache_insert(const Job& J, const uint32_t x[4], const uint32_t w[4]) {
@@ -493,7 +582,7 @@ __device__ __forceinline__ uint32_t merge_entry(const DevModel& M, const Job& J,
     // ---- initial symbols (A.3) + the cache key ----
     uint32_t m = 0;
     for (uint32_t k = 0; k < npfx; ++k) U[m++] = M.prefix_syms[k];
-    unsigned long long k0 = 0, k1 = 0;
+    unsigned long long k0 = 0, k1 = 0, k2 = 0, k3 = 0;
     for (uint32_t p = 0; p < len; ++p) {
         uint32_t unit = M.inert, pb = 0;
         const uint32_t cnt = char_symbols(M, byte1, at, pos + p, pos, pos + len, &unit, &pb);
@@ -502,7 +591,9 @@ __device__ __forceinline__ uint32_t merge_entry(const DevModel& M, const Job& J,
             for (uint32_t k = 0; k < cnt; ++k) U[m++] = __ldg(M.sym_pool + pb + k);
         const unsigned long long b = at(pos + p);
         if (p < 8) k0 |= b << (8 * p);
-        else if (p < 15) k1 |= b << (8 * (p - 8));
+        else if (p < 16) k1 |= b << (8 * (p - 8));
+        else if (S > 16 && p < 24) k2 |= b << (8 * (p - 16));
+        else if (S > 16 && p < 31) k3 |= b << (8 * (p - 24));
     }
     // ---- merge loop (A.4).  The first slot of every initial pair is prefetched so that the probes overlap.
     // Symbols never move: a merged-away symbol is cleared in `alive` and neighbours are found with bit scans, so the
@@ -561,14 +652,28 @@ __device__ __forceinline__ uint32_t merge_entry(const DevModel& M, const Job& J,
         }
         for (; k < room; ++k) dst[k] = HOLE;
     }
-    if (M.cache_ok && len <= (uint32_t)CACHE_KEY_MAX && total >= 1 && total <= (uint32_t)CACHE_IDS) {
-        uint32_t key[4], pw[4];
-        key[0] = (uint32_t)k0;
-        key[1] = (uint32_t)(k0 >> 32);
-        key[2] = (uint32_t)k1;
-        key[3] = (uint32_t)(k1 >> 32) | ((0x80u | (first << 4) | len) << 24);
+    if (M.cache_ok && total >= 1 && total <= (uint32_t)CACHE_IDS) {
+        uint32_t pw[4];
         val_pack(t5, total, pw);
-        cache_insert(J, key, pw);
+        if (len <= (uint32_t)CACHE_KEY_MAX) {
+            uint32_t key[4];
+            key[0] = (uint32_t)k0;
+            key[1] = (uint32_t)(k0 >> 32);
+            key[2] = (uint32_t)k1;
+            key[3] = ((uint32_t)(k1 >> 32) & 0x00FFFFFFu) | ((0x80u | (first << 4) | len) << 24);
+            cache_insert(J, key, pw);
+        } else if (S > 16 && len <= (uint32_t)CACHE2_KEY_MAX) {
+            uint32_t key[8];
+            key[0] = (uint32_t)k0;
+            key[1] = (uint32_t)(k0 >> 32);
+            key[2] = (uint32_t)k1;
+            key[3] = (uint32_t)(k1 >> 32);
+            key[4] = (uint32_t)k2;
+            key[5] = (uint32_t)(k2 >> 32);
+            key[6] = (uint32_t)k3;
+            key[7] = (uint32_t)(k3 >> 32) | ((0x80u | (first << 5) | len) << 24);
+            cache2_insert(J, key, pw);
+        }
     }
     return room - total;
 }

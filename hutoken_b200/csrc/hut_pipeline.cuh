@@ -17,6 +17,7 @@ struct __align__(16) WarpSm {
 
 struct TileSm {
     uint4 kmask[16];            // kmask[len]: byte masks of a 16-byte key holding len text bytes
+    uint4 kmask32[64];          // kmask32[2 * len], [2 * len + 1]: the same for the 32-byte keys of the second cache
     uint32_t byte1[256];
     WarpSm w[WPB];
 };
@@ -149,6 +150,11 @@ __global__ void __launch_bounds__(NT, 4) tile_kernel(const __grid_constant__ Dev
         auto wm = [&](int rem) -> uint32_t { return rem >= 4 ? 0xFFFFFFFFu : (rem <= 0 ? 0u : ((1u << (8 * rem)) - 1u)); };
         sm.kmask[tid] = make_uint4(wm(tid), wm(tid - 4), wm(tid - 8), wm(tid - 12));
     }
+    if (tid < 64) {
+        const int len = tid >> 1, o = (tid & 1) * 16;
+        auto wm = [&](int rem) -> uint32_t { return rem >= 4 ? 0xFFFFFFFFu : (rem <= 0 ? 0u : ((1u << (8 * rem)) - 1u)); };
+        sm.kmask32[tid] = make_uint4(wm(len - o), wm(len - o - 4), wm(len - o - 8), wm(len - o - 12));
+    }
     if (lane == 0) {
         mbar_init(&ws.mbar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -279,11 +285,21 @@ __global__ void __launch_bounds__(NT, 4) tile_kernel(const __grid_constant__ Dev
             // state: 0 nothing, 1 ids ready, 2 cache miss merged by this warp (batches of 32), 3 long pretoken ->
             // long_kernel, 4 miss too long for the cache / the small per-lane arrays -> miss_kernel
             uint32_t state = 0;
+            // pretokens of 16..31 bytes (rare): second cache, 32-byte keys
+            const bool keyed2 = !dummy && !keyed && len <= CACHE2_KEY_MAX && M.cache_ok;
+            bool hit2 = false;
+            if (__any_sync(FULL, keyed2)) {
+                if (keyed2) {
+                    uint32_t k32[8];
+                    build_key32(ws.text, sm.kmask32, s, len, first, k32);
+                    hit2 = cache2_lookup(J, k32, w);
+                }
+            }
             if (!dummy) {
-                if (keyed && M.cache_ok && cache_lookup(J, key, w)) state = 1;
+                if (hit2 || (keyed && M.cache_ok && cache_lookup(J, key, w))) state = 1;
                 else if ((uint32_t)len > M.miss_len_max) state = 3;
-                else state = (keyed && (uint32_t)len * M.kmax + (first ? M.n_prefix_syms : 0u) <= (uint32_t)MISS_SMALL)
-                                 ? 2u : 4u;
+                else state = (len <= CACHE2_KEY_MAX &&
+                              (uint32_t)len * M.kmax + (first ? M.n_prefix_syms : 0u) <= (uint32_t)MISS_SMALL) ? 2u : 4u;
             }
             // ---- counts -> offsets inside the tile's slot.  A miss reserves room for its worst case. ----
             uint32_t c = 0;
