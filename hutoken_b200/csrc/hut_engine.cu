@@ -185,7 +185,7 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     dm.compat_cut = ctx->opt.max_pretoken == 0;
     dm.limit = ctx->opt.max_pretoken ? ctx->opt.max_pretoken : 262144ull;  // core.c:27-28
 
-    d->cache_bits = ctx->opt.cache_log2_slots ? ctx->opt.cache_log2_slots : 21;
+    d->cache_bits = ctx->opt.cache_log2_slots ? ctx->opt.cache_log2_slots : 22;
     if (d->cache_bits < 10) d->cache_bits = 10;
     if (d->cache_bits > 26) d->cache_bits = 26;
     CU(ctx, cudaMalloc(&d->cache, sizeof(CacheSlot) << d->cache_bits));

@@ -213,6 +213,15 @@ __device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t
                  "l"(src), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
+// one 32-byte cache slot = one L2 sector, fetched by a single 256-bit load (LDG.E.256, sm_100+) that bypasses L1
+// (a slot is not re-read soon by the same SM) and is kept in L2 against the streamed text and ids.  Measured on
+// the 1 GiB bench: -2 % kernel time against two 128-bit default loads; evict_first hints on the text TMA and the
+// staging stores made no difference and are not used.
+__device__ __forceinline__ void ld_slot256(const void* p, uint4& a, uint4& b) {
+    asm volatile("ld.global.L1::no_allocate.L2::evict_last.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
+                 : "l"(p));
+}
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 __device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) {
@@ -356,8 +365,8 @@ __device__ __forceinline__ bool cache_lookup(const Job& J, const uint32_t x[4], 
     uint32_t i = cache_hash(x, J.cache_bits);
 #pragma unroll 1
     for (int p = 0; p < CACHE_PROBES; ++p) {
-        const uint4* s = reinterpret_cast<const uint4*>(J.cache + i);
-        const uint4 a = s[0], b = s[1];
+        uint4 a, b;
+        ld_slot256(J.cache + i, a, b);
         if ((a.x | a.y) == 0) return false;
         if (a.x == x[0] && a.y == x[1] && a.z == x[2] && a.w == x[3]) {
             w[0] = b.x;

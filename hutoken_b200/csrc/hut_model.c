@@ -509,6 +509,125 @@ static uint32_t merge_small(const hut_model* m, uint32_t* u, uint32_t n) {
     }
 }
 
+/* ------------------------------------------------------------------------------------------------
+ * merges file (lib.c:573-663): lines "left right"; '#' lines skipped; a rule is accepted when left, right and
+ * left+right are all vocab keys; rank = index among the accepted rules; a later rule with the same
+ * (left_id, right_id) replaces the earlier one (hashmap_set, hashmap.c:207-214) but keeps its own rank.
+ * *active = 0 when the file has no candidate line at all: the reference then leaves merges_map NULL and
+ * encodes through the string path (lib.c:593,653-655).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+    int32_t l, r, m;
+    uint32_t rank;
+} merge_rule;
+
+#define HUT_MERGES_LINE 10000 /* MAX_LINE_LENGTH, lib.c:71: longer lines are seen in pieces, as by the reference */
+
+static int load_merges(const char* path, const strtab* vocab, merge_rule** out, size_t* n_out, int* active,
+                       char* msg, size_t msglen) {
+    *out = NULL;
+    *n_out = 0;
+    *active = 0;
+    FILE* f = fopen(path, "r");
+    if (!f) return fail(msg, msglen, HUT_ERR_FILE_NOT_FOUND, "Could not open merges file.");
+    char* line = malloc(HUT_MERGES_LINE);
+    char* cat = malloc(2 * HUT_MERGES_LINE);
+    if (!line || !cat) {
+        free(line);
+        free(cat);
+        fclose(f);
+        return fail(msg, msglen, HUT_ERR_MEMORY, "out of memory");
+    }
+    size_t line_count = 0;
+    while (fgets(line, HUT_MERGES_LINE, f))
+        if (line[0] != '#' && strchr(line, ' ') != NULL) line_count++;
+    int rc = HUT_OK;
+    if (line_count > 0) {
+        *active = 1;
+        merge_rule* rules = malloc(line_count * sizeof *rules);
+        size_t cap = 64;
+        while (cap < line_count * 2 + 8) cap <<= 1;
+        uint32_t* slot = malloc(cap * sizeof *slot); /* (l, r) -> index into rules, for "last wins" */
+        if (!rules || !slot) {
+            free(rules);
+            free(slot);
+            rc = fail(msg, msglen, HUT_ERR_MEMORY, "out of memory");
+            goto done;
+        }
+        memset(slot, 0xFF, cap * sizeof *slot);
+        size_t n = 0;
+        uint32_t rank = 0;
+        fseek(f, 0L, SEEK_SET);
+        while (fgets(line, HUT_MERGES_LINE, f) && rank < line_count) {
+            if (line[0] == '#') continue;
+            line[strcspn(line, "\r\n")] = 0;
+            char* save = NULL;
+            char* ls = strtok_r(line, " ", &save);
+            char* rs = strtok_r(NULL, " ", &save);
+            if (!ls || !rs) continue;
+            size_t ll = strlen(ls), rl = strlen(rs);
+            memcpy(cat, ls, ll);
+            memcpy(cat + ll, rs, rl);
+            long li = strtab_find(vocab, (const uint8_t*)ls, ll);
+            long ri = strtab_find(vocab, (const uint8_t*)rs, rl);
+            long mi = strtab_find(vocab, (const uint8_t*)cat, ll + rl);
+            if (li < 0 || ri < 0 || mi < 0) continue;
+            merge_rule R = {vocab->val[li], vocab->val[ri], vocab->val[mi], rank++};
+            uint64_t key = ((uint64_t)(uint32_t)R.l << 32) | (uint32_t)R.r;
+            size_t i = (size_t)hut_mix64(key) & (cap - 1);
+            while (slot[i] != 0xFFFFFFFFu && !(rules[slot[i]].l == R.l && rules[slot[i]].r == R.r)) i = (i + 1) & (cap - 1);
+            if (slot[i] == 0xFFFFFFFFu) {
+                slot[i] = (uint32_t)n;
+                rules[n++] = R;
+            } else {
+                rules[slot[i]] = R;
+            }
+        }
+        free(slot);
+        *out = rules;
+        *n_out = n;
+    }
+done:
+    free(line);
+    free(cat);
+    fclose(f);
+    return rc;
+}
+
+static int cmp_rule_rank(const void* a, const void* b) {
+    const merge_rule *x = a, *y = b;
+    return (x->rank > y->rank) - (x->rank < y->rank);
+}
+
+/* open-addressing table from the builder's packed (L,R,M) entries */
+static int build_pair_tab(hut_model* m, const builder* b) {
+    free(m->pair_tab);
+    m->pair_count = 0;
+    m->pair_cap = 1024;
+    while (m->pair_cap < b->n_pairs * 4 + 16) m->pair_cap <<= 1; /* load <= 0.25: ~1.2 probes per lookup */
+    m->pair_tab = malloc((size_t)m->pair_cap * sizeof(uint64_t));
+    if (!m->pair_tab) return 0;
+    memset(m->pair_tab, 0xFF, (size_t)m->pair_cap * sizeof(uint64_t));
+    for (size_t k = 0; k < b->n_pairs; ++k) {
+        uint64_t e = b->pairs[k], key = e >> 21;
+        uint32_t mask = m->pair_cap - 1;
+        uint32_t i = hut_pair_hash((uint32_t)(key >> 21), (uint32_t)key & HUT_UNIT_MASK, mask);
+        int dup = 0;
+        while (m->pair_tab[i] != HUT_PAIR_EMPTY) {
+            if ((m->pair_tab[i] >> 21) == key) { /* same (L,R) => same concatenation => same M */
+                dup = 1;
+                break;
+            }
+            i = (i + 1) & mask;
+        }
+        if (!dup) {
+            m->pair_tab[i] = e;
+            m->pair_count++;
+        }
+    }
+    return 1;
+}
+
 void hut_model_free(hut_model* m) {
     if (!m) return;
     if (m->unit_str)
@@ -724,30 +843,9 @@ int hut_model_load(hut_model** out, const char* vocab_path, const char* special_
         if (u < m->n_units && m->unit_len[u] > m->max_unit_len) m->max_unit_len = m->unit_len[u];
     }
 
-    m->pair_cap = 1024;
-    while (m->pair_cap < b.n_pairs * 4 + 16) m->pair_cap <<= 1; /* load <= 0.25: ~1.2 probes per lookup */
-    m->pair_tab = malloc((size_t)m->pair_cap * sizeof(uint64_t));
-    if (!m->pair_tab) {
+    if (!build_pair_tab(m, &b)) {
         rc = fail(msg, msglen, HUT_ERR_MEMORY, "out of memory");
         goto out;
-    }
-    memset(m->pair_tab, 0xFF, (size_t)m->pair_cap * sizeof(uint64_t));
-    for (size_t k = 0; k < b.n_pairs; ++k) {
-        uint64_t e = b.pairs[k], key = e >> 21;
-        uint32_t mask = m->pair_cap - 1;
-        uint32_t i = hut_pair_hash((uint32_t)(key >> 21), (uint32_t)key & HUT_UNIT_MASK, mask);
-        int dup = 0;
-        while (m->pair_tab[i] != HUT_PAIR_EMPTY) {
-            if ((m->pair_tab[i] >> 21) == key) { /* same (L,R) => same concatenation => same M */
-                dup = 1;
-                break;
-            }
-            i = (i + 1) & mask;
-        }
-        if (!dup) {
-            m->pair_tab[i] = e;
-            m->pair_count++;
-        }
     }
 
     /* ---- per-byte symbol pools, raw-char tables ---- */

@@ -45,7 +45,7 @@ typedef struct hut_model_desc {
 
 typedef struct hut_options {
     uint32_t struct_size;      /* sizeof(hut_options), for forward compatibility */
-    uint32_t cache_log2_slots; /* unique-pretoken cache size; 0 = default (2^20 slots of 32 B per device) */
+    uint32_t cache_log2_slots; /* unique-pretoken cache size; 0 = default (2^22 slots of 32 B per device) */
     uint64_t max_pretoken;     /* 0 = reference-compatible: a document is cut at its first pretoken longer than
                                   262144 bytes (core.c:27-28,402-407,503).  Otherwise: no cut; pretokens up to this
                                   many bytes are merged (block-cooperative path), longer ones are an error. */
