@@ -91,10 +91,11 @@ class Engine:
     """One model on one or more GPUs of this box."""
 
     def __init__(self, vocab_path, special_path, prefix=None, is_byte_encoder=False, devices=None,
-                 max_pretoken=0, cache_log2_slots=0, big_slots=0, chunk_mb=0):
+                 max_pretoken=0, cache_log2_slots=0, big_slots=0, chunk_mb=0, merges_path=None):
         lib = load_library()
         desc = _Desc(os.fsencode(vocab_path), os.fsencode(special_path),
-                     None if prefix is None else prefix.encode("utf-8"), int(bool(is_byte_encoder)), -1, None, None)
+                     None if prefix is None else prefix.encode("utf-8"), int(bool(is_byte_encoder)), -1, None,
+                     None if merges_path is None else os.fsencode(merges_path))
         opt = _Options(C.sizeof(_Options), cache_log2_slots, max_pretoken, big_slots, chunk_mb)
         err = C.create_string_buffer(512)
         h = C.c_void_p()

@@ -271,7 +271,6 @@ extern "C" int hut_create(const hut_model_desc* desc, const hut_options* opt, co
     if (!desc || !out || !desc->vocab_file_path || !desc->special_file_path)
         return fail(HUT_STATUS_ARG, "vocab_file_path and special_file_path are required");
     if (desc->pattern) return fail(HUT_STATUS_UNSUPPORTED, "regex pattern pretokenisation is not supported by the B200 engine");
-    if (desc->merges_file_path) return fail(HUT_STATUS_UNSUPPORTED, "merges-file (id-keyed) encoding is not supported by the B200 engine");
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
         return fail(HUT_STATUS_CUDA, "no CUDA device: the hutoken_b200 engine has no CPU fallback");
@@ -280,7 +279,7 @@ extern "C" int hut_create(const hut_model_desc* desc, const hut_options* opt, co
     if (opt) memcpy(&ctx->opt, opt, opt->struct_size < sizeof ctx->opt ? opt->struct_size : sizeof ctx->opt);
     char msg[256] = "";
     int rc = hut_model_load(&ctx->model, desc->vocab_file_path, desc->special_file_path, desc->prefix,
-                            desc->is_byte_encoder, msg, sizeof msg);
+                            desc->is_byte_encoder, desc->merges_file_path, msg, sizeof msg);
     if (rc != HUT_OK) {
         free(ctx);
         return fail(rc, msg);

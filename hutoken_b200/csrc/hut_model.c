@@ -628,6 +628,195 @@ static int build_pair_tab(hut_model* m, const builder* b) {
     return 1;
 }
 
+/* ------------------------------------------------------------------------------------------------
+ * id-keyed merge path (core.c:211-337, 453-474; rules from load_merges).  The kernels stay as they are: they
+ * merge the adjacent pair with the smallest unit index M found in the pair table and print out_id[unit].  Here
+ *   - symbols are ids, not strings: one "base" unit per id that a single UTF-8 character of the vocab maps to
+ *     (core.c:460-474; an unknown character is the inert unit: -1 never matches a rule), then
+ *   - one unit per rule, in rank order (unit index order == rank order, so distinct_values = 1), printing the
+ *     rule's merge_id;
+ *   - every unit that prints id x stands for x in later lookups, so rule (a, b) gets one pair-table entry per
+ *     (unit printing a, unit printing b).  With one rule per merged id (every real merges file) that is one
+ *     entry per rule.
+ * The string-mode tables built before are replaced, except the constant "prefix alone" ids, which the
+ * reference always computes through the string path (core.c:421-446).
+ * ---------------------------------------------------------------------------------------------- */
+static int apply_merges(hut_model* m, builder* b, const strtab* vocab, const enc_table* et, uint8_t* const special[256],
+                        const char* prefix, size_t plen, merge_rule* rules, size_t n_rules, char* msg, size_t msglen) {
+    int rc = HUT_OK;
+    const size_t V = (size_t)m->max_value + 1;
+    int32_t* base_of = malloc(V * sizeof *base_of);
+    uint32_t *pstart = NULL, *plist = NULL;
+    if (!base_of) return fail(msg, msglen, HUT_ERR_MEMORY, "out of memory");
+    memset(base_of, 0xFF, V * sizeof *base_of);
+    for (size_t i = 0; i < vocab->n; ++i)
+        if (vocab->len[i] == (uint32_t)lead_len(vocab->str[i][0])) base_of[vocab->val[i]] = 0;
+    uint32_t n_base = 0;
+    for (size_t id = 0; id < V; ++id)
+        if (base_of[id] == 0) base_of[id] = (int32_t)n_base++;
+    qsort(rules, n_rules, sizeof *rules, cmp_rule_rank);
+    const size_t n_units = (size_t)n_base + n_rules;
+    if (n_units > HUT_MAX_UNITS) {
+        rc = fail(msg, msglen, HUT_ERR_UNSUPPORTED, "vocabulary too large for 21-bit unit ids");
+        goto done;
+    }
+    /* units no longer have strings */
+    for (size_t i = 0; i < b->units.n; ++i) free(b->units.str[i]);
+    free(b->units.str);
+    free(b->units.len);
+    b->units.str = calloc(n_units ? n_units : 1, sizeof *b->units.str);
+    b->units.len = calloc(n_units ? n_units : 1, sizeof *b->units.len);
+    b->units.n = n_units;
+    m->unit_str = b->units.str;
+    m->unit_len = b->units.len;
+    free(m->out_id);
+    free(m->rank_of);
+    m->out_id = malloc((n_units + 1) * sizeof(int32_t));
+    m->rank_of = malloc((n_units + 1) * sizeof(int32_t));
+    if (!b->units.str || !b->units.len || !m->out_id || !m->rank_of) {
+        rc = fail(msg, msglen, HUT_ERR_MEMORY, "out of memory");
+        goto done;
+    }
+    for (size_t id = 0; id < V; ++id)
+        if (base_of[id] >= 0) m->out_id[base_of[id]] = (int32_t)id;
+    for (size_t k = 0; k < n_rules; ++k) m->out_id[n_base + k] = rules[k].m;
+    m->out_id[n_units] = -1;
+    for (size_t u = 0; u < n_units; ++u) m->rank_of[u] = (int32_t)u;
+    m->rank_of[n_units] = INT_MAX;
+    m->n_vocab = m->n_units = m->inert = (uint32_t)n_units;
+    m->distinct_values = 1;
+    m->identity_ids = 0;
+    m->max_unit_len = 0;
+    m->merges_mode = 1;
+    m->n_merge_rules = (uint32_t)n_rules;
+
+    /* units printing each id (CSR) */
+    pstart = calloc(V + 1, sizeof *pstart);
+    plist = malloc((n_units ? n_units : 1) * sizeof *plist);
+    if (!pstart || !plist) {
+        rc = fail(msg, msglen, HUT_ERR_MEMORY, "out of memory");
+        goto done;
+    }
+    for (size_t u = 0; u < n_units; ++u) pstart[m->out_id[u] + 1]++;
+    for (size_t id = 0; id < V; ++id) pstart[id + 1] += pstart[id];
+    {
+        uint32_t* fill = calloc(V, sizeof *fill);
+        if (!fill) {
+            rc = fail(msg, msglen, HUT_ERR_MEMORY, "out of memory");
+            goto done;
+        }
+        for (size_t u = 0; u < n_units; ++u) {
+            const int32_t id = m->out_id[u];
+            plist[pstart[id] + fill[id]++] = (uint32_t)u;
+        }
+        free(fill);
+    }
+    b->n_pairs = 0;
+    for (size_t k = 0; k < n_rules; ++k) {
+        const int32_t a = rules[k].l, c = rules[k].r;
+        for (uint32_t i = pstart[a]; i < pstart[a + 1]; ++i)
+            for (uint32_t j = pstart[c]; j < pstart[c + 1]; ++j) {
+                if (b->n_pairs >= ((size_t)1 << 24)) {
+                    rc = fail(msg, msglen, HUT_ERR_UNSUPPORTED, "merges file expands to more than 2^24 unit pairs");
+                    goto done;
+                }
+                if (!add_pair(b, plist[i], plist[j], (uint32_t)(n_base + k))) {
+                    rc = fail(msg, msglen, HUT_ERR_MEMORY, "out of memory");
+                    goto done;
+                }
+            }
+    }
+    if (!build_pair_tab(m, b)) {
+        rc = fail(msg, msglen, HUT_ERR_MEMORY, "out of memory");
+        goto done;
+    }
+
+#define CHAR_UNIT(P, N, OUT)                                                        \
+    do {                                                                            \
+        long j_ = strtab_find(vocab, (P), (N));                                     \
+        int32_t bu_ = j_ >= 0 ? base_of[vocab->val[j_]] : -1;                       \
+        (OUT) = bu_ >= 0 ? (uint32_t)bu_ : m->inert;                                \
+    } while (0)
+
+    /* ---- initial symbols: one per UTF-8 character of the encoded form (core.c:460-474) ---- */
+    uint32_t st[64], ln[64];
+    {
+        size_t pool_cap = 256 * 4, pool_n = 0;
+        free(m->sym_pool);
+        m->sym_pool = malloc(pool_cap * sizeof(uint32_t));
+        m->max_sym_per_char = 1;
+        for (int c = 0; c < 256; ++c) {
+            m->sym_off[c] = (uint32_t)pool_n;
+            if (c == 0 || !et->present[c]) continue;
+            if (!m->is_byte_encoder && !special[c]) continue;
+            long cnt = segment(et->enc[c], et->len[c], 0, st, ln, 64);
+            if (cnt <= 0 || cnt > 64) {
+                rc = fail(msg, msglen, HUT_ERR_UNSUPPORTED,
+                          "special-chars replacement does not split into whole characters on its own");
+                goto done;
+            }
+            if ((uint32_t)cnt > m->max_sym_per_char) m->max_sym_per_char = (uint32_t)cnt;
+            if (pool_n + (size_t)cnt > pool_cap) {
+                pool_cap = (pool_n + (size_t)cnt) * 2;
+                m->sym_pool = realloc(m->sym_pool, pool_cap * sizeof(uint32_t));
+            }
+            for (long k = 0; k < cnt; ++k) CHAR_UNIT(et->enc[c] + st[k], ln[k], m->sym_pool[pool_n++]);
+        }
+        m->sym_off[256] = (uint32_t)pool_n;
+    }
+    m->ascii_unit[0] = m->inert;
+    for (int c = 1; c < 128; ++c) {
+        uint8_t ch = (uint8_t)c;
+        CHAR_UNIT(&ch, 1, m->ascii_unit[c]);
+    }
+    free(m->char_tab);
+    m->char_tab = NULL;
+    m->char_cap = 0;
+    if (!m->is_byte_encoder) {
+        uint32_t n_chars = 0;
+        for (size_t i = 0; i < vocab->n; ++i) {
+            uint32_t l = vocab->len[i];
+            if (l >= 2 && l <= 4 && (uint32_t)lead_len(vocab->str[i][0]) == l) n_chars++;
+        }
+        m->char_cap = 64;
+        while (m->char_cap < n_chars * 2 + 8) m->char_cap <<= 1;
+        m->char_tab = malloc((size_t)m->char_cap * sizeof(uint64_t));
+        if (!m->char_tab) {
+            rc = fail(msg, msglen, HUT_ERR_MEMORY, "out of memory");
+            goto done;
+        }
+        memset(m->char_tab, 0xFF, (size_t)m->char_cap * sizeof(uint64_t));
+        for (size_t i = 0; i < vocab->n; ++i) {
+            uint32_t l = vocab->len[i];
+            if (!(l >= 2 && l <= 4 && (uint32_t)lead_len(vocab->str[i][0]) == l)) continue;
+            uint32_t key = 0, u;
+            for (uint32_t q = 0; q < l; ++q) key |= (uint32_t)vocab->str[i][q] << (8 * q);
+            CHAR_UNIT(vocab->str[i], l, u);
+            uint32_t mask = m->char_cap - 1, h = (uint32_t)(hut_mix64(key) >> 32) & mask;
+            while (m->char_tab[h] != HUT_CHAR_EMPTY) h = (h + 1) & mask;
+            m->char_tab[h] = ((uint64_t)key << 32) | u;
+        }
+    }
+    if (m->has_prefix) { /* the raw prefix is prepended to the first pretoken and split with it (core.c:448-474) */
+        uint32_t pst[256], pln[256];
+        long n_pfx = segment((const uint8_t*)prefix, plen, 0, pst, pln, 256);
+        if (n_pfx <= 0 || n_pfx > 256) {
+            rc = fail(msg, msglen, HUT_ERR_UNSUPPORTED, "prefix does not split into whole characters on its own");
+            goto done;
+        }
+        free(m->prefix_syms);
+        m->n_prefix_syms = (uint32_t)n_pfx;
+        m->prefix_syms = malloc((size_t)n_pfx * sizeof(uint32_t));
+        for (long k = 0; k < n_pfx; ++k) CHAR_UNIT((const uint8_t*)prefix + pst[k], pln[k], m->prefix_syms[k]);
+    }
+#undef CHAR_UNIT
+done:
+    free(base_of);
+    free(pstart);
+    free(plist);
+    return rc;
+}
+
 void hut_model_free(hut_model* m) {
     if (!m) return;
     if (m->unit_str)
@@ -645,7 +834,7 @@ void hut_model_free(hut_model* m) {
 }
 
 int hut_model_load(hut_model** out, const char* vocab_path, const char* special_path, const char* prefix,
-                   int is_byte_encoder, char* msg, size_t msglen) {
+                   int is_byte_encoder, const char* merges_path, char* msg, size_t msglen) {
     int rc = HUT_OK;
     hut_model* m = calloc(1, sizeof *m);
     uint8_t* special[256] = {0};
@@ -914,6 +1103,18 @@ int hut_model_load(hut_model** out, const char* vocab_path, const char* special_
         free(tmp);
     }
     free(pfx_alone);
+
+    /* ---- optional merges file: switch the tables to the id-keyed path ---- */
+    if (merges_path) {
+        merge_rule* rules = NULL;
+        size_t n_rules = 0;
+        int active = 0;
+        rc = load_merges(merges_path, &vocab, &rules, &n_rules, &active, msg, msglen);
+        if (rc == HUT_OK && active)
+            rc = apply_merges(m, &b, &vocab, &et, special, prefix, plen, rules, n_rules, msg, msglen);
+        free(rules);
+        if (rc != HUT_OK) goto out;
+    }
 
     /* ownership of the unit arrays moved into the model */
     b.units.str = NULL;

@@ -77,12 +77,16 @@ typedef struct hut_model {
     int32_t* prefix_alone_ids;
 
     uint32_t max_unit_len;
+
+    /* ---- merges-file mode (core.c:211-337): units are ids, see apply_merges() in hut_model.c ---- */
+    int merges_mode;
+    uint32_t n_merge_rules;
 } hut_model;
 
-/* Loads the files and builds every table.  Returns HUT_OK or an error class; msg receives the exact
+/* Loads the files and builds every table (merges_path may be NULL: string-keyed ranks, core.c:66-209).  Returns HUT_OK or an error class; msg receives the exact
  * message string the reference raises for the same failure where one exists. */
 int hut_model_load(hut_model** out, const char* vocab_path, const char* special_path, const char* prefix,
-                   int is_byte_encoder, char* msg, size_t msglen);
+                   int is_byte_encoder, const char* merges_path, char* msg, size_t msglen);
 void hut_model_free(hut_model* m);
 
 /* table hash shared by host builder and device probes */

@@ -40,7 +40,8 @@ typedef struct hut_model_desc {
     int is_byte_encoder;           /* GPT-2 byte-level mode (pretokenizer.c:138-146) */
     int special_token_id;          /* parsed and unused by the reference (lib.c:197); ignored */
     const char* pattern;           /* regex pretokenisation (core.c:352-399): must be NULL -> HUT_STATUS_UNSUPPORTED */
-    const char* merges_file_path;  /* id-keyed merge path (core.c:211-337): must be NULL -> HUT_STATUS_UNSUPPORTED */
+    const char* merges_file_path;  /* NULL, or a merges file (lib.c:573-663): ranks and merged ids then come from
+                                      (left_id, right_id) rules, core.c:211-337 */
 } hut_model_desc;
 
 typedef struct hut_options {

@@ -111,6 +111,12 @@ static int32_t omap_get(const omap* m, const uint8_t* key, size_t len) {
     return s->key ? s->value : -1;
 }
 
+/* struct MergeRule (bpe.h:11-16) in an open-addressing table keyed by (left_id, right_id) */
+struct orule {
+    int32_t left, right, merge, rank;
+    int used;
+};
+
 /* ------------------------------------------------------------------------------------------------ */
 struct hut_oracle {
     omap vocab;
@@ -121,6 +127,10 @@ struct hut_oracle {
     uint32_t prefix_len;
     int is_byte_encoder;
     int limit_mode;
+    /* merges-file mode (lib.c:573-663): (left_id, right_id) -> rule; NULL map = string path */
+    struct orule* rules;
+    size_t rules_cap; /* power of two; 0 = merges_map is NULL */
+    size_t n_rules;
 };
 
 static void set_err(char* err, size_t errlen, const char* type, const char* msg) {
@@ -306,11 +316,85 @@ hut_oracle* hut_oracle_load(const char* vocab_path, const char* special_path, co
     return o;
 }
 
+/* ------------------------------------------------------------------------------------------------
+ * Merges file (lib.c:573-663).  Candidate lines = not starting with '#' and containing a space
+ * (lib.c:587-591); none => merges_map stays NULL (string path).  Accepted rule = left, right and
+ * left+right are vocab keys (lib.c:620-640); rank counts accepted rules (lib.c:643); hashmap_set
+ * replaces an earlier rule with the same (left_id, right_id) (hashmap.c:207-214).
+ * ---------------------------------------------------------------------------------------------- */
+static uint64_t rule_hash(int32_t l, int32_t r) { /* pair_hash, bpe.c:32-41 (any hash would do) */
+    uint64_t x = ((uint64_t)(uint32_t)l << 32) | (uint32_t)r;
+    x = (x ^ (x >> 30)) * 0xbf58476d1ce4e5b9ull;
+    x = (x ^ (x >> 27)) * 0x94d049bb133111ebull;
+    return x ^ (x >> 31);
+}
+
+static const struct orule* rule_find(const hut_oracle* o, int32_t l, int32_t r) {
+    if (!o->rules_cap) return NULL;
+    size_t i = (size_t)rule_hash(l, r) & (o->rules_cap - 1);
+    while (o->rules[i].used) {
+        if (o->rules[i].left == l && o->rules[i].right == r) return &o->rules[i];
+        i = (i + 1) & (o->rules_cap - 1);
+    }
+    return NULL;
+}
+
+int hut_oracle_load_merges(hut_oracle* o, const char* path, char* err, size_t errlen) {
+    FILE* f = fopen(path, "r");
+    if (!f) {
+        set_err(err, errlen, "FileNotFoundError", "Could not open merges file.");
+        return 0;
+    }
+    enum { LINE = 10000 }; /* MAX_LINE_LENGTH, lib.c:71 */
+    char* line = malloc(LINE);
+    size_t line_count = 0;
+    while (fgets(line, LINE, f))
+        if (line[0] != '#' && strchr(line, ' ') != NULL) line_count++;
+    if (line_count > 0) {
+        o->rules_cap = 64;
+        while (o->rules_cap < 2 * line_count + 8) o->rules_cap <<= 1;
+        o->rules = calloc(o->rules_cap, sizeof *o->rules);
+        fseek(f, 0L, SEEK_SET);
+        size_t accepted = 0;
+        int32_t rank = 0;
+        uint8_t* cat = malloc(2 * LINE);
+        while (fgets(line, LINE, f) && accepted < line_count) {
+            if (line[0] == '#') continue;
+            line[strcspn(line, "\r\n")] = 0;
+            char* save = NULL;
+            char* ls = strtok_r(line, " ", &save);
+            char* rs = strtok_r(NULL, " ", &save);
+            if (!ls || !rs) continue;
+            size_t ll = strlen(ls), rl = strlen(rs);
+            memcpy(cat, ls, ll);
+            memcpy(cat + ll, rs, rl);
+            const omap_slot* a = omap_find(&o->vocab, (const uint8_t*)ls, ll);
+            const omap_slot* b = omap_find(&o->vocab, (const uint8_t*)rs, rl);
+            const omap_slot* c = omap_find(&o->vocab, cat, ll + rl);
+            if (!a->key || !b->key || !c->key) continue;
+            size_t i = (size_t)rule_hash(a->value, b->value) & (o->rules_cap - 1);
+            while (o->rules[i].used && !(o->rules[i].left == a->value && o->rules[i].right == b->value))
+                i = (i + 1) & (o->rules_cap - 1);
+            if (!o->rules[i].used) o->n_rules++;
+            o->rules[i] = (struct orule){a->value, b->value, c->value, rank++, 1};
+            accepted++;
+        }
+        free(cat);
+    }
+    free(line);
+    fclose(f);
+    return 1;
+}
+
+size_t hut_oracle_merge_rules(const hut_oracle* o) { return o->n_rules; }
+int hut_oracle_merges_active(const hut_oracle* o) { return o->rules_cap != 0; }
+
 void hut_oracle_free(hut_oracle* o) {
     if (!o) return;
     omap_free(&o->vocab);
     for (int i = 0; i < 256; ++i) free(o->special[i]);
     free(o->prefix);
+    free(o->rules);
     free(o);
 }
 
@@ -627,7 +711,53 @@ static void merge_symbols(const hut_oracle* o, scratch* s, const uint8_t* e, siz
     g_stats.probes += (m - 1) + 2 * (m - live) + live;
 }
 
-/* encode() (core.c:339-511), default parser path (no regex pattern, no merges file). */
+/* bpe_encode_arena_ids (core.c:211-337): same lazy-deletion loop keyed by (left_id, right_id) rules;
+ * get_pair_rank_from_ids (core.c:724-736).  tok[] holds m ids (-1 = character not in the vocab, core.c:467-471). */
+static void merge_ids(const hut_oracle* o, scratch* s, int32_t* tok, size_t m, idvec* out) {
+    if (m == 0) return;
+    for (size_t i = 0; i < m; ++i) {
+        s->prev[i] = (int32_t)i - 1;
+        s->next[i] = (int32_t)i + 1;
+        s->dead[i] = 0;
+    }
+    s->next[m - 1] = -1;
+    s->h.n = 0;
+    for (size_t i = 0; i + 1 < m; ++i) { /* core.c:244-256 */
+        const struct orule* r = rule_find(o, tok[i], tok[i + 1]);
+        if (r) heap_push(&s->h, (cand){r->rank, (uint32_t)i, (uint32_t)i + 1});
+    }
+    size_t live = m;
+    while (s->h.n) { /* core.c:258-325 */
+        cand c = heap_pop(&s->h);
+        int32_t l = (int32_t)c.left, r = (int32_t)c.right;
+        if (s->dead[l] || s->dead[r]) continue;
+        if (s->next[l] != r) continue;
+        const struct orule* rule = rule_find(o, tok[l], tok[r]);
+        if (!rule || rule->rank != c.rank) continue;
+        tok[l] = rule->merge;
+        s->dead[r] = 1;
+        live--;
+        int32_t p = s->prev[l], nx = s->next[r];
+        s->next[l] = nx;
+        if (nx != -1) s->prev[nx] = l;
+        if (p != -1) {
+            const struct orule* q = rule_find(o, tok[p], tok[l]);
+            if (q) heap_push(&s->h, (cand){q->rank, (uint32_t)p, (uint32_t)l});
+        }
+        if (nx != -1) {
+            const struct orule* q = rule_find(o, tok[l], tok[nx]);
+            if (q) heap_push(&s->h, (cand){q->rank, (uint32_t)l, (uint32_t)nx});
+        }
+    }
+    for (size_t i = 0; i < m; ++i) /* core.c:327-336 */
+        if (!s->dead[i]) idvec_push(out, tok[i]);
+    g_stats.pretokens += 1;
+    g_stats.symbols += m;
+    g_stats.tokens += live;
+    g_stats.probes += (m - 1) + 2 * (m - live) + live;
+}
+
+/* encode() (core.c:339-511), default parser path (no regex pattern); string or merges-file ranks. */
 static void encode_doc(const hut_oracle* o, scratch* s, const uint8_t* text, size_t len, idvec* out) {
     const uint8_t* z = memchr(text, 0, len);
     if (z) len = (size_t)(z - text);
@@ -649,8 +779,17 @@ static void encode_doc(const hut_oracle* o, scratch* s, const uint8_t* text, siz
         byte_encode(o, text + pos, wl, (add_prefix && o->prefix) ? o->prefix : NULL, o->prefix_len, &s->enc);
         add_prefix = 0; /* core.c:451 */
         scratch_reserve(s, s->enc.n + 1);
-        size_t m = split_symbols(s->enc.p, s->enc.n, 1, s->sp);
-        merge_symbols(o, s, s->enc.p, m, out);
+        if (o->rules_cap) { /* core.c:456-474: one UTF-8 character per symbol, id or -1 */
+            size_t m = split_symbols(s->enc.p, s->enc.n, 0, s->sp);
+            int32_t* tok = malloc((m ? m : 1) * sizeof *tok);
+            for (size_t i = 0; i < m; ++i)
+                tok[i] = omap_get(&o->vocab, s->enc.p + s->sp[i].start, s->sp[i].end - s->sp[i].start);
+            merge_ids(o, s, tok, m, out);
+            free(tok);
+        } else {
+            size_t m = split_symbols(s->enc.p, s->enc.n, 1, s->sp);
+            merge_symbols(o, s, s->enc.p, m, out);
+        }
         pos += wl;
     }
 }

@@ -27,6 +27,12 @@ hut_oracle* hut_oracle_load(const char* vocab_path, const char* special_path, co
                             int is_byte_encoder, char* err, size_t errlen);
 void hut_oracle_free(hut_oracle* o);
 
+/* Optional merges file (lib.c:573-663): switches encode to the id-keyed path (core.c:211-337) unless the file
+ * holds no candidate line.  Returns 1, or 0 with err set when the file cannot be opened. */
+int hut_oracle_load_merges(hut_oracle* o, const char* path, char* err, size_t errlen);
+size_t hut_oracle_merge_rules(const hut_oracle* o); /* distinct (left_id, right_id) rules */
+int hut_oracle_merges_active(const hut_oracle* o);
+
 /* limit_mode 0: reference-compatible (document cut at the first pretoken > 262144 bytes, core.c:402-407,503)
  * limit_mode 1: no limit (the restatement has no arena / stack bounds). */
 void hut_oracle_set_limit_mode(hut_oracle* o, int limit_mode);

@@ -60,6 +60,10 @@ def _load():
     lib.hut_oracle_vocab_lookup.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t]
     lib.hut_oracle_vocab_lines.restype = C.c_size_t
     lib.hut_oracle_vocab_lines.argtypes = [C.c_void_p]
+    lib.hut_oracle_load_merges.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_size_t]
+    lib.hut_oracle_merge_rules.restype = C.c_size_t
+    lib.hut_oracle_merge_rules.argtypes = [C.c_void_p]
+    lib.hut_oracle_merges_active.argtypes = [C.c_void_p]
     _lib = lib
     return lib
 
@@ -71,7 +75,8 @@ class OracleError(Exception):
 class Oracle:
     """CPU restatement of hutoken.initialize + encode / batch_encode (default parser path)."""
 
-    def __init__(self, vocab_path, special_path, prefix=None, is_byte_encoder=False, no_limit=False):
+    def __init__(self, vocab_path, special_path, prefix=None, is_byte_encoder=False, no_limit=False,
+                 merges_path=None):
         lib = _load()
         err = C.create_string_buffer(512)
         h = lib.hut_oracle_load(os.fsencode(vocab_path), os.fsencode(special_path),
@@ -83,6 +88,9 @@ class Oracle:
         self._lib = lib
         if no_limit:
             lib.hut_oracle_set_limit_mode(self._h, 1)
+        if merges_path is not None:
+            if not lib.hut_oracle_load_merges(self._h, os.fsencode(merges_path), err, len(err)):
+                raise OracleError(err.value.decode("utf-8", "replace"))
 
     def close(self):
         if getattr(self, "_h", None):

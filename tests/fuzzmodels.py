@@ -108,3 +108,33 @@ def random_model(rng: random.Random, tmpdir: str, byte_mode: bool, name: str):
             entries.append((entries[i][0], entries[j][1]))
     synth.write_vocab(vocab, entries)
     return vocab, special, dict(prefix=prefix, is_byte_encoder=byte_mode)
+
+
+def random_merges(rng: random.Random, vocab_path: str, out_path: str) -> str:
+    """A merges file (lib.c:573-663) over an existing vocab: rules in random order (ranks unrelated to ids), unknown
+    tokens, comments, repeated pairs (the later rank wins), rules sharing a merged token."""
+    import make_merges
+    vocab = make_merges.read_vocab(vocab_path)
+    keys = [k for k in vocab if not any(b in k for b in b" \r\n") and not k.startswith(b"#")]
+    keyset = set(keys)
+    rules = []
+    for tok in keys:
+        cuts = make_merges._chars(tok)
+        for c in cuts[:-1]:
+            if tok[:c] in keyset and tok[c:] in keyset and rng.random() < 0.8:
+                rules.append((tok[:c], tok[c:]))
+    rng.shuffle(rules)
+    lines = []
+    for l, r in rules:
+        lines.append(l + b" " + r)
+        k = rng.random()
+        if k < 0.03:
+            lines.append(b"# comment")
+        elif k < 0.06 and keys:
+            lines.append(rng.choice(keys) + b" nosuchtoken")
+        elif k < 0.10:
+            pl, pr = rng.choice(rules)
+            lines.append(pl + b"  " + pr)
+    with open(out_path, "wb") as f:
+        f.write(b"\n".join(lines) + (b"\n" if lines else b""))
+    return out_path

@@ -24,7 +24,7 @@ def lib():
             subprocess.run(["gcc", "-O2", "-g", "-std=c11", "-fPIC", "-shared", "-o", _SO] + _SRCS, check=True)
         L = C.CDLL(_SO)
         L.harness_load.restype = C.c_void_p
-        L.harness_load.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_size_t,
+        L.harness_load.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_char_p, C.c_size_t,
                                    C.POINTER(C.c_int)]
         L.harness_free.argtypes = [C.c_void_p]
         L.harness_encode.restype = C.c_size_t
@@ -41,12 +41,13 @@ def lib():
 
 
 class HostModel:
-    def __init__(self, vocab, special, prefix=None, is_byte_encoder=False):
+    def __init__(self, vocab, special, prefix=None, is_byte_encoder=False, merges=None):
         L = lib()
         msg = C.create_string_buffer(512)
         st = C.c_int()
         h = L.harness_load(os.fsencode(vocab), os.fsencode(special), None if prefix is None else prefix.encode(),
-                           int(bool(is_byte_encoder)), msg, len(msg), C.byref(st))
+                           int(bool(is_byte_encoder)), None if merges is None else os.fsencode(merges), msg,
+                           len(msg), C.byref(st))
         self.status, self.message = st.value, msg.value.decode("utf-8", "replace")
         self._h = C.c_void_p(h) if h else None
 
@@ -55,7 +56,7 @@ class HostModel:
 
     def encode(self, text):
         data = text.encode("utf-8") if isinstance(text, str) else bytes(text)
-        cap = 2 * len(data) + 64
+        cap = 8 * len(data) + 64
         out = np.empty(cap, dtype=np.int32)
         n = lib().harness_encode(self._h, data, len(data), out.ctypes.data, cap)
         assert n <= cap

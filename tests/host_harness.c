@@ -115,10 +115,10 @@ size_t harness_encode(const hut_model* m, const uint8_t* t, size_t n, int32_t* o
     return w;
 }
 
-hut_model* harness_load(const char* vocab, const char* special, const char* prefix, int byte_mode, char* msg,
-                        size_t msglen, int* status) {
+hut_model* harness_load(const char* vocab, const char* special, const char* prefix, int byte_mode, const char* merges,
+                        char* msg, size_t msglen, int* status) {
     hut_model* m = NULL;
-    *status = hut_model_load(&m, vocab, special, prefix, byte_mode, msg, msglen);
+    *status = hut_model_load(&m, vocab, special, prefix, byte_mode, merges, msg, msglen);
     return m;
 }
 

@@ -1,0 +1,209 @@
+"""Merges-file mode: initialize(..., merges_file_path=) switches the reference to the id-keyed
+merge loop (lib.c:573-663 loader, core.c:211-337 bpe_encode_arena_ids, core.c:456-474 symbol split).
+
+CPU part: the oracle's restatement of that path is pinned to the reference (committed golden fixtures made from the
+unmodified reference .so + the .so itself on random models), and the engine's HOST tables (hut_model.c apply_merges:
+units per id / per rule, pair table keyed by unit pairs) reproduce the oracle when walked by tests/host_harness.c.
+GPU part (-m gpu): the CUDA engine through the C-ABI against the oracle, bit-exact.
+"""
+import json
+import os
+import random
+import tempfile
+
+import numpy as np
+import pytest
+
+import fuzzmodels as F
+import harness
+import synth
+from common import ROOT, assert_same
+from oracle import oracle as O
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+SMALL = ["gpt2_small", "llama_small"]
+
+needs_ref = pytest.mark.skipif(O.ref_path() is None and not os.path.isdir("/root/reference/src"),
+                               reason="reference build (oracle/_ref) not available")
+
+
+def _oracle(name, **kw):
+    v, s = synth.PATHS[name]
+    return O.Oracle(v, s, merges_path=synth.MERGES[name], **synth.MODEL_KW[name], **kw)
+
+
+def _golden(name):
+    with open(os.path.join(GOLDEN, f"encode_merges_{name}.json")) as f:
+        return json.load(f)
+
+
+@pytest.mark.parametrize("name", SMALL)
+def test_oracle_merges_matches_golden(name):
+    g = _golden(name)
+    orc = _oracle(name)
+    texts = [bytes.fromhex(c["text_hex"]) for c in g["cases"]]
+    assert orc.batch_encode(texts) == [c["ids"] for c in g["cases"]]
+    # the fixture really exercises the other path: the string-keyed ranks give different ids on some cases
+    v, s = synth.PATHS[name]
+    plain = O.Oracle(v, s, **synth.MODEL_KW[name])
+    assert plain.batch_encode(texts) != [c["ids"] for c in g["cases"]]
+
+
+@pytest.mark.parametrize("name", SMALL)
+def test_host_tables_merges_match_golden(name):
+    g = _golden(name)
+    v, s = synth.PATHS[name]
+    hm = harness.HostModel(v, s, merges=synth.MERGES[name], **synth.MODEL_KW[name])
+    assert hm.ok(), hm.message
+    info = hm.info()
+    assert info["distinct_values"] == 1 and info["identity_ids"] == 0 and info["pair_count"] > 1000
+    for c in g["cases"]:
+        t = bytes.fromhex(c["text_hex"])
+        assert hm.encode(t) == c["ids"], t[:40]
+
+
+def test_merges_loader_edge_cases():
+    """lib.c:575-583 missing file; lib.c:587-593,653-655 a file without candidate lines leaves the string path on."""
+    name = "gpt2_small"
+    v, s = synth.PATHS[name]
+    kw = synth.MODEL_KW[name]
+    tmp = tempfile.mkdtemp()
+    with pytest.raises(O.OracleError, match="Could not open merges file"):
+        O.Oracle(v, s, merges_path=os.path.join(tmp, "nope.txt"), **kw)
+    hm = harness.HostModel(v, s, merges=os.path.join(tmp, "nope.txt"), **kw)
+    assert not hm.ok() and hm.status == 1 and hm.message == "Could not open merges file."
+    texts = ["hello world", " árvíztűrő tükörfúrógép 123", "a\nb"]
+    plain = O.Oracle(v, s, **kw).batch_encode(texts)
+    for body in ("", "# only a comment\n#another\n", "nospace\n\n"):
+        p = os.path.join(tmp, "m.txt")
+        with open(p, "w") as f:
+            f.write(body)
+        assert O.Oracle(v, s, merges_path=p, **kw).batch_encode(texts) == plain
+        hm = harness.HostModel(v, s, merges=p, **kw)
+        assert hm.ok() and [hm.encode(t) for t in texts] == plain
+    # candidate lines but no acceptable rule: the id path with an empty rule set = one id per character
+    p = os.path.join(tmp, "m2.txt")
+    with open(p, "w") as f:
+        f.write("nosuch token\n")
+    got = O.Oracle(v, s, merges_path=p, **kw).encode("hello")
+    assert len(got) == 5
+    hm = harness.HostModel(v, s, merges=p, **kw)
+    assert hm.ok() and hm.encode("hello") == got
+
+
+def _fuzz_cases(byte_mode, seeds, tmp):
+    for seed in seeds:
+        rng = random.Random(9000 + seed)
+        v, s, kw = F.random_model(rng, tmp, byte_mode, f"mm{seed}")
+        mp = F.random_merges(rng, v, os.path.join(tmp, f"mm{seed}_merges.txt"))
+        texts = [F.random_text(rng, rng.randint(0, 60)) for _ in range(60)]
+        yield seed, v, s, kw, mp, texts
+
+
+@needs_ref
+@pytest.mark.parametrize("byte_mode", [True, False])
+def test_oracle_merges_matches_reference_on_fuzz_models(byte_mode):
+    ref = O.load_ref()
+    tmp = tempfile.mkdtemp()
+    for seed, v, s, kw, mp, texts in _fuzz_cases(byte_mode, range(40), tmp):
+        ref.initialize(v, s, kw["prefix"], kw["is_byte_encoder"], merges_file_path=mp)
+        want = ref.batch_encode(texts, 2)
+        orc = O.Oracle(v, s, merges_path=mp, **kw)
+        got = orc.batch_encode(texts)
+        for t, g, w in zip(texts, got, want):
+            assert g == w, (seed, kw, t, g, w)
+        orc.close()
+
+
+@needs_ref
+@pytest.mark.parametrize("name", SMALL)
+def test_oracle_merges_matches_reference_on_corpus(name):
+    ref = O.load_ref()
+    v, s = synth.PATHS[name]
+    kw = synth.MODEL_KW[name]
+    ref.initialize(v, s, kw["prefix"], kw["is_byte_encoder"], merges_file_path=synth.MERGES[name])
+    orc = _oracle(name)
+    data, offs = synth.corpus(103, 1 << 20, special_every=200)
+    docs = [d.decode("utf-8") for d in synth.docs_of(data, offs)]
+    want = ref.batch_encode(docs, 4)
+    ids, tok = orc.encode_packed(data, offs)
+    assert np.array_equal(np.fromiter((x for w in want for x in w), dtype=np.int32), ids)
+    assert tok.tolist() == [0] + np.cumsum([len(w) for w in want]).tolist()
+
+
+@pytest.mark.parametrize("byte_mode", [True, False])
+def test_host_tables_merges_match_oracle_on_fuzz_models(byte_mode):
+    """Rules in random rank order, repeated pairs, several rules merging into one token, unknown characters."""
+    tmp = tempfile.mkdtemp()
+    for seed, v, s, kw, mp, texts in _fuzz_cases(byte_mode, range(40), tmp):
+        orc = O.Oracle(v, s, merges_path=mp, **kw)
+        hm = harness.HostModel(v, s, merges=mp, **kw)
+        if not hm.ok():
+            assert hm.status == 5, hm.message  # a refused table must say so, never mis-encode
+            continue
+        for t in texts:
+            assert hm.encode(t) == orc.encode(t), (seed, kw, t)
+        hm.close()
+        orc.close()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# GPU
+# ---------------------------------------------------------------------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", SMALL)
+def test_gpu_merges_golden_and_corpus(name):
+    from hutoken_b200 import capi
+    v, s = synth.PATHS[name]
+    eng = capi.Engine(v, s, merges_path=synth.MERGES[name], **synth.MODEL_KW[name])
+    g = _golden(name)
+    texts = [bytes.fromhex(c["text_hex"]) for c in g["cases"]]
+    got = eng.batch_encode(texts)
+    for t, a, c in zip(texts, got, g["cases"]):
+        assert a == c["ids"], (name, t[:40], a[:16], c["ids"][:16])
+    orc = _oracle(name)
+    for seed, special_every in ((41, 0), (42, 200)):
+        data, offs = synth.corpus(seed, 3 << 20, special_every=special_every)
+        ids, tok = eng.encode_packed(data, offs)
+        oids, otok = orc.encode_packed(data, offs)
+        assert_same(ids, tok, oids, otok, f"merges {name} seed {seed}")
+    # medium / long pretokens go through miss_kernel and long_kernel with the same tables
+    rng = random.Random(8)
+    longs = ["go " + "".join(rng.choice("abcdeégőz") for _ in range(n)) + " end" for n in (40, 700, 5000, 70000)]
+    assert eng.batch_encode(longs) == orc.batch_encode(longs)
+    eng.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("byte_mode", [True, False])
+def test_gpu_merges_fuzz_models(byte_mode):
+    from hutoken_b200 import capi
+    tmp = tempfile.mkdtemp()
+    for seed, v, s, kw, mp, texts in _fuzz_cases(byte_mode, range(30), tmp):
+        try:
+            eng = capi.Engine(v, s, merges_path=mp, **kw)
+        except Exception as e:  # refused tables only (HUT_STATUS_UNSUPPORTED)
+            assert "split" in str(e) or "span" in str(e), e
+            continue
+        orc = O.Oracle(v, s, merges_path=mp, **kw)
+        got, want = eng.batch_encode(texts), orc.batch_encode(texts)
+        for t, g, w in zip(texts, got, want):
+            assert g == w, (seed, kw, t, g, w)
+        eng.close()
+        orc.close()
+
+
+@pytest.mark.gpu
+def test_gpu_merges_python_surface():
+    """_hutoken.initialize(..., merges_file_path=) as hutoken.py:112 calls it for hub models."""
+    from hutoken_b200 import _hutoken as ext
+    name = "gpt2_small"
+    v, s = synth.PATHS[name]
+    ext.initialize(v, s, None, True, merges_file_path=synth.MERGES[name])
+    orc = _oracle(name)
+    texts = ["hello world", " árvíztűrő tükörfúrógép 123", "x\n\ny"]
+    assert [ext.encode(t) for t in texts] == orc.batch_encode(texts)
+    assert ext.batch_encode(texts, 4) == orc.batch_encode(texts)
+    with pytest.raises(FileNotFoundError, match="Could not open merges file."):
+        ext.initialize(v, s, None, True, merges_file_path="/nonexistent/merges.txt")
+    ext.initialize(v, s, None, True)  # back to the string path for the tests that follow

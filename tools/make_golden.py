@@ -7,6 +7,7 @@ engine -- to the reference's behaviour (the reference ships no g
 
 Fixtures:
   encode_<model>.json   {"model", "kwargs", "cases": [{"text_hex", "ids"}]}   ids = _hutoken.encode / batch_encode
+  encode_merges_<model>.json   the same with merges_file_path= (id-keyed merge path), small models only
   pretokens.json        {"cases": [{"text_hex", "lengths"}]}                   parser_next_token (parser.c:24-88)
 
 Input strings: the 28 parser cases of the reference's tests/test_parser.c:77-108, the sentences / paragraphs of
@@ -71,10 +72,13 @@ def fuzz_texts(seed, n):
     return [F.random_text(rng, rng.randint(0, 40)) for _ in range(n)]
 
 
-def encode_golden(ref, name):
+def encode_golden(ref, name, merges=None):
     v, s = synth.PATHS[name]
     kw = synth.MODEL_KW[name]
-    ref.initialize(v, s, kw["prefix"], kw["is_byte_encoder"])
+    if merges:  # id-keyed path (lib.c:573-663, core.c:211-337)
+        ref.initialize(v, s, kw["prefix"], kw["is_byte_encoder"], merges_file_path=merges)
+    else:
+        ref.initialize(v, s, kw["prefix"], kw["is_byte_encoder"])
     texts = PARSER_CASES + SENTENCES + PROBES + fuzz_texts(77, 120)
     texts += synthetic_docs(11, 48 << 10, 0)[:12] + synthetic_docs(12, 48 << 10, 200)[:12]
     cases = []
@@ -88,8 +92,11 @@ def encode_golden(ref, name):
         "nul_cut": {"text_hex": _hex("ab\0cd"), "ids": ref.batch_encode(["ab\0cd"], 1)[0]},
         "zero_threads": ref.batch_encode(["hello", "world"], 0),
     }
-    return {"model": name, "kwargs": kw, "vocab": os.path.relpath(v, ROOT), "special": os.path.relpath(s, ROOT),
-            "cases": cases, "extra": extra}
+    out = {"model": name, "kwargs": kw, "vocab": os.path.relpath(v, ROOT), "special": os.path.relpath(s, ROOT),
+           "cases": cases, "extra": extra}
+    if merges:
+        out["merges"] = os.path.relpath(merges, ROOT)
+    return out
 
 
 class _Slice(C.Structure):
@@ -139,6 +146,11 @@ def main():
         with open(os.path.join(GOLDEN, f"encode_{name}.json"), "w") as f:
             json.dump(g, f, separators=(",", ":"))
         print(name, len(g["cases"]), "cases,", sum(len(c["ids"]) for c in g["cases"]), "ids")
+    for name in ("gpt2_small", "llama_small"):  # merges-file mode; data/*_2k.merges.txt come from tools/make_merges.py
+        g = encode_golden(ref, name, merges=synth.MERGES[name])
+        with open(os.path.join(GOLDEN, f"encode_merges_{name}.json"), "w") as f:
+            json.dump(g, f, separators=(",", ":"))
+        print(name, "merges:", len(g["cases"]), "cases,", sum(len(c["ids"]) for c in g["cases"]), "ids")
     p = pretoken_golden()
     with open(os.path.join(GOLDEN, "pretokens.json"), "w") as f:
         json.dump(p, f, separators=(",", ":"))

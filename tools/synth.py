@@ -237,6 +237,12 @@ PATHS = {
     "llama_small": (os.path.join(DATA_DIR, "llama_2k.vocab.txt"), os.path.join(DATA_DIR, "llama_special.txt")),
 }
 
+# merges files (lib.c:573-663) derived from the small vocabularies by tools/make_merges.py --noise
+MERGES = {
+    "gpt2_small": os.path.join(DATA_DIR, "gpt2_2k.merges.txt"),
+    "llama_small": os.path.join(DATA_DIR, "llama_2k.merges.txt"),
+}
+
 MODEL_KW = {
     "gpt2": dict(prefix=None, is_byte_encoder=True),
     "gpt2_small": dict(prefix=None, is_byte_encoder=True),
