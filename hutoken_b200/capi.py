@@ -38,6 +38,11 @@ class _Result(C.Structure):
                 ("n_docs", C.c_uint64)]
 
 
+class _TextResult(C.Structure):
+    _fields_ = [("text", C.POINTER(C.c_uint8)), ("text_offsets", C.POINTER(C.c_uint64)), ("n_bytes", C.c_uint64),
+                ("n_docs", C.c_uint64)]
+
+
 class Stats(C.Structure):
     _fields_ = [("pretokens", C.c_uint64), ("cache_hits", C.c_uint64), ("warp_merges", C.c_uint64),
                 ("block_merges", C.c_uint64), ("big_merges", C.c_uint64), ("cut_documents", C.c_uint64),
@@ -71,6 +76,10 @@ def load_library():
     lib.hut_encode_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(_Result)]
     lib.hut_encode_device.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64,
                                       C.c_void_p, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint64), C.c_void_p]
+    lib.hut_decode_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(_TextResult)]
+    lib.hut_decode_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64,
+                                      C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.c_void_p]
+    lib.hut_decode_stats.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
     lib.hut_cache_reset.argtypes = [C.c_void_p]
     lib.hut_host_alloc.restype = C.c_void_p
     lib.hut_host_alloc.argtypes = [C.c_size_t]
@@ -149,6 +158,32 @@ class Engine:
         self._check(self._lib.hut_encode_device(self._h, dev_index, d_bytes, n_bytes, d_offs, n_docs, d_ids,
                                                 ids_capacity, d_tok, C.byref(n), stream))
         return int(n.value)
+
+    def decode_packed(self, ids, tok):
+        """ids int32[n], tok uint64[ndocs+1] (host) -> (text uint8[n_bytes], text_offsets uint64[ndocs+1])."""
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        tok = np.ascontiguousarray(tok, dtype=np.uint64)
+        nd = len(tok) - 1
+        res = _TextResult()
+        self._check(self._lib.hut_decode_batch(self._h, ids.ctypes.data, tok.ctypes.data, nd, C.byref(res)))
+        n = int(res.n_bytes)
+        text = np.ctypeslib.as_array(res.text, shape=(n,)).copy() if n else np.zeros(0, np.uint8)
+        offs = np.ctypeslib.as_array(res.text_offsets, shape=(nd + 1,)).copy()
+        return text, offs
+
+    def batch_decode_bytes(self, lists):
+        tok = np.zeros(len(lists) + 1, dtype=np.uint64)
+        if lists:
+            tok[1:] = np.cumsum([len(x) for x in lists])
+        ids = np.fromiter((i for x in lists for i in x), dtype=np.int32, count=int(tok[-1]))
+        text, offs = self.decode_packed(ids, tok)
+        raw = text.tobytes()
+        return [raw[int(offs[i]):int(offs[i + 1])] for i in range(len(lists))]
+
+    def decode_stats(self):
+        ms, n = C.c_double(), C.c_uint64()
+        self._lib.hut_decode_stats(self._h, C.byref(ms), C.byref(n))
+        return {"kernel_ms": ms.value, "kernel_launches": n.value}
 
     def cache_reset(self):
         self._check(self._lib.hut_cache_reset(self._h))

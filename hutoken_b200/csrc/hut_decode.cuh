@@ -1,0 +1,330 @@
+// Decode path on the device: ids -> text.
+//
+// Replaces decode() (core.c:513-581: bounds check, concatenation of vocab_decode[id]) and pretokenizer_decode
+// (pretokenizer.c:197-296: strip the prefix once, then left to right: longest special-chars replacement found by
+// descending the trie of ac.c:27-50 -> the byte it stands for; otherwise byte mode: one UTF-8 character -> the byte
+// with that code point, '?' above 255; plain mode: the character is copied).
+//
+// The scan is greedy and sequential (where a step starts depends on where the previous one ended), so it is done
+// in two parts per 1024-byte tile of a document's raw text: every position computes the step it WOULD take
+// (independent, parallel), then the positions really visited are found by binary lifting over those steps
+// (next^(2^k) tables in shared memory) from the tile's entry offset, which the previous tile hands over.
+//
+// Data layout: ids int32[n] + tok_off uint64[ndocs+1] -> len32[n] -> (scan) raw_off uint64[n+1] -> raw bytes
+// (documents back to back, 64 zero bytes of padding) -> dec bytes written at the same base (a step never emits more
+// bytes than it consumes) + doc_len uint32[ndocs] -> (scan) text_off uint64[ndocs+1] -> text packed.
+#pragma once
+#include <cstdint>
+
+#include "hut_model.h"
+
+namespace hut {
+
+struct DecModel {
+    const uint32_t* dec_off;   // [vocab_lines + 1]
+    const uint32_t* dec_len;   // [vocab_lines], HUT_DEC_MISSING if no line carries the id
+    const uint8_t* dec_pool;
+    uint32_t vocab_lines;
+    const unsigned long long* trie_edge;
+    uint32_t trie_mask;        // 0xFFFFFFFF when the trie is empty
+    const int16_t* trie_out;
+    const uint8_t* trie_depth;
+    const uint32_t* root_child;  // [256]
+    const uint8_t* prefix;
+    uint32_t prefix_len;
+    int byte_mode;
+};
+
+constexpr int DEC_TILE = 1024;   // raw bytes per tile
+constexpr int DEC_LOOK = 32;     // look-ahead: the longest replacement is 26 bytes (32-byte line buffer, lib.c:483)
+constexpr int DEC_NT = 128;
+constexpr int DEC_LEVELS = 11;   // 2^10 hops cover a tile; one more level keeps the loop uniform
+constexpr int SCAN_NT = 256;
+constexpr int SCAN_ITEMS = 16;   // per thread
+constexpr int SCAN_BLOCK = SCAN_NT * SCAN_ITEMS;
+
+// ------------------------------------------------------------------------------------------------
+// exclusive scan uint32[n] -> uint64[n + 1] (three kernels: block sums, scan of the sums, local scan + base)
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long block_exclusive_u64(unsigned long long v, unsigned long long* total,
+                                                                  unsigned long long* sm /* [32] */) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    unsigned long long inc = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const unsigned long long t = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+        if (lane >= d) inc += t;
+    }
+    if (lane == 31) sm[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned long long w = lane < nw ? sm[lane] : 0ull, winc = w;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned long long t = __shfl_up_sync(0xFFFFFFFFu, winc, d);
+            if (lane >= d) winc += t;
+        }
+        sm[lane] = winc - w;
+        if (lane == 31) *total = winc;
+    }
+    __syncthreads();
+    const unsigned long long r = sm[warp] + inc - v;
+    __syncthreads();
+    return r;
+}
+
+__global__ void __launch_bounds__(SCAN_NT) scan_sums_kernel(const uint32_t* in, unsigned long long n,
+                                                            unsigned long long* bsum) {
+    __shared__ unsigned long long sm[32];
+    __shared__ unsigned long long tot;
+    const unsigned long long base = (unsigned long long)blockIdx.x * SCAN_BLOCK;
+    unsigned long long s = 0;
+    for (int k = 0; k < SCAN_ITEMS; ++k) {
+        const unsigned long long i = base + (unsigned long long)k * SCAN_NT + threadIdx.x;
+        if (i < n) s += in[i];
+    }
+    block_exclusive_u64(s, &tot, sm);
+    if (threadIdx.x == 0) bsum[blockIdx.x] = tot;
+}
+
+__global__ void __launch_bounds__(1024) scan_top_kernel(unsigned long long* bsum, uint32_t nblocks) {
+    __shared__ unsigned long long sm[32];
+    __shared__ unsigned long long tot;
+    unsigned long long carry = 0;
+    for (uint32_t b0 = 0; b0 < nblocks; b0 += 1024) {
+        const uint32_t i = b0 + threadIdx.x;
+        const unsigned long long v = i < nblocks ? bsum[i] : 0ull;
+        const unsigned long long ex = block_exclusive_u64(v, &tot, sm);
+        if (i < nblocks) bsum[i] = carry + ex;
+        carry += tot;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(SCAN_NT) scan_apply_kernel(const uint32_t* in, unsigned long long n,
+                                                             const unsigned long long* bsum, unsigned long long* out) {
+    __shared__ unsigned long long sm[32];
+    __shared__ unsigned long long tot;
+    // thread t owns SCAN_ITEMS consecutive items, so its partial sums are a plain running sum
+    const unsigned long long first = (unsigned long long)blockIdx.x * SCAN_BLOCK + (unsigned long long)threadIdx.x * SCAN_ITEMS;
+    uint32_t v[SCAN_ITEMS];
+    unsigned long long s = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) {
+        v[k] = first + k < n ? in[first + k] : 0u;
+        s += v[k];
+    }
+    unsigned long long run = bsum[blockIdx.x] + block_exclusive_u64(s, &tot, sm);
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) {
+        if (first + k <= n) out[first + k] = run;  // index n receives the grand total
+        run += v[k];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// ids -> token lengths (bounds check of core.c:520-531), token bytes -> raw text
+// ------------------------------------------------------------------------------------------------
+__global__ void dec_len_kernel(DecModel D, const int32_t* ids, unsigned long long n, uint32_t* len32,
+                               unsigned int* bad) {
+    const unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int32_t id = ids[i];
+    uint32_t l = HUT_DEC_MISSING;
+    if (id >= 0 && (uint32_t)id < D.vocab_lines) l = __ldg(D.dec_len + id);
+    if (l == HUT_DEC_MISSING) {
+        atomicExch(bad, 1u);
+        l = 0;
+    }
+    len32[i] = l;
+}
+
+__global__ void dec_gather_kernel(DecModel D, const int32_t* ids, unsigned long long n,
+                                  const unsigned long long* raw_off, uint8_t* raw) {
+    const unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i > n) return;
+    if (i == n) {  // zero padding read by the last tile's look-ahead
+        uint8_t* p = raw + raw_off[n];
+        for (int k = 0; k < 64; ++k) p[k] = 0;
+        return;
+    }
+    const int32_t id = ids[i];
+    if (id < 0 || (uint32_t)id >= D.vocab_lines) return;
+    const uint32_t l = __ldg(D.dec_len + id);
+    if (l == HUT_DEC_MISSING) return;
+    const uint8_t* src = D.dec_pool + __ldg(D.dec_off + id);
+    uint8_t* dst = raw + raw_off[i];
+    for (uint32_t k = 0; k < l; ++k) dst[k] = __ldg(src + k);
+}
+
+// ------------------------------------------------------------------------------------------------
+// raw text -> decoded text, one CTA per document (grid-stride), tile by tile
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t trie_child(const DecModel& D, uint32_t node, uint32_t byte) {
+    const uint32_t key = (node << 8) | byte;
+    uint32_t i = hut_trie_hash(key, D.trie_mask);
+    for (;;) {
+        const unsigned long long s = __ldg(D.trie_edge + i);
+        if (s == HUT_TRIE_EMPTY) return 0u;
+        if ((uint32_t)(s >> 32) == key) return (uint32_t)s;
+        i = (i + 1) & D.trie_mask;
+    }
+}
+
+struct DecSm {
+    uint8_t raw[DEC_TILE + DEC_LOOK + 32];
+    uint16_t nxt[DEC_LEVELS][DEC_TILE];  // nxt[k][i] = position after 2^k steps from i; >= tile_len: left the tile
+    uint8_t eb[DEC_TILE];                // byte emitted by a replacement / byte-mode step
+    uint8_t el[DEC_TILE];                // bytes emitted when position i is visited (0 = copy `cl` raw bytes)
+    uint32_t root_child[256];
+    unsigned long long scan[32];
+    unsigned long long tot;
+    uint32_t entry;
+};
+
+__global__ void __launch_bounds__(DEC_NT) dec_doc_kernel(DecModel D, const unsigned long long* tok_off,
+                                                         unsigned long long ndocs, const unsigned long long* raw_off,
+                                                         const uint8_t* raw, uint8_t* dec, uint32_t* doc_len) {
+    __shared__ DecSm sm;
+    const int tid = threadIdx.x;
+    for (int i = tid; i < 256; i += DEC_NT) sm.root_child[i] = D.root_child[i];
+    __syncthreads();
+    for (unsigned long long d = blockIdx.x; d < ndocs; d += gridDim.x) {
+        const unsigned long long r0 = raw_off[tok_off[d]], r1 = raw_off[tok_off[d + 1]];
+        const unsigned long long rlen = r1 - r0;
+        unsigned long long written = 0;
+        // ---- prefix, stripped once when the raw text starts with it (pretokenizer.c:209-215) ----
+        if (tid == 0) {
+            uint32_t e = 0;
+            if (D.prefix_len && rlen >= D.prefix_len) {
+                bool same = true;
+                for (uint32_t k = 0; k < D.prefix_len; ++k) same = same && raw[r0 + k] == D.prefix[k];
+                if (same) e = D.prefix_len;
+            }
+            sm.entry = e;
+        }
+        __syncthreads();
+        for (unsigned long long t0 = 0; t0 < rlen; t0 += DEC_TILE) {
+            const uint32_t tile_len = rlen - t0 < DEC_TILE ? (uint32_t)(rlen - t0) : (uint32_t)DEC_TILE;
+            const uint32_t avail = rlen - t0 < DEC_TILE + DEC_LOOK ? (uint32_t)(rlen - t0) : (uint32_t)(DEC_TILE + DEC_LOOK);
+            for (uint32_t i = tid; i < DEC_TILE + DEC_LOOK; i += DEC_NT) sm.raw[i] = i < avail ? raw[r0 + t0 + i] : 0;
+            uint32_t entry = sm.entry;
+            __syncthreads();
+            if (entry >= tile_len) {  // the previous step jumped over this whole tile (prefix / replacement at its end)
+                if (tid == 0) sm.entry = entry - tile_len;
+                __syncthreads();
+                continue;
+            }
+            // ---- the step every position would take ----
+            for (uint32_t i = tid; i < tile_len; i += DEC_NT) {
+                const uint32_t b0 = sm.raw[i];
+                uint32_t step = 0, out = 0, emit = 1;
+                uint32_t node = sm.root_child[b0];
+                if (node) {  // longest replacement starting here (never past the end of the document)
+                    uint32_t q = i + 1;
+                    for (;;) {
+                        const int o = __ldg(D.trie_out + node);
+                        if (o >= 0) {
+                            step = __ldg(D.trie_depth + node);
+                            out = (uint32_t)o;
+                        }
+                        if (q >= avail) break;
+                        node = trie_child(D, node, sm.raw[q]);
+                        if (!node) break;
+                        ++q;
+                    }
+                }
+                if (!step) {
+                    const uint32_t b1 = sm.raw[i + 1], b2 = sm.raw[i + 2], b3 = sm.raw[i + 3];
+                    uint32_t cl, cp;
+                    if (b0 < 0x80) { cl = 1; cp = b0; }
+                    else if ((b0 & 0xE0) == 0xC0) { cl = 2; cp = ((b0 & 0x1F) << 6) | (b1 & 0x3F); }
+                    else if ((b0 & 0xF0) == 0xE0) { cl = 3; cp = ((b0 & 0x0F) << 12) | ((b1 & 0x3F) << 6) | (b2 & 0x3F); }
+                    else if ((b0 & 0xF8) == 0xF0) { cl = 4; cp = ((b0 & 0x07) << 18) | ((b1 & 0x3F) << 12) | ((b2 & 0x3F) << 6) | (b3 & 0x3F); }
+                    else { cl = 1; cp = 0xFFFD; }
+                    step = cl;
+                    if (D.byte_mode) {
+                        out = cp < 256 ? cp : (uint32_t)'?';  // pretokenizer.c:247-254
+                    } else {  // the character is copied (pretokenizer.c:283-287), clamped to the document
+                        const unsigned long long left = rlen - t0 - i;
+                        emit = left < cl ? (uint32_t)left : cl;
+                        out = 0x100;  // marker: copy raw bytes
+                    }
+                }
+                sm.nxt[0][i] = (uint16_t)(i + step);
+                sm.eb[i] = (uint8_t)out;
+                sm.el[i] = (uint8_t)(out == 0x100 ? 0x80 | emit : 1);
+            }
+            __syncthreads();
+            // ---- binary lifting ----
+            for (int k = 1; k < DEC_LEVELS; ++k) {
+                for (uint32_t i = tid; i < tile_len; i += DEC_NT) {
+                    const uint32_t v = sm.nxt[k - 1][i];
+                    sm.nxt[k][i] = v >= tile_len ? (uint16_t)v : sm.nxt[k - 1][v];
+                }
+                __syncthreads();
+            }
+            // hops that stay inside the tile, counted from the entry
+            uint32_t H = 0;
+            {
+                uint32_t pos = entry;
+                for (int k = DEC_LEVELS - 1; k >= 0; --k) {
+                    const uint32_t v = sm.nxt[k][pos];
+                    if (v < tile_len) {
+                        pos = v;
+                        H += 1u << k;
+                    }
+                }
+                if (tid == 0) sm.entry = sm.nxt[0][pos] - tile_len;  // hand-over to the next tile
+            }
+            const uint32_t nodes = H + 1;
+            const uint32_t per = (nodes + DEC_NT - 1) / DEC_NT;
+            const uint32_t h0 = tid * per;
+            uint32_t pos = entry, mine = 0;
+            if (h0 < nodes) {
+                for (int k = DEC_LEVELS - 1; k >= 0; --k)
+                    if (h0 & (1u << k)) pos = sm.nxt[k][pos];
+                uint32_t p = pos;
+                for (uint32_t h = h0; h < nodes && h < h0 + per; ++h) {
+                    mine += sm.el[p] & 0x7Fu;
+                    p = sm.nxt[0][p];
+                }
+            }
+            const unsigned long long ex = block_exclusive_u64(mine, &sm.tot, sm.scan);
+            if (h0 < nodes) {
+                uint8_t* o = dec + r0 + written + ex;
+                uint32_t p = pos;
+                for (uint32_t h = h0; h < nodes && h < h0 + per; ++h) {
+                    const uint32_t e = sm.el[p];
+                    if (e & 0x80u) {
+                        for (uint32_t k = 0; k < (e & 0x7Fu); ++k) *o++ = sm.raw[p + k];
+                    } else {
+                        *o++ = sm.eb[p];
+                    }
+                    p = sm.nxt[0][p];
+                }
+            }
+            written += sm.tot;
+            __syncthreads();
+        }
+        if (tid == 0) doc_len[d] = (uint32_t)written;
+        __syncthreads();
+    }
+}
+
+// decoded bytes of each document -> packed text
+__global__ void dec_pack_kernel(const unsigned long long* tok_off, unsigned long long ndocs,
+                                const unsigned long long* raw_off, const uint8_t* dec,
+                                const unsigned long long* text_off, uint8_t* text) {
+    const unsigned long long w = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    const unsigned long long nw = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
+    for (unsigned long long d = w; d < ndocs; d += nw) {
+        const uint8_t* src = dec + raw_off[tok_off[d]];
+        uint8_t* dst = text + text_off[d];
+        const unsigned long long n = text_off[d + 1] - text_off[d];
+        for (unsigned long long i = lane; i < n; i += 32) dst[i] = src[i];
+    }
+}
+
+}  // namespace hut

@@ -1,0 +1,219 @@
+/* hut_decode_batch / hut_decode_device: host orchestration of the decode kernels (hut_decode.cuh).
+ * Included at the end of hut_engine.cu (needs hut_ctx / hut_dev).  Device 0 of the context does the work: decode is
+ * a per-document gather + scan, and ranks of a multi-GPU job each decode their own documents. */
+
+struct hut_decstate {
+    DecModel dm;
+    int ready;
+    int32_t* d_ids;
+    size_t d_ids_cap;
+    unsigned long long* d_tok;
+    size_t d_tok_cap;
+    uint32_t* d_len32;
+    size_t d_len32_cap;
+    unsigned long long* d_raw_off;
+    size_t d_raw_off_cap;
+    unsigned long long* d_bsum;
+    size_t d_bsum_cap;
+    uint8_t* d_raw;
+    size_t d_raw_cap;
+    uint8_t* d_dec;
+    size_t d_dec_cap;
+    uint32_t* d_doc_len;
+    size_t d_doc_len_cap;
+    unsigned long long* d_text_off;
+    size_t d_text_off_cap;
+    uint8_t* d_text;
+    size_t d_text_cap;
+    unsigned int* d_bad;
+    uint8_t* h_text;
+    size_t h_text_cap;
+    unsigned long long* h_text_off;
+    size_t h_text_off_cap;
+    cudaEvent_t ev[2];
+    float last_ms;
+    unsigned last_launches;
+};
+
+static void dec_free(hut_decstate* s) {
+    if (!s) return;
+    cudaFree(s->d_ids);
+    cudaFree(s->d_tok);
+    cudaFree(s->d_len32);
+    cudaFree(s->d_raw_off);
+    cudaFree(s->d_bsum);
+    cudaFree(s->d_raw);
+    cudaFree(s->d_dec);
+    cudaFree(s->d_doc_len);
+    cudaFree(s->d_text_off);
+    cudaFree(s->d_text);
+    cudaFree(s->d_bad);
+    cudaFreeHost(s->h_text);
+    cudaFreeHost(s->h_text_off);
+    if (s->ev[0]) cudaEventDestroy(s->ev[0]);
+    if (s->ev[1]) cudaEventDestroy(s->ev[1]);
+    free(s);
+}
+
+static int dec_init(hut_ctx* ctx) {
+    if (ctx->dec && ctx->dec->ready) return HUT_STATUS_OK;
+    hut_dev* d = &ctx->dev[0];
+    const hut_model* m = ctx->model;
+    CU(ctx, cudaSetDevice(d->device));
+    if (!ctx->dec) ctx->dec = (hut_decstate*)calloc(1, sizeof(hut_decstate));
+    if (!ctx->dec) return set_err(ctx, HUT_STATUS_MEMORY, "%s", "out of memory");
+    hut_decstate* s = ctx->dec;
+    DecModel& D = s->dm;
+    CU(ctx, upload(d, m->dec_off, (size_t)m->vocab_lines + 1, &D.dec_off));
+    CU(ctx, upload(d, m->dec_len, (size_t)m->vocab_lines, &D.dec_len));
+    CU(ctx, upload(d, m->dec_pool, (size_t)m->dec_pool_len + 16, &D.dec_pool));
+    D.vocab_lines = m->vocab_lines;
+    CU(ctx, upload(d, (const unsigned long long*)m->trie_edge, m->trie_cap, &D.trie_edge));
+    D.trie_mask = m->trie_cap - 1;
+    CU(ctx, upload(d, m->trie_out, m->trie_nodes, &D.trie_out));
+    CU(ctx, upload(d, m->trie_depth, m->trie_nodes, &D.trie_depth));
+    CU(ctx, upload(d, m->trie_root_child, 256, &D.root_child));
+    CU(ctx, upload(d, m->prefix_bytes, m->prefix_len, &D.prefix));
+    D.prefix_len = m->prefix_len;
+    D.byte_mode = m->is_byte_encoder;
+    CU(ctx, cudaMalloc(&s->d_bad, sizeof(unsigned int)));
+    CU(ctx, cudaEventCreate(&s->ev[0]));
+    CU(ctx, cudaEventCreate(&s->ev[1]));
+    s->ready = 1;
+    return HUT_STATUS_OK;
+}
+
+/* exclusive scan uint32[n] -> uint64[n + 1] on `st` */
+static int dec_scan(hut_ctx* ctx, hut_decstate* s, const uint32_t* in, unsigned long long n, unsigned long long* out,
+                    cudaStream_t st) {
+    const unsigned long long nb = n / SCAN_BLOCK + 1;
+    if (nb > 0x7FFFFFFFull) return set_err(ctx, HUT_STATUS_ARG, "%s", "too many items");
+    CU(ctx, grow(&s->d_bsum, &s->d_bsum_cap, (size_t)nb));
+    scan_sums_kernel<<<(unsigned)nb, SCAN_NT, 0, st>>>(in, n, s->d_bsum);
+    scan_top_kernel<<<1, 1024, 0, st>>>(s->d_bsum, (uint32_t)nb);
+    scan_apply_kernel<<<(unsigned)nb, SCAN_NT, 0, st>>>(in, n, s->d_bsum, out);
+    s->last_launches += 3;
+    return HUT_STATUS_OK;
+}
+
+/* ids + tok_off resident on device 0 -> packed text + text_off on the device (buffers owned by the context).
+ * *n_text receives the text length.  Synchronises the stream twice (raw length, text length). */
+static int dec_run(hut_ctx* ctx, const int32_t* d_ids, unsigned long long n_ids, const unsigned long long* d_tok,
+                   unsigned long long n_docs, unsigned long long* n_text, cudaStream_t st) {
+    hut_decstate* s = ctx->dec;
+    hut_dev* d = &ctx->dev[0];
+    const DecModel& D = s->dm;
+    s->last_launches = 0;
+    CU(ctx, grow(&s->d_len32, &s->d_len32_cap, (size_t)n_ids + 1));
+    CU(ctx, grow(&s->d_raw_off, &s->d_raw_off_cap, (size_t)n_ids + 2));
+    CU(ctx, grow(&s->d_doc_len, &s->d_doc_len_cap, (size_t)n_docs + 1));
+    CU(ctx, grow(&s->d_text_off, &s->d_text_off_cap, (size_t)n_docs + 2));
+    CU(ctx, cudaEventRecord(s->ev[0], st));
+    CU(ctx, cudaMemsetAsync(s->d_bad, 0, sizeof(unsigned int), st));
+    if (n_ids) {
+        dec_len_kernel<<<(unsigned)((n_ids + 255) / 256), 256, 0, st>>>(D, d_ids, n_ids, s->d_len32, s->d_bad);
+        s->last_launches++;
+    }
+    int rc = dec_scan(ctx, s, s->d_len32, n_ids, s->d_raw_off, st);
+    if (rc != HUT_STATUS_OK) return rc;
+    unsigned long long raw_total = 0;
+    unsigned int bad = 0;
+    CU(ctx, cudaMemcpyAsync(&raw_total, s->d_raw_off + n_ids, sizeof raw_total, cudaMemcpyDeviceToHost, st));
+    CU(ctx, cudaMemcpyAsync(&bad, s->d_bad, sizeof bad, cudaMemcpyDeviceToHost, st));
+    CU(ctx, cudaStreamSynchronize(st));
+    if (bad)  /* core.c:522-530 */
+        return set_err(ctx, HUT_STATUS_VALUE, "%s", "Element must be non-negative and less than vocab size.");
+    CU(ctx, grow(&s->d_raw, &s->d_raw_cap, (size_t)raw_total + 128));
+    CU(ctx, grow(&s->d_dec, &s->d_dec_cap, (size_t)raw_total + 128));
+    dec_gather_kernel<<<(unsigned)((n_ids + 1 + 255) / 256), 256, 0, st>>>(D, d_ids, n_ids, s->d_raw_off, s->d_raw);
+    s->last_launches++;
+    if (n_docs) {
+        const unsigned long long want = n_docs < (unsigned long long)d->sms * 12 ? n_docs : (unsigned long long)d->sms * 12;
+        dec_doc_kernel<<<(unsigned)want, DEC_NT, 0, st>>>(D, d_tok, n_docs, s->d_raw_off, s->d_raw, s->d_dec, s->d_doc_len);
+        s->last_launches++;
+    }
+    rc = dec_scan(ctx, s, s->d_doc_len, n_docs, s->d_text_off, st);
+    if (rc != HUT_STATUS_OK) return rc;
+    unsigned long long text_total = 0;
+    CU(ctx, cudaMemcpyAsync(&text_total, s->d_text_off + n_docs, sizeof text_total, cudaMemcpyDeviceToHost, st));
+    CU(ctx, cudaStreamSynchronize(st));
+    CU(ctx, grow(&s->d_text, &s->d_text_cap, (size_t)text_total + 16));
+    if (n_docs) {
+        const unsigned long long blocks = (n_docs + 7) / 8;
+        const unsigned long long cap = (unsigned long long)d->sms * 16;
+        dec_pack_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, st>>>(d_tok, n_docs, s->d_raw_off, s->d_dec,
+                                                                                 s->d_text_off, s->d_text);
+        s->last_launches++;
+    }
+    CU(ctx, cudaEventRecord(s->ev[1], st));
+    CU(ctx, cudaGetLastError());
+    *n_text = text_total;
+    return HUT_STATUS_OK;
+}
+
+extern "C" int hut_decode_batch(hut_ctx* ctx, const int32_t* ids, const uint64_t* tok_offsets, uint64_t n_docs,
+                                hut_text_result* result) {
+    if (!ctx) return HUT_STATUS_STATE;
+    if (!result || (!tok_offsets && n_docs)) return set_err(ctx, HUT_STATUS_ARG, "%s", "null argument");
+    int rc = dec_init(ctx);
+    if (rc != HUT_STATUS_OK) return rc;
+    hut_decstate* s = ctx->dec;
+    hut_dev* d = &ctx->dev[0];
+    CU(ctx, cudaSetDevice(d->device));
+    const unsigned long long base = n_docs ? tok_offsets[0] : 0, n_ids = n_docs ? tok_offsets[n_docs] - base : 0;
+    for (uint64_t i = 0; i < n_docs; ++i)
+        if (tok_offsets[i + 1] < tok_offsets[i]) return set_err(ctx, HUT_STATUS_ARG, "%s", "tok_offsets must not decrease");
+    if (n_ids && !ids) return set_err(ctx, HUT_STATUS_ARG, "%s", "null argument");
+    cudaStream_t st = d->stream;
+    CU(ctx, grow(&s->d_ids, &s->d_ids_cap, (size_t)n_ids + 1));
+    CU(ctx, grow(&s->d_tok, &s->d_tok_cap, (size_t)n_docs + 1));
+    CU(ctx, grow_host(&s->h_text_off, &s->h_text_off_cap, (size_t)n_docs + 1, false));
+    /* offsets rebased to the first id of the batch */
+    for (uint64_t i = 0; i <= n_docs; ++i) s->h_text_off[i] = n_docs ? tok_offsets[i] - base : 0;
+    CU(ctx, cudaMemcpyAsync(s->d_tok, s->h_text_off, ((size_t)n_docs + 1) * sizeof(unsigned long long),
+                            cudaMemcpyHostToDevice, st));
+    if (n_ids) CU(ctx, cudaMemcpyAsync(s->d_ids, ids + base, (size_t)n_ids * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    CU(ctx, cudaStreamSynchronize(st)); /* h_text_off is reused below */
+    unsigned long long n_text = 0;
+    rc = dec_run(ctx, s->d_ids, n_ids, s->d_tok, n_docs, &n_text, st);
+    if (rc != HUT_STATUS_OK) return rc;
+    CU(ctx, grow_host(&s->h_text, &s->h_text_cap, (size_t)n_text + 1, false));
+    if (n_text) CU(ctx, cudaMemcpyAsync(s->h_text, s->d_text, (size_t)n_text, cudaMemcpyDeviceToHost, st));
+    CU(ctx, cudaMemcpyAsync(s->h_text_off, s->d_text_off, ((size_t)n_docs + 1) * sizeof(unsigned long long),
+                            cudaMemcpyDeviceToHost, st));
+    CU(ctx, cudaStreamSynchronize(st));
+    s->h_text[n_text] = 0;
+    cudaEventElapsedTime(&s->last_ms, s->ev[0], s->ev[1]);
+    result->text = s->h_text;
+    result->text_offsets = (const uint64_t*)s->h_text_off;
+    result->n_bytes = n_text;
+    result->n_docs = n_docs;
+    return HUT_STATUS_OK;
+}
+
+extern "C" int hut_decode_device(hut_ctx* ctx, const int32_t* d_ids, uint64_t n_ids, const uint64_t* d_tok_offsets,
+                                 uint64_t n_docs, const uint8_t** d_text_out, const uint64_t** d_text_offsets_out,
+                                 uint64_t* n_bytes_out, void* stream) {
+    if (!ctx) return HUT_STATUS_STATE;
+    int rc = dec_init(ctx);
+    if (rc != HUT_STATUS_OK) return rc;
+    hut_dev* d = &ctx->dev[0];
+    CU(ctx, cudaSetDevice(d->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : d->stream;
+    unsigned long long n_text = 0;
+    rc = dec_run(ctx, d_ids, n_ids, (const unsigned long long*)d_tok_offsets, n_docs, &n_text, st);
+    if (rc != HUT_STATUS_OK) return rc;
+    CU(ctx, cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&ctx->dec->last_ms, ctx->dec->ev[0], ctx->dec->ev[1]);
+    if (d_text_out) *d_text_out = ctx->dec->d_text;
+    if (d_text_offsets_out) *d_text_offsets_out = (const uint64_t*)ctx->dec->d_text_off;
+    if (n_bytes_out) *n_bytes_out = n_text;
+    return HUT_STATUS_OK;
+}
+
+extern "C" int hut_decode_stats(const hut_ctx* ctx, double* kernel_ms, uint64_t* kernel_launches) {
+    if (!ctx || !ctx->dec) return HUT_STATUS_STATE;
+    if (kernel_ms) *kernel_ms = ctx->dec->last_ms;
+    if (kernel_launches) *kernel_launches = ctx->dec->last_launches;
+    return HUT_STATUS_OK;
+}

@@ -13,6 +13,7 @@
 
 #include "../../include/hutoken_b200.h"
 #include "hut_model.h"
+#include "hut_decode.cuh"
 #include "hut_pipeline.cuh"
 
 using namespace hut;
@@ -49,7 +50,7 @@ struct hut_dev {
     cudaStream_t stream;        // kernels
     cudaStream_t s_in, s_out;   // H2D / D2H copies of the host-buffer API
     DevModel dm;
-    void* allocs[24];
+    void* allocs[48];
     int nalloc;
     CacheSlot* cache;
     uint32_t cache_bits;
@@ -87,8 +88,12 @@ struct hut_dev {
     hut_stats stats;
 };
 
+struct hut_decstate;
+static void dec_free(hut_decstate* s);
+
 struct hut_ctx {
     hut_model* model;
+    hut_decstate* dec;  // decode-side device state, created by the first hut_decode_* call
     int ndev;
     hut_dev dev[MAX_DEV];
     hut_options opt;
@@ -312,6 +317,8 @@ extern "C" int hut_create(const hut_model_desc* desc, const hut_options* opt, co
 
 extern "C" void hut_destroy(hut_ctx* ctx) {
     if (!ctx) return;
+    if (ctx->ndev) cudaSetDevice(ctx->dev[0].device);
+    dec_free(ctx->dec);
     for (int i = 0; i < ctx->ndev; ++i) dev_free(&ctx->dev[i]);
     cudaFreeHost(ctx->h_ids);
     cudaFreeHost(ctx->h_tok);
@@ -756,3 +763,5 @@ extern "C" int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64
     result->n_docs = n_docs;
     return HUT_STATUS_OK;
 }
+
+#include "hut_decode_api.inl"

@@ -229,8 +229,17 @@ done:
 }
 
 /* lib.c:460-566 */
-static int load_special(const char* path, uint8_t* special[256], uint32_t special_len[256], char* msg,
-                        size_t msglen) {
+typedef struct {
+    uint8_t bytes[32];
+    uint32_t len;
+    int byte;
+} special_line;
+
+static int load_special(const char* path, uint8_t* special[256], uint32_t special_len[256], special_line** lines,
+                        size_t* n_lines, char* msg, size_t msglen) {
+    size_t cap_lines = 0;
+    *lines = NULL;
+    *n_lines = 0;
     FILE* f = fopen(path, "r");
     if (!f) return fail(msg, msglen, HUT_ERR_FILE_NOT_FOUND, "Could not open special characters file.");
     char buf[32];
@@ -268,6 +277,20 @@ static int load_special(const char* path, uint8_t* special[256], uint32_t specia
         }
         memcpy(special[index], vs, keep);
         special_len[index] = (uint32_t)keep;
+        if (*n_lines == cap_lines) { /* every line goes into the decode trie, in file order (lib.c:555-556) */
+            cap_lines = cap_lines ? cap_lines * 2 : 128;
+            special_line* nl = realloc(*lines, cap_lines * sizeof **lines);
+            if (!nl) {
+                rc = fail(msg, msglen, HUT_ERR_MEMORY, "out of memory");
+                break;
+            }
+            *lines = nl;
+        }
+        special_line* L = &(*lines)[(*n_lines)++];
+        /* the reference stores the value as a C string: it ends at an embedded NUL */
+        L->len = (uint32_t)strnlen(vs, keep);
+        memcpy(L->bytes, vs, L->len);
+        L->byte = (int)index;
     }
     fclose(f);
     return rc;
@@ -507,6 +530,100 @@ static uint32_t merge_small(const hut_model* m, uint32_t* u, uint32_t n) {
         memmove(u + bi + 1, u + bi + 2, (n - bi - 2) * sizeof *u);
         n--;
     }
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * decode tables.  vocab_decode[value] = key (lib.c:423-433): when several keys carry one id the reference keeps
+ * whichever its hash map iterates last; here the key stated last in the file wins (ids are unique in every real
+ * vocabulary).  Ids >= vocab_lines are never decodable (core.c:522).
+ * Trie = ac_automaton_add_string per special-chars line, in file order (ac.c:27-50): a repeated pattern keeps the
+ * later byte.  The failure links the reference also builds are not used by its decoder (pretokenizer.c:224-240).
+ * ---------------------------------------------------------------------------------------------- */
+uint32_t hut_model_trie_child(const hut_model* m, uint32_t node, uint8_t byte) {
+    if (!m->trie_cap) return 0;
+    const uint32_t key = (node << 8) | byte, mask = m->trie_cap - 1;
+    uint32_t i = hut_trie_hash(key, mask);
+    for (;;) {
+        uint64_t s = m->trie_edge[i];
+        if (s == HUT_TRIE_EMPTY) return 0;
+        if ((uint32_t)(s >> 32) == key) return (uint32_t)s;
+        i = (i + 1) & mask;
+    }
+}
+
+static int build_decode_tables(hut_model* m, const strtab* vocab, const special_line* lines, size_t n_lines,
+                               const char* prefix, size_t plen) {
+    const uint32_t V = m->vocab_lines;
+    m->dec_off = calloc((size_t)V + 1, sizeof(uint32_t));
+    m->dec_len = malloc(((size_t)V ? V : 1) * sizeof(uint32_t));
+    uint32_t* who = malloc(((size_t)V ? V : 1) * sizeof(uint32_t));
+    if (!m->dec_off || !m->dec_len || !who) {
+        free(who);
+        return 0;
+    }
+    memset(who, 0xFF, ((size_t)V ? V : 1) * sizeof(uint32_t));
+    for (size_t i = 0; i < vocab->n; ++i)
+        if (vocab->val[i] >= 0 && (uint32_t)vocab->val[i] < V) who[vocab->val[i]] = (uint32_t)i;
+    size_t total = 0;
+    for (uint32_t id = 0; id < V; ++id) total += who[id] != 0xFFFFFFFFu ? vocab->len[who[id]] : 0;
+    m->dec_pool = malloc(total + 16);
+    if (!m->dec_pool || total > 0xFFFFFFF0u) {
+        free(who);
+        return 0;
+    }
+    size_t at = 0;
+    for (uint32_t id = 0; id < V; ++id) {
+        m->dec_off[id] = (uint32_t)at;
+        if (who[id] == 0xFFFFFFFFu) {
+            m->dec_len[id] = HUT_DEC_MISSING;
+            continue;
+        }
+        m->dec_len[id] = vocab->len[who[id]];
+        memcpy(m->dec_pool + at, vocab->str[who[id]], vocab->len[who[id]]);
+        at += vocab->len[who[id]];
+    }
+    m->dec_off[V] = (uint32_t)at;
+    m->dec_pool_len = (uint32_t)at;
+    memset(m->dec_pool + at, 0, 16);
+    free(who);
+
+    size_t max_nodes = 1;
+    for (size_t k = 0; k < n_lines; ++k) max_nodes += lines[k].len;
+    m->trie_out = malloc(max_nodes * sizeof(int16_t));
+    m->trie_depth = malloc(max_nodes);
+    m->trie_cap = 64;
+    while (m->trie_cap < max_nodes * 2 + 8) m->trie_cap <<= 1;
+    m->trie_edge = malloc((size_t)m->trie_cap * sizeof(uint64_t));
+    if (!m->trie_out || !m->trie_depth || !m->trie_edge) return 0;
+    memset(m->trie_edge, 0xFF, (size_t)m->trie_cap * sizeof(uint64_t));
+    m->trie_out[0] = -1;
+    m->trie_depth[0] = 0;
+    m->trie_nodes = 1;
+    for (size_t k = 0; k < n_lines; ++k) {
+        uint32_t node = 0;
+        for (uint32_t i = 0; i < lines[k].len; ++i) {
+            uint32_t child = hut_model_trie_child(m, node, lines[k].bytes[i]);
+            if (!child) {
+                child = m->trie_nodes++;
+                m->trie_out[child] = -1;
+                m->trie_depth[child] = (uint8_t)(i + 1);
+                const uint32_t key = (node << 8) | lines[k].bytes[i], mask = m->trie_cap - 1;
+                uint32_t h = hut_trie_hash(key, mask);
+                while (m->trie_edge[h] != HUT_TRIE_EMPTY) h = (h + 1) & mask;
+                m->trie_edge[h] = ((uint64_t)key << 32) | child;
+                if (node == 0) m->trie_root_child[lines[k].bytes[i]] = child;
+            }
+            node = child;
+        }
+        if (node) m->trie_out[node] = (int16_t)lines[k].byte;
+    }
+    if (plen) {
+        m->prefix_bytes = malloc(plen);
+        if (!m->prefix_bytes) return 0;
+        memcpy(m->prefix_bytes, prefix, plen);
+        m->prefix_len = (uint32_t)plen;
+    }
+    return 1;
 }
 
 /* ------------------------------------------------------------------------------------------------
@@ -830,6 +947,13 @@ void hut_model_free(hut_model* m) {
     free(m->char_tab);
     free(m->prefix_syms);
     free(m->prefix_alone_ids);
+    free(m->dec_off);
+    free(m->dec_len);
+    free(m->dec_pool);
+    free(m->trie_edge);
+    free(m->trie_out);
+    free(m->trie_depth);
+    free(m->prefix_bytes);
     free(m);
 }
 
@@ -844,6 +968,8 @@ int hut_model_load(hut_model** out, const char* vocab_path, const char* special_
     memset(&b, 0, sizeof b);
     uint32_t* order = NULL;
     uint8_t(*expansion)[2] = NULL;
+    special_line* sp_lines = NULL;
+    size_t n_sp_lines = 0;
     if (!m || !strtab_init(&vocab)) {
         free(m);
         return fail(msg, msglen, HUT_ERR_MEMORY, "out of memory");
@@ -855,7 +981,7 @@ int hut_model_load(hut_model** out, const char* vocab_path, const char* special_
         goto out;
     }
     if ((rc = load_vocab(vocab_path, &vocab, &m->vocab_lines, msg, msglen)) != HUT_OK) goto out;
-    if ((rc = load_special(special_path, special, special_len, msg, msglen)) != HUT_OK) goto out;
+    if ((rc = load_special(special_path, special, special_len, &sp_lines, &n_sp_lines, msg, msglen)) != HUT_OK) goto out;
     if (vocab.n > HUT_MAX_UNITS / 2) {
         rc = fail(msg, msglen, HUT_ERR_UNSUPPORTED, "vocabulary too large for 21-bit unit ids");
         goto out;
@@ -1104,6 +1230,12 @@ int hut_model_load(hut_model** out, const char* vocab_path, const char* special_
     }
     free(pfx_alone);
 
+    /* ---- decode tables ---- */
+    if (!build_decode_tables(m, &vocab, sp_lines, n_sp_lines, prefix, plen)) {
+        rc = fail(msg, msglen, HUT_ERR_MEMORY, "out of memory");
+        goto out;
+    }
+
     /* ---- optional merges file: switch the tables to the id-keyed path ---- */
     if (merges_path) {
         merge_rule* rules = NULL;
@@ -1121,6 +1253,7 @@ int hut_model_load(hut_model** out, const char* vocab_path, const char* special_
     b.units.len = NULL;
 
 out:
+    free(sp_lines);
     for (int c = 0; c < 256; ++c) free(special[c]);
     free(expansion);
     free(order);

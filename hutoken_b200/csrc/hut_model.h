@@ -22,6 +22,8 @@ extern "C" {
 #define HUT_MAX_UNITS (HUT_UNIT_MASK - 2u) /* top ids reserved: INERT */
 #define HUT_PAIR_EMPTY 0xFFFFFFFFFFFFFFFFull
 #define HUT_CHAR_EMPTY 0xFFFFFFFFFFFFFFFFull
+#define HUT_TRIE_EMPTY 0xFFFFFFFFFFFFFFFFull
+#define HUT_DEC_MISSING 0xFFFFFFFFu
 
 /* error classes -> Python exception types at the CPython boundary (lib.c error conventions) */
 enum {
@@ -78,6 +80,25 @@ typedef struct hut_model {
 
     uint32_t max_unit_len;
 
+    /* ---- decode side (core.c:513-581, pretokenizer.c:197-296, ac.c:27-50) ------------------------------
+     * dec_off/dec_pool: bytes of the token printed for each id in [0, vocab_lines); dec_off[i] == HUT_DEC_MISSING
+     *   marks an id no vocab line carries (the reference reads an uninitialised pointer there; we refuse it).
+     * trie of the special-chars replacement strings, one node per distinct prefix, root = 0:
+     *   trie_edge: open addressing, slot = (node << 8 | byte) << 32 | child, empty = all ones;
+     *   trie_out[node] = byte the replacement stands for, or -1;  depth of a node = pattern length.          */
+    uint32_t* dec_off;  /* [vocab_lines + 1] */
+    uint32_t* dec_len;  /* [vocab_lines]; HUT_DEC_MISSING if absent */
+    uint8_t* dec_pool;
+    uint32_t dec_pool_len;
+    uint64_t* trie_edge;
+    uint32_t trie_cap; /* power of two */
+    int16_t* trie_out;
+    uint8_t* trie_depth;
+    uint32_t trie_nodes;
+    uint32_t trie_root_child[256]; /* child of the root per byte, 0 = none */
+    uint8_t* prefix_bytes; /* raw prefix string (decode strips it once at the start, pretokenizer.c:209-215) */
+    uint32_t prefix_len;
+
     /* ---- merges-file mode (core.c:211-337): units are ids, see apply_merges() in hut_model.c ---- */
     int merges_mode;
     uint32_t n_merge_rules;
@@ -111,6 +132,12 @@ static inline uint32_t hut_pair_hash(uint32_t l, uint32_t r, uint32_t mask) {
 /* host-side lookups (used by the builder itself and by tests/host_harness.c) */
 uint32_t hut_model_pair_lookup(const hut_model* m, uint32_t l, uint32_t r); /* unit or HUT_UNIT_MASK if none */
 uint32_t hut_model_char_lookup(const hut_model* m, const uint8_t* p, uint32_t len);
+uint32_t hut_model_trie_child(const hut_model* m, uint32_t node, uint8_t byte); /* 0 if none */
+
+#ifdef __CUDACC__
+__host__ __device__
+#endif
+static inline uint32_t hut_trie_hash(uint32_t key, uint32_t mask) { return (key * 0x9E3779B1u >> 7) & mask; }
 
 #ifdef __cplusplus
 }

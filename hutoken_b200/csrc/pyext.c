@@ -232,14 +232,128 @@ static PyObject* p_batch_encode_packed(PyObject* self, PyObject* args) {
     return out;
 }
 
+/* ---- decode side ------------------------------------------------------------------------------------------ */
+static int32_t* g_dec_ids = NULL;
+static uint64_t* g_dec_offs = NULL;
+static size_t g_dec_ids_cap = 0, g_dec_offs_cap = 0;
+
+static int ensure_dec(size_t n_ids, size_t n_docs) {
+    if (n_ids + 1 > g_dec_ids_cap) {
+        size_t cap = (n_ids + 1) * 2;
+        int32_t* p = realloc(g_dec_ids, cap * sizeof *p);
+        if (!p) return 0;
+        g_dec_ids = p;
+        g_dec_ids_cap = cap;
+    }
+    if (n_docs + 2 > g_dec_offs_cap) {
+        size_t cap = (n_docs + 2) * 2;
+        uint64_t* p = realloc(g_dec_offs, cap * sizeof *p);
+        if (!p) return 0;
+        g_dec_offs = p;
+        g_dec_offs_cap = cap;
+    }
+    return 1;
+}
+
+/* (int)PyLong_AsLong(item) as lib.c:923,1015: a non-integer item leaves an exception set, which we surface */
+static int list_to_ids(PyObject* list, int32_t* out) {
+    Py_ssize_t n = PyList_GET_SIZE(list);
+    for (Py_ssize_t i = 0; i < n; ++i) {
+        long v = PyLong_AsLong(PyList_GET_ITEM(list, i));
+        if (v == -1 && PyErr_Occurred()) return 0;
+        out[i] = (v < INT32_MIN || v > INT32_MAX) ? -1 : (int32_t)v; /* out of range either way (core.c:522) */
+    }
+    return 1;
+}
+
+/* PyUnicode_FromString (lib.c:946,1066): the C string ends at the first 0x00 */
+static PyObject* text_to_str(const uint8_t* p, uint64_t n) {
+    const void* z = memchr(p, 0, (size_t)n);
+    return PyUnicode_DecodeUTF8((const char*)p, z ? (Py_ssize_t)((const uint8_t*)z - p) : (Py_ssize_t)n, NULL);
+}
+
+/* decode(tokens) -- lib.c:876-955, format "O" */
 static PyObject* p_decode(PyObject* self, PyObject* args) {
     if (!g_ctx) {
         PyErr_SetString(PyExc_RuntimeError, NOT_INIT_DEC);
         return NULL;
     }
-    PyErr_SetString(PyExc_RuntimeError,
-                    "decode is outside the B200 encode engine's scope (SURVEY.md 8(f) N1: next row)");
-    return NULL;
+    PyObject* tokens = NULL;
+    if (!PyArg_ParseTuple(args, "O", &tokens)) {
+        PyErr_SetString(PyExc_TypeError, "Failed to parse arguments. Expected a single list of tokens.");
+        return NULL;
+    }
+    if (!PyList_Check(tokens)) {
+        PyErr_SetString(PyExc_TypeError, "Argument must be a list of integers");
+        return NULL;
+    }
+    Py_ssize_t n = PyList_GET_SIZE(tokens);
+    if (!ensure_dec((size_t)n, 1)) return PyErr_NoMemory();
+    if (!list_to_ids(tokens, g_dec_ids)) return NULL;
+    g_dec_offs[0] = 0;
+    g_dec_offs[1] = (uint64_t)n;
+    hut_text_result res;
+    int rc;
+    Py_BEGIN_ALLOW_THREADS
+    rc = hut_decode_batch(g_ctx, g_dec_ids, g_dec_offs, 1, &res);
+    Py_END_ALLOW_THREADS
+    if (rc != HUT_STATUS_OK) return raise_status(rc, hut_last_error(g_ctx));
+    return text_to_str(res.text, res.n_bytes);
+}
+
+/* batch_decode(tokens, num_threads=1) -- lib.c:957-1085, format "O|i"; num_threads is accepted and unused */
+static PyObject* p_batch_decode(PyObject* self, PyObject* args) {
+    if (!g_ctx) {
+        PyErr_SetString(PyExc_RuntimeError, NOT_INIT_DEC);
+        return NULL;
+    }
+    PyObject* tokens = NULL;
+    int num_threads = 1;
+    if (!PyArg_ParseTuple(args, "O|i", &tokens, &num_threads)) {
+        PyErr_SetString(PyExc_TypeError, "Failed to parse arguments. Expected a single list of tokens.");
+        return NULL;
+    }
+    Py_ssize_t nd = PyList_Check(tokens) ? PyList_GET_SIZE(tokens) : -1;
+    if (nd <= 0) { /* PyList_Size of a non-list is -1 in the reference too (lib.c:979-983) */
+        PyErr_Clear();
+        PyErr_SetString(PyExc_ValueError, "No tokens provided.");
+        return NULL;
+    }
+    size_t total = 0;
+    for (Py_ssize_t i = 0; i < nd; ++i) {
+        PyObject* item = PyList_GET_ITEM(tokens, i);
+        if (!PyList_Check(item)) {
+            PyErr_SetString(PyExc_TypeError, "Each item must be a list of integers.");
+            return NULL;
+        }
+        total += (size_t)PyList_GET_SIZE(item);
+    }
+    if (!ensure_dec(total, (size_t)nd)) return PyErr_NoMemory();
+    size_t at = 0;
+    for (Py_ssize_t i = 0; i < nd; ++i) {
+        PyObject* item = PyList_GET_ITEM(tokens, i);
+        g_dec_offs[i] = at;
+        if (!list_to_ids(item, g_dec_ids + at)) return NULL;
+        at += (size_t)PyList_GET_SIZE(item);
+    }
+    g_dec_offs[nd] = at;
+    hut_text_result res;
+    int rc;
+    Py_BEGIN_ALLOW_THREADS
+    rc = hut_decode_batch(g_ctx, g_dec_ids, g_dec_offs, (uint64_t)nd, &res);
+    Py_END_ALLOW_THREADS
+    if (rc != HUT_STATUS_OK) return raise_status(rc, hut_last_error(g_ctx));
+    PyObject* result = PyList_New(nd);
+    if (!result) return PyErr_NoMemory();
+    for (Py_ssize_t i = 0; i < nd; ++i) {
+        PyObject* str = text_to_str(res.text + res.text_offsets[i], res.text_offsets[i + 1] - res.text_offsets[i]);
+        if (!str) {
+            Py_DECREF(result);
+            return NULL;
+        }
+        PyList_SET_ITEM(result, i, str);
+    }
+    return result;
 }
 
 static PyObject* p_out_of_scope(PyObject* self, PyObject* args) {
@@ -255,7 +369,7 @@ static PyMethodDef methods[] = {
     {"batch_encode", p_batch_encode, METH_VARARGS, "Encodes list of strings"},
     {"batch_encode_packed", p_batch_encode_packed, METH_VARARGS, "Encodes packed documents into packed ids"},
     {"decode", p_decode, METH_VARARGS, "Decodes list of ints"},
-    {"batch_decode", p_decode, METH_VARARGS, "Decodes list of lists of ints"},
+    {"batch_decode", p_batch_decode, METH_VARARGS, "Decodes list of lists of ints"},
     {NULL, NULL, 0, NULL}};
 
 static struct PyModuleDef moduledef = {PyModuleDef_HEAD_INIT, "huToken", "B200-native hutoken encode engine", -1,

@@ -94,6 +94,33 @@ int hut_encode_device(hut_ctx* ctx, int dev_index, const uint8_t* d_bytes, uint6
                       const uint64_t* d_doc_offsets, uint64_t n_docs, int32_t* d_ids, uint64_t ids_capacity,
                       uint64_t* d_tok_offsets, uint64_t* n_ids_out, void* stream);
 
+/* ---- decode (core.c:513-581 decode(), pretokenizer.c:197-296 pretokenizer_decode; p_decode / p_batch_decode,
+ * lib.c:876-1085) ------------------------------------------------------------------------------------------- */
+typedef struct hut_text_result {
+    const uint8_t* text;          /* decoded bytes of all documents, packed; NUL-terminated after n_bytes */
+    const uint64_t* text_offsets; /* n_docs + 1: document d is text[text_offsets[d] .. text_offsets[d+1]) */
+    uint64_t n_bytes;
+    uint64_t n_docs;
+} hut_text_result;
+
+/* Host buffers: ids of document d are ids[tok_offsets[d] .. tok_offsets[d+1]) (the layout hut_encode_batch returns).
+ * An id < 0, >= hut_vocab_lines() or carried by no vocab line fails the whole call with HUT_STATUS_VALUE and the
+ * reference's message "Element must be non-negative and less than vocab size." (core.c:522-530).  The text may
+ * contain 0x00 bytes (a replacement standing for byte 0); the reference's binding cuts each string there
+ * (PyUnicode_FromString, lib.c:946,1066) and so does ours.  The result lives in pinned host memory owned by the
+ * context until the next decode call.  Runs on the context's first device. */
+int hut_decode_batch(hut_ctx* ctx, const int32_t* ids, const uint64_t* tok_offsets, uint64_t n_docs,
+                     hut_text_result* result);
+
+/* Same with ids / offsets resident on the context's first device; the outputs are device pointers owned by the
+ * context (valid until the next decode call).  d_tok_offsets must start at 0.  stream: cudaStream_t or NULL. */
+int hut_decode_device(hut_ctx* ctx, const int32_t* d_ids, uint64_t n_ids, const uint64_t* d_tok_offsets,
+                      uint64_t n_docs, const uint8_t** d_text_out, const uint64_t** d_text_offsets_out,
+                      uint64_t* n_bytes_out, void* stream);
+
+/* device time (CUDA events on the launch stream) and kernel count of the last decode call */
+int hut_decode_stats(const hut_ctx* ctx, double* kernel_ms, uint64_t* kernel_launches);
+
 /* Drops the unique-pretoken cache of every device (it otherwise persists across calls). */
 int hut_cache_reset(hut_ctx* ctx);
 

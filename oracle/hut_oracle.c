@@ -25,6 +25,7 @@ typedef struct {
     uint8_t* key; /* malloc'd, not NUL-terminated */
     uint32_t len;
     int32_t value;
+    uint32_t seq; /* order of first insertion (decode: among keys sharing an id the one stated last wins) */
 } omap_slot;
 
 typedef struct {
@@ -100,6 +101,7 @@ static int omap_set(omap* m, const uint8_t* key, size_t len, int32_t value) {
     memcpy(s->key, key, len);
     s->len = (uint32_t)len;
     s->value = value;
+    s->seq = (uint32_t)m->count;
     m->count++;
     if (len > m->max_key_len) m->max_key_len = (uint32_t)len;
     return 1;
@@ -117,6 +119,13 @@ struct orule {
     int used;
 };
 
+/* struct ACNode (ac.h): children by byte, output_value = the byte the pattern stands for or -1 */
+struct otrie {
+    int32_t child[256];
+    int out;
+    uint32_t depth;
+};
+
 /* ------------------------------------------------------------------------------------------------ */
 struct hut_oracle {
     omap vocab;
@@ -127,6 +136,10 @@ struct hut_oracle {
     uint32_t prefix_len;
     int is_byte_encoder;
     int limit_mode;
+    /* decode side: vocab_decode[] (lib.c:423-433) and the special-chars trie (ac.c:27-50, lib.c:555-556) */
+    const omap_slot** dec; /* [vocab_lines], NULL = no line carries the id */
+    struct otrie* trie;
+    size_t trie_n, trie_cap;
     /* merges-file mode (lib.c:573-663): (left_id, right_id) -> rule; NULL map = string path */
     struct orule* rules;
     size_t rules_cap; /* power of two; 0 = merges_map is NULL */
@@ -249,6 +262,35 @@ static int load_vocab(hut_oracle* o, const char* path, char* err, size_t errlen)
  * 0..256 accepted by the reference (lib.c:516; 256 overflows its arrays -- we reject it), the LAST
  * character of the value is always dropped as the presumed newline (lib.c:528-531), an empty value
  * is an error (lib.c:533-543). */
+/* ac_automaton_add_string (ac.c:27-50): a repeated pattern keeps the later output value */
+static int32_t trie_new(hut_oracle* o, uint32_t depth) {
+    if (o->trie_n == o->trie_cap) {
+        o->trie_cap = o->trie_cap ? o->trie_cap * 2 : 64;
+        o->trie = realloc(o->trie, o->trie_cap * sizeof *o->trie);
+    }
+    struct otrie* t = &o->trie[o->trie_n];
+    memset(t->child, 0, sizeof t->child);
+    t->out = -1;
+    t->depth = depth;
+    return (int32_t)o->trie_n++;
+}
+
+static void trie_add(hut_oracle* o, const uint8_t* pat, size_t len, int value) {
+    if (!o->trie_n) trie_new(o, 0);
+    int32_t cur = 0;
+    for (size_t i = 0; i < len; ++i) {
+        if (!o->trie[cur].child[pat[i]]) {
+            int32_t c = trie_new(o, (uint32_t)i + 1);
+            o->trie[cur].child[pat[i]] = c;
+        }
+        cur = o->trie[cur].child[pat[i]];
+    }
+    if (cur) {
+        o->trie[cur].out = value;
+        o->trie[cur].depth = (uint32_t)len;
+    }
+}
+
 static int load_special(hut_oracle* o, const char* path, char* err, size_t errlen) {
     FILE* f = fopen(path, "r");
     if (!f) {
@@ -290,6 +332,7 @@ static int load_special(hut_oracle* o, const char* path, char* err, size_t errle
         o->special[index] = malloc(keep);
         memcpy(o->special[index], vs, keep);
         o->special_len[index] = (uint32_t)keep;
+        trie_add(o, (const uint8_t*)vs, strnlen(vs, keep), (int)index); /* lib.c:555: the value as a C string */
     }
     fclose(f);
     return ok;
@@ -395,6 +438,8 @@ void hut_oracle_free(hut_oracle* o) {
     for (int i = 0; i < 256; ++i) free(o->special[i]);
     free(o->prefix);
     free(o->rules);
+    free(o->dec);
+    free(o->trie);
     free(o);
 }
 
@@ -824,3 +869,80 @@ int hut_oracle_encode_batch(const hut_oracle* o, const uint8_t* bytes, const uin
 }
 
 void hut_oracle_get_stats(hut_oracle_stats* out) { *out = g_stats; }
+/* ------------------------------------------------------------------------------------------------
+ * decode() (core.c:513-581) + pretokenizer_decode (pretokenizer.c:197-296).
+ * Returns 0 and the malloc'd text (*len bytes, may contain 0x00; the reference's binding cuts there), or -1 for an
+ * id outside [0, vocab_lines) or carried by no line (core.c:522-530; the second case is an uninitialised pointer in
+ * the reference).  Bytes the reference would read past the end of the raw text (a truncated UTF-8 character at its
+ * very end) count as 0 / are not copied.
+ * ---------------------------------------------------------------------------------------------- */
+static void build_dec(hut_oracle* o) {
+    o->dec = calloc(o->vocab_lines ? o->vocab_lines : 1, sizeof *o->dec);
+    for (size_t i = 0; i < o->vocab.cap; ++i) {
+        const omap_slot* s = &o->vocab.slots[i];
+        if (!s->key || s->value < 0 || (size_t)s->value >= o->vocab_lines) continue;
+        if (!o->dec[s->value] || o->dec[s->value]->seq < s->seq) o->dec[s->value] = s;
+    }
+}
+
+int hut_oracle_decode(hut_oracle* o, const int32_t* ids, size_t n, uint8_t** text, size_t* len) {
+    if (!o->dec) build_dec(o);
+    size_t total = 0;
+    for (size_t i = 0; i < n; ++i) {
+        if (ids[i] < 0 || (size_t)ids[i] >= o->vocab_lines || !o->dec[ids[i]]) return -1;
+        total += o->dec[ids[i]]->len;
+    }
+    uint8_t* raw = calloc(total + 8, 1);
+    size_t at = 0;
+    for (size_t i = 0; i < n; ++i) {
+        memcpy(raw + at, o->dec[ids[i]]->key, o->dec[ids[i]]->len);
+        at += o->dec[ids[i]]->len;
+    }
+    uint8_t* out = malloc(total + 8);
+    size_t p = 0, w = 0;
+    if (o->prefix && total >= o->prefix_len && memcmp(raw, o->prefix, o->prefix_len) == 0) p = o->prefix_len;
+    while (p < total) {
+        int best = -1;
+        size_t best_len = 0;
+        int32_t cur = 0;
+        for (size_t q = p; q < total && o->trie_n; ++q) { /* pretokenizer.c:224-240 / 262-278 */
+            int32_t c = o->trie[cur].child[raw[q]];
+            if (!c) break;
+            cur = c;
+            if (o->trie[cur].out != -1) {
+                best = o->trie[cur].out;
+                best_len = o->trie[cur].depth;
+            }
+        }
+        if (best >= 0) {
+            out[w++] = (uint8_t)best;
+            p += best_len;
+            continue;
+        }
+        const uint8_t* c = raw + p;
+        size_t cl = (size_t)lead_len(c[0]);
+        if (o->is_byte_encoder) { /* utf8_to_codepoint, pretokenizer.c:176-195,243-255 */
+            uint32_t cp;
+            if (c[0] < 0x80) cp = c[0];
+            else if ((c[0] & 0xE0) == 0xC0) cp = ((c[0] & 0x1Fu) << 6) | (c[1] & 0x3Fu);
+            else if ((c[0] & 0xF0) == 0xE0) cp = ((c[0] & 0x0Fu) << 12) | ((c[1] & 0x3Fu) << 6) | (c[2] & 0x3Fu);
+            else if ((c[0] & 0xF8) == 0xF0)
+                cp = ((c[0] & 0x07u) << 18) | ((c[1] & 0x3Fu) << 12) | ((c[2] & 0x3Fu) << 6) | (c[3] & 0x3Fu);
+            else cp = 0xFFFD;
+            out[w++] = cp < 256 ? (uint8_t)cp : (uint8_t)'?';
+        } else { /* pretokenizer.c:283-287 */
+            size_t k = cl < total - p ? cl : total - p;
+            memcpy(out + w, c, k);
+            w += k;
+        }
+        p += cl;
+    }
+    free(raw);
+    out[w] = 0;
+    *text = out;
+    *len = w;
+    return 0;
+}
+
+void hut_oracle_free_text(uint8_t* t) { free(t); }
+

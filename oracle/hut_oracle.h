@@ -47,6 +47,12 @@ void hut_oracle_free_ids(int32_t* ids);
 int hut_oracle_encode_batch(const hut_oracle* o, const uint8_t* bytes, const uint64_t* offs, uint64_t ndocs,
                             int32_t** ids, uint64_t* tok_offs);
 
+/* decode() (core.c:513-581) + pretokenizer_decode (pretokenizer.c:197-296): ids -> bytes.  Returns 0, or -1 for an
+ * id that cannot be decoded ("Element must be non-negative and less than vocab size.").  *text is malloc'd
+ * (hut_oracle_free_text), NUL-terminated after *len bytes and may contain 0x00 inside. */
+int hut_oracle_decode(hut_oracle* o, const int32_t* ids, size_t n, uint8_t** text, size_t* len);
+void hut_oracle_free_text(uint8_t* t);
+
 /* parser_next_token (parser.c:24-88): length in bytes of the pretoken starting at text[pos]; 0 at end. */
 size_t hut_oracle_next_pretoken(const uint8_t* text, size_t len, size_t pos);
 

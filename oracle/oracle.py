@@ -60,6 +60,9 @@ def _load():
     lib.hut_oracle_vocab_lookup.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t]
     lib.hut_oracle_vocab_lines.restype = C.c_size_t
     lib.hut_oracle_vocab_lines.argtypes = [C.c_void_p]
+    lib.hut_oracle_decode.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.POINTER(C.c_uint8)),
+                                      C.POINTER(C.c_size_t)]
+    lib.hut_oracle_free_text.argtypes = [C.POINTER(C.c_uint8)]
     lib.hut_oracle_load_merges.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_size_t]
     lib.hut_oracle_merge_rules.restype = C.c_size_t
     lib.hut_oracle_merge_rules.argtypes = [C.c_void_p]
@@ -130,6 +133,21 @@ class Oracle:
         data = np.frombuffer(b"".join(datas) + b"\0", dtype=np.uint8)
         ids, tok = self.encode_packed(data, offs)
         return [ids[int(tok[i]):int(tok[i + 1])].tolist() for i in range(len(datas))]
+
+    def decode_bytes(self, ids) -> bytes:
+        """decode() + pretokenizer_decode: the raw bytes (the reference's binding then cuts at the first 0x00)."""
+        arr = np.ascontiguousarray(ids, dtype=np.int32)
+        text = C.POINTER(C.c_uint8)()
+        n = C.c_size_t()
+        if self._lib.hut_oracle_decode(self._h, arr.ctypes.data, len(arr), C.byref(text), C.byref(n)) != 0:
+            raise ValueError("Element must be non-negative and less than vocab size.")
+        out = bytes(C.cast(text, C.POINTER(C.c_uint8 * n.value)).contents) if n.value else b""
+        self._lib.hut_oracle_free_text(text)
+        return out
+
+    def decode(self, ids) -> str:
+        """What hutoken.decode returns: PyUnicode_FromString of the C string (lib.c:946)."""
+        return self.decode_bytes(ids).split(b"\0", 1)[0].decode("utf-8")
 
     def stats(self) -> dict:
         s = _Stats()

@@ -29,6 +29,8 @@ def lib():
         L.harness_free.argtypes = [C.c_void_p]
         L.harness_encode.restype = C.c_size_t
         L.harness_encode.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t, C.c_void_p, C.c_size_t]
+        L.harness_decode.restype = C.c_size_t
+        L.harness_decode.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
         L.harness_pretokens.restype = C.c_size_t
         L.harness_pretokens.argtypes = [C.c_char_p, C.c_size_t, C.c_void_p, C.c_size_t]
         L.harness_info.argtypes = [C.c_void_p, C.c_void_p]
@@ -61,6 +63,18 @@ class HostModel:
         n = lib().harness_encode(self._h, data, len(data), out.ctypes.data, cap)
         assert n <= cap
         return out[:n].tolist()
+
+    def decode_bytes(self, ids):
+        arr = np.ascontiguousarray(ids, dtype=np.int32)
+        cap = 64 * len(arr) + 64
+        out = np.empty(cap, dtype=np.uint8)
+        n = lib().harness_decode(self._h, arr.ctypes.data, len(arr), out.ctypes.data, cap)
+        if n == C.c_size_t(-1).value:
+            raise ValueError("Element must be non-negative and less than vocab size.")
+        if n > cap:
+            out = np.empty(n, dtype=np.uint8)
+            n = lib().harness_decode(self._h, arr.ctypes.data, len(arr), out.ctypes.data, n)
+        return out[:n].tobytes()
 
     def info(self):
         out = np.zeros(8, dtype=np.uint32)

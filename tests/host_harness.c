@@ -124,6 +124,58 @@ hut_model* harness_load(const char* vocab, const char* special, const char* pref
 
 void harness_free(hut_model* m) { hut_model_free(m); }
 
+/* table-driven decode of one id list with the decode tables the device reads (dec_off / dec_len / dec_pool, trie
+ * edges / outputs / depths, prefix): returns the byte count, or (size_t)-1 for an undecodable id */
+size_t harness_decode(const hut_model* m, const int32_t* ids, size_t n, uint8_t* out, size_t cap) {
+    size_t total = 0;
+    for (size_t i = 0; i < n; ++i) {
+        if (ids[i] < 0 || (uint32_t)ids[i] >= m->vocab_lines || m->dec_len[ids[i]] == HUT_DEC_MISSING) return (size_t)-1;
+        total += m->dec_len[ids[i]];
+    }
+    uint8_t* raw = calloc(total + 8, 1);
+    size_t at = 0;
+    for (size_t i = 0; i < n; ++i) {
+        memcpy(raw + at, m->dec_pool + m->dec_off[ids[i]], m->dec_len[ids[i]]);
+        at += m->dec_len[ids[i]];
+    }
+    size_t p = 0, w = 0;
+    if (m->prefix_len && total >= m->prefix_len && memcmp(raw, m->prefix_bytes, m->prefix_len) == 0) p = m->prefix_len;
+    while (p < total) {
+        uint32_t node = m->trie_root_child[raw[p]], step = 0, outb = 0;
+        size_t q = p + 1;
+        while (node) {
+            if (m->trie_out[node] >= 0) {
+                step = m->trie_depth[node];
+                outb = (uint32_t)m->trie_out[node];
+            }
+            if (q >= total) break;
+            node = hut_model_trie_child(m, node, raw[q++]);
+        }
+        if (step) {
+            if (w < cap) out[w] = (uint8_t)outb;
+            w++;
+            p += step;
+            continue;
+        }
+        const uint8_t* c = raw + p;
+        uint32_t cl = (c[0] & 0x80) == 0 ? 1 : (c[0] & 0xE0) == 0xC0 ? 2 : (c[0] & 0xF0) == 0xE0 ? 3 : (c[0] & 0xF8) == 0xF0 ? 4 : 1;
+        if (m->is_byte_encoder) {
+            uint32_t cp = cl == 1 ? ((c[0] & 0x80) ? 0xFFFD : c[0])
+                          : cl == 2 ? ((c[0] & 0x1Fu) << 6) | (c[1] & 0x3Fu)
+                          : cl == 3 ? ((c[0] & 0x0Fu) << 12) | ((c[1] & 0x3Fu) << 6) | (c[2] & 0x3Fu)
+                                    : ((c[0] & 0x07u) << 18) | ((c[1] & 0x3Fu) << 12) | ((c[2] & 0x3Fu) << 6) | (c[3] & 0x3Fu);
+            if (w < cap) out[w] = cp < 256 ? (uint8_t)cp : (uint8_t)'?';
+            w++;
+        } else {
+            for (uint32_t k = 0; k < cl && p + k < total; ++k, ++w)
+                if (w < cap) out[w] = c[k];
+        }
+        p += cl;
+    }
+    free(raw);
+    return w;
+}
+
 void harness_info(const hut_model* m, uint32_t* out) {
     out[0] = m->n_vocab;
     out[1] = m->n_units;

@@ -8,6 +8,7 @@ engine -- to the reference's behaviour (the reference ships no g
 Fixtures:
   encode_<model>.json   {"model", "kwargs", "cases": [{"text_hex", "ids"}]}   ids = _hutoken.encode / batch_encode
   encode_merges_<model>.json   the same with merges_file_path= (id-keyed merge path), small models only
+  decode_<model>.json   {"cases": [{"ids", "text_hex"} | {"ids", "error", "message"}]}   _hutoken.decode / batch_decode
   pretokens.json        {"cases": [{"text_hex", "lengths"}]}                   parser_next_token (parser.c:24-88)
 
 Input strings: the 28 parser cases of the reference's tests/test_parser.c:77-108, the sentences / paragraphs of
@@ -99,6 +100,30 @@ def encode_golden(ref, name, merges=None):
     return out
 
 
+def decode_golden(ref, name):
+    """_hutoken.decode / batch_decode (lib.c:876-1085) on ids the reference itself produced, on random valid ids
+    (byte-level pieces that do not form UTF-8 raise UnicodeDecodeError in PyUnicode_FromString) and on bad ids."""
+    v, s = synth.PATHS[name]
+    kw = synth.MODEL_KW[name]
+    ref.initialize(v, s, kw["prefix"], kw["is_byte_encoder"])
+    texts = PARSER_CASES + SENTENCES + PROBES[:-2] + fuzz_texts(79, 60) + synthetic_docs(13, 32 << 10, 200)[:8]
+    n_lines = sum(1 for _ in open(v, "rb"))
+    rng = random.Random(17)
+    id_lists = [[i for i in ref.encode(t) if i >= 0] for t in texts]
+    id_lists += [[rng.randrange(n_lines) for _ in range(rng.randint(1, 30))] for _ in range(60)]
+    id_lists += [[], [0], [n_lines - 1], [n_lines], [-1], [5, n_lines + 7, 3]]
+    cases = []
+    for ids in id_lists:
+        try:
+            cases.append({"ids": ids, "text_hex": _hex(ref.decode(ids))})
+        except Exception as e:  # ValueError (bad id) or UnicodeDecodeError
+            cases.append({"ids": ids, "error": type(e).__name__, "message": str(e)[:80]})
+    ok = [c["ids"] for c in cases if "text_hex" in c and c["ids"]]
+    for nt in (1, 4):
+        assert [_hex(t) for t in ref.batch_decode(ok, nt)] == [c["text_hex"] for c in cases if "text_hex" in c and c["ids"]]
+    return {"model": name, "kwargs": kw, "vocab_lines": n_lines, "cases": cases}
+
+
 class _Slice(C.Structure):
     _fields_ = [("start", C.c_void_p), ("length", C.c_size_t)]
 
@@ -151,6 +176,11 @@ def main():
         with open(os.path.join(GOLDEN, f"encode_merges_{name}.json"), "w") as f:
             json.dump(g, f, separators=(",", ":"))
         print(name, "merges:", len(g["cases"]), "cases,", sum(len(c["ids"]) for c in g["cases"]), "ids")
+    for name in ("gpt2_small", "llama_small", "gpt2", "llama"):
+        g = decode_golden(ref, name)
+        with open(os.path.join(GOLDEN, f"decode_{name}.json"), "w") as f:
+            json.dump(g, f, separators=(",", ":"))
+        print(name, "decode:", len(g["cases"]), "cases,", sum("error" in c for c in g["cases"]), "errors")
     p = pretoken_golden()
     with open(os.path.join(GOLDEN, "pretokens.json"), "w") as f:
         json.dump(p, f, separators=(",", ":"))
