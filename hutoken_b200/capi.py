@@ -54,7 +54,7 @@ class Stats(C.Structure):
 
 EXPORTS = ["hut_create", "hut_destroy", "hut_last_error", "hut_encode_batch", "hut_encode_device",
            "hut_cache_reset", "hut_host_alloc", "hut_host_free", "hut_get_stats", "hut_vocab_lines",
-           "hut_device_count", "hut_plan_shards"]
+           "hut_device_count", "hut_plan_shards", "hut_decode_batch", "hut_decode_device", "hut_decode_stats"]
 
 _lib = None
 
