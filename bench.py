@@ -50,6 +50,7 @@ def parse_args():
     ap.add_argument("--chunk-mb", type=int, default=0, help="hut_options.chunk_mb of the e2e leg (0 = library default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-decode", action="store_true", help="skip the decode leg (ids -> text on the device)")
     ap.add_argument("--check", action="store_true", help="also verify a sample of the output against the oracle")
     return ap.parse_args()
 
@@ -267,6 +268,18 @@ def pinned_u8(capi_lib, n):
     return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(n,))
 
 
+class _DevView:
+    """A device buffer owned by the engine, exposed to torch through __cuda_array_interface__ (no copy)."""
+
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+def _device_equal(torch, ptr, d_text, n, dev):
+    got = torch.as_tensor(_DevView(ptr, n), device=dev)
+    return bool(torch.equal(got, d_text[:n]))
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -349,6 +362,33 @@ def run_ours(args):
         barrier()
         e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
 
+    # ---- decode leg: the ids just produced, resident on the device, back to text ----
+    dec = None
+    if not args.no_decode:
+        try:
+            n_text = 0
+            for _ in range(2):
+                _, _, n_text = eng.decode_device(d_ids.data_ptr(), n_ids, d_tok.data_ptr(), ndocs, stream=sh)
+            d0, d1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            dsteps = max(1, min(args.steps, 5))
+            torch.cuda.synchronize(dev)
+            d0.record(stream)
+            for _ in range(dsteps):
+                t_ptr, _, n_text = eng.decode_device(d_ids.data_ptr(), n_ids, d_tok.data_ptr(), ndocs, stream=sh)
+            d1.record(stream)
+            torch.cuda.synchronize(dev)
+            dms = d0.elapsed_time(d1) / dsteps
+            dst = eng.decode_stats()
+            # round trip: byte mode with a complete byte alphabet decodes back to the input exactly
+            same = None
+            if n_text == nbytes:
+                same = _device_equal(torch, t_ptr, d_text, nbytes, dev)
+            dec = {"value": n_text / (dms * 1e-3) / 1e6, "unit": "decoded MB/s (ids resident in HBM)", "ms_per_step": dms,
+                   "kernel_ms": dst["kernel_ms"], "gpu_launches_per_step": int(dst["kernel_launches"]),
+                   "text_bytes": int(n_text), "round_trip_equals_input": same}
+        except ValueError as e:  # ids the vocabulary cannot print (-1): nothing to decode
+            dec = {"value": None, "note": str(e)}
+
     # ---- max over ranks / whole-job sums (hutoken_b200/dist.py; covered on CPU by tests/test_dist_cpu.py) ----
     from hutoken_b200 import dist as D
 
@@ -403,6 +443,8 @@ def run_ours(args):
                                                    "big_merges")},
             "corpus_gen_s": gen_s,
         }
+        if dec is not None:
+            line["decode"] = dec
         if e2e_ms_max is not None:
             line["e2e"] = {"value": total_bytes / (e2e_ms_max * 1e-3) / 1e6, "unit": UNIT,
                            "h2d_bytes_per_step": int(nbytes + 8 * (ndocs + 1)),

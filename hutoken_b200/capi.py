@@ -180,6 +180,14 @@ class Engine:
         raw = text.tobytes()
         return [raw[int(offs[i]):int(offs[i + 1])] for i in range(len(lists))]
 
+    def decode_device(self, d_ids, n_ids, d_tok, n_docs, stream=None):
+        """ids / offsets resident on the context's first device -> (d_text address, d_text_offsets address, n_bytes);
+        the outputs are device buffers owned by the context."""
+        t, o, n = C.c_void_p(), C.c_void_p(), C.c_uint64()
+        self._check(self._lib.hut_decode_device(self._h, d_ids, n_ids, d_tok, n_docs, C.byref(t), C.byref(o),
+                                                C.byref(n), stream))
+        return t.value, o.value, int(n.value)
+
     def decode_stats(self):
         ms, n = C.c_double(), C.c_uint64()
         self._lib.hut_decode_stats(self._h, C.byref(ms), C.byref(n))

@@ -219,14 +219,14 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     // MAXW - 1 bytes past the tile) + the prefix ids of every document starting in it
     d->stride = (uint32_t)(OWN + MAXW) * (dm.kmax + (m->has_prefix ? m->n_prefix_syms + m->n_prefix_alone : 0u));
     d->med_cap = 4096u * dm.kmax + m->n_prefix_syms + 64;
-    d->cta_scratch_words = 4ull * d->med_cap;
+    d->cta_scratch_words = 5ull * d->med_cap + 8;  // U, MG, NX, PV + tournament-tree levels
     CU(ctx, cudaMalloc(&d->cta_scratch, d->cta_scratch_words * sizeof(uint32_t) * d->long_grid));
     d->big_slots = ctx->opt.big_slots ? ctx->opt.big_slots : (ctx->opt.max_pretoken > (64ull << 20) ? 2 : 8);
     if (d->big_slots > 32) d->big_slots = 32;
     unsigned long long bc = dm.limit * dm.kmax + m->n_prefix_syms + 64;
     if (bc > 0xFFFFFFF0ull) return set_err(ctx, HUT_STATUS_ARG, "%s", "max_pretoken too large");
     d->big_cap = (uint32_t)bc;
-    d->big_slot_words = 4ull * d->big_cap;
+    d->big_slot_words = 5ull * d->big_cap + 8;
     CU(ctx, cudaMalloc(&d->big_pool, d->big_slot_words * sizeof(uint32_t) * d->big_slots));
     return HUT_STATUS_OK;
 }

@@ -690,7 +690,11 @@ __device__ __forceinline__ uint32_t merge_entry(const DevModel& M, const Job& J,
 // ------------------------------------------------------------------------------------------------
 // long_kernel helpers: one CTA (LNT threads) per deferred pretoken
 // ------------------------------------------------------------------------------------------------
+constexpr int TREE_SM_KEYS = 1024 + 32 + 8;  // tournament-tree levels of up to 1024 keys stay in shared memory
+constexpr int TREE_MAX_LEVELS = 7;           // 32^7 positions
+
 struct LongSm {
+    unsigned long long tree[TREE_SM_KEYS];
     uint32_t byte1[256];
     unsigned long long red64[LNW];
     uint32_t red32[LNW];
@@ -789,14 +793,14 @@ __device__ unsigned long long find_run_end(const Job& J, LongSm& sm, unsigned lo
 
 // ------------------------------------------------------------------------------------------------
 // block-cooperative merge of one pretoken [gs, ge) with its symbol arrays in global memory (L2):
-// U unit, MG merged unit of pair (i, next(i)), NX / PV linked list.  One merge per round, chosen by a
-// block-wide min over (rank, index) -- the same order as the reference heap.
+// U unit, MG merged unit of pair (i, next(i)), NX / PV linked list, T tournament-tree levels.  One merge per round,
+// the pair with the smallest (rank, index) -- the same order as the reference heap -- read from the tree's root.
 // cta_merge_run leaves the survivors in U (dead = ENDLINK) and returns their number (+ the ids emitted alone
 // before the first pretoken); 0xFFFFFFFF if the symbol count exceeds cap.  cta_merge_emit writes the ids.
 // ------------------------------------------------------------------------------------------------
 __device__ uint32_t cta_merge_run(const DevModel& M, const Job& J, LongSm& sm, unsigned long long gs,
                                   unsigned long long ge, bool with_prefix, bool alone_first, uint32_t* U, uint32_t* MG,
-                                  uint32_t* NX, uint32_t* PV, uint32_t cap, uint32_t* m_out) {
+                                  uint32_t* NX, uint32_t* PV, unsigned long long* T, uint32_t cap, uint32_t* m_out) {
     const uint32_t tid = threadIdx.x;
     auto at = [&](unsigned long long p) -> uint32_t { return (uint32_t)__ldg(J.text + p); };
     const unsigned long long len = ge - gs;
@@ -833,31 +837,117 @@ __device__ uint32_t cta_merge_run(const DevModel& M, const Job& J, LongSm& sm, u
         PV[i] = i ? i - 1 : ENDLINK;
     }
     __syncthreads();
-    for (;;) {
-        unsigned long long best = ~0ull;
-        for (uint32_t i = tid; i < m; i += LNT) {
-            uint32_t mg = MG[i];
-            if (mg != NONE) {
-                unsigned long long key = ((unsigned long long)rank_of_unit(M, mg) << 32) | i;
-                best = key < best ? key : best;
+    // ---- tournament tree over the keys (rank << 32 | position), fan-out 32: level l holds the minimum of every group
+    // of 32 entries of the level below (level -1 = the positions themselves, keyed from MG).  The merge order is the
+    // reference heap's (rank, left index) order (queue.c:162-164); picking the next merge costs one read of the root
+    // and refreshing it after a merge costs one warp-wide minimum per level for the (at most three) touched groups,
+    // instead of a pass over all m positions.  Small levels live in shared memory, the rest in the scratch area.
+    const uint32_t lane = tid & 31u, warp = tid >> 5;
+    unsigned long long* lv[TREE_MAX_LEVELS];
+    uint32_t lcnt[TREE_MAX_LEVELS];
+    int nl = 0;
+    {
+        uint32_t c = m, sm_used = 0;
+        unsigned long long* g = T;
+        do {
+            c = (c + 31u) >> 5;
+            lcnt[nl] = c;
+            if (c <= (uint32_t)TREE_SM_KEYS - sm_used && c <= 1024u) {
+                lv[nl] = sm.tree + sm_used;
+                sm_used += c;
+            } else {
+                lv[nl] = g;
+                g += c;
             }
+            ++nl;
+        } while (c > 1u && nl < TREE_MAX_LEVELS);
+    }
+    auto pos_key = [&](uint32_t pos) -> unsigned long long {
+        if (pos >= m) return ~0ull;
+        const uint32_t mg = MG[pos];
+        return mg == NONE ? ~0ull : (((unsigned long long)rank_of_unit(M, mg) << 32) | pos);
+    };
+    auto warp_min = [&](unsigned long long k) -> unsigned long long {
+#pragma unroll
+        for (int d = 16; d; d >>= 1) {
+            const unsigned long long o = __shfl_xor_sync(0xFFFFFFFFu, k, d);
+            k = o < k ? o : k;
         }
-        best = block_min64(sm, best);
-        if (best == ~0ull) break;
-        if (tid == 0) {
-            uint32_t i = (uint32_t)best, j = NX[i];
-            U[i] = MG[i];
-            U[j] = ENDLINK;  // dead
-            MG[j] = NONE;
-            uint32_t nj = NX[j];
-            NX[i] = nj;
-            if (nj != ENDLINK) PV[nj] = i;
-            uint32_t p = PV[i];
-            if (p != ENDLINK) MG[p] = pair_probe(M, U[p], U[i]);
-            MG[i] = (nj != ENDLINK) ? pair_probe(M, U[i], U[nj]) : NONE;
+        return k;
+    };
+    for (uint32_t g = warp; g < lcnt[0]; g += LNW) {
+        const unsigned long long k = warp_min(pos_key(g * 32u + lane));
+        if (lane == 0) lv[0][g] = k;
+    }
+    __syncthreads();
+    for (int l = 1; l < nl; ++l) {
+        for (uint32_t g = warp; g < lcnt[l]; g += LNW) {
+            const uint32_t c = g * 32u + lane;
+            const unsigned long long k = warp_min(c < lcnt[l - 1] ? lv[l - 1][c] : ~0ull);
+            if (lane == 0) lv[l][g] = k;
         }
         __syncthreads();
     }
+    if (warp == 0) {
+        const int top = nl - 1;
+        for (;;) {
+            const unsigned long long best = *reinterpret_cast<volatile unsigned long long*>(lv[top]);
+            if (best == ~0ull) break;
+            const uint32_t i = (uint32_t)best;
+            uint32_t p = ENDLINK, j = ENDLINK;
+            if (lane == 0) {
+                j = NX[i];
+                U[i] = MG[i];
+                U[j] = ENDLINK;  // dead
+                MG[j] = NONE;
+                const uint32_t nj = NX[j];
+                NX[i] = nj;
+                if (nj != ENDLINK) PV[nj] = i;
+                p = PV[i];
+                if (p != ENDLINK) MG[p] = pair_probe(M, U[p], U[i]);
+                MG[i] = (nj != ENDLINK) ? pair_probe(M, U[i], U[nj]) : NONE;
+            }
+            p = __shfl_sync(0xFFFFFFFFu, p, 0);
+            j = __shfl_sync(0xFFFFFFFFu, j, 0);
+            __syncwarp();
+            uint32_t a0 = i >> 5, a1 = j >> 5, a2 = p != ENDLINK ? p >> 5 : a0;
+            {
+                unsigned long long k = warp_min(pos_key(a0 * 32u + lane));
+                if (lane == 0) lv[0][a0] = k;
+                if (a1 != a0) {
+                    k = warp_min(pos_key(a1 * 32u + lane));
+                    if (lane == 0) lv[0][a1] = k;
+                }
+                if (a2 != a0 && a2 != a1) {
+                    k = warp_min(pos_key(a2 * 32u + lane));
+                    if (lane == 0) lv[0][a2] = k;
+                }
+            }
+            __syncwarp();
+            for (int l = 1; l <= top; ++l) {
+                a0 >>= 5;
+                a1 >>= 5;
+                a2 >>= 5;
+                const unsigned long long* below = lv[l - 1];
+                const uint32_t nb = lcnt[l - 1];
+                uint32_t c = a0 * 32u + lane;
+                unsigned long long k = warp_min(c < nb ? below[c] : ~0ull);
+                if (lane == 0) lv[l][a0] = k;
+                if (a1 != a0) {
+                    c = a1 * 32u + lane;
+                    k = warp_min(c < nb ? below[c] : ~0ull);
+                    if (lane == 0) lv[l][a1] = k;
+                }
+                if (a2 != a0 && a2 != a1) {
+                    c = a2 * 32u + lane;
+                    k = warp_min(c < nb ? below[c] : ~0ull);
+                    if (lane == 0) lv[l][a2] = k;
+                }
+                __syncwarp();
+            }
+        }
+    }
+    __syncthreads();
     uint32_t live = 0;
     for (uint32_t i = tid; i < m; i += LNT) live += (U[i] != ENDLINK);
     uint32_t tot2;

@@ -528,8 +528,11 @@ __global__ void __launch_bounds__(LNT) long_kernel(const DevModel M, const Job J
             cap = J.big_cap;
             n_big++;
         }
+        // tournament-tree levels behind the four arrays (8-byte aligned; the areas hold 5 * cap + 8 words)
+        unsigned long long* T = reinterpret_cast<unsigned long long*>(
+            (reinterpret_cast<uintptr_t>(PV + cap) + 7u) & ~(uintptr_t)7u);
         uint32_t m = 0;
-        uint32_t cnt = cta_merge_run(M, J, sm, gs, ge, with_prefix, alone_first, U, MG, NX, PV, cap, &m);
+        uint32_t cnt = cta_merge_run(M, J, sm, gs, ge, with_prefix, alone_first, U, MG, NX, PV, T, cap, &m);
         if (cnt == 0xFFFFFFFFu) {
             set_flag(J, FLAG_BIG_CAP);
             cnt = 0;

@@ -126,12 +126,13 @@ def test_reference_cut_at_overlong_pretoken():
     name = "gpt2_small"
     eng, orc = engine_for(name), oracle_for(name)
     docs = ["before one", "keep this " + "a" * (262144 + 8) + " dropped tail", "after one",
-            "b" * 262145, "x " + "c" * 262144 + " kept"]
+            "b" * 262145, "x " + "c" * 262144 + " kept",
+            "configs[4]: a 16 MiB whitespace-free run " + "abcdefgh" * (2 << 20) + " tail", "last one"]
     data, offs = pack(docs)
     ids, tok = eng.encode_packed(data, offs)
     oids, otok = orc.encode_packed(data, offs)
     assert_same(ids, tok, oids, otok, name)
-    assert eng.stats()["cut_documents"] == 2
+    assert eng.stats()["cut_documents"] == 3
 
 
 def test_device_resident_api():
