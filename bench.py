@@ -268,6 +268,30 @@ def pinned_u8(capi_lib, n):
     return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(n,))
 
 
+_ALL_CPUS = None
+
+
+def bind_to_gpu_numa_node(index):
+    """Restricts this process to the CPUs NVML reports as local to GPU `index`, so that the pinned text / id
+    buffers of the e2e leg are allocated on the socket the GPU hangs off (8 ranks otherwise share one node's
+    memory controllers and the inter-socket link).  Best effort: any failure leaves the affinity unchanged."""
+    global _ALL_CPUS
+    try:
+        import pynvml
+        _ALL_CPUS = os.sched_getaffinity(0)
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+        return sorted(cpus)
+    except Exception:
+        return None
+
+
 class _DevView:
     """A device buffer owned by the engine, exposed to torch through __cuda_array_interface__ (no copy)."""
 
@@ -292,6 +316,7 @@ def run_ours(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the engine has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
+    bind_to_gpu_numa_node(local)  # before any pinned allocation: first touch places it on the GPU's own node
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
@@ -453,6 +478,8 @@ def run_ours(args):
                            "api": "hut_encode_batch (host buffers in pinned memory -> ids in pinned memory)"}
         if not args.no_cpu_baseline and world >= 1:
             try:
+                if _ALL_CPUS:
+                    os.sched_setaffinity(0, _ALL_CPUS)  # the CPU baseline gets every host core
                 run, kind, nthreads = load_reference(args.model)
                 r = time_reference(run, kind, data, offs, args.cpu_seconds)
                 line["cpu_baseline"] = {

@@ -29,6 +29,7 @@ struct DecModel {
     uint32_t trie_mask;        // 0xFFFFFFFF when the trie is empty
     const int16_t* trie_out;
     const uint8_t* trie_depth;
+    uint32_t trie_nodes;
     const uint32_t* root_child;  // [256]
     const uint8_t* prefix;
     uint32_t prefix_len;
@@ -160,23 +161,29 @@ __global__ void dec_gather_kernel(DecModel D, const int32_t* ids, unsigned long 
 // ------------------------------------------------------------------------------------------------
 // raw text -> decoded text, one CTA per document (grid-stride), tile by tile
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t trie_child(const DecModel& D, uint32_t node, uint32_t byte) {
+__device__ __forceinline__ uint32_t trie_child(const unsigned long long* edge, uint32_t mask, uint32_t node,
+                                               uint32_t byte) {
     const uint32_t key = (node << 8) | byte;
-    uint32_t i = hut_trie_hash(key, D.trie_mask);
+    uint32_t i = hut_trie_hash(key, mask);
     for (;;) {
-        const unsigned long long s = __ldg(D.trie_edge + i);
+        const unsigned long long s = edge[i];
         if (s == HUT_TRIE_EMPTY) return 0u;
         if ((uint32_t)(s >> 32) == key) return (uint32_t)s;
-        i = (i + 1) & D.trie_mask;
+        i = (i + 1) & mask;
     }
 }
 
+constexpr int DEC_TRIE_SM = 512;  // tries of up to this many edge slots / nodes are staged in shared memory
+
 struct DecSm {
-    uint8_t raw[DEC_TILE + DEC_LOOK + 32];
+    uint4 rawbuf[(DEC_TILE + DEC_LOOK + 16 + 16 + 48) / 16];  // the tile at its global 16-byte phase + look-ahead
     uint16_t nxt[DEC_LEVELS][DEC_TILE];  // nxt[k][i] = position after 2^k steps from i; >= tile_len: left the tile
     uint8_t eb[DEC_TILE];                // byte emitted by a replacement / byte-mode step
-    uint8_t el[DEC_TILE];                // bytes emitted when position i is visited (0 = copy `cl` raw bytes)
+    uint8_t el[DEC_TILE];                // 1, or 0x80 | n: copy n raw bytes (plain mode)
     uint32_t root_child[256];
+    unsigned long long tedge[DEC_TRIE_SM];
+    int16_t tout[DEC_TRIE_SM];
+    uint8_t tdepth[DEC_TRIE_SM];
     unsigned long long scan[32];
     unsigned long long tot;
     uint32_t entry;
@@ -188,6 +195,16 @@ __global__ void __launch_bounds__(DEC_NT) dec_doc_kernel(DecModel D, const unsig
     __shared__ DecSm sm;
     const int tid = threadIdx.x;
     for (int i = tid; i < 256; i += DEC_NT) sm.root_child[i] = D.root_child[i];
+    // small tries (every practical special-chars table) are walked in shared memory
+    const bool trie_sm = D.trie_mask < (uint32_t)DEC_TRIE_SM;
+    if (trie_sm) {
+        for (uint32_t i = tid; i <= D.trie_mask; i += DEC_NT) sm.tedge[i] = D.trie_edge[i];
+        for (uint32_t i = tid; i < (uint32_t)DEC_TRIE_SM; i += DEC_NT) {
+            sm.tout[i] = i < D.trie_nodes ? D.trie_out[i] : (int16_t)-1;
+            sm.tdepth[i] = i < D.trie_nodes ? D.trie_depth[i] : (uint8_t)0;
+        }
+    }
+    const unsigned long long* const edge = trie_sm ? sm.tedge : D.trie_edge;
     __syncthreads();
     for (unsigned long long d = blockIdx.x; d < ndocs; d += gridDim.x) {
         const unsigned long long r0 = raw_off[tok_off[d]], r1 = raw_off[tok_off[d + 1]];
@@ -207,8 +224,16 @@ __global__ void __launch_bounds__(DEC_NT) dec_doc_kernel(DecModel D, const unsig
         for (unsigned long long t0 = 0; t0 < rlen; t0 += DEC_TILE) {
             const uint32_t tile_len = rlen - t0 < DEC_TILE ? (uint32_t)(rlen - t0) : (uint32_t)DEC_TILE;
             const uint32_t avail = rlen - t0 < DEC_TILE + DEC_LOOK ? (uint32_t)(rlen - t0) : (uint32_t)(DEC_TILE + DEC_LOOK);
-            for (uint32_t i = tid; i < DEC_TILE + DEC_LOOK; i += DEC_NT) sm.raw[i] = i < avail ? raw[r0 + t0 + i] : 0;
+            // ---- stage the tile with 16-byte loads at its global phase; bytes past the document read as 0 ----
+            const unsigned long long gbase = r0 + t0;
+            const uint32_t mis = (uint32_t)((reinterpret_cast<uintptr_t>(raw) + gbase) & 15u);
+            const uint4* gsrc = reinterpret_cast<const uint4*>(raw + gbase - mis);
+            const uint32_t nwords = (mis + avail + 15u) >> 4;
+            for (uint32_t w = tid; w < nwords; w += DEC_NT) sm.rawbuf[w] = gsrc[w];
+            uint8_t* const rw = reinterpret_cast<uint8_t*>(sm.rawbuf) + mis;
             uint32_t entry = sm.entry;
+            __syncthreads();
+            if (avail < (uint32_t)(DEC_TILE + DEC_LOOK) && tid < 40) rw[avail + tid] = 0;
             __syncthreads();
             if (entry >= tile_len) {  // the previous step jumped over this whole tile (prefix / replacement at its end)
                 if (tid == 0) sm.entry = entry - tile_len;
@@ -216,32 +241,35 @@ __global__ void __launch_bounds__(DEC_NT) dec_doc_kernel(DecModel D, const unsig
                 continue;
             }
             // ---- the step every position would take ----
+            // `simple` stays true while every character start steps exactly over its own well-formed character: then
+            // the positions visited are the character starts and no lifting is needed
+            bool simple = true;
             for (uint32_t i = tid; i < tile_len; i += DEC_NT) {
-                const uint32_t b0 = sm.raw[i];
+                const uint32_t b0 = rw[i];
                 uint32_t step = 0, out = 0, emit = 1;
                 uint32_t node = sm.root_child[b0];
                 if (node) {  // longest replacement starting here (never past the end of the document)
                     uint32_t q = i + 1;
                     for (;;) {
-                        const int o = __ldg(D.trie_out + node);
+                        const int o = trie_sm ? (int)sm.tout[node] : (int)__ldg(D.trie_out + node);
                         if (o >= 0) {
-                            step = __ldg(D.trie_depth + node);
+                            step = trie_sm ? (uint32_t)sm.tdepth[node] : (uint32_t)__ldg(D.trie_depth + node);
                             out = (uint32_t)o;
                         }
                         if (q >= avail) break;
-                        node = trie_child(D, node, sm.raw[q]);
+                        node = trie_child(edge, D.trie_mask, node, rw[q]);
                         if (!node) break;
                         ++q;
                     }
                 }
+                const uint32_t b1 = rw[i + 1], b2 = rw[i + 2], b3 = rw[i + 3];
+                uint32_t cl, cp;
+                if (b0 < 0x80) { cl = 1; cp = b0; }
+                else if ((b0 & 0xE0) == 0xC0) { cl = 2; cp = ((b0 & 0x1F) << 6) | (b1 & 0x3F); }
+                else if ((b0 & 0xF0) == 0xE0) { cl = 3; cp = ((b0 & 0x0F) << 12) | ((b1 & 0x3F) << 6) | (b2 & 0x3F); }
+                else if ((b0 & 0xF8) == 0xF0) { cl = 4; cp = ((b0 & 0x07) << 18) | ((b1 & 0x3F) << 12) | ((b2 & 0x3F) << 6) | (b3 & 0x3F); }
+                else { cl = 1; cp = 0xFFFD; }
                 if (!step) {
-                    const uint32_t b1 = sm.raw[i + 1], b2 = sm.raw[i + 2], b3 = sm.raw[i + 3];
-                    uint32_t cl, cp;
-                    if (b0 < 0x80) { cl = 1; cp = b0; }
-                    else if ((b0 & 0xE0) == 0xC0) { cl = 2; cp = ((b0 & 0x1F) << 6) | (b1 & 0x3F); }
-                    else if ((b0 & 0xF0) == 0xE0) { cl = 3; cp = ((b0 & 0x0F) << 12) | ((b1 & 0x3F) << 6) | (b2 & 0x3F); }
-                    else if ((b0 & 0xF8) == 0xF0) { cl = 4; cp = ((b0 & 0x07) << 18) | ((b1 & 0x3F) << 12) | ((b2 & 0x3F) << 6) | (b3 & 0x3F); }
-                    else { cl = 1; cp = 0xFFFD; }
                     step = cl;
                     if (D.byte_mode) {
                         out = cp < 256 ? cp : (uint32_t)'?';  // pretokenizer.c:247-254
@@ -251,12 +279,51 @@ __global__ void __launch_bounds__(DEC_NT) dec_doc_kernel(DecModel D, const unsig
                         out = 0x100;  // marker: copy raw bytes
                     }
                 }
+                if ((b0 & 0xC0) != 0x80) {  // a character start
+                    bool ok = step == cl && (rw[i + cl] & 0xC0) != 0x80;
+                    if (cl > 1) ok = ok && (b1 & 0xC0) == 0x80;
+                    if (cl > 2) ok = ok && (b2 & 0xC0) == 0x80;
+                    if (cl > 3) ok = ok && (b3 & 0xC0) == 0x80;
+                    simple = simple && ok;
+                }
                 sm.nxt[0][i] = (uint16_t)(i + step);
                 sm.eb[i] = (uint8_t)out;
                 sm.el[i] = (uint8_t)(out == 0x100 ? 0x80 | emit : 1);
             }
-            __syncthreads();
-            // ---- binary lifting ----
+            simple = __syncthreads_and(simple && (rw[entry] & 0xC0) != 0x80) != 0;
+            if (simple) {
+                // ---- fast path: thread t owns positions [8t, 8t + 8); visited = character starts from the entry on ----
+                const uint32_t p0 = (uint32_t)tid * (DEC_TILE / DEC_NT);
+                uint32_t mine = 0;
+#pragma unroll
+                for (uint32_t k = 0; k < DEC_TILE / DEC_NT; ++k) {
+                    const uint32_t i = p0 + k;
+                    if (i >= entry && i < tile_len && (rw[i] & 0xC0) != 0x80) mine += sm.el[i] & 0x7Fu;
+                }
+                const unsigned long long ex = block_exclusive_u64(mine, &sm.tot, sm.scan);
+                uint8_t* o = dec + r0 + written + ex;
+#pragma unroll
+                for (uint32_t k = 0; k < DEC_TILE / DEC_NT; ++k) {
+                    const uint32_t i = p0 + k;
+                    if (i >= entry && i < tile_len && (rw[i] & 0xC0) != 0x80) {
+                        const uint32_t e = sm.el[i];
+                        if (e & 0x80u) {
+                            for (uint32_t c = 0; c < (e & 0x7Fu); ++c) *o++ = rw[i + c];
+                        } else {
+                            *o++ = sm.eb[i];
+                        }
+                    }
+                }
+                if (tid == 0) {  // hand-over: the first character start at or after the end of the tile
+                    uint32_t k = 0;
+                    while (k < 4 && (rw[tile_len + k] & 0xC0) == 0x80) ++k;
+                    sm.entry = k;
+                }
+                written += sm.tot;
+                __syncthreads();
+                continue;
+            }
+            // ---- general path: binary lifting ----
             for (int k = 1; k < DEC_LEVELS; ++k) {
                 for (uint32_t i = tid; i < tile_len; i += DEC_NT) {
                     const uint32_t v = sm.nxt[k - 1][i];
@@ -297,7 +364,7 @@ __global__ void __launch_bounds__(DEC_NT) dec_doc_kernel(DecModel D, const unsig
                 for (uint32_t h = h0; h < nodes && h < h0 + per; ++h) {
                     const uint32_t e = sm.el[p];
                     if (e & 0x80u) {
-                        for (uint32_t k = 0; k < (e & 0x7Fu); ++k) *o++ = sm.raw[p + k];
+                        for (uint32_t k = 0; k < (e & 0x7Fu); ++k) *o++ = rw[p + k];
                     } else {
                         *o++ = sm.eb[p];
                     }

@@ -70,6 +70,7 @@ static int dec_init(hut_ctx* ctx) {
     D.vocab_lines = m->vocab_lines;
     CU(ctx, upload(d, (const unsigned long long*)m->trie_edge, m->trie_cap, &D.trie_edge));
     D.trie_mask = m->trie_cap - 1;
+    D.trie_nodes = m->trie_nodes;
     CU(ctx, upload(d, m->trie_out, m->trie_nodes, &D.trie_out));
     CU(ctx, upload(d, m->trie_depth, m->trie_nodes, &D.trie_depth));
     CU(ctx, upload(d, m->trie_root_child, 256, &D.root_child));
