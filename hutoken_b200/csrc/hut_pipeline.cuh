@@ -286,9 +286,9 @@ __global__ void __launch_bounds__(NT, 4) tile_kernel(const __grid_constant__ Dev
             // long_kernel, 4 miss too long for the cache / the small per-lane arrays -> miss_kernel
             uint32_t state = 0;
             // pretokens of 16..31 bytes (rare): second cache, 32-byte keys
-            const bool keyed2 = !dummy && !keyed && len <= CACHE2_KEY_MAX && M.cache_ok;
             bool hit2 = false;
-            if (__any_sync(FULL, keyed2)) {
+            if (__any_sync(FULL, !keyed)) {
+                const bool keyed2 = !dummy && !keyed && len <= CACHE2_KEY_MAX && M.cache_ok;
                 if (keyed2) {
                     uint32_t k32[8];
                     build_key32(ws.text, sm.kmask32, s, len, first, k32);
@@ -323,6 +323,9 @@ __global__ void __launch_bounds__(NT, 4) tile_kernel(const __grid_constant__ Dev
                 if (cs > 3) p[3] = sext21(w[3]);
                 if (cs > 4) p[4] = val_id4(w);
             }
+            // everything below up to the per-document offsets concerns pretokens the cache did not answer: one vote
+            // decides for the whole round (99 % of the rounds skip it)
+            if (__any_sync(FULL, state >= 2)) {
             // ---- cache misses -> this warp's queue; every 32 of them are merged at once, one per lane ----
             const uint32_t m2 = __ballot_sync(FULL, state == 2);
             if (m2) {
@@ -379,6 +382,7 @@ __global__ void __launch_bounds__(NT, 4) tile_kernel(const __grid_constant__ Dev
                 }
                 def_head = __shfl_sync(FULL, def_head, 0);
                 def_tail = __shfl_sync(FULL, def_tail, 0);
+            }
             }
             if (tile_docs && !dummy && dsb) {  // documents starting at this pretoken: slot entries before it
                 const unsigned long long gpos = (unsigned long long)(g0 + s);
