@@ -65,11 +65,11 @@ struct hut_dev {
     unsigned long long big_slot_words;
     uint32_t big_cap, big_slots;
     int grid, long_grid, sms;
-    uint32_t stride;
+    uint32_t stride, slot_extra;
     // grow-only temporaries of the pipeline
     int32_t* stage;
     size_t stage_cap;
-    uint32_t* tilebuf;  // cnt | tot | first_doc | def_first, ntiles + 1 entries each
+    uint32_t* tilebuf;  // cnt | tot | first_doc | def_first | slot_docs, ntiles + 1 entries each
     size_t tilebuf_cap;
     unsigned long long* bsum;
     size_t bsum_cap;
@@ -217,7 +217,8 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
 
     // ids a 960-byte tile can produce: one per symbol of the pretokens STARTING in it (the last one may run up to
     // MAXW - 1 bytes past the tile) + the prefix ids of every document starting in it
-    d->stride = (uint32_t)(OWN + MAXW) * (dm.kmax + (m->has_prefix ? m->n_prefix_syms + m->n_prefix_alone : 0u));
+    d->stride = (uint32_t)(OWN + MAXW) * dm.kmax;
+    d->slot_extra = m->has_prefix ? m->n_prefix_syms + m->n_prefix_alone : 0u;
     d->med_cap = 4096u * dm.kmax + m->n_prefix_syms + 64;
     d->cta_scratch_words = 5ull * d->med_cap + 8;  // U, MG, NX, PV + tournament-tree levels
     CU(ctx, cudaMalloc(&d->cta_scratch, d->cta_scratch_words * sizeof(uint32_t) * d->long_grid));
@@ -391,8 +392,8 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     const uint32_t nblocks = (ntiles + SCAN_BLK - 1) / SCAN_BLK;
     if (def_want < (size_t)ntiles / 8 + 65536) def_want = (size_t)ntiles / 8 + 65536;
     if (long_want < (size_t)n_bytes / 16 + (1u << 20)) long_want = (size_t)n_bytes / 16 + (1u << 20);
-    CU(ctx, grow(&d->stage, &d->stage_cap, (size_t)ntiles * d->stride));
-    CU(ctx, grow(&d->tilebuf, &d->tilebuf_cap, 4 * ((size_t)ntiles + 1)));
+    CU(ctx, grow(&d->stage, &d->stage_cap, (size_t)ntiles * d->stride + (size_t)n_docs * d->slot_extra + 64));
+    CU(ctx, grow(&d->tilebuf, &d->tilebuf_cap, 5 * ((size_t)ntiles + 1)));
     CU(ctx, grow(&d->bsum, &d->bsum_cap, (size_t)nblocks));
     CU(ctx, grow(&d->def, &d->def_cap, def_want));
     CU(ctx, grow(&d->long_ids, &d->long_cap, long_want));
@@ -410,6 +411,8 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     J.tok_off = (unsigned long long*)d_tok_offsets;
     J.ntiles = ntiles;
     J.stride = d->stride;
+    J.slot_extra = d->slot_extra;
+    J.slot_docs = d->tilebuf + 4 * ((size_t)ntiles + 1);
     J.stage = d->stage;
     J.cnt = d->tilebuf;
     J.tot = J.cnt + ((size_t)ntiles + 1);
@@ -439,6 +442,10 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     CU(ctx, cudaMemsetAsync(J.first_doc, 0xFF, ((size_t)ntiles + 1) * sizeof(uint32_t), st));
     init_kernel<<<1, 32, 0, st>>>(J);
     if (n_docs) doc_kernel<<<(unsigned)((n_docs + 255) / 256), 256, 0, st>>>(J);
+    if (J.slot_extra) {
+        slot_docs_kernel<<<(unsigned)(((size_t)ntiles + 1 + 255) / 256), 256, 0, st>>>(J, d->tilebuf + 4 * ((size_t)ntiles + 1));
+        d->stats.kernel_launches += 1;
+    }
     CU(ctx, cudaEventRecord(f->ev[1], st));
     // tile_kernel merges the cache misses it can key itself (batches of 32, one per lane) and lists the rest, which
     // miss_kernel merges afterwards

@@ -47,6 +47,21 @@ __global__ void doc_kernel(Job J) {
 }
 
 // scalar restatement (hut_classify.h) of one 32-byte chunk: only used when an over-long UTF-8 form is in the tile
+// documents starting before each tile (lower bound of the tile's first byte in doc_off): the variable part of the
+// staging slot offsets of a prefix model, see stage_slot()
+__global__ void slot_docs_kernel(Job J, uint32_t* out) {
+    const unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t > J.ntiles) return;
+    const unsigned long long pos = t * OWN;
+    unsigned long long a = 0, b = J.ndocs;
+    while (a < b) {
+        const unsigned long long mid = (a + b) >> 1;
+        if (J.doc_off[mid] < pos) a = mid + 1;
+        else b = mid;
+    }
+    out[t] = (uint32_t)a;
+}
+
 __device__ __noinline__ void generic_chunk(const WarpSm& ws, int lane, uint32_t* ST, uint32_t* NU) {
     auto dsbit = [&](int x) -> uint32_t { return (x >= 0 && x < SPAN) ? ((ws.dsm[x >> 5] >> (x & 31)) & 1u) : 0u; };
     auto lead = [&](int x) -> uint32_t {
@@ -126,7 +141,7 @@ __device__ __forceinline__ uint32_t run_batch(const DevModel& M, const Job& J, c
         const uint32_t loff = (uint32_t)(pos_off >> 40);
         const uint32_t len = E.z & 0xFFu, first = (E.z >> 8) & 1u, room = E.z >> 16;
         slack = merge_entry<MISS_SMALL>(M, J, byte1, pos, len, first, room,
-                                        J.stage + (unsigned long long)E.w * J.stride + loff);
+                                        stage_slot(J, E.w) + loff);
         if (slack && E.w != cur_tile) {
             atomicSub(&J.tot[E.w], slack);
             slack = 0;
@@ -268,7 +283,7 @@ __global__ void __launch_bounds__(NT, 4) tile_kernel(const __grid_constant__ Dev
         uint32_t def_head = NODOC, def_tail = NODOC;
         bool holes = false;
         uint32_t slack = 0;                     // room reserved for misses of this tile that stayed unused
-        int32_t* const slot = J.stage + (unsigned long long)tile * J.stride;
+        int32_t* const slot = stage_slot(J, tile);
         for (uint32_t r0 = 0; r0 < n; r0 += 32) {
             const uint32_t q = r0 + lane;
             const bool active = q < n;
@@ -442,7 +457,7 @@ __global__ void __launch_bounds__(MNT) miss_kernel(const DevModel M, const Job J
         const uint32_t len = E.meta & 0xFFu, first = (E.meta >> 8) & 1u, room = E.meta >> 16;
         const unsigned long long tile = pos / OWN;
         const uint32_t slack = merge_entry<MISS_SYMS>(M, J, byte1, pos, len, first, room,
-                                                      J.stage + tile * J.stride + loff);
+                                                      stage_slot(J, tile) + loff);
         if (slack) atomicSub(&J.tot[tile], slack);
         n_done++;
     }
@@ -758,7 +773,7 @@ __global__ void __launch_bounds__(256) compact_kernel(const Job J) {
         const uint32_t c = J.cnt[tile];
         const uint32_t ns = c & CNT_MASK;
         unsigned long long o = tile_base(J, tile);
-        const int32_t* src = J.stage + (unsigned long long)tile * J.stride;
+        const int32_t* src = stage_slot(J, tile);
         if (!(c & (CNT_CHAIN | CNT_HOLES))) {
             copy_ids(J, src, o, ns);
             continue;
@@ -807,7 +822,7 @@ __global__ void fixdoc_kernel(const Job J) {
     if ((c & (CNT_HOLES | CNT_CHAIN)) == CNT_HOLES) return;  // compact_kernel has translated these already
     unsigned long long v = J.tok_off[d];  // entries of the tile's slot before the document
     if (c & CNT_HOLES) {
-        const int32_t* src = J.stage + t * J.stride;
+        const int32_t* src = stage_slot(J, t);
         uint32_t h = 0;
         for (uint32_t i = 0; i < (uint32_t)v; ++i) h += src[i] == HOLE;
         v -= h;
