@@ -8,7 +8,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libhutoken_b200.so")
+LIB_PATH = os.environ.get("HUTOKEN_B200_LIB") or os.path.join(_HERE, "libhutoken_b200.so")  # override: A/B runs
 
 STATUS_NAMES = {0: "OK", 1: "FILE_NOT_FOUND", 2: "VALUE", 3: "MEMORY", 4: "CUDA", 5: "UNSUPPORTED", 6: "ARG",
                 7: "STATE", 8: "CAPACITY"}
