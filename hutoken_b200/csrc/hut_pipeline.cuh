@@ -766,7 +766,7 @@ __device__ __forceinline__ void compact_tile_holes(const Job& J, uint32_t tile, 
 
 // staging slots -> dense ids (warp per tile); drops the HOLEs left by deferred cache misses and splices in the ids
 // of the pretokens long_kernel merged
-__global__ void __launch_bounds__(256) compact_kernel(const Job J) {
+__global__ void __launch_bounds__(256, 8) compact_kernel(const Job J) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t gw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), nw = gridDim.x * (blockDim.x >> 5);
     for (uint32_t tile = gw; tile < J.ntiles; tile += nw) {
