@@ -173,6 +173,7 @@ __device__ __forceinline__ uint32_t trie_child(const unsigned long long* edge, u
     }
 }
 
+constexpr int DEC_D1 = 4;        // depth-1 trie nodes with a direct second-byte table (GPT-2's table has three)
 constexpr int DEC_TRIE_SM = 512;  // tries of up to this many edge slots / nodes are staged in shared memory
 
 struct DecSm {
@@ -184,6 +185,10 @@ struct DecSm {
     unsigned long long tedge[DEC_TRIE_SM];
     int16_t tout[DEC_TRIE_SM];
     uint8_t tdepth[DEC_TRIE_SM];
+    uint8_t tkid[DEC_TRIE_SM];           // node has children
+    uint8_t d1slot[DEC_TRIE_SM];         // 1 + row of pair2 for the children of the root, 0 otherwise
+    uint16_t pair2[DEC_D1][256];         // child of a depth-1 node by the second byte: no hashing for 2-byte patterns
+    uint32_t use_d1;
     unsigned long long scan[32];
     unsigned long long tot;
     uint32_t entry;
@@ -205,7 +210,35 @@ __global__ void __launch_bounds__(DEC_NT) dec_doc_kernel(DecModel D, const unsig
         }
     }
     const unsigned long long* const edge = trie_sm ? sm.tedge : D.trie_edge;
+    for (uint32_t i = tid; i < (uint32_t)DEC_TRIE_SM; i += DEC_NT) {
+        sm.tkid[i] = 0;
+        sm.d1slot[i] = 0;
+    }
+    for (uint32_t i = tid; i < (uint32_t)DEC_D1 * 256u; i += DEC_NT) sm.pair2[i >> 8][i & 255u] = 0;
     __syncthreads();
+    if (tid == 0) {
+        uint32_t n1 = 0;
+        bool ok = trie_sm;
+        for (int b = 0; b < 256 && ok; ++b) {
+            const uint32_t n = sm.root_child[b];
+            if (!n || sm.d1slot[n]) continue;
+            if (n1 == (uint32_t)DEC_D1) ok = false;
+            else sm.d1slot[n] = (uint8_t)(++n1);
+        }
+        sm.use_d1 = ok ? 1u : 0u;
+    }
+    __syncthreads();
+    if (sm.use_d1) {
+        for (uint32_t i = tid; i <= D.trie_mask; i += DEC_NT) {
+            const unsigned long long e = sm.tedge[i];
+            if (e == HUT_TRIE_EMPTY) continue;
+            const uint32_t key = (uint32_t)(e >> 32), parent = key >> 8;
+            sm.tkid[parent] = 1;
+            if (sm.d1slot[parent]) sm.pair2[sm.d1slot[parent] - 1][key & 255u] = (uint16_t)e;
+        }
+    }
+    __syncthreads();
+    const bool use_d1 = sm.use_d1 != 0;
     for (unsigned long long d = blockIdx.x; d < ndocs; d += gridDim.x) {
         const unsigned long long r0 = raw_off[tok_off[d]], r1 = raw_off[tok_off[d + 1]];
         const unsigned long long rlen = r1 - r0;
@@ -247,22 +280,41 @@ __global__ void __launch_bounds__(DEC_NT) dec_doc_kernel(DecModel D, const unsig
             for (uint32_t i = tid; i < tile_len; i += DEC_NT) {
                 const uint32_t b0 = rw[i];
                 uint32_t step = 0, out = 0, emit = 1;
+                const uint32_t b1 = rw[i + 1], b2 = rw[i + 2], b3 = rw[i + 3];
                 uint32_t node = sm.root_child[b0];
                 if (node) {  // longest replacement starting here (never past the end of the document)
-                    uint32_t q = i + 1;
-                    for (;;) {
-                        const int o = trie_sm ? (int)sm.tout[node] : (int)__ldg(D.trie_out + node);
+                    auto walk = [&](uint32_t nd, uint32_t q) {
+                        for (;;) {
+                            const int o = trie_sm ? (int)sm.tout[nd] : (int)__ldg(D.trie_out + nd);
+                            if (o >= 0) {
+                                step = trie_sm ? (uint32_t)sm.tdepth[nd] : (uint32_t)__ldg(D.trie_depth + nd);
+                                out = (uint32_t)o;
+                            }
+                            if (q >= avail) break;
+                            nd = trie_child(edge, D.trie_mask, nd, rw[q]);
+                            if (!nd) break;
+                            ++q;
+                        }
+                    };
+                    if (use_d1) {  // one- and two-byte replacements without hashing
+                        int o = sm.tout[node];
                         if (o >= 0) {
-                            step = trie_sm ? (uint32_t)sm.tdepth[node] : (uint32_t)__ldg(D.trie_depth + node);
+                            step = 1;
                             out = (uint32_t)o;
                         }
-                        if (q >= avail) break;
-                        node = trie_child(edge, D.trie_mask, node, rw[q]);
-                        if (!node) break;
-                        ++q;
+                        const uint32_t n2 = i + 1 < avail ? (uint32_t)sm.pair2[sm.d1slot[node] - 1][b1] : 0u;
+                        if (n2) {
+                            if (sm.tkid[n2]) {
+                                walk(n2, i + 2);
+                            } else if ((o = sm.tout[n2]) >= 0) {
+                                step = 2;
+                                out = (uint32_t)o;
+                            }
+                        }
+                    } else {
+                        walk(node, i + 1);
                     }
                 }
-                const uint32_t b1 = rw[i + 1], b2 = rw[i + 2], b3 = rw[i + 3];
                 uint32_t cl, cp;
                 if (b0 < 0x80) { cl = 1; cp = b0; }
                 else if ((b0 & 0xE0) == 0xC0) { cl = 2; cp = ((b0 & 0x1F) << 6) | (b1 & 0x3F); }

@@ -69,7 +69,7 @@ struct hut_dev {
     // grow-only temporaries of the pipeline
     int32_t* stage;
     size_t stage_cap;
-    uint32_t* tilebuf;  // cnt | tot | first_doc | def_first | slot_docs, ntiles + 1 entries each
+    uint32_t* tilebuf;  // cnt | tot | first_doc | def_first (ntiles + 1 entries each) | slot_off (uint64)
     size_t tilebuf_cap;
     unsigned long long* bsum;
     size_t bsum_cap;
@@ -393,7 +393,7 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     if (def_want < (size_t)ntiles / 8 + 65536) def_want = (size_t)ntiles / 8 + 65536;
     if (long_want < (size_t)n_bytes / 16 + (1u << 20)) long_want = (size_t)n_bytes / 16 + (1u << 20);
     CU(ctx, grow(&d->stage, &d->stage_cap, (size_t)ntiles * d->stride + (size_t)n_docs * d->slot_extra + 64));
-    CU(ctx, grow(&d->tilebuf, &d->tilebuf_cap, 5 * ((size_t)ntiles + 1)));
+    CU(ctx, grow(&d->tilebuf, &d->tilebuf_cap, 6 * ((size_t)ntiles + 1) + 4));
     CU(ctx, grow(&d->bsum, &d->bsum_cap, (size_t)nblocks));
     CU(ctx, grow(&d->def, &d->def_cap, def_want));
     CU(ctx, grow(&d->long_ids, &d->long_cap, long_want));
@@ -412,7 +412,7 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     J.ntiles = ntiles;
     J.stride = d->stride;
     J.slot_extra = d->slot_extra;
-    J.slot_docs = d->tilebuf + 4 * ((size_t)ntiles + 1);
+    J.slot_off = reinterpret_cast<unsigned long long*>(d->tilebuf + 4 * ((size_t)ntiles + 1));  // 16-byte aligned
     J.stage = d->stage;
     J.cnt = d->tilebuf;
     J.tot = J.cnt + ((size_t)ntiles + 1);
@@ -442,10 +442,9 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     CU(ctx, cudaMemsetAsync(J.first_doc, 0xFF, ((size_t)ntiles + 1) * sizeof(uint32_t), st));
     init_kernel<<<1, 32, 0, st>>>(J);
     if (n_docs) doc_kernel<<<(unsigned)((n_docs + 255) / 256), 256, 0, st>>>(J);
-    if (J.slot_extra) {
-        slot_docs_kernel<<<(unsigned)(((size_t)ntiles + 1 + 255) / 256), 256, 0, st>>>(J, d->tilebuf + 4 * ((size_t)ntiles + 1));
-        d->stats.kernel_launches += 1;
-    }
+    slot_docs_kernel<<<(unsigned)(((size_t)ntiles + 1 + 255) / 256), 256, 0, st>>>(
+        J, reinterpret_cast<unsigned long long*>(d->tilebuf + 4 * ((size_t)ntiles + 1)));
+    d->stats.kernel_launches += 1;
     CU(ctx, cudaEventRecord(f->ev[1], st));
     // tile_kernel merges the cache misses it can key itself (batches of 32, one per lane) and lists the rest, which
     // miss_kernel merges afterwards

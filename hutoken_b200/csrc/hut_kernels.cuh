@@ -156,8 +156,8 @@ struct Job {
     uint32_t ntiles;
     uint32_t stride;           // ids per staging slot of a tile in which no document starts
     uint32_t slot_extra;       // more ids per document starting in the tile (prefix symbols / ids); 0 = no prefix
-    const uint32_t* slot_docs; // [ntiles + 1] documents starting before each tile (only when slot_extra != 0)
-    int32_t* stage;            // tile t's slot starts at t * stride + slot_docs[t] * slot_extra
+    const unsigned long long* slot_off;  // [ntiles + 1] start of each tile's slot: t * stride + docs_before(t) * slot_extra
+    int32_t* stage;
     uint32_t tile_lo, tile_hi; // tiles of the current segment
     uint32_t seg;
     MissEntry* miss;
@@ -190,9 +190,7 @@ struct Job {
 // staging slot of a tile: room for one id per symbol of the pretokens starting in it, plus the prefix ids of the
 // documents starting in it (so a prefix model does not pay the prefix room on every tile)
 __device__ __forceinline__ int32_t* stage_slot(const Job& J, unsigned long long tile) {
-    unsigned long long o = tile * J.stride;
-    if (J.slot_extra) o += (unsigned long long)__ldg(J.slot_docs + tile) * J.slot_extra;
-    return J.stage + o;
+    return J.stage + __ldg(J.slot_off + tile);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -47,19 +47,22 @@ __global__ void doc_kernel(Job J) {
 }
 
 // scalar restatement (hut_classify.h) of one 32-byte chunk: only used when an over-long UTF-8 form is in the tile
-// documents starting before each tile (lower bound of the tile's first byte in doc_off): the variable part of the
-// staging slot offsets of a prefix model, see stage_slot()
-__global__ void slot_docs_kernel(Job J, uint32_t* out) {
+// start of every tile's staging slot: tile * stride, plus slot_extra ids for each document starting before the tile
+// (lower bound of the tile's first byte in doc_off) for a prefix model; see stage_slot()
+__global__ void slot_docs_kernel(Job J, unsigned long long* out) {
     const unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t > J.ntiles) return;
-    const unsigned long long pos = t * OWN;
-    unsigned long long a = 0, b = J.ndocs;
-    while (a < b) {
-        const unsigned long long mid = (a + b) >> 1;
-        if (J.doc_off[mid] < pos) a = mid + 1;
-        else b = mid;
+    unsigned long long a = 0;
+    if (J.slot_extra) {
+        const unsigned long long pos = t * OWN;
+        unsigned long long b = J.ndocs;
+        while (a < b) {
+            const unsigned long long mid = (a + b) >> 1;
+            if (J.doc_off[mid] < pos) a = mid + 1;
+            else b = mid;
+        }
     }
-    out[t] = (uint32_t)a;
+    out[t] = t * J.stride + a * J.slot_extra;
 }
 
 __device__ __noinline__ void generic_chunk(const WarpSm& ws, int lane, uint32_t* ST, uint32_t* NU) {
@@ -183,6 +186,7 @@ __global__ void __launch_bounds__(NT, 4) tile_kernel(const __grid_constant__ Dev
     const uint32_t gw = blockIdx.x * WPB + warp, nw = gridDim.x * WPB;
 
     for (uint32_t tile = J.tile_lo + gw; tile < J.tile_hi; tile += nw) {
+        const unsigned long long slot_o = __ldg(J.slot_off + tile);  // asked for early: used only after the classifier
         const long long g0 = (long long)tile * OWN - BACK;  // global position of span index 0
         const long long lo = g0 < 0 ? 0 : g0;
         const long long hi = (g0 + LOADB) < (long long)J.nbytes ? (g0 + LOADB) : (long long)J.nbytes;
@@ -283,7 +287,7 @@ __global__ void __launch_bounds__(NT, 4) tile_kernel(const __grid_constant__ Dev
         uint32_t def_head = NODOC, def_tail = NODOC;
         bool holes = false;
         uint32_t slack = 0;                     // room reserved for misses of this tile that stayed unused
-        int32_t* const slot = stage_slot(J, tile);
+        int32_t* const slot = J.stage + slot_o;
         for (uint32_t r0 = 0; r0 < n; r0 += 32) {
             const uint32_t q = r0 + lane;
             const bool active = q < n;
