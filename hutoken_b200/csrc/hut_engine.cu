@@ -203,7 +203,8 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     CU(ctx, cudaMalloc(&d->cut, sizeof(CutRanges)));
 
     int per_sm = 0, sms = 0;
-    CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile_kernel, NT, 0));
+    if (m->has_prefix) CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile_kernel<true>, NT, 0));
+    else CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile_kernel<false>, NT, 0));
     CU(ctx, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
     if (per_sm < 1) per_sm = 1;
     d->sms = sms;
@@ -452,7 +453,9 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     J.tile_hi = ntiles;
     J.seg = 0;
     const uint32_t want = (ntiles + WPB - 1) / WPB;
-    tile_kernel<<<want < (uint32_t)d->grid ? want : (uint32_t)d->grid, NT, 0, st>>>(d->dm, J);
+    const uint32_t tile_grid = want < (uint32_t)d->grid ? want : (uint32_t)d->grid;
+    if (d->dm.has_prefix) tile_kernel<true><<<tile_grid, NT, 0, st>>>(d->dm, J);
+    else tile_kernel<false><<<tile_grid, NT, 0, st>>>(d->dm, J);
     {
         const uint32_t mg = ntiles / 4 + 1;
         miss_kernel<<<mg < (uint32_t)d->miss_grid ? mg : (uint32_t)d->miss_grid, MNT, 0, st>>>(d->dm, J);

@@ -156,6 +156,9 @@ __device__ __forceinline__ uint32_t run_batch(const DevModel& M, const Job& J, c
     return slack;
 }
 
+// PFX: the model has a prefix (first pretoken of a document keyed apart, staging slots of uneven size read from
+// J.slot_off); without one the slot of a tile is tile * stride, a warp-uniform product that needs no load.
+template <bool PFX>
 __global__ void __launch_bounds__(NT, 4) tile_kernel(const __grid_constant__ DevModel M, const __grid_constant__ Job J) {
     __shared__ TileSm sm;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -186,7 +189,8 @@ __global__ void __launch_bounds__(NT, 4) tile_kernel(const __grid_constant__ Dev
     const uint32_t gw = blockIdx.x * WPB + warp, nw = gridDim.x * WPB;
 
     for (uint32_t tile = J.tile_lo + gw; tile < J.tile_hi; tile += nw) {
-        const unsigned long long slot_o = __ldg(J.slot_off + tile);  // asked for early: used only after the classifier
+        unsigned long long slot_o = 0;
+        if (PFX) slot_o = __ldg(J.slot_off + tile);  // asked for early: used only after the classifier
         const long long g0 = (long long)tile * OWN - BACK;  // global position of span index 0
         const long long lo = g0 < 0 ? 0 : g0;
         const long long hi = (g0 + LOADB) < (long long)J.nbytes ? (g0 + LOADB) : (long long)J.nbytes;
@@ -287,7 +291,7 @@ __global__ void __launch_bounds__(NT, 4) tile_kernel(const __grid_constant__ Dev
         uint32_t def_head = NODOC, def_tail = NODOC;
         bool holes = false;
         uint32_t slack = 0;                     // room reserved for misses of this tile that stayed unused
-        int32_t* const slot = J.stage + slot_o;
+        int32_t* const slot = J.stage + (PFX ? slot_o : (unsigned long long)tile * J.stride);
         for (uint32_t r0 = 0; r0 < n; r0 += 32) {
             const uint32_t q = r0 + lane;
             const bool active = q < n;
@@ -297,7 +301,7 @@ __global__ void __launch_bounds__(NT, 4) tile_kernel(const __grid_constant__ Dev
             const bool keyed = len <= CACHE_KEY_MAX;
             uint32_t dsb = 0;
             if (tile_docs) dsb = (ws.dsm[s >> 5] >> (s & 31)) & 1u;
-            const uint32_t first = M.has_prefix ? dsb : 0u;
+            const uint32_t first = PFX ? dsb : 0u;
             uint32_t key[4], w[4] = {0u, 0u, 0u, 0u};
             const uint32_t b0 = build_key(ws.text, sm.kmask, s, keyed ? len : 0, first, key);
             const bool dummy = !active || b0 == 0;       // NUL boundary (zero fill past the end of the text)
