@@ -605,7 +605,12 @@ extern "C" int hut_plan_shards(const uint64_t* doc_offsets, uint64_t n_docs, int
 struct chunk_plan {
     uint64_t doc_lo, doc_hi, byte_lo, byte_hi, n_ids, id_base;
     int dev, buf;
+    cudaEvent_t tr[6];  // HUTOKEN_B200_TRACE: upload, kernels, download (start / end each); null otherwise
 };
+#define TRACE(p, i, stream)                                      \
+    do {                                                         \
+        if ((p)->tr[i]) CU(ctx, cudaEventRecord((p)->tr[i], stream)); \
+    } while (0)
 
 static int drain_outputs(hut_ctx* ctx) {
     for (int i = 0; i < ctx->ndev; ++i) {
@@ -644,12 +649,17 @@ static int chunk_issue(hut_ctx* ctx, const uint8_t* bytes, const uint64_t* doc_o
         c->h_off_cap = n;
     }
     for (uint64_t i = 0; i <= nd; ++i) c->h_off[i] = doc_offsets[p->doc_lo + i] - p->byte_lo;
+    TRACE(p, 0, d->s_in);
     if (nb) CU(ctx, cudaMemcpyAsync(c->d_text, bytes + p->byte_lo, nb, cudaMemcpyHostToDevice, d->s_in));
     CU(ctx, cudaMemcpyAsync(c->d_off, c->h_off, (nd + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, d->s_in));
     CU(ctx, cudaEventRecord(c->ev_in, d->s_in));
+    TRACE(p, 1, d->s_in);
     CU(ctx, cudaStreamWaitEvent(d->stream, c->ev_in, 0));
-    return launch_shard(ctx, d, &d->fl[p->buf], c->d_text, nb, (const uint64_t*)c->d_off, nd, c->d_ids, c->d_ids_cap,
-                        (uint64_t*)c->d_tok, d->stream, 0, 0);
+    TRACE(p, 2, d->stream);
+    const int rc = launch_shard(ctx, d, &d->fl[p->buf], c->d_text, nb, (const uint64_t*)c->d_off, nd, c->d_ids,
+                                c->d_ids_cap, (uint64_t*)c->d_tok, d->stream, 0, 0);
+    if (rc == HUT_STATUS_OK) TRACE(p, 3, d->stream);
+    return rc;
 }
 
 /* waits for the chunk's kernels, then starts the download of its ids and offsets into the final pinned buffers */
@@ -677,6 +687,7 @@ static int chunk_complete(hut_ctx* ctx, chunk_plan* p, uint64_t id_base, uint64_
         ctx->h_ids_cap = need;
         CU(ctx, cudaSetDevice(d->device));
     }
+    TRACE(p, 4, d->s_out);
     if (p->n_ids)
         CU(ctx, cudaMemcpyAsync(ctx->h_ids + id_base, c->d_ids, p->n_ids * sizeof(int32_t), cudaMemcpyDeviceToHost,
                                 d->s_out));
@@ -685,6 +696,7 @@ static int chunk_complete(hut_ctx* ctx, chunk_plan* p, uint64_t id_base, uint64_
         CU(ctx, cudaMemcpyAsync(ctx->h_tok + p->doc_lo, c->d_tok, nd * sizeof(uint64_t), cudaMemcpyDeviceToHost,
                                 d->s_out));
     CU(ctx, cudaEventRecord(c->ev_out, d->s_out));
+    TRACE(p, 5, d->s_out);
     c->out_pending = 1;
     return HUT_STATUS_OK;
 }
@@ -722,6 +734,12 @@ extern "C" int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64
         plan[k].buf = (k / ndev) & 1;
     }
     free(bounds);
+    const bool trace = getenv("HUTOKEN_B200_TRACE") != nullptr;  // per-chunk timeline on stderr (profiles/README.md)
+    if (trace)
+        for (int k = 0; k < nch; ++k) {
+            cudaSetDevice(ctx->dev[plan[k].dev].device);
+            for (int i = 0; i < 6; ++i) cudaEventCreate(&plan[k].tr[i]);
+        }
     int rc = HUT_STATUS_OK;
     auto bail = [&](int st) {
         for (int i = 0; i < ctx->ndev; ++i) {
@@ -755,6 +773,17 @@ extern "C" int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64
     rc = drain_outputs(ctx);
     if (rc != HUT_STATUS_OK) return bail(rc);
     for (int i = 0; i < ndev; ++i) ctx->dev[i].cb[0].out_pending = ctx->dev[i].cb[1].out_pending = 0;
+    if (trace) {
+        for (int k = 0; k < nch; ++k) {
+            float t[6] = {0, 0, 0, 0, 0, 0};
+            for (int i = 0; i < 6; ++i) cudaEventElapsedTime(&t[i], plan[plan[k].dev].tr[0], plan[k].tr[i]);
+            fprintf(stderr, "hut trace chunk %d dev %d MB %.1f ids %llu | up %.3f-%.3f | kernels %.3f-%.3f | down %.3f-%.3f ms\n",
+                    k, plan[k].dev, (double)(plan[k].byte_hi - plan[k].byte_lo) / 1048576.0,
+                    (unsigned long long)plan[k].n_ids, t[0], t[1], t[2], t[3], t[4], t[5]);
+        }
+        for (int k = 0; k < nch; ++k)
+            for (int i = 0; i < 6; ++i) cudaEventDestroy(plan[k].tr[i]);
+    }
     // per-chunk offsets are local: add each chunk's base (host side, one add per document -- 8(e))
     for (int k = 0; k < nch; ++k)
         if (plan[k].id_base)
