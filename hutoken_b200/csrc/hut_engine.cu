@@ -747,6 +747,10 @@ extern "C" int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64
             cudaDeviceSynchronize();
             ctx->dev[i].cb[0].out_pending = ctx->dev[i].cb[1].out_pending = 0;
         }
+        if (trace)
+            for (int k = 0; k < nch; ++k)
+                for (int i = 0; i < 6; ++i)
+                    if (plan[k].tr[i]) cudaEventDestroy(plan[k].tr[i]);
         free(plan);
         return st;
     };
