@@ -189,6 +189,7 @@ struct DecSm {
     uint8_t d1slot[DEC_TRIE_SM];         // 1 + row of pair2 for the children of the root, 0 otherwise
     uint16_t pair2[DEC_D1][256];         // child of a depth-1 node by the second byte: no hashing for 2-byte patterns
     uint32_t use_d1;
+    uint4 outbuf[(DEC_TILE + 32) / 16];  // one-pass path: the tile's output at the 16-byte phase of its destination
     unsigned long long scan[32];
     unsigned long long tot;
     uint32_t entry;
@@ -272,6 +273,104 @@ __global__ void __launch_bounds__(DEC_NT) dec_doc_kernel(DecModel D, const unsig
                 if (tid == 0) sm.entry = entry - tile_len;
                 __syncthreads();
                 continue;
+            }
+            // ---- one-pass path (direct second-byte table): thread t owns positions [8t, 8t + 8) and keeps the step and
+            //      the output of each in registers.  If every visited position is the start of a well-formed character
+            //      and steps exactly over it (an ordinary character, or a replacement as long as its first
+            //      character), the visited positions are the character starts from the entry on: one block scan of
+            //      the emitted lengths places the bytes and nothing else is needed. ----
+            if (use_d1) {
+                const uint32_t p0 = (uint32_t)tid * 8u;
+                const uint32_t* wp = reinterpret_cast<const uint32_t*>(sm.rawbuf) + ((mis + p0) >> 2);
+                const uint32_t sh = ((mis + p0) & 3u) * 8u;
+                const uint32_t r0_ = wp[0], r1_ = wp[1], r2_ = wp[2], r3_ = wp[3];
+                const uint32_t x[3] = {__funnelshift_r(r0_, r1_, sh), __funnelshift_r(r1_, r2_, sh),
+                                       __funnelshift_r(r2_, r3_, sh)};
+                auto B = [&](int k) -> uint32_t { return (x[k >> 2] >> ((k & 3) * 8)) & 0xFFu; };
+                bool ok = true;
+                uint32_t mine = 0;
+                uint32_t outs[2] = {0u, 0u};  // byte k: the byte position p0 + k emits (replacement / byte mode)
+                uint32_t emits = 0;           // nibble k: bytes position p0 + k emits; bit 3 = they are copied from the text
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const uint32_t i = p0 + k;
+                    const uint32_t c0 = B(k), c1 = B(k + 1), c2 = B(k + 2), c3 = B(k + 3);
+                    if ((c0 & 0xC0u) == 0x80u || i < entry || i >= tile_len) continue;
+                    uint32_t cl, cp;
+                    bool wf;  // continuation bytes in place, and the byte after the character is not one
+                    if (c0 < 0x80u) { cl = 1; cp = c0; wf = (c1 & 0xC0u) != 0x80u; }
+                    else if ((c0 & 0xE0u) == 0xC0u) {
+                        cl = 2; cp = ((c0 & 0x1Fu) << 6) | (c1 & 0x3Fu);
+                        wf = (c1 & 0xC0u) == 0x80u && (c2 & 0xC0u) != 0x80u;
+                    } else if ((c0 & 0xF0u) == 0xE0u) {
+                        cl = 3; cp = ((c0 & 0x0Fu) << 12) | ((c1 & 0x3Fu) << 6) | (c2 & 0x3Fu);
+                        wf = (c1 & 0xC0u) == 0x80u && (c2 & 0xC0u) == 0x80u && (c3 & 0xC0u) != 0x80u;
+                    } else if ((c0 & 0xF8u) == 0xF0u) {
+                        cl = 4; cp = ((c0 & 0x07u) << 18) | ((c1 & 0x3Fu) << 12) | ((c2 & 0x3Fu) << 6) | (c3 & 0x3Fu);
+                        wf = (c1 & 0xC0u) == 0x80u && (c2 & 0xC0u) == 0x80u && (c3 & 0xC0u) == 0x80u &&
+                             (B(k + 4) & 0xC0u) != 0x80u;
+                    } else { cl = 1; cp = 0xFFFDu; wf = (c1 & 0xC0u) != 0x80u; }
+                    uint32_t step = 0, out = 0, emit = 1;
+                    const uint32_t node = sm.root_child[c0];
+                    if (node) {  // longest replacement starting here: one or two bytes without hashing
+                        int o = sm.tout[node];
+                        if (o >= 0) { step = 1; out = (uint32_t)o; }
+                        const uint32_t n2 = i + 1 < avail ? (uint32_t)sm.pair2[sm.d1slot[node] - 1][c1] : 0u;
+                        if (n2) {
+                            if (sm.tkid[n2]) wf = false;  // a longer replacement may start here: general path
+                            else if ((o = sm.tout[n2]) >= 0) { step = 2; out = (uint32_t)o; }
+                        }
+                    }
+                    if (!step) {
+                        step = cl;
+                        if (D.byte_mode) out = cp < 256u ? cp : (uint32_t)'?';  // pretokenizer.c:247-254
+                        else emit = 8u | cl;                                     // copied (pretokenizer.c:283-287)
+                    }
+                    ok = ok && wf && step == cl;
+                    outs[k >> 2] |= (out & 0xFFu) << ((k & 3) * 8);
+                    emits |= emit << (4 * k);
+                    mine += emit & 7u;
+                }
+                const bool one_pass = __syncthreads_and(ok && (rw[entry] & 0xC0u) != 0x80u) != 0;
+                if (one_pass) {
+                    const unsigned long long ex = block_exclusive_u64(mine, &sm.tot, sm.scan);
+                    uint8_t* const dst = dec + r0 + written;
+                    const uint32_t ph = (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u);
+                    uint8_t* ob = reinterpret_cast<uint8_t*>(sm.outbuf) + ph + (uint32_t)ex;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const uint32_t e = (emits >> (4 * k)) & 15u;
+                        if (!e) continue;
+                        if (e & 8u) {
+                            for (uint32_t c = 0; c < (e & 7u); ++c) *ob++ = (uint8_t)B(k + (int)c);
+                        } else {
+                            *ob++ = (uint8_t)(outs[k >> 2] >> ((k & 3) * 8));
+                        }
+                    }
+                    const uint32_t total = (uint32_t)sm.tot;
+                    if (tid == 0) {  // hand-over: the first character start at or after the end of the tile
+                        uint32_t k = 0;
+                        while (k < 4 && (rw[tile_len + k] & 0xC0) == 0x80) ++k;
+                        sm.entry = k;
+                    }
+                    __syncthreads();
+                    // staged bytes -> global: 16-byte stores where the destination is aligned, bytes at the two ends
+                    const uint32_t end = ph + total;
+                    const uint8_t* const sb = reinterpret_cast<const uint8_t*>(sm.outbuf);
+                    uint8_t* const gb = dst - ph;  // 16-byte aligned
+                    for (uint32_t w = tid; w * 16u < end; w += DEC_NT) {
+                        const uint32_t lo = w * 16u, hi = lo + 16u;
+                        if (lo >= ph && hi <= end) {
+                            reinterpret_cast<uint4*>(gb)[w] = sm.outbuf[w];
+                        } else {
+                            const uint32_t a = lo > ph ? lo : ph, b = hi < end ? hi : end;
+                            for (uint32_t q = a; q < b; ++q) gb[q] = sb[q];
+                        }
+                    }
+                    written += total;
+                    __syncthreads();
+                    continue;
+                }
             }
             // ---- the step every position would take ----
             // `simple` stays true while every character start steps exactly over its own well-formed character: then
