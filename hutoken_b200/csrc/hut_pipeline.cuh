@@ -4,6 +4,10 @@
 
 #include "hut_kernels.cuh"
 
+#ifndef HUT_TILE_CTAS
+#define HUT_TILE_CTAS 4  // resident CTAs per SM tile_kernel is compiled for (64 registers per thread)
+#endif
+
 namespace hut {
 
 // shared memory of ONE WARP of tile_kernel
@@ -159,7 +163,7 @@ __device__ __forceinline__ uint32_t run_batch(const DevModel& M, const Job& J, c
 // PFX: the model has a prefix (first pretoken of a document keyed apart, staging slots of uneven size read from
 // J.slot_off); without one the slot of a tile is tile * stride, a warp-uniform product that needs no load.
 template <bool PFX>
-__global__ void __launch_bounds__(NT, 4) tile_kernel(const __grid_constant__ DevModel M, const __grid_constant__ Job J) {
+__global__ void __launch_bounds__(NT, HUT_TILE_CTAS) tile_kernel(const __grid_constant__ DevModel M, const __grid_constant__ Job J) {
     __shared__ TileSm sm;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t FULL = 0xFFFFFFFFu;
