@@ -10,9 +10,10 @@
 // (independent, parallel), then the positions really visited are found by binary lifting over those steps
 // (next^(2^k) tables in shared memory) from the tile's entry offset, which the previous tile hands over.
 //
-// Data layout: ids int32[n] + tok_off uint64[ndocs+1] -> len32[n] -> (scan) raw_off uint64[n+1] -> raw bytes
-// (documents back to back, 64 zero bytes of padding) -> dec bytes written at the same base (a step never emits more
-// bytes than it consumes) + doc_len uint32[ndocs] -> (scan) text_off uint64[ndocs+1] -> text packed.
+// Data layout: ids int32[n] + tok_off uint64[ndocs+1] -> sub_len uint32[n/256] (token bytes per 256 ids) -> (scan)
+// sub_off uint64[n/256+1] -> raw bytes (documents back to back, 64 zero bytes of padding) -> dec bytes written at the
+// same base (a step never emits more bytes than it consumes) + doc_raw uint64[ndocs] + doc_len uint32[ndocs] ->
+// (scan) text_off uint64[ndocs+1] -> text packed.
 #pragma once
 #include <cstdint>
 
@@ -124,38 +125,120 @@ __global__ void __launch_bounds__(SCAN_NT) scan_apply_kernel(const uint32_t* in,
 }
 
 // ------------------------------------------------------------------------------------------------
-// ids -> token lengths (bounds check of core.c:520-531), token bytes -> raw text
+// ids -> token lengths (bounds check of core.c:520-531) summed per sub-block of DEC_SUB ids; after the scan of the
+// sub-block sums, token bytes -> raw text.  No per-id offset array is kept: a position inside a sub-block is
+// recomputed from the ids (the length table is 4 bytes per vocab line and stays in L1 / L2).
 // ------------------------------------------------------------------------------------------------
-__global__ void dec_len_kernel(DecModel D, const int32_t* ids, unsigned long long n, uint32_t* len32,
-                               unsigned int* bad) {
-    const unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const int32_t id = ids[i];
-    uint32_t l = HUT_DEC_MISSING;
-    if (id >= 0 && (uint32_t)id < D.vocab_lines) l = __ldg(D.dec_len + id);
-    if (l == HUT_DEC_MISSING) {
-        atomicExch(bad, 1u);
-        l = 0;
-    }
-    len32[i] = l;
+constexpr int DEC_SUB = 256;
+
+// HUT_DEC_MISSING for an id outside the vocabulary or carried by no line
+__device__ __forceinline__ uint32_t dec_token_len(const DecModel& D, int32_t id) {
+    return (id >= 0 && (uint32_t)id < D.vocab_lines) ? __ldg(D.dec_len + id) : (uint32_t)HUT_DEC_MISSING;
 }
 
-__global__ void dec_gather_kernel(DecModel D, const int32_t* ids, unsigned long long n,
-                                  const unsigned long long* raw_off, uint8_t* raw) {
-    const unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i > n) return;
-    if (i == n) {  // zero padding read by the last tile's look-ahead
-        uint8_t* p = raw + raw_off[n];
-        for (int k = 0; k < 64; ++k) p[k] = 0;
-        return;
+// warp per sub-block, 8 consecutive ids per lane
+__global__ void __launch_bounds__(256) dec_sub_kernel(DecModel D, const int32_t* ids, unsigned long long n,
+                                                      uint32_t* sub_len, unsigned int* bad) {
+    const int lane = threadIdx.x & 31;
+    const unsigned long long blk = (unsigned long long)blockIdx.x * 8u + (threadIdx.x >> 5);
+    if (blk * DEC_SUB >= n) return;
+    const unsigned long long i0 = blk * DEC_SUB + (unsigned long long)lane * 8u;
+    int32_t id[8];
+    if (i0 + 8 <= n && (reinterpret_cast<uintptr_t>(ids) & 15u) == 0) {
+        const int4 a = reinterpret_cast<const int4*>(ids + i0)[0], b = reinterpret_cast<const int4*>(ids + i0)[1];
+        id[0] = a.x; id[1] = a.y; id[2] = a.z; id[3] = a.w;
+        id[4] = b.x; id[5] = b.y; id[6] = b.z; id[7] = b.w;
+    } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) id[k] = i0 + k < n ? ids[i0 + k] : 0;
     }
-    const int32_t id = ids[i];
-    if (id < 0 || (uint32_t)id >= D.vocab_lines) return;
-    const uint32_t l = __ldg(D.dec_len + id);
-    if (l == HUT_DEC_MISSING) return;
-    const uint8_t* src = D.dec_pool + __ldg(D.dec_off + id);
-    uint8_t* dst = raw + raw_off[i];
-    for (uint32_t k = 0; k < l; ++k) dst[k] = __ldg(src + k);
+    uint32_t sum = 0;
+    bool missing = false;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        if (i0 + k >= n) continue;
+        const uint32_t l = dec_token_len(D, id[k]);
+        if (l == HUT_DEC_MISSING) missing = true;
+        else sum += l;
+    }
+    if (missing) atomicExch(bad, 1u);
+#pragma unroll
+    for (int d = 16; d; d >>= 1) sum += __shfl_xor_sync(0xFFFFFFFFu, sum, d);
+    if (lane == 0) sub_len[blk] = sum;
+}
+
+// Warp per sub-block (n / DEC_SUB + 1 of them: the last one also writes the 64 zero bytes the last tile's
+// look-ahead reads).  Every lane takes 8 consecutive ids, the warp scans their lengths, the token bytes are put
+// together in shared memory at the 16-byte phase of their destination and leave in 16-byte stores.
+constexpr int GATHER_WARPS = 8;
+constexpr int GATHER_STAGE = 2048;  // bytes of one sub-block that fit the staging buffer; larger ones are written directly
+
+__global__ void __launch_bounds__(GATHER_WARPS * 32) dec_gather_kernel(DecModel D, const int32_t* ids,
+                                                                       unsigned long long n,
+                                                                       const unsigned long long* sub_off,
+                                                                       uint8_t* raw) {
+    __shared__ uint4 stage[GATHER_WARPS][(GATHER_STAGE + 32) / 16];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned long long blk = (unsigned long long)blockIdx.x * GATHER_WARPS + warp;
+    if (blk > n / DEC_SUB) return;  // warps never synchronise with each other
+    const unsigned long long i0 = blk * DEC_SUB + (unsigned long long)lane * 8u;
+    int32_t id[8];
+    if (i0 + 8 <= n && (reinterpret_cast<uintptr_t>(ids) & 15u) == 0) {
+        const int4 a = reinterpret_cast<const int4*>(ids + i0)[0], b = reinterpret_cast<const int4*>(ids + i0)[1];
+        id[0] = a.x; id[1] = a.y; id[2] = a.z; id[3] = a.w;
+        id[4] = b.x; id[5] = b.y; id[6] = b.z; id[7] = b.w;
+    } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) id[k] = i0 + k < n ? ids[i0 + k] : -1;
+    }
+    uint32_t l[8], mine = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        l[k] = dec_token_len(D, id[k]);
+        if (l[k] == HUT_DEC_MISSING) l[k] = 0;
+        mine += l[k];
+    }
+    uint32_t inc = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+        if (lane >= d) inc += t;
+    }
+    const uint32_t total = __shfl_sync(0xFFFFFFFFu, inc, 31), before = inc - mine;
+    uint8_t* const gdst = raw + sub_off[blk];
+    if (total <= (uint32_t)GATHER_STAGE) {
+        const uint32_t ph = (uint32_t)(reinterpret_cast<uintptr_t>(gdst) & 15u);
+        uint8_t* sp = reinterpret_cast<uint8_t*>(stage[warp]) + ph + before;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            if (!l[k]) continue;
+            const uint8_t* src = D.dec_pool + __ldg(D.dec_off + id[k]);
+            for (uint32_t c = 0; c < l[k]; ++c) *sp++ = __ldg(src + c);
+        }
+        __syncwarp();
+        const uint32_t end = ph + total;
+        const uint8_t* const sb = reinterpret_cast<const uint8_t*>(stage[warp]);
+        uint8_t* const gb = gdst - ph;  // 16-byte aligned
+        for (uint32_t w = lane; w * 16u < end; w += 32) {
+            const uint32_t lo = w * 16u, hi = lo + 16u;
+            if (lo >= ph && hi <= end) {
+                reinterpret_cast<uint4*>(gb)[w] = stage[warp][w];
+            } else {
+                const uint32_t a = lo > ph ? lo : ph, b = hi < end ? hi : end;
+                for (uint32_t q = a; q < b; ++q) gb[q] = sb[q];
+            }
+        }
+    } else {
+        uint8_t* dst = gdst + before;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            if (!l[k]) continue;
+            const uint8_t* src = D.dec_pool + __ldg(D.dec_off + id[k]);
+            for (uint32_t c = 0; c < l[k]; ++c) *dst++ = __ldg(src + c);
+        }
+    }
+    if (blk == n / DEC_SUB)
+        for (int k = lane; k < 64; k += 32) gdst[total + k] = 0;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -195,9 +278,10 @@ struct DecSm {
     uint32_t entry;
 };
 
-__global__ void __launch_bounds__(DEC_NT) dec_doc_kernel(DecModel D, const unsigned long long* tok_off,
-                                                         unsigned long long ndocs, const unsigned long long* raw_off,
-                                                         const uint8_t* raw, uint8_t* dec, uint32_t* doc_len) {
+__global__ void __launch_bounds__(DEC_NT) dec_doc_kernel(DecModel D, const int32_t* ids, const unsigned long long* tok_off,
+                                                         unsigned long long ndocs, const unsigned long long* sub_off,
+                                                         const uint8_t* raw, uint8_t* dec, uint32_t* doc_len,
+                                                         unsigned long long* doc_raw) {
     __shared__ DecSm sm;
     const int tid = threadIdx.x;
     for (int i = tid; i < 256; i += DEC_NT) sm.root_child[i] = D.root_child[i];
@@ -241,8 +325,22 @@ __global__ void __launch_bounds__(DEC_NT) dec_doc_kernel(DecModel D, const unsig
     __syncthreads();
     const bool use_d1 = sm.use_d1 != 0;
     for (unsigned long long d = blockIdx.x; d < ndocs; d += gridDim.x) {
-        const unsigned long long r0 = raw_off[tok_off[d]], r1 = raw_off[tok_off[d + 1]];
+        // raw offset of id index t: the scanned sum of its sub-block + the lengths of the ids before it inside the
+        // sub-block, added up by the whole CTA
+        auto raw_at = [&](unsigned long long t) -> unsigned long long {
+            unsigned long long part = 0;
+            for (unsigned long long j = (t & ~(unsigned long long)(DEC_SUB - 1)) + tid; j < t; j += DEC_NT) {
+                const uint32_t l = dec_token_len(D, ids[j]);
+                if (l != HUT_DEC_MISSING) part += l;
+            }
+            block_exclusive_u64(part, &sm.tot, sm.scan);
+            const unsigned long long r = sub_off[t / DEC_SUB] + sm.tot;
+            __syncthreads();  // sm.tot is written again by the next call
+            return r;
+        };
+        const unsigned long long r0 = raw_at(tok_off[d]), r1 = raw_at(tok_off[d + 1]);
         const unsigned long long rlen = r1 - r0;
+        if (tid == 0) doc_raw[d] = r0;
         unsigned long long written = 0;
         // ---- prefix, stripped once when the raw text starts with it (pretokenizer.c:209-215) ----
         if (tid == 0) {
@@ -530,18 +628,32 @@ __global__ void __launch_bounds__(DEC_NT) dec_doc_kernel(DecModel D, const unsig
     }
 }
 
-// decoded bytes of each document -> packed text
-__global__ void dec_pack_kernel(const unsigned long long* tok_off, unsigned long long ndocs,
-                                const unsigned long long* raw_off, const uint8_t* dec,
+// decoded bytes of each document -> packed text.  Warp per document; 16-byte stores at the destination's alignment,
+// the source read as aligned 32-bit words and shifted into place (both ends of the document byte by byte)
+__global__ void dec_pack_kernel(unsigned long long ndocs, const unsigned long long* doc_raw, const uint8_t* dec,
                                 const unsigned long long* text_off, uint8_t* text) {
     const unsigned long long w = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     const unsigned long long nw = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
     for (unsigned long long d = w; d < ndocs; d += nw) {
-        const uint8_t* src = dec + raw_off[tok_off[d]];
+        const uint8_t* src = dec + doc_raw[d];
         uint8_t* dst = text + text_off[d];
         const unsigned long long n = text_off[d + 1] - text_off[d];
-        for (unsigned long long i = lane; i < n; i += 32) dst[i] = src[i];
+        unsigned long long head = (16u - (reinterpret_cast<uintptr_t>(dst) & 15u)) & 15u;
+        if (head > n) head = n;
+        for (unsigned long long i = lane; i < head; i += 32) dst[i] = src[i];
+        const uint8_t* s2 = src + head;
+        const unsigned long long nwords = (n - head) >> 4;
+        const uint32_t mis = (uint32_t)(reinterpret_cast<uintptr_t>(s2) & 3u), sh = mis * 8u;
+        const uint32_t* sw = reinterpret_cast<const uint32_t*>(s2 - mis);
+        uint4* dw = reinterpret_cast<uint4*>(dst + head);
+        for (unsigned long long q = lane; q < nwords; q += 32) {
+            const uint32_t* p = sw + 4 * q;
+            const uint32_t r0 = p[0], r1 = p[1], r2 = p[2], r3 = p[3], r4 = p[4];  // d_dec has 128 spare bytes
+            dw[q] = make_uint4(__funnelshift_r(r0, r1, sh), __funnelshift_r(r1, r2, sh), __funnelshift_r(r2, r3, sh),
+                               __funnelshift_r(r3, r4, sh));
+        }
+        for (unsigned long long i = head + (nwords << 4) + lane; i < n; i += 32) dst[i] = src[i];
     }
 }
 

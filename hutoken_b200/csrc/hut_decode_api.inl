@@ -9,10 +9,12 @@ struct hut_decstate {
     size_t d_ids_cap;
     unsigned long long* d_tok;
     size_t d_tok_cap;
-    uint32_t* d_len32;
-    size_t d_len32_cap;
-    unsigned long long* d_raw_off;
-    size_t d_raw_off_cap;
+    uint32_t* d_sub_len;          // token bytes per sub-block of DEC_SUB ids
+    size_t d_sub_len_cap;
+    unsigned long long* d_sub_off;  // their exclusive scan
+    size_t d_sub_off_cap;
+    unsigned long long* d_doc_raw;  // raw offset of every document
+    size_t d_doc_raw_cap;
     unsigned long long* d_bsum;
     size_t d_bsum_cap;
     uint8_t* d_raw;
@@ -39,8 +41,9 @@ static void dec_free(hut_decstate* s) {
     if (!s) return;
     cudaFree(s->d_ids);
     cudaFree(s->d_tok);
-    cudaFree(s->d_len32);
-    cudaFree(s->d_raw_off);
+    cudaFree(s->d_sub_len);
+    cudaFree(s->d_sub_off);
+    cudaFree(s->d_doc_raw);
     cudaFree(s->d_bsum);
     cudaFree(s->d_raw);
     cudaFree(s->d_dec);
@@ -105,32 +108,37 @@ static int dec_run(hut_ctx* ctx, const int32_t* d_ids, unsigned long long n_ids,
     hut_dev* d = &ctx->dev[0];
     const DecModel& D = s->dm;
     s->last_launches = 0;
-    CU(ctx, grow(&s->d_len32, &s->d_len32_cap, (size_t)n_ids + 1));
-    CU(ctx, grow(&s->d_raw_off, &s->d_raw_off_cap, (size_t)n_ids + 2));
+    const unsigned long long nsub = (n_ids + DEC_SUB - 1) / DEC_SUB;
+    if (n_ids / DEC_SUB + 1 > 0x7FFFFFFFull) return set_err(ctx, HUT_STATUS_ARG, "%s", "too many ids in one call");
+    CU(ctx, grow(&s->d_sub_len, &s->d_sub_len_cap, (size_t)nsub + 1));
+    CU(ctx, grow(&s->d_sub_off, &s->d_sub_off_cap, (size_t)nsub + 2));
+    CU(ctx, grow(&s->d_doc_raw, &s->d_doc_raw_cap, (size_t)n_docs + 1));
     CU(ctx, grow(&s->d_doc_len, &s->d_doc_len_cap, (size_t)n_docs + 1));
     CU(ctx, grow(&s->d_text_off, &s->d_text_off_cap, (size_t)n_docs + 2));
     CU(ctx, cudaEventRecord(s->ev[0], st));
     CU(ctx, cudaMemsetAsync(s->d_bad, 0, sizeof(unsigned int), st));
-    if (n_ids) {
-        dec_len_kernel<<<(unsigned)((n_ids + 255) / 256), 256, 0, st>>>(D, d_ids, n_ids, s->d_len32, s->d_bad);
+    if (nsub) {
+        dec_sub_kernel<<<(unsigned)((nsub + 7) / 8), 256, 0, st>>>(D, d_ids, n_ids, s->d_sub_len, s->d_bad);
         s->last_launches++;
     }
-    int rc = dec_scan(ctx, s, s->d_len32, n_ids, s->d_raw_off, st);
+    int rc = dec_scan(ctx, s, s->d_sub_len, nsub, s->d_sub_off, st);
     if (rc != HUT_STATUS_OK) return rc;
     unsigned long long raw_total = 0;
     unsigned int bad = 0;
-    CU(ctx, cudaMemcpyAsync(&raw_total, s->d_raw_off + n_ids, sizeof raw_total, cudaMemcpyDeviceToHost, st));
+    CU(ctx, cudaMemcpyAsync(&raw_total, s->d_sub_off + nsub, sizeof raw_total, cudaMemcpyDeviceToHost, st));
     CU(ctx, cudaMemcpyAsync(&bad, s->d_bad, sizeof bad, cudaMemcpyDeviceToHost, st));
     CU(ctx, cudaStreamSynchronize(st));
     if (bad)  /* core.c:522-530 */
         return set_err(ctx, HUT_STATUS_VALUE, "%s", "Element must be non-negative and less than vocab size.");
     CU(ctx, grow(&s->d_raw, &s->d_raw_cap, (size_t)raw_total + 128));
     CU(ctx, grow(&s->d_dec, &s->d_dec_cap, (size_t)raw_total + 128));
-    dec_gather_kernel<<<(unsigned)((n_ids + 1 + 255) / 256), 256, 0, st>>>(D, d_ids, n_ids, s->d_raw_off, s->d_raw);
+    dec_gather_kernel<<<(unsigned)((n_ids / DEC_SUB + 1 + GATHER_WARPS - 1) / GATHER_WARPS), GATHER_WARPS * 32, 0, st>>>(
+        D, d_ids, n_ids, s->d_sub_off, s->d_raw);
     s->last_launches++;
     if (n_docs) {
         const unsigned long long want = n_docs < (unsigned long long)d->sms * 12 ? n_docs : (unsigned long long)d->sms * 12;
-        dec_doc_kernel<<<(unsigned)want, DEC_NT, 0, st>>>(D, d_tok, n_docs, s->d_raw_off, s->d_raw, s->d_dec, s->d_doc_len);
+        dec_doc_kernel<<<(unsigned)want, DEC_NT, 0, st>>>(D, d_ids, d_tok, n_docs, s->d_sub_off, s->d_raw, s->d_dec,
+                                                          s->d_doc_len, s->d_doc_raw);
         s->last_launches++;
     }
     rc = dec_scan(ctx, s, s->d_doc_len, n_docs, s->d_text_off, st);
@@ -142,7 +150,7 @@ static int dec_run(hut_ctx* ctx, const int32_t* d_ids, unsigned long long n_ids,
     if (n_docs) {
         const unsigned long long blocks = (n_docs + 7) / 8;
         const unsigned long long cap = (unsigned long long)d->sms * 16;
-        dec_pack_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, st>>>(d_tok, n_docs, s->d_raw_off, s->d_dec,
+        dec_pack_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, st>>>(n_docs, s->d_doc_raw, s->d_dec,
                                                                                  s->d_text_off, s->d_text);
         s->last_launches++;
     }
