@@ -392,42 +392,37 @@ __global__ void __launch_bounds__(DEC_NT) dec_doc_kernel(DecModel D, const int32
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
                     const uint32_t i = p0 + k;
-                    const uint32_t c0 = B(k), c1 = B(k + 1), c2 = B(k + 2), c3 = B(k + 3);
-                    if ((c0 & 0xC0u) == 0x80u || i < entry || i >= tile_len) continue;
-                    uint32_t cl, cp;
-                    bool wf;  // continuation bytes in place, and the byte after the character is not one
-                    if (c0 < 0x80u) { cl = 1; cp = c0; wf = (c1 & 0xC0u) != 0x80u; }
-                    else if ((c0 & 0xE0u) == 0xC0u) {
-                        cl = 2; cp = ((c0 & 0x1Fu) << 6) | (c1 & 0x3Fu);
-                        wf = (c1 & 0xC0u) == 0x80u && (c2 & 0xC0u) != 0x80u;
-                    } else if ((c0 & 0xF0u) == 0xE0u) {
-                        cl = 3; cp = ((c0 & 0x0Fu) << 12) | ((c1 & 0x3Fu) << 6) | (c2 & 0x3Fu);
-                        wf = (c1 & 0xC0u) == 0x80u && (c2 & 0xC0u) == 0x80u && (c3 & 0xC0u) != 0x80u;
-                    } else if ((c0 & 0xF8u) == 0xF0u) {
-                        cl = 4; cp = ((c0 & 0x07u) << 18) | ((c1 & 0x3Fu) << 12) | ((c2 & 0x3Fu) << 6) | (c3 & 0x3Fu);
-                        wf = (c1 & 0xC0u) == 0x80u && (c2 & 0xC0u) == 0x80u && (c3 & 0xC0u) == 0x80u &&
-                             (B(k + 4) & 0xC0u) != 0x80u;
-                    } else { cl = 1; cp = 0xFFFDu; wf = (c1 & 0xC0u) != 0x80u; }
-                    uint32_t step = 0, out = 0, emit = 1;
-                    const uint32_t node = sm.root_child[c0];
+                    const uint32_t c0 = B(k), c1 = B(k + 1), c2 = B(k + 2), c3 = B(k + 3), c4 = B(k + 4);
+                    // branch-free classification: neighbouring lanes sit on characters of different classes
+                    const bool live = (c0 & 0xC0u) != 0x80u && i >= entry && i < tile_len;
+                    uint32_t cl = c0 < 0x80u ? 1u : ((0x43221111u >> ((c0 >> 2) & 0x1Cu)) & 7u);
+                    if (c0 >= 0xF8u) cl = 1;  // not a lead byte: one byte, U+FFFD -> '?'
+                    const uint32_t cont = ((c1 & 0xC0u) == 0x80u ? 1u : 0u) | ((c2 & 0xC0u) == 0x80u ? 2u : 0u) |
+                                          ((c3 & 0xC0u) == 0x80u ? 4u : 0u) | ((c4 & 0xC0u) == 0x80u ? 8u : 0u);
+                    // continuation bytes in place and the byte after the character is not one; three- and four-byte
+                    // forms with a zero lead payload can be over-long encodings of code points below 256, which the
+                    // reference decodes to that byte: left to the general path
+                    bool wf = (cont & ((1u << cl) - 1u)) == (1u << (cl - 1u)) - 1u && !(cl >= 3u && (c0 & 0x0Fu) == 0u);
+                    uint32_t out = c0 < 0x80u ? c0
+                                              : (cl == 2u && (c0 & 0x1Cu) == 0u) ? (((c0 & 3u) << 6) | (c1 & 0x3Fu))
+                                                                                 : (uint32_t)'?';  // pretokenizer.c:247-254
+                    uint32_t step = cl, emit = D.byte_mode ? 1u : (8u | cl);  // plain mode: copied (pretokenizer.c:283-287)
+                    const uint32_t node = live ? sm.root_child[c0] : 0u;
                     if (node) {  // longest replacement starting here: one or two bytes without hashing
                         int o = sm.tout[node];
-                        if (o >= 0) { step = 1; out = (uint32_t)o; }
+                        if (o >= 0) { step = 1; out = (uint32_t)o; emit = 1; }
                         const uint32_t n2 = i + 1 < avail ? (uint32_t)sm.pair2[sm.d1slot[node] - 1][c1] : 0u;
                         if (n2) {
                             if (sm.tkid[n2]) wf = false;  // a longer replacement may start here: general path
-                            else if ((o = sm.tout[n2]) >= 0) { step = 2; out = (uint32_t)o; }
+                            else if ((o = sm.tout[n2]) >= 0) { step = 2; out = (uint32_t)o; emit = 1; }
                         }
                     }
-                    if (!step) {
-                        step = cl;
-                        if (D.byte_mode) out = cp < 256u ? cp : (uint32_t)'?';  // pretokenizer.c:247-254
-                        else emit = 8u | cl;                                     // copied (pretokenizer.c:283-287)
+                    ok = ok && (!live || (wf && step == cl));
+                    if (live) {
+                        outs[k >> 2] |= (out & 0xFFu) << ((k & 3) * 8);
+                        emits |= emit << (4 * k);
+                        mine += emit & 7u;
                     }
-                    ok = ok && wf && step == cl;
-                    outs[k >> 2] |= (out & 0xFFu) << ((k & 3) * 8);
-                    emits |= emit << (4 * k);
-                    mine += emit & 7u;
                 }
                 const bool one_pass = __syncthreads_and(ok && (rw[entry] & 0xC0u) != 0x80u) != 0;
                 if (one_pass) {
