@@ -263,3 +263,73 @@ def test_gpu_decode_python_surface():
         ext.batch_decode([])
     with pytest.raises(TypeError, match="Each item must be a list of integers."):
         ext.batch_decode([[1], 2])
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# every byte as a token: ragged, over-long and invalid UTF-8 through both decode paths
+# ---------------------------------------------------------------------------------------------------------------
+def _all_bytes_model(tmp):
+    """Vocab of the single bytes 0x01..0xFF (id = byte - 1) + GPT-2's special-chars table."""
+    v = os.path.join(tmp, "bytes.vocab.txt")
+    with open(v, "w") as f:
+        for b in range(1, 256):
+            f.write(f"0x{b:02X} == {b - 1}\n")
+    return v, synth.PATHS["gpt2_small"][1]
+
+
+def _byte_cases(rng):
+    """Byte strings (no 0x00): well-formed text (whole tiles take the one-pass path), the same with anomalies dropped
+    in (over-long forms E0 80 xx / F0 80 80 xx / C0 xx, invalid leads F8.., stray continuation bytes, truncated
+    characters, replacement strings cut short), and pure noise; short ones and ones spanning several 1 KiB tiles."""
+    good = "árvíztűrő tükörfúrógép hello, world! 123 ĠĊ ▁x € 😀 ".encode("utf-8")
+    odd = [b"\xE0\x80\x81", b"\xE0\x81\xBF", b"\xF0\x80\x80\x81", b"\xC0\x81", b"\xC1\xBF", b"\xF8", b"\xFF", b"\x80",
+           b"\xBF\xBF", b"\xC3", b"\xE2\x96", b"\xF0\x9F\x98", b"\xC4", b"\xC4\xA0\xC4", b"\xED\xA0\x80", b"\xF4\x90\x80\x80"]
+    out = [b"", b"a", b"\xC3", b"\xE0\x80\x81", good]
+    for n in (5, 40, 300, 1020, 1024, 1030, 2500, 9000):
+        t = (good * (n // len(good) + 1))[:n]
+        out.append(t)
+        for _ in range(3):
+            cut = sorted(rng.randrange(len(t) + 1) for _ in range(rng.randint(1, 6)))
+            parts, last = [], 0
+            for c in cut:
+                parts += [t[last:c], rng.choice(odd)]
+                last = c
+            out.append(b"".join(parts + [t[last:]]))
+        out.append(bytes(rng.randrange(1, 256) for _ in range(n)))
+    return out
+
+
+@needs_ref
+@pytest.mark.parametrize("byte_mode", [True, False])
+def test_oracle_decode_matches_reference_on_all_bytes_vocab(byte_mode):
+    ref = O.load_ref()
+    v, s = _all_bytes_model(tempfile.mkdtemp())
+    ref.initialize(v, s, None, byte_mode)
+    orc = O.Oracle(v, s, prefix=None, is_byte_encoder=byte_mode)
+    for raw in _byte_cases(random.Random(77)):
+        ids = [b - 1 for b in raw]
+        got = orc.decode_bytes(ids).split(b"\0", 1)[0]
+        try:
+            want = ref.decode(ids).encode("utf-8")
+        except UnicodeDecodeError:
+            with pytest.raises(UnicodeDecodeError):
+                got.decode("utf-8")
+            continue
+        assert got == want, (byte_mode, raw[:40])
+    orc.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("byte_mode", [True, False])
+def test_gpu_decode_all_bytes_vocab(byte_mode):
+    from hutoken_b200 import capi
+    v, s = _all_bytes_model(tempfile.mkdtemp())
+    eng = capi.Engine(v, s, prefix=None, is_byte_encoder=byte_mode)
+    orc = O.Oracle(v, s, prefix=None, is_byte_encoder=byte_mode)
+    cases = _byte_cases(random.Random(77))
+    lists = [[b - 1 for b in raw] for raw in cases]
+    got = eng.batch_decode_bytes(lists)
+    for raw, x, g in zip(cases, lists, got):
+        assert g == orc.decode_bytes(x), (byte_mode, raw[:40])
+    eng.close()
+    orc.close()
