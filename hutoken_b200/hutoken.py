@@ -58,6 +58,55 @@ def batch_encode(texts, num_threads=1):
         raise RuntimeError(f"hutoken: Error encoding texts: {e}")
 
 
+def pack_texts(texts):
+    """list of str / bytes -> (data: bytes, offsets: uint64 ndarray of len(texts) + 1).  Each text is cut at its
+    first NUL, as batch_encode does (strdup at lib.c:772)."""
+    import numpy as np
+    if not isinstance(texts, (list, tuple)):
+        raise TypeError("Invalid arguments. Expected a list of strings.")
+    parts = []
+    offs = np.zeros(len(texts) + 1, dtype=np.uint64)
+    at = 0
+    for i, t in enumerate(texts):
+        if isinstance(t, str):
+            t = t.encode("utf-8")
+        elif not isinstance(t, (bytes, bytearray, memoryview)):
+            raise TypeError("Invalid arguments. Expected a list of strings.")
+        t = bytes(t)
+        nul = t.find(b"\0")
+        if nul >= 0:
+            t = t[:nul]
+        parts.append(t)
+        at += len(t)
+        offs[i + 1] = at
+    return b"".join(parts), offs
+
+
+def batch_encode_packed(texts, offsets=None):
+    """Zero-object variant of batch_encode (no counterpart in hutoken.py, whose
+    batch_encode builds one PyLong per id, lib.c:840-868).
+
+    batch_encode_packed(list_of_texts)        -> (ids: int32 ndarray, tok_offsets: uint64 ndarray of n_docs + 1)
+    batch_encode_packed(data, offsets)        -> the same for documents already packed back to back in one
+                                                 bytes-like `data`, document i = data[offsets[i]:offsets[i + 1]]
+    Document i's ids are ids[tok_offsets[i]:tok_offsets[i + 1]]; they equal batch_encode(texts)[i]."""
+    import numpy as np
+    ext = _ext()
+    try:
+        if offsets is None:
+            data, offsets = pack_texts(texts)
+        else:
+            data = texts
+            offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+            if offsets.ndim != 1 or len(offsets) < 1 or (np.diff(offsets.astype(np.int64)) < 0).any():
+                raise ValueError("offsets must be a non-decreasing uint64 array with n_docs + 1 entries")
+        ids, tok = ext.batch_encode_packed(data, offsets)
+        return np.frombuffer(ids, dtype=np.int32), np.frombuffer(tok, dtype=np.uint64)
+    except Exception as e:
+        traceback.print_exc(file=sys.stderr)
+        raise RuntimeError(f"hutoken: Error encoding texts: {e}")
+
+
 def decode(tokens):
     ext = _ext()
     try:

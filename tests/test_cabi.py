@@ -45,6 +45,25 @@ def test_extension_method_table():
         _hutoken.initialize("only-one-argument")  # special_file_path is mandatory (lib.c:203)
 
 
+def test_packed_surface_host_side():
+    """pack_texts / batch_encode_packed: host-side packing and argument checks; no device needed."""
+    import numpy as np
+    import hutoken_b200 as hutoken
+    data, offs = hutoken.pack_texts(["ab", "", "őű", b"raw\xff", "cut\0here"])
+    assert data == "ab".encode() + "őű".encode() + b"raw\xff" + b"cut"
+    assert offs.dtype == np.uint64 and offs.tolist() == [0, 2, 2, 6, 10, 13]
+    assert hutoken.pack_texts([])[1].tolist() == [0]
+    with pytest.raises(TypeError, match="Expected a list of strings"):
+        hutoken.pack_texts("not a list")
+    with pytest.raises(TypeError, match="Expected a list of strings"):
+        hutoken.pack_texts([1, 2])
+    # before initialize(): the reference's message, wrapped like batch_encode's (hutoken.py:134-139)
+    with pytest.raises(RuntimeError, match="hutoken: Error encoding texts: Vocabulary is not initialized"):
+        hutoken.batch_encode_packed(["x"])
+    with pytest.raises(RuntimeError, match="non-decreasing"):
+        hutoken.batch_encode_packed(b"abcd", [0, 3, 2])
+
+
 def test_no_cpu_fallback_without_device():
     """On a box without a GPU hut_create must fail with a CUDA status, not fall back to anything."""
     code = (

@@ -171,6 +171,20 @@ def test_python_surface():
         assert hutoken.batch_encode(texts, nt) == orc.batch_encode(texts)
     assert hutoken.batch_encode(texts, 0) == [[], [], [], []]  # no workers => nothing encoded (lib.c:779-794)
     assert hutoken.batch_encode(["ab\0cd"], 1) == [orc.encode("ab")]  # strdup cut (lib.c:772)
+    # packed surface: same ids as the list API, as int32 / uint64 arrays
+    many = texts + ["ab\0cd", "őű € 😂", "x" * 70000]
+    ids, tok = hutoken.batch_encode_packed(many)
+    assert ids.dtype == np.int32 and tok.dtype == np.uint64 and len(tok) == len(many) + 1
+    assert [ids[tok[i]:tok[i + 1]].tolist() for i in range(len(many))] == hutoken.batch_encode(many, 1)
+    data, offs = hutoken.pack_texts(many)
+    ids2, tok2 = hutoken.batch_encode_packed(data, offs)
+    assert np.array_equal(ids, ids2) and np.array_equal(tok, tok2)
+    ids0, tok0 = hutoken.batch_encode_packed([])
+    assert len(ids0) == 0 and tok0.tolist() == [0]
+    with pytest.raises(RuntimeError, match="Error encoding texts"):
+        hutoken.batch_encode_packed(b"ab\0cd", [0, 5])  # a NUL inside a packed document is refused, not cut
+    with pytest.raises(RuntimeError, match="exceed"):
+        hutoken.batch_encode_packed(b"abc", [0, 9])
     with pytest.raises(RuntimeError, match="embedded null"):
         hutoken.encode("ab\0cd")
     with pytest.raises(RuntimeError, match="Expected a list of strings"):
