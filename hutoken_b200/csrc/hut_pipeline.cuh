@@ -296,9 +296,46 @@ __global__ void __launch_bounds__(NT, HUT_TILE_CTAS) tile_kernel(const __grid_co
         bool holes = false;
         uint32_t slack = 0;                     // room reserved for misses of this tile that stayed unused
         int32_t* const slot = J.stage + (PFX ? slot_o : (unsigned long long)tile * J.stride);
+#ifdef HUT_PIPE_PROBE
+        // software pipeline of the cache probe: the first slot of round r + 1 is requested right after round r's
+        // compare, so that the scan and the stores of round r run under its latency (one request per lane and round,
+        // as before)
+        int n_s = BACK, n_e = BACK;
+        uint32_t n_dsb = 0, n_b0 = 0, n_i = 0, n_key[4] = {0u, 0u, 0u, 0u};
+        uint4 n_a = make_uint4(0, 0, 0, 0), n_b = make_uint4(0, 0, 0, 0);
+        auto prep = [&](uint32_t r) {
+            const uint32_t q = r + lane;
+            const bool active = q < n;
+            n_s = active ? ws.pstart[q] : BACK;
+            n_e = active ? ws.pstart[q + 1] : BACK;
+            const int len = n_e - n_s;
+            const bool keyed = len <= CACHE_KEY_MAX;
+            n_dsb = 0;
+            if (tile_docs) n_dsb = (ws.dsm[n_s >> 5] >> (n_s & 31)) & 1u;
+            n_b0 = build_key(ws.text, sm.kmask, n_s, keyed ? len : 0, PFX ? n_dsb : 0u, n_key);
+            n_a = make_uint4(0, 0, 0, 0);
+            if (active && n_b0 != 0 && keyed && M.cache_ok) {
+                n_i = cache_hash(n_key, J.cache_bits);
+                ld_slot256(J.cache + n_i, n_a, n_b);
+            }
+        };
+        if (n) prep(0);
+#endif
         for (uint32_t r0 = 0; r0 < n; r0 += 32) {
             const uint32_t q = r0 + lane;
             const bool active = q < n;
+#ifdef HUT_PIPE_PROBE
+            const int s = n_s, e = n_e;
+            const int len = e - s;
+            const bool keyed = len <= CACHE_KEY_MAX;
+            const uint32_t dsb = n_dsb;
+            const uint32_t first = PFX ? dsb : 0u;
+            uint32_t key[4] = {n_key[0], n_key[1], n_key[2], n_key[3]}, w[4] = {0u, 0u, 0u, 0u};
+            const uint32_t b0 = n_b0;
+            const bool dummy = !active || b0 == 0;
+            const uint4 pa = n_a, pb = n_b;
+            const uint32_t pi = n_i;
+#else
             const int s = active ? ws.pstart[q] : BACK;
             const int e = active ? ws.pstart[q + 1] : BACK;
             const int len = e - s;                       // > MAXW when the end lies beyond the halo (BEYOND)
@@ -309,6 +346,7 @@ __global__ void __launch_bounds__(NT, HUT_TILE_CTAS) tile_kernel(const __grid_co
             uint32_t key[4], w[4] = {0u, 0u, 0u, 0u};
             const uint32_t b0 = build_key(ws.text, sm.kmask, s, keyed ? len : 0, first, key);
             const bool dummy = !active || b0 == 0;       // NUL boundary (zero fill past the end of the text)
+#endif
             // state: 0 nothing, 1 ids ready, 2 cache miss merged by this warp (batches of 32), 3 long pretoken ->
             // long_kernel, 4 miss too long for the cache / the small per-lane arrays -> miss_kernel
             uint32_t state = 0;
@@ -322,8 +360,28 @@ __global__ void __launch_bounds__(NT, HUT_TILE_CTAS) tile_kernel(const __grid_co
                     hit2 = cache2_lookup(J, k32, w);
                 }
             }
+#ifdef HUT_PIPE_PROBE
+            bool hit1 = false;
+            if (!dummy && !hit2 && keyed && M.cache_ok) {
+                if ((pa.x | pa.y) == 0) {
+                    hit1 = false;
+                } else if (pa.x == key[0] && pa.y == key[1] && pa.z == key[2] && pa.w == key[3]) {
+                    w[0] = pb.x;
+                    w[1] = pb.y;
+                    w[2] = pb.z;
+                    w[3] = pb.w;
+                    hit1 = val_count(pb.x) != 0;
+                } else {
+                    hit1 = cache_lookup_from(J, key, w, (pi + 1) & ((1u << J.cache_bits) - 1), CACHE_PROBES - 1);
+                }
+            }
+            if (r0 + 32 < n) prep(r0 + 32);
+            if (!dummy) {
+                if (hit2 || hit1) state = 1;
+#else
             if (!dummy) {
                 if (hit2 || (keyed && M.cache_ok && cache_lookup(J, key, w))) state = 1;
+#endif
                 else if ((uint32_t)len > M.miss_len_max) state = 3;
                 else state = (len <= CACHE2_KEY_MAX &&
                               (uint32_t)len * M.kmax + (first ? M.n_prefix_syms : 0u) <= (uint32_t)MISS_SMALL) ? 2u : 4u;
