@@ -289,6 +289,9 @@ __global__ void __launch_bounds__(NT, HUT_TILE_CTAS) tile_kernel(const __grid_co
             if (lane == 31) ws.pstart[n] = bnd ? (uint16_t)(31 * CHUNK + __ffs(bnd) - 1) : (uint16_t)BEYOND;
         }
         __syncwarp();
+#ifdef HUT_EXP_NOROUND
+        n = 0;  // timing experiment only: staging + classify + enumerate without the rounds
+#endif
 
         // ---- rounds of up to 32 pretokens, one per lane ----
         uint32_t run = 0;                       // entries of this tile's staging slot used so far

@@ -6,6 +6,7 @@
  */
 #define PY_SSIZE_T_CLEAN
 #include <Python.h>
+#include <pthread.h>
 #include <string.h>
 
 #include "../../include/hutoken_b200.h"
@@ -15,6 +16,19 @@ static uint8_t* g_pack = NULL; /* pinned packing buffer (grow-only) */
 static size_t g_pack_cap = 0;
 static uint64_t* g_offs = NULL;
 static size_t g_offs_cap = 0;
+
+/* One engine call at a time.  g_ctx, the packing buffers above, the decode buffers below and the context's pinned
+ * result are process-global (the reference, lib.c:782, uses per-call buffers instead), and include/hutoken_b200.h
+ * allows one host thread per context: every method takes this mutex before it touches them and drops it after the
+ * result has been converted to Python objects.  The GIL is released while waiting, so a thread that holds the
+ * mutex and wants the GIL back can always get it. */
+static pthread_mutex_t g_mu = PTHREAD_MUTEX_INITIALIZER;
+static void engine_lock(void) {
+    Py_BEGIN_ALLOW_THREADS
+    pthread_mutex_lock(&g_mu);
+    Py_END_ALLOW_THREADS
+}
+static void engine_unlock(void) { pthread_mutex_unlock(&g_mu); }
 
 static const char* NOT_INIT_ENC =
     "Vocabulary is not initialized for encoding. Call 'initialize_encode' function first."; /* lib.c:671-676 */
@@ -98,8 +112,11 @@ static PyObject* p_initialize(PyObject* self, PyObject* args, PyObject* kwargs) 
     rc = hut_create(&desc, &opt, nd ? devs : NULL, nd, &ctx, err, sizeof err);
     Py_END_ALLOW_THREADS
     if (rc != HUT_STATUS_OK) return raise_status(rc, err);
-    if (g_ctx) hut_destroy(g_ctx); /* re-initialise replaces the model (the reference leaks it, lib.c:129-145) */
+    engine_lock(); /* no encode / decode call is inside the old context now */
+    hut_ctx* old = g_ctx;
     g_ctx = ctx;
+    engine_unlock();
+    if (old) hut_destroy(old); /* re-initialise replaces the model (the reference leaks it, lib.c:129-145) */
     Py_RETURN_NONE;
 }
 
@@ -126,17 +143,24 @@ static PyObject* p_encode(PyObject* self, PyObject* args) {
     char* text = NULL;
     if (!PyArg_ParseTuple(args, "s", &text)) return NULL;
     size_t len = strlen(text);
-    if (!ensure_pack(len, 1)) return PyErr_NoMemory();
-    memcpy(g_pack, text, len);
-    g_offs[0] = 0;
-    g_offs[1] = len;
-    hut_result res;
-    int rc;
-    Py_BEGIN_ALLOW_THREADS
-    rc = hut_encode_batch(g_ctx, g_pack, g_offs, 1, &res);
-    Py_END_ALLOW_THREADS
-    if (rc != HUT_STATUS_OK) return raise_status(rc, hut_last_error(g_ctx));
-    return ids_to_list(res.ids, res.n_ids);
+    engine_lock();
+    PyObject* out = NULL;
+    if (!ensure_pack(len, 1)) {
+        PyErr_NoMemory();
+    } else {
+        memcpy(g_pack, text, len);
+        g_offs[0] = 0;
+        g_offs[1] = len;
+        hut_result res;
+        int rc;
+        Py_BEGIN_ALLOW_THREADS
+        rc = hut_encode_batch(g_ctx, g_pack, g_offs, 1, &res);
+        Py_END_ALLOW_THREADS
+        if (rc != HUT_STATUS_OK) raise_status(rc, hut_last_error(g_ctx));
+        else out = ids_to_list(res.ids, res.n_ids);
+    }
+    engine_unlock();
+    return out;
 }
 
 /* batch_encode(texts, num_threads=1) -- lib.c:722-874, format "O|i".  num_threads only keeps its one
@@ -159,42 +183,60 @@ static PyObject* p_batch_encode(PyObject* self, PyObject* args) {
         for (Py_ssize_t i = 0; i < n; ++i) PyList_SET_ITEM(result, i, PyList_New(0));
         return result;
     }
-    /* pass 1: sizes (each text is cut at its first NUL, like strdup at lib.c:772) */
+    /* sizing and packing both happen under the mutex with the GIL held throughout, so the list cannot change in
+     * between.  pass 1: sizes (each text is cut at its first NUL, like strdup at lib.c:772) */
+    engine_lock();
+    PyObject* result = NULL;
     size_t total = 0;
     for (Py_ssize_t i = 0; i < n; ++i) {
         const char* s = PyUnicode_AsUTF8(PyList_GET_ITEM(texts, i));
         if (!s) {
             PyErr_SetString(PyExc_TypeError, "Invalid arguments. Expected a list of strings.");
-            return NULL;
+            goto out;
         }
         total += strlen(s);
     }
-    if (!ensure_pack(total, (size_t)n)) return PyErr_NoMemory();
-    size_t at = 0;
-    for (Py_ssize_t i = 0; i < n; ++i) {
-        const char* s = PyUnicode_AsUTF8(PyList_GET_ITEM(texts, i));
-        size_t l = strlen(s);
-        g_offs[i] = at;
-        memcpy(g_pack + at, s, l);
-        at += l;
+    if (!ensure_pack(total, (size_t)n)) {
+        PyErr_NoMemory();
+        goto out;
     }
-    g_offs[n] = at;
-    hut_result res;
-    int rc;
-    Py_BEGIN_ALLOW_THREADS
-    rc = hut_encode_batch(g_ctx, g_pack, g_offs, (uint64_t)n, &res);
-    Py_END_ALLOW_THREADS
-    if (rc != HUT_STATUS_OK) return raise_status(rc, hut_last_error(g_ctx));
-    PyObject* result = PyList_New(n);
-    if (!result) return PyErr_NoMemory();
-    for (Py_ssize_t i = 0; i < n; ++i) {
-        PyObject* sub = ids_to_list(res.ids + res.tok_offsets[i], res.tok_offsets[i + 1] - res.tok_offsets[i]);
-        if (!sub) {
-            Py_DECREF(result);
-            return NULL;
+    {
+        size_t at = 0;
+        for (Py_ssize_t i = 0; i < n; ++i) {
+            const char* s = PyUnicode_AsUTF8(PyList_GET_ITEM(texts, i));
+            size_t l = strlen(s);
+            g_offs[i] = at;
+            memcpy(g_pack + at, s, l);
+            at += l;
         }
-        PyList_SET_ITEM(result, i, sub);
+        g_offs[n] = at;
     }
+    {
+        hut_result res;
+        int rc;
+        Py_BEGIN_ALLOW_THREADS
+        rc = hut_encode_batch(g_ctx, g_pack, g_offs, (uint64_t)n, &res);
+        Py_END_ALLOW_THREADS
+        if (rc != HUT_STATUS_OK) {
+            raise_status(rc, hut_last_error(g_ctx));
+            goto out;
+        }
+        result = PyList_New(n);
+        if (!result) {
+            PyErr_NoMemory();
+            goto out;
+        }
+        for (Py_ssize_t i = 0; i < n; ++i) {
+            PyObject* sub = ids_to_list(res.ids + res.tok_offsets[i], res.tok_offsets[i + 1] - res.tok_offsets[i]);
+            if (!sub) {
+                Py_CLEAR(result);
+                goto out;
+            }
+            PyList_SET_ITEM(result, i, sub);
+        }
+    }
+out:
+    engine_unlock();
     return result;
 }
 
@@ -213,11 +255,16 @@ static PyObject* p_batch_encode_packed(PyObject* self, PyObject* args) {
     } else {
         uint64_t nd = (uint64_t)offs.len / 8 - 1;
         const uint64_t* o = (const uint64_t*)offs.buf;
-        if (o[nd] > (uint64_t)data.len) {
+        int sorted = 1; /* decreasing offsets would underflow the shard planner's byte counts */
+        for (uint64_t i = 0; i < nd && sorted; ++i) sorted = o[i] <= o[i + 1];
+        if (!sorted) {
+            PyErr_SetString(PyExc_ValueError, "offsets must be non-decreasing");
+        } else if (o[nd] > (uint64_t)data.len) {
             PyErr_SetString(PyExc_ValueError, "offsets exceed the data buffer");
         } else {
             hut_result res;
             int rc;
+            engine_lock();
             Py_BEGIN_ALLOW_THREADS
             rc = hut_encode_batch(g_ctx, (const uint8_t*)data.buf, o, nd, &res);
             Py_END_ALLOW_THREADS
@@ -225,6 +272,7 @@ static PyObject* p_batch_encode_packed(PyObject* self, PyObject* args) {
             else
                 out = Py_BuildValue("(y#y#)", (const char*)res.ids, (Py_ssize_t)(res.n_ids * 4),
                                     (const char*)res.tok_offsets, (Py_ssize_t)((nd + 1) * 8));
+            engine_unlock();
         }
     }
     PyBuffer_Release(&data);
@@ -287,18 +335,24 @@ static PyObject* p_decode(PyObject* self, PyObject* args) {
         PyErr_SetString(PyExc_TypeError, "Argument must be a list of integers");
         return NULL;
     }
+    engine_lock();
+    PyObject* out = NULL;
     Py_ssize_t n = PyList_GET_SIZE(tokens);
-    if (!ensure_dec((size_t)n, 1)) return PyErr_NoMemory();
-    if (!list_to_ids(tokens, g_dec_ids)) return NULL;
-    g_dec_offs[0] = 0;
-    g_dec_offs[1] = (uint64_t)n;
-    hut_text_result res;
-    int rc;
-    Py_BEGIN_ALLOW_THREADS
-    rc = hut_decode_batch(g_ctx, g_dec_ids, g_dec_offs, 1, &res);
-    Py_END_ALLOW_THREADS
-    if (rc != HUT_STATUS_OK) return raise_status(rc, hut_last_error(g_ctx));
-    return text_to_str(res.text, res.n_bytes);
+    if (!ensure_dec((size_t)n, 1)) {
+        PyErr_NoMemory();
+    } else if (list_to_ids(tokens, g_dec_ids)) {
+        g_dec_offs[0] = 0;
+        g_dec_offs[1] = (uint64_t)n;
+        hut_text_result res;
+        int rc;
+        Py_BEGIN_ALLOW_THREADS
+        rc = hut_decode_batch(g_ctx, g_dec_ids, g_dec_offs, 1, &res);
+        Py_END_ALLOW_THREADS
+        if (rc != HUT_STATUS_OK) raise_status(rc, hut_last_error(g_ctx));
+        else out = text_to_str(res.text, res.n_bytes);
+    }
+    engine_unlock();
+    return out;
 }
 
 /* batch_decode(tokens, num_threads=1) -- lib.c:957-1085, format "O|i"; num_threads is accepted and unused */
@@ -319,40 +373,57 @@ static PyObject* p_batch_decode(PyObject* self, PyObject* args) {
         PyErr_SetString(PyExc_ValueError, "No tokens provided.");
         return NULL;
     }
+    engine_lock(); /* sizes are taken under the mutex: nothing runs between sizing and filling the buffers */
+    PyObject* result = NULL;
     size_t total = 0;
     for (Py_ssize_t i = 0; i < nd; ++i) {
         PyObject* item = PyList_GET_ITEM(tokens, i);
         if (!PyList_Check(item)) {
             PyErr_SetString(PyExc_TypeError, "Each item must be a list of integers.");
-            return NULL;
+            goto out;
         }
         total += (size_t)PyList_GET_SIZE(item);
     }
-    if (!ensure_dec(total, (size_t)nd)) return PyErr_NoMemory();
-    size_t at = 0;
-    for (Py_ssize_t i = 0; i < nd; ++i) {
-        PyObject* item = PyList_GET_ITEM(tokens, i);
-        g_dec_offs[i] = at;
-        if (!list_to_ids(item, g_dec_ids + at)) return NULL;
-        at += (size_t)PyList_GET_SIZE(item);
+    if (!ensure_dec(total, (size_t)nd)) {
+        PyErr_NoMemory();
+        goto out;
     }
-    g_dec_offs[nd] = at;
-    hut_text_result res;
-    int rc;
-    Py_BEGIN_ALLOW_THREADS
-    rc = hut_decode_batch(g_ctx, g_dec_ids, g_dec_offs, (uint64_t)nd, &res);
-    Py_END_ALLOW_THREADS
-    if (rc != HUT_STATUS_OK) return raise_status(rc, hut_last_error(g_ctx));
-    PyObject* result = PyList_New(nd);
-    if (!result) return PyErr_NoMemory();
-    for (Py_ssize_t i = 0; i < nd; ++i) {
-        PyObject* str = text_to_str(res.text + res.text_offsets[i], res.text_offsets[i + 1] - res.text_offsets[i]);
-        if (!str) {
-            Py_DECREF(result);
-            return NULL;
+    {
+        size_t at = 0;
+        for (Py_ssize_t i = 0; i < nd; ++i) {
+            PyObject* item = PyList_GET_ITEM(tokens, i);
+            g_dec_offs[i] = at;
+            if (!list_to_ids(item, g_dec_ids + at)) goto out;
+            at += (size_t)PyList_GET_SIZE(item);
         }
-        PyList_SET_ITEM(result, i, str);
+        g_dec_offs[nd] = at;
     }
+    {
+        hut_text_result res;
+        int rc;
+        Py_BEGIN_ALLOW_THREADS
+        rc = hut_decode_batch(g_ctx, g_dec_ids, g_dec_offs, (uint64_t)nd, &res);
+        Py_END_ALLOW_THREADS
+        if (rc != HUT_STATUS_OK) {
+            raise_status(rc, hut_last_error(g_ctx));
+            goto out;
+        }
+        result = PyList_New(nd);
+        if (!result) {
+            PyErr_NoMemory();
+            goto out;
+        }
+        for (Py_ssize_t i = 0; i < nd; ++i) {
+            PyObject* str = text_to_str(res.text + res.text_offsets[i], res.text_offsets[i + 1] - res.text_offsets[i]);
+            if (!str) {
+                Py_CLEAR(result);
+                goto out;
+            }
+            PyList_SET_ITEM(result, i, str);
+        }
+    }
+out:
+    engine_unlock();
     return result;
 }
 

@@ -135,6 +135,55 @@ def test_reference_cut_at_overlong_pretoken():
     assert eng.stats()["cut_documents"] == 3
 
 
+@pytest.mark.parametrize("name", ["gpt2", "llama"])
+def test_no_limit_long_runs(name):
+    """configs[4] as north_star words it: single-class runs of 256 KiB + 8 ... 16 MiB really MERGED on the GPU (opt-in
+    no-limit mode, hut_options.max_pretoken) and compared with the CPU restatement in its no-limit mode -- the
+    reference itself cuts such a document (core.c:402-407,503).  Merge order: core.c:111-176, queue.c:152-199."""
+    eng = engine_for(name, max_pretoken=32 << 20)
+    orc = oracle_for(name, no_limit=True)
+    rng = random.Random(77)
+    docs = ["before"]
+    for n in (262152, 1 << 20, 4 << 20, 16 << 20):
+        docs.append("go " + "".join(rng.choices("abcdefghijklmnopqrstuvwxyz", k=n)) + " end")
+    docs += ["0123456789" * 30000, "between", "é" * 140000 + " x", "after"]
+    data, offs = pack(docs)
+    ids, tok = eng.encode_packed(data, offs)
+    oids, otok = orc.encode_packed(data, offs)
+    assert_same(ids, tok, oids, otok, f"no-limit {name}")
+    st = eng.stats()
+    assert st["big_merges"] >= 4 and st["cut_documents"] == 0
+    # a pretoken beyond the configured working area is an error, never a silent cut
+    small = engine_for(name, max_pretoken=300000)
+    from hutoken_b200 import capi
+    with pytest.raises(capi.HutError, match="max_pretoken"):
+        small.encode_packed(*pack(["x" * 300001]))
+    ids, tok = small.encode_packed(*pack(["y" * 300000 + " z"]))
+    oids, otok = orc.encode_packed(*pack(["y" * 300000 + " z"]))
+    assert_same(ids, tok, oids, otok, f"no-limit at the limit {name}")
+
+
+def test_one_context_over_distinct_devices():
+    """hut_create over ALL distinct GPUs of the box (the product's own multi-GPU entry, HUTOKEN_B200_DEVICES):
+    chunks dealt round-robin to physically different devices.  Skipped on a one-GPU box."""
+    import torch
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    for name in ("gpt2", "llama_small"):
+        eng, orc = engine_for(name, devices=tuple(range(n)), chunk_mb=2), oracle_for(name)
+        assert eng.device_count == n
+        data, offs = synth.corpus(61, 24 << 20, special_every=250)
+        oids, otok = orc.encode_packed(data, offs)
+        for _ in range(2):
+            ids, tok = eng.encode_packed(data, offs)
+            assert_same(ids, tok, oids, otok, f"{name} over {n} distinct devices")
+        for d in range(n):
+            assert eng.stats(d)["pretokens"] > 0, f"device {d} got no work"
+        ids, tok = eng.encode_packed(*pack(["only one document"]))
+        assert ids.tolist() == orc.encode("only one document")
+
+
 def test_device_resident_api():
     """hut_encode_device: text and ids stay on the GPU (the path bench.py times)."""
     import torch
@@ -194,6 +243,43 @@ def test_python_surface():
     orc = oracle_for("llama_small")
     for t in ("hello world", " hello", "x\ny"):
         assert hutoken.encode(t) == orc.encode(t)
+
+
+def test_python_surface_from_two_threads():
+    """The extension's buffers and the context are process-global; calls from several Python threads are serialised
+    by the module mutex (pyext.c) and must all come back right (the reference's batch_encode, lib.c:782, is
+    callable from threads because it uses per-call buffers)."""
+    import threading
+    import hutoken_b200 as hutoken
+    v, s = synth.PATHS["gpt2_small"]
+    hutoken.initialize(v, s, is_byte_encoder=True)
+    orc = oracle_for("gpt2_small")
+    rng = random.Random(3)
+    batches = [[F.random_text(rng, rng.randint(0, 400)) for _ in range(rng.randint(1, 300))] for _ in range(8)]
+    batches[3] = ["x" * 300000, "tail"]  # forces the pinned packing buffer to grow under the other thread's feet
+    want = [orc.batch_encode(b) for b in batches]
+    errors = []
+
+    def work(k):
+        try:
+            for rep in range(6):
+                for i in range(k, len(batches), 2):
+                    got = hutoken.batch_encode(batches[i], 2)
+                    if got != want[i]:
+                        errors.append((k, rep, i))
+                    if hutoken.encode(batches[i][0]) != want[i][0]:
+                        errors.append((k, rep, i, "encode"))
+                    if hutoken.decode(want[0][0]) is None:
+                        errors.append((k, rep, i, "decode"))
+        except Exception as e:  # noqa: BLE001
+            errors.append(repr(e))
+
+    th = [threading.Thread(target=work, args=(k,)) for k in range(2)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert not errors, errors[:5]
 
 
 @pytest.mark.parametrize("devices,chunk_mb", [([0], 1), ([0, 0], 1), ([0, 0, 0], 2)])

@@ -138,9 +138,9 @@ def test_host_tables_merges_match_oracle_on_fuzz_models(byte_mode):
     for seed, v, s, kw, mp, texts in _fuzz_cases(byte_mode, range(40), tmp):
         orc = O.Oracle(v, s, merges_path=mp, **kw)
         hm = harness.HostModel(v, s, merges=mp, **kw)
-        if not hm.ok():
-            assert hm.status == 5, hm.message  # a refused table must say so, never mis-encode
-            continue
+        # hut_model.c may refuse a table shape (HUT_STATUS_UNSUPPORTED, listed in INTEGRATION.md) but never
+        # mis-encode; on this fuzz family it refuses NONE, and the bound is asserted so that it cannot creep up
+        assert hm.ok(), (seed, hm.status, hm.message)
         for t in texts:
             assert hm.encode(t) == orc.encode(t), (seed, kw, t)
         hm.close()
@@ -180,11 +180,8 @@ def test_gpu_merges_fuzz_models(byte_mode):
     from hutoken_b200 import capi
     tmp = tempfile.mkdtemp()
     for seed, v, s, kw, mp, texts in _fuzz_cases(byte_mode, range(30), tmp):
-        try:
-            eng = capi.Engine(v, s, merges_path=mp, **kw)
-        except Exception as e:  # refused tables only (HUT_STATUS_UNSUPPORTED)
-            assert "split" in str(e) or "span" in str(e), e
-            continue
+        eng = capi.Engine(v, s, merges_path=mp, **kw)  # refusal bound of this fuzz family: 0 of 30 (asserted on
+        # the CPU side too, test_host_model_merges_matches_oracle_on_fuzz_models)
         orc = O.Oracle(v, s, merges_path=mp, **kw)
         got, want = eng.batch_encode(texts), orc.batch_encode(texts)
         for t, g, w in zip(texts, got, want):
