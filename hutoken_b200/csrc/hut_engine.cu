@@ -20,11 +20,20 @@ using namespace hut;
 
 #define MAX_DEV 16
 
-/* one launched shard whose counters have not been read yet */
+/* one launched shard whose counters have not been read yet.  Each flight owns the device-side state its kernels
+ * write (counters, look-back words, deferred-pretoken list), so that the next chunk can be queued behind it without
+ * touching anything the host may still want to look at (patch phase, cuts). */
 struct hut_flight {
     Job job;
+    Counters* ctr;       // device counters
     Counters* h_ctr;     // pinned mirror of the device counters, copied at the end of the launch
-    cudaEvent_t ev[4];   // start, before / after tile_kernel, end
+    uint32_t* tilebuf;   // status (uint64 per tile) | first_doc | tot | def_first (ntiles + 1 uint32 each)
+    size_t tilebuf_cap;
+    unsigned long long* bsum;
+    size_t bsum_cap;
+    DefEntry* def;
+    size_t def_cap;
+    cudaEvent_t ev[4];   // start, before / after tile2_kernel, end
     cudaEvent_t done;    // counters are in h_ctr
 };
 
@@ -56,7 +65,6 @@ struct hut_dev {
     uint32_t cache_bits;
     CacheSlot2* cache2;
     uint32_t cache2_bits;
-    Counters* ctr;
     CutRanges* cut;
     uint32_t* cta_scratch;
     unsigned long long cta_scratch_words;
@@ -65,25 +73,12 @@ struct hut_dev {
     unsigned long long big_slot_words;
     uint32_t big_cap, big_slots;
     int grid, long_grid, sms;
-    uint32_t stride, slot_extra;
-    // grow-only temporaries of the pipeline
-    int32_t* stage;
-    size_t stage_cap;
-    uint32_t* tilebuf;  // cnt | tot | first_doc | def_first (ntiles + 1 entries each) | slot_off (uint64)
-    size_t tilebuf_cap;
-    unsigned long long* bsum;
-    size_t bsum_cap;
-    DefEntry* def;
-    size_t def_cap;
-    MissEntry* miss;
-    size_t miss_cap;
-    int miss_grid;
+    // grow-only temporaries of the patch phase (shards with long pretokens) and of the document cuts
     int32_t* long_ids;
     size_t long_cap;
-    int32_t* cut_tmp;
-    size_t cut_tmp_cap;
+    int32_t* tmp_ids;
+    size_t tmp_ids_cap;
     hut_flight fl[2];
-    hut_flight* ctr_owner;  // the flight whose launch last (re)set the device counters
     hut_chunkbuf cb[2];
     hut_stats stats;
 };
@@ -139,6 +134,8 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
         for (int i = 0; i < 4; ++i) CU(ctx, cudaEventCreate(&d->fl[b].ev[i]));
         CU(ctx, cudaEventCreateWithFlags(&d->fl[b].done, cudaEventDisableTiming));
         CU(ctx, cudaMallocHost(&d->fl[b].h_ctr, sizeof(Counters)));
+        CU(ctx, cudaMalloc(&d->fl[b].ctr, sizeof(Counters)));
+        CU(ctx, cudaMemset(d->fl[b].ctr, 0, sizeof(Counters)));
         CU(ctx, cudaEventCreateWithFlags(&d->cb[b].ev_in, cudaEventDisableTiming));
         CU(ctx, cudaEventCreateWithFlags(&d->cb[b].ev_out, cudaEventDisableTiming));
     }
@@ -157,14 +154,8 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     dm.has_prefix = m->has_prefix;
     dm.cache_ok = (m->max_value < (1 << 20)) ? 1 : 0;  // ids are packed as signed 21-bit fields
     dm.kmax = m->max_sym_per_char ? m->max_sym_per_char : 1;
-    {   // pretokens up to this many bytes are merged by one lane of miss_kernel (<= MISS_SYMS symbols incl. prefix)
-        const uint32_t pfx = m->has_prefix ? m->n_prefix_syms : 0u;
-        uint32_t lmax = pfx < (uint32_t)MISS_SYMS ? ((uint32_t)MISS_SYMS - pfx) / dm.kmax : 0u;
-        if (lmax > (uint32_t)MAXW) lmax = MAXW;
-        if (m->n_prefix_alone > 8) lmax = 0;
-        dm.miss_len_max = lmax;
-        dm.first_extra = m->has_prefix ? (m->n_prefix_syms > m->n_prefix_alone ? m->n_prefix_syms : m->n_prefix_alone) : 0u;
-    }
+    dm.miss_len_max = MAXW;
+    dm.first_extra = 0;
     CU(ctx, upload(d, m->sym_off, 257, &dm.sym_off));
     CU(ctx, upload(d, m->sym_pool, m->sym_off[256], &dm.sym_pool));
     uint32_t byte1[256];
@@ -198,28 +189,16 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     d->cache2_bits = d->cache_bits > 4 ? d->cache_bits - 4 : 6;  // long pretokens are rare
     CU(ctx, cudaMalloc(&d->cache2, sizeof(CacheSlot2) << d->cache2_bits));
     CU(ctx, cudaMemset(d->cache2, 0, sizeof(CacheSlot2) << d->cache2_bits));
-    CU(ctx, cudaMalloc(&d->ctr, sizeof(Counters)));
-    CU(ctx, cudaMemset(d->ctr, 0, sizeof(Counters)));
     CU(ctx, cudaMalloc(&d->cut, sizeof(CutRanges)));
 
     int per_sm = 0, sms = 0;
-    if (m->has_prefix) CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile_kernel<true>, NT, 0));
-    else CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile_kernel<false>, NT, 0));
+    if (m->has_prefix) CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile2_kernel<true>, NT, 0));
+    else CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile2_kernel<false>, NT, 0));
     CU(ctx, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
     if (per_sm < 1) per_sm = 1;
     d->sms = sms;
     d->grid = per_sm * sms;
     d->long_grid = 2 * sms;
-    {
-        int per = 0;
-        CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, miss_kernel, MNT, 0));
-        d->miss_grid = (per < 1 ? 1 : per) * sms;
-    }
-
-    // ids a 960-byte tile can produce: one per symbol of the pretokens STARTING in it (the last one may run up to
-    // MAXW - 1 bytes past the tile) + the prefix ids of every document starting in it
-    d->stride = (uint32_t)(OWN + MAXW) * dm.kmax;
-    d->slot_extra = m->has_prefix ? m->n_prefix_syms + m->n_prefix_alone : 0u;
     d->med_cap = 4096u * dm.kmax + m->n_prefix_syms + 64;
     d->cta_scratch_words = 5ull * d->med_cap + 8;  // U, MG, NX, PV + tournament-tree levels
     CU(ctx, cudaMalloc(&d->cta_scratch, d->cta_scratch_words * sizeof(uint32_t) * d->long_grid));
@@ -239,17 +218,11 @@ static void dev_free(hut_dev* d) {
     for (int i = 0; i < d->nalloc; ++i) cudaFree(d->allocs[i]);
     cudaFree(d->cache);
     cudaFree(d->cache2);
-    cudaFree(d->ctr);
     cudaFree(d->cut);
     cudaFree(d->cta_scratch);
     cudaFree(d->big_pool);
-    cudaFree(d->stage);
-    cudaFree(d->tilebuf);
-    cudaFree(d->bsum);
-    cudaFree(d->def);
-    cudaFree(d->miss);
     cudaFree(d->long_ids);
-    cudaFree(d->cut_tmp);
+    cudaFree(d->tmp_ids);
     for (int b = 0; b < 2; ++b) {
         hut_chunkbuf* c = &d->cb[b];
         cudaFree(c->d_text);
@@ -260,6 +233,10 @@ static void dev_free(hut_dev* d) {
         if (c->ev_in) cudaEventDestroy(c->ev_in);
         if (c->ev_out) cudaEventDestroy(c->ev_out);
         cudaFreeHost(d->fl[b].h_ctr);
+        cudaFree(d->fl[b].ctr);
+        cudaFree(d->fl[b].tilebuf);
+        cudaFree(d->fl[b].bsum);
+        cudaFree(d->fl[b].def);
         for (int i = 0; i < 4; ++i)
             if (d->fl[b].ev[i]) cudaEventDestroy(d->fl[b].ev[i]);
         if (d->fl[b].done) cudaEventDestroy(d->fl[b].done);
@@ -371,11 +348,20 @@ static cudaError_t grow(T** p, size_t* cap, size_t need) {
     return e;
 }
 
-/* launches the kernel pipeline for one resident shard on `st`; the device must be current */
+/* the pieces of a flight's tile buffer */
+static void job_tile_arrays(Job* J, hut_flight* f, uint32_t ntiles) {
+    J->status = reinterpret_cast<unsigned long long*>(f->tilebuf);
+    J->first_doc = f->tilebuf + 2 * (size_t)ntiles;
+    J->tot = J->first_doc + ((size_t)ntiles + 1);
+    J->def_first = J->tot + ((size_t)ntiles + 1);
+}
+
+/* launches the kernel pipeline for one resident shard on `st`; the device must be current.  Common path: two small
+ * kernels + tile2_kernel, which leaves the ids at their final position; the patch phase for long pretokens is started
+ * by finish_shard when the counters ask for it. */
 static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* d_bytes, uint64_t n_bytes,
                         const uint64_t* d_doc_offsets, uint64_t n_docs, int32_t* d_ids, uint64_t ids_capacity,
-                        uint64_t* d_tok_offsets, cudaStream_t st, size_t def_want, size_t long_want,
-                        size_t miss_want = 0) {
+                        uint64_t* d_tok_offsets, cudaStream_t st, size_t def_want) {
     if (n_docs >= 0xFFFFFFF0ull) return set_err(ctx, HUT_STATUS_ARG, "%s", "too many documents in one shard");
     if ((uintptr_t)d_bytes & 15) return set_err(ctx, HUT_STATUS_ARG, "%s", "device text buffer must be 16-byte aligned");
     const uint64_t ntiles64 = (n_bytes + OWN - 1) / OWN;
@@ -383,24 +369,18 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     const uint32_t ntiles = (uint32_t)ntiles64;
     if (ntiles == 0) {
         CU(ctx, cudaMemsetAsync(d_tok_offsets, 0, (n_docs + 1) * sizeof(uint64_t), st));
-        CU(ctx, cudaMemsetAsync(d->ctr, 0, offsetof(Counters, events), st));
+        CU(ctx, cudaMemsetAsync(f->ctr, 0, offsetof(Counters, events), st));
         for (int i = 0; i < 4; ++i) CU(ctx, cudaEventRecord(f->ev[i], st));
         memset(&f->job, 0, sizeof f->job);
-        CU(ctx, cudaMemcpyAsync(f->h_ctr, d->ctr, offsetof(Counters, events), cudaMemcpyDeviceToHost, st));
+        CU(ctx, cudaMemcpyAsync(f->h_ctr, f->ctr, offsetof(Counters, events), cudaMemcpyDeviceToHost, st));
         CU(ctx, cudaEventRecord(f->done, st));
         return HUT_STATUS_OK;
     }
     const uint32_t nblocks = (ntiles + SCAN_BLK - 1) / SCAN_BLK;
     if (def_want < (size_t)ntiles / 8 + 65536) def_want = (size_t)ntiles / 8 + 65536;
-    if (long_want < (size_t)n_bytes / 16 + (1u << 20)) long_want = (size_t)n_bytes / 16 + (1u << 20);
-    CU(ctx, grow(&d->stage, &d->stage_cap, (size_t)ntiles * d->stride + (size_t)n_docs * d->slot_extra + 64));
-    CU(ctx, grow(&d->tilebuf, &d->tilebuf_cap, 6 * ((size_t)ntiles + 1) + 4));
-    CU(ctx, grow(&d->bsum, &d->bsum_cap, (size_t)nblocks));
-    CU(ctx, grow(&d->def, &d->def_cap, def_want));
-    CU(ctx, grow(&d->long_ids, &d->long_cap, long_want));
-    if (miss_want < (size_t)n_bytes / 96 + 65536) miss_want = (size_t)n_bytes / 96 + 65536;
-    if (n_bytes > (1ull << 40) - 1) return set_err(ctx, HUT_STATUS_ARG, "%s", "shard too large (max 1 TB)");
-    CU(ctx, grow(&d->miss, &d->miss_cap, miss_want));
+    CU(ctx, grow(&f->tilebuf, &f->tilebuf_cap, 5 * ((size_t)ntiles + 1) + 4));
+    CU(ctx, grow(&f->bsum, &f->bsum_cap, (size_t)nblocks));
+    CU(ctx, grow(&f->def, &f->def_cap, def_want));
     Job J;
     memset(&J, 0, sizeof J);
     J.text = d_bytes;
@@ -411,23 +391,12 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     J.out_cap = ids_capacity;
     J.tok_off = (unsigned long long*)d_tok_offsets;
     J.ntiles = ntiles;
-    J.stride = d->stride;
-    J.slot_extra = d->slot_extra;
-    J.slot_off = reinterpret_cast<unsigned long long*>(d->tilebuf + 4 * ((size_t)ntiles + 1));  // 16-byte aligned
-    J.stage = d->stage;
-    J.cnt = d->tilebuf;
-    J.tot = J.cnt + ((size_t)ntiles + 1);
-    J.first_doc = J.tot + ((size_t)ntiles + 1);
-    J.def_first = J.first_doc + ((size_t)ntiles + 1);
-    J.bsum = d->bsum;
+    job_tile_arrays(&J, f, ntiles);
+    J.bsum = f->bsum;
     J.nblocks = nblocks;
-    J.def = d->def;
-    J.def_cap = d->def_cap > 0xFFFFFFF0ull ? 0xFFFFFFF0u : (uint32_t)d->def_cap;
-    J.miss = d->miss;
-    J.miss_cap = d->miss_cap > 0xFFFFFFF0ull ? 0xFFFFFFF0u : (uint32_t)d->miss_cap;
-    J.long_ids = d->long_ids;
-    J.long_cap = d->long_cap;
-    J.ctr = d->ctr;
+    J.def = f->def;
+    J.def_cap = f->def_cap > 0xFFFFFFF0ull ? 0xFFFFFFF0u : (uint32_t)f->def_cap;
+    J.ctr = f->ctr;
     J.cache = d->cache;
     J.cache_bits = d->cache_bits;
     J.cache2 = d->cache2;
@@ -440,100 +409,119 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     J.big_cap = d->big_cap;
     J.big_slots = d->big_slots;
     CU(ctx, cudaEventRecord(f->ev[0], st));
+    // look-back words = 0 ("nothing known"), first_doc = NODOC: one memset each
+    CU(ctx, cudaMemsetAsync(J.status, 0, (size_t)ntiles * sizeof(unsigned long long), st));
     CU(ctx, cudaMemsetAsync(J.first_doc, 0xFF, ((size_t)ntiles + 1) * sizeof(uint32_t), st));
     init_kernel<<<1, 32, 0, st>>>(J);
     if (n_docs) doc_kernel<<<(unsigned)((n_docs + 255) / 256), 256, 0, st>>>(J);
-    slot_docs_kernel<<<(unsigned)(((size_t)ntiles + 1 + 255) / 256), 256, 0, st>>>(
-        J, reinterpret_cast<unsigned long long*>(d->tilebuf + 4 * ((size_t)ntiles + 1)));
-    d->stats.kernel_launches += 1;
     CU(ctx, cudaEventRecord(f->ev[1], st));
-    // tile_kernel merges the cache misses it can key itself (batches of 32, one per lane) and lists the rest, which
-    // miss_kernel merges afterwards
-    J.tile_lo = 0;
-    J.tile_hi = ntiles;
-    J.seg = 0;
     const uint32_t want = (ntiles + WPB - 1) / WPB;
     const uint32_t tile_grid = want < (uint32_t)d->grid ? want : (uint32_t)d->grid;
-    if (d->dm.has_prefix) tile_kernel<true><<<tile_grid, NT, 0, st>>>(d->dm, J);
-    else tile_kernel<false><<<tile_grid, NT, 0, st>>>(d->dm, J);
-    {
-        const uint32_t mg = ntiles / 4 + 1;
-        miss_kernel<<<mg < (uint32_t)d->miss_grid ? mg : (uint32_t)d->miss_grid, MNT, 0, st>>>(d->dm, J);
-    }
-    const uint32_t nlaunch = 2;
+    if (d->dm.has_prefix) tile2_kernel<true><<<tile_grid, NT, 0, st>>>(d->dm, J);
+    else tile2_kernel<false><<<tile_grid, NT, 0, st>>>(d->dm, J);
     CU(ctx, cudaEventRecord(f->ev[2], st));
-    long_kernel<<<d->long_grid, LNT, 0, st>>>(d->dm, J);
-    scan1_kernel<<<nblocks, 1024, 0, st>>>(J);
-    scan2_kernel<<<1, 1024, 0, st>>>(J);
-    const uint32_t cgrid = (ntiles + 7) / 8;
-    compact_kernel<<<cgrid < (uint32_t)d->sms * 8u ? cgrid : (uint32_t)d->sms * 8u, 256, 0, st>>>(J);
-    fixdoc_kernel<<<(unsigned)((n_docs + 1 + 255) / 256), 256, 0, st>>>(J);
     CU(ctx, cudaEventRecord(f->ev[3], st));
     CU(ctx, cudaGetLastError());
-    d->stats.kernel_launches += nlaunch + (n_docs ? 7 : 6);
+    d->stats.kernel_launches += n_docs ? 3 : 2;
     f->job = J;
-    d->ctr_owner = f;
-    CU(ctx, cudaMemcpyAsync(f->h_ctr, d->ctr, offsetof(Counters, events), cudaMemcpyDeviceToHost, st));
+    CU(ctx, cudaMemcpyAsync(f->h_ctr, f->ctr, offsetof(Counters, events), cudaMemcpyDeviceToHost, st));
     CU(ctx, cudaEventRecord(f->done, st));
     return HUT_STATUS_OK;
 }
 
 static void stats_begin(hut_dev* d) { memset(&d->stats, 0, sizeof d->stats); }
 
-/* waits for the flight's counters: re-runs with larger side buffers if they overflowed, applies document cuts,
+/* Patch phase of a shard that holds pretokens of more than 32 bytes / symbols (rare in ordinary text): long_kernel
+ * merges them, the ids behind each of them move right to make room and the deferred ids are spliced in.  Runs on the
+ * flight's own state, so chunks queued behind it are not disturbed. */
+static int patch_phase(hut_ctx* ctx, hut_dev* d, hut_flight* f, cudaStream_t st, float* ms_out) {
+    Job J = f->job;
+    const Counters* c = f->h_ctr;
+    const uint64_t total_pre = c->total_ids;
+    size_t long_want = (size_t)(J.nbytes / 16) + (1u << 20);
+    cudaEvent_t e0 = f->ev[0], e1 = f->ev[3];  // the main launch's events have been read already
+    CU(ctx, cudaEventRecord(e0, st));
+    for (int attempt = 0;; ++attempt) {
+        CU(ctx, grow(&d->long_ids, &d->long_cap, long_want));
+        J.long_ids = d->long_ids;
+        J.long_cap = d->long_cap;
+        CU(ctx, cudaMemsetAsync(J.tot, 0, ((size_t)J.ntiles + 1) * sizeof(uint32_t), st));
+        CU(ctx, cudaMemsetAsync(J.def_first, 0xFF, ((size_t)J.ntiles + 1) * sizeof(uint32_t), st));
+        long_reset_kernel<<<1, 32, 0, st>>>(J);
+        long_kernel<<<d->long_grid, LNT, 0, st>>>(d->dm, J);
+        CU(ctx, cudaMemcpyAsync(f->h_ctr, f->ctr, offsetof(Counters, events), cudaMemcpyDeviceToHost, st));
+        CU(ctx, cudaStreamSynchronize(st));
+        d->stats.kernel_launches += 2;
+        if (!(c->flags & FLAG_LONG_CAP) || attempt == 3) break;
+        long_want = (size_t)c->long_used + (size_t)c->long_used / 8 + 4096;  // the bump pointer kept counting
+    }
+    if (c->flags & (FLAG_LONG_CAP | FLAG_BIG_CAP)) return HUT_STATUS_OK;  // reported by the caller
+    CU(ctx, grow(&d->tmp_ids, &d->tmp_ids_cap, (size_t)total_pre + 1));
+    if (total_pre)
+        CU(ctx, cudaMemcpyAsync(d->tmp_ids, J.out, total_pre * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+    J.pre = d->tmp_ids;
+    scan1_kernel<<<J.nblocks, 1024, 0, st>>>(J);
+    scan2_kernel<<<1, 1024, 0, st>>>(J);
+    const uint32_t cgrid = (J.ntiles + 7) / 8;
+    patch_kernel<<<cgrid < (uint32_t)d->sms * 8u ? cgrid : (uint32_t)d->sms * 8u, 256, 0, st>>>(J);
+    patch_doc_kernel<<<(unsigned)((J.ndocs + 1 + 255) / 256), 256, 0, st>>>(J);
+    CU(ctx, cudaGetLastError());
+    CU(ctx, cudaEventRecord(e1, st));
+    CU(ctx, cudaMemcpyAsync(f->h_ctr, f->ctr, offsetof(Counters, events), cudaMemcpyDeviceToHost, st));
+    CU(ctx, cudaStreamSynchronize(st));
+    d->stats.kernel_launches += 4;
+    f->job = J;
+    cudaEventElapsedTime(ms_out, e0, e1);
+    return HUT_STATUS_OK;
+}
+
+/* waits for the flight's counters: runs the patch phase if the shard has long pretokens, applies document cuts,
  * accumulates stats */
 static int finish_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, uint64_t n_docs, int32_t* d_ids,
                         uint64_t* d_tok_offsets, uint64_t* n_ids_out, cudaStream_t st) {
     const Counters* c = f->h_ctr;
     for (int attempt = 0;; ++attempt) {
         CU(ctx, cudaEventSynchronize(f->done));
-        if (!(c->flags & (FLAG_DEF_CAP | FLAG_LONG_CAP | FLAG_MISS_CAP)) || attempt == 4) break;
-        // rare: many / very long deferred pretokens.  The counters kept counting, so they state the need.
-        CU(ctx, cudaStreamSynchronize(st));  // later chunks queued behind this one still use the side buffers
+        if (!(c->flags & FLAG_DEF_CAP) || attempt == 3) break;
+        // rare: very many long pretokens.  The counter kept counting, so it states the need.
         const Job J = f->job;
-        const size_t def_want = (size_t)c->n_def + 1024, long_want = (size_t)c->long_used * 2 + 4096;
-        // the miss count of a run that overflowed is only a lower bound (later segments saw a colder cache)
-        const size_t miss_want = (c->flags & FLAG_MISS_CAP) ? (size_t)c->n_miss * 2 + 65536 : 0;
         int rc = launch_shard(ctx, d, f, J.text, J.nbytes, (const uint64_t*)J.doc_off, J.ndocs, J.out, J.out_cap,
-                              (uint64_t*)J.tok_off, st, def_want, long_want, miss_want);
+                              (uint64_t*)J.tok_off, st, (size_t)c->n_def + (size_t)c->n_def / 8 + 1024);
         if (rc != HUT_STATUS_OK) return rc;
     }
-    float ms_all = 0, ms_main = 0;
+    float ms_all = 0, ms_main = 0, ms_patch = 0;
     cudaEventElapsedTime(&ms_all, f->ev[0], f->ev[3]);
     cudaEventElapsedTime(&ms_main, f->ev[1], f->ev[2]);
     d->stats.pretokens += c->st_pretokens;
     d->stats.cache_hits += c->st_hits;
     d->stats.warp_merges += c->st_warp;
     d->stats.block_merges += c->st_block;
-    d->stats.big_merges += c->st_big;
-    d->stats.kernel_ms += ms_all;
+    if (c->flags & FLAG_DEF_CAP)
+        return set_err(ctx, HUT_STATUS_MEMORY, "%s", "the list of long pretokens could not be sized");
+    if (c->flags & FLAG_OUT_CAP) return set_err(ctx, HUT_STATUS_CAPACITY, "%s", "output id buffer too small");
+    if (c->flags & FLAG_NUL)
+        return set_err(ctx, HUT_STATUS_VALUE, "%s", "document contains a 0x00 byte (cut documents at NUL before calling)");
+    if (c->n_def && f->job.ntiles) {
+        int rc = patch_phase(ctx, d, f, st, &ms_patch);
+        if (rc != HUT_STATUS_OK) return rc;
+        d->stats.big_merges += c->st_big;
+    }
+    d->stats.kernel_ms += ms_all + ms_patch;
     d->stats.main_kernel_ms += ms_main;
     uint64_t total = c->total_ids;
     if (c->flags & FLAG_OUT_CAP) return set_err(ctx, HUT_STATUS_CAPACITY, "%s", "output id buffer too small");
     if (c->flags & FLAG_BIG_CAP)
         return set_err(ctx, HUT_STATUS_UNSUPPORTED, "%s", "a pretoken exceeds the configured max_pretoken working area");
-    if (c->flags & (FLAG_DEF_CAP | FLAG_LONG_CAP | FLAG_MISS_CAP))
+    if (c->flags & FLAG_LONG_CAP)
         return set_err(ctx, HUT_STATUS_MEMORY, "%s", "side buffers for long pretokens could not be sized");
     if (c->flags & FLAG_EVENTS)
         return set_err(ctx, HUT_STATUS_UNSUPPORTED, "%s", "too many over-long pretokens in one call");
-    if (c->flags & FLAG_NUL)
-        return set_err(ctx, HUT_STATUS_VALUE, "%s", "document contains a 0x00 byte (cut documents at NUL before calling)");
     if (c->n_events) {
-        // reference-compatible cut (core.c:402-407,503): drop the rest of each affected document.  The events are
-        // still in the device counters only if no later chunk has started: drain the stream and re-read them.
-        CU(ctx, cudaStreamSynchronize(st));
-        if (d->ctr_owner != f) {  // a later chunk reset the counters: run this one again, alone
-            const Job J = f->job;
-            int rc = launch_shard(ctx, d, f, J.text, J.nbytes, (const uint64_t*)J.doc_off, J.ndocs, J.out, J.out_cap,
-                                  (uint64_t*)J.tok_off, st, d->def_cap, d->long_cap);
-            if (rc != HUT_STATUS_OK) return rc;
-            CU(ctx, cudaEventSynchronize(f->done));
-            total = c->total_ids;
-        }
-        CU(ctx, grow(&d->cut_tmp, &d->cut_tmp_cap, (size_t)total));
-        CU(ctx, cudaMemcpyAsync(d->cut_tmp, d_ids, total * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+        // reference-compatible cut (core.c:402-407,503): drop the rest of each affected document
+        CU(ctx, grow(&d->tmp_ids, &d->tmp_ids_cap, (size_t)total + 1));
+        CU(ctx, cudaMemcpyAsync(d->tmp_ids, d_ids, total * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
         cut_prepare_kernel<<<1, 1, 0, st>>>(f->job, d->cut);
-        cut_apply_ids_kernel<<<592, 256, 0, st>>>(d->cut_tmp, d_ids, total, d->cut);
+        cut_apply_ids_kernel<<<592, 256, 0, st>>>(d->tmp_ids, d_ids, total, d->cut);
         cut_apply_offs_kernel<<<148, 256, 0, st>>>((unsigned long long*)d_tok_offsets, n_docs + 1, d->cut);
         CU(ctx, cudaGetLastError());
         CutRanges head;
@@ -558,7 +546,7 @@ extern "C" int hut_encode_device(hut_ctx* ctx, int dev_index, const uint8_t* d_b
     cudaStream_t st = stream ? (cudaStream_t)stream : d->stream;
     stats_begin(d);
     hut_flight* f = &d->fl[0];
-    int rc = launch_shard(ctx, d, f, d_bytes, n_bytes, d_doc_offsets, n_docs, d_ids, ids_capacity, d_tok_offsets, st, 0, 0);
+    int rc = launch_shard(ctx, d, f, d_bytes, n_bytes, d_doc_offsets, n_docs, d_ids, ids_capacity, d_tok_offsets, st, 0);
     if (rc != HUT_STATUS_OK) return rc;
     return finish_shard(ctx, d, f, n_docs, d_ids, d_tok_offsets, n_ids_out, st);
 }
@@ -657,7 +645,7 @@ static int chunk_issue(hut_ctx* ctx, const uint8_t* bytes, const uint64_t* doc_o
     CU(ctx, cudaStreamWaitEvent(d->stream, c->ev_in, 0));
     TRACE(p, 2, d->stream);
     const int rc = launch_shard(ctx, d, &d->fl[p->buf], c->d_text, nb, (const uint64_t*)c->d_off, nd, c->d_ids,
-                                c->d_ids_cap, (uint64_t*)c->d_tok, d->stream, 0, 0);
+                                c->d_ids_cap, (uint64_t*)c->d_tok, d->stream, 0);
     if (rc == HUT_STATUS_OK) TRACE(p, 3, d->stream);
     return rc;
 }
@@ -707,6 +695,8 @@ extern "C" int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64
     if (!result || !doc_offsets || (n_docs && !bytes && doc_offsets[n_docs] != doc_offsets[0]))
         return set_err(ctx, HUT_STATUS_ARG, "%s", "bad argument");
     memset(result, 0, sizeof *result);
+    for (uint64_t i = 0; i < n_docs; ++i)  // decreasing offsets would underflow every byte count below
+        if (doc_offsets[i] > doc_offsets[i + 1]) return set_err(ctx, HUT_STATUS_ARG, "%s", "doc_offsets must be non-decreasing");
     const uint64_t total_bytes = doc_offsets[n_docs] - doc_offsets[0];
     // ---- plan: contiguous document ranges balanced by bytes (hut_plan_shards), dealt round-robin to the devices;
     //      every device works on two chunks at a time: upload of chunk k+1 | kernels of chunk k | download of k-1 ----
@@ -780,6 +770,7 @@ extern "C" int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64
     if (trace) {
         for (int k = 0; k < nch; ++k) {
             float t[6] = {0, 0, 0, 0, 0, 0};
+            // times are relative to the device's first chunk: chunk k runs on device k % ndev, so chunk `dev` is it
             for (int i = 0; i < 6; ++i) cudaEventElapsedTime(&t[i], plan[plan[k].dev].tr[0], plan[k].tr[i]);
             fprintf(stderr, "hut trace chunk %d dev %d MB %.1f ids %llu | up %.3f-%.3f | kernels %.3f-%.3f | down %.3f-%.3f ms\n",
                     k, plan[k].dev, (double)(plan[k].byte_hi - plan[k].byte_lo) / 1048576.0,

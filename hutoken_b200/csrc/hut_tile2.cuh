@@ -48,6 +48,50 @@ struct TileSm2 {
     WarpSm2 w[WPB];
 };
 
+// scalar restatement (hut_classify.h) of one 32-byte chunk: only used when an over-long UTF-8 form is in the tile
+__device__ __noinline__ void generic_chunk(const uint8_t* text, const uint32_t* dsm, int lane, uint32_t* ST, uint32_t* NU) {
+    auto dsbit = [&](int x) -> uint32_t { return (x >= 0 && x < SPAN) ? ((dsm[x >> 5] >> (x & 31)) & 1u) : 0u; };
+    auto lead = [&](int x) -> uint32_t {
+        uint32_t b0 = text[x], b1 = text[x + 1], b2 = text[x + 2], b3 = text[x + 3];
+        if (dsbit(x + 1)) b1 = b2 = b3 = 0;
+        else if (dsbit(x + 2)) b2 = b3 = 0;
+        else if (dsbit(x + 3)) b3 = 0;
+        return hut_lead_class(b0, b1, b2, b3);
+    };
+    auto code = [&](int x) -> uint32_t {
+        if (x < 0) return HC_END;
+        const uint32_t b0 = text[x];
+        if ((b0 & 0xC0u) == 0x80u) {
+            for (int k = 1; k <= 3; ++k) {
+                const int q = x - k;
+                if (q < 0) break;
+                if ((text[q] & 0xC0u) == 0x80u) continue;
+                if ((lead(q) >> 4) > (uint32_t)k) return HC_CONT;
+                break;
+            }
+            return HC_BAD;
+        }
+        return lead(x) & 15u;
+    };
+    uint32_t st = 0, nu = 0;
+    for (int j = 0; j < 32; ++j) {
+        const int x = lane * 32 + j;
+        const uint32_t c = code(x);
+        if (c == HC_END) {
+            nu |= 1u << j;
+            continue;
+        }
+        if (c == HC_CONT) continue;
+        const uint32_t p1 = code(x - 1);
+        uint32_t pc = p1;
+        for (int k = 2; pc == HC_CONT && k <= 4; ++k) pc = code(x - k);
+        const int lone = dsbit(x - 1) || code(x - 2) != HC_SPACE;
+        if (hut_is_start(c, (int)dsbit(x), p1, pc, lone)) st |= 1u << j;
+    }
+    *ST = st;
+    *NU = nu;
+}
+
 __device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
     unsigned long long v;
     asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
@@ -199,7 +243,6 @@ __global__ void __launch_bounds__(NT, HUT_TILE_CTAS) tile2_kernel(const __grid_c
     __shared__ TileSm2 sm;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t FULL = 0xFFFFFFFFu;
-    const uint32_t lt_mask = (1u << lane) - 1u;
     WarpSm2& ws = sm.w[warp];
 
     for (int i = tid; i < 256; i += NT) sm.byte1[i] = M.byte1[i];
@@ -386,107 +429,159 @@ __global__ void __launch_bounds__(NT, HUT_TILE_CTAS) tile2_kernel(const __grid_c
                 if (lane >= d) inc += t;
             }
             const uint32_t H = __shfl_sync(FULL, inc, 31);
-            uint32_t off = inc - c;                      // position of this lane's ids behind `run`
+            const uint32_t off = inc - c;                // ids of the round's hits in the lanes before this one
             const uint32_t need = __ballot_sync(FULL, active && !hit);
             if (need == 0) {
+                // ---- every pretoken of the round was answered by the cache ----
                 if (run + H > (uint32_t)IDCAP) flush();
-            } else {
-                // ---- some pretokens were not answered by the cache (about one round in four on a cold cache) ----
-                // upper bound of what the round can produce; if it may not fit, earlier ids leave first, and if the
-                // round alone may not fit it is handled in four parts of 8 lanes (8 * LANE_IDS_MAX <= IDCAP)
-                const uint32_t UB = H + (uint32_t)__popc(need) * (uint32_t)LANE_IDS_MAX;
-                if (run + UB > (uint32_t)IDCAP) flush();
-                const int nparts = UB > (uint32_t)IDCAP ? 4 : 1;
-                uint32_t extra = 0;      // ids of the misses in lanes before this one
-                uint32_t taken = 0;      // ids of this round that have left already (parts flushed in between)
-                for (int part = 0; part < nparts; ++part) {
-                    const uint32_t pmask = nparts == 1 ? FULL : (0xFFu << (8 * part));
-                    if (part) {  // everything before this part leaves: positions restart at 0
-                        const uint32_t upto = __shfl_sync(FULL, off + extra, 8 * part) - taken;
-                        run += upto;   // ids of the earlier parts, complete in the slice
-                        flush();
-                        taken += upto;
-                    }
-                    uint32_t mm = need & pmask;
-                    while (mm) {
-                        const int j = __ffs((int)mm) - 1;
-                        mm &= mm - 1;
-                        const int sj = __shfl_sync(FULL, s, j), ej = __shfl_sync(FULL, e, j);
-                        const uint32_t fj = __shfl_sync(FULL, first, j), bj = __shfl_sync(FULL, b0, j);
-                        const uint32_t pos = run + __shfl_sync(FULL, off + extra, j) - taken;  // slice index of its ids
-                        const int lj = ej - sj;
-                        uint32_t total = 0xFFFFFFFFu;
-                        if (bj == 0) total = 0;  // a NUL in the text: the call fails (FLAG_NUL); emit nothing
-                        else if (lj <= MAXW) total = wmerge_one(M, sm.byte1, ws.text, ws.sc, sj, lj, fj, ws.ids + pos);
-                        if (total == 0xFFFFFFFFu) {  // more than 32 bytes / symbols -> side list, patch phase
-                            if (lane == 0) {
-                                defer_push2(J, tile, (unsigned long long)(g0 + sj), flushed + pos,
-                                            ej == (int)BEYOND ? 0u : (uint32_t)lj, fj, def_head, def_tail);
-                            }
-                            def_head = __shfl_sync(FULL, def_head, 0);
-                            def_tail = __shfl_sync(FULL, def_tail, 0);
-                            n_def++;
-                            total = 0;
-                        } else if (bj != 0) {
-                            n_miss++;
-                            if (M.cache_ok && total >= 1u && total <= (uint32_t)CACHE_IDS && lj <= CACHE2_KEY_MAX) {
-                                if (lane == j) {  // the owner still holds the key
-                                    int32_t t5[CACHE_IDS];
-#pragma unroll
-                                    for (int z = 0; z < CACHE_IDS; ++z) t5[z] = (uint32_t)z < total ? ws.ids[pos + z] : 0;
-                                    bool fits = true;  // ids are packed as signed 21-bit fields
-#pragma unroll
-                                    for (int z = 0; z < CACHE_IDS; ++z) fits = fits && t5[z] >= -(1 << 20) && t5[z] < (1 << 20);
-                                    if (fits) {
-                                        uint32_t pw[4];
-                                        val_pack(t5, total, pw);
-                                        if (keyed) cache_insert(J, key, pw);
-                                        else {
-                                            uint32_t k32[8];
-                                            build_key32(ws.text, sm.kmask32, s, len, first, k32);
-                                            cache2_insert(J, k32, pw);
-                                        }
-                                    }
-                                }
-                            }
-                        }
-                        if (lane > j) extra += total;
-                    }
-                }
-                const uint32_t X = __shfl_sync(FULL, extra, 31) + ((need >> 31) ? 0u : 0u);
-                // `extra` of lane 31 misses the ids of a miss IN lane 31: add them through the round total below
-                off = off + extra - taken;
-                // total ids of the round = position behind the last lane's ids
-                uint32_t last_total = 0;
-                {
-                    // ids of lane 31's own pretoken: hits have c; a miss wrote `total` ids, recovered as the
-                    // difference between the positions; simpler: recompute from the slice positions
-                    (void)X;
-                }
-                // round total: H + all miss ids.  Sum of miss ids = extra of a virtual lane 32.
-                // Every lane added `total` for misses in lanes < itself; lane 31's own miss is not in any `extra`.
-                // It is tracked separately:
-                last_total = 0;
-                (void)last_total;
-            }
-            // ---- ids of the hits -> the slice ----
-            {
                 int32_t* const p = ws.ids + run + off;
                 if (c > 0) p[0] = sext21(w[0]);
                 if (c > 1) p[1] = sext21(w[1]);
                 if (c > 2) p[2] = sext21(w[2]);
                 if (c > 3) p[3] = sext21(w[3]);
                 if (c > 4) p[4] = val_id4(w);
+                if (tile_docs && active && dsb) {  // documents starting at this pretoken: ids of the tile before it
+                    const unsigned long long gpos = (unsigned long long)(g0 + s);
+                    unsigned long long d = dfirst;
+                    while (d < J.ndocs && J.doc_off[d] < gpos) ++d;
+                    while (d < J.ndocs && J.doc_off[d] == gpos) J.tok_off[d++] = flushed + run + off;
+                }
+                run += H;
+                continue;
             }
-            if (tile_docs && active && dsb) {  // documents starting at this pretoken: ids of the tile before it
+            // ---- some pretokens were not answered by the cache (about one round in four on a cold cache): they are
+            // merged by the whole warp, in lane order, so that the position of everybody's ids is known when it is
+            // needed.  V(lane) = off + extra = ids of the round before this lane's.  UB = what the round can produce
+            // at most; if that may not fit behind `run`, the earlier ids leave first, and if the round alone may not
+            // fit it is handled in four parts of 8 lanes (8 * LANE_IDS_MAX <= IDCAP) with a flush in between. ----
+            const uint32_t UB = H + (uint32_t)__popc(need) * (uint32_t)LANE_IDS_MAX;
+            if (run + UB > (uint32_t)IDCAP) flush();
+            const int nparts = UB > (uint32_t)IDCAP ? 4 : 1;
+            const uint32_t tl0 = flushed + run;  // tile-local position of the round's first id
+            int rbase = (int)run;                // slice index of the round's first id (negative after a part flush)
+            uint32_t extra = 0;                  // ids of the misses in the lanes before this one
+            uint32_t extra_all = 0;              // ids of all misses of the round so far
+            for (int part = 0; part < nparts; ++part) {
+                const uint32_t pmask = nparts == 1 ? FULL : (0xFFu << (8 * part));
+                if (part) {  // the ids of the lanes before this part are complete: they leave, positions restart
+                    const uint32_t v0 = __shfl_sync(FULL, off + extra, 8 * part);
+                    run = (uint32_t)(rbase + (int)v0);
+                    flush();
+                    rbase = -(int)v0;
+                }
+                uint32_t mm = need & pmask;
+                while (mm) {
+                    const int j = __ffs((int)mm) - 1;
+                    mm &= mm - 1;
+                    const int sj = __shfl_sync(FULL, s, j), ej = __shfl_sync(FULL, e, j);
+                    const uint32_t fj = __shfl_sync(FULL, first, j), bj = __shfl_sync(FULL, b0, j);
+                    const uint32_t vj = __shfl_sync(FULL, off + extra, j);
+                    const int lj = ej - sj;
+                    uint32_t total = 0xFFFFFFFFu;
+                    if (bj == 0) total = 0;  // a NUL in the text: the call fails (FLAG_NUL); emit nothing, cache nothing
+                    else if (lj <= MAXW)
+                        total = wmerge_one(M, sm.byte1, ws.text, ws.sc, sj, lj, fj, ws.ids + (rbase + (int)vj));
+                    if (total == 0xFFFFFFFFu) {  // more than 32 bytes / symbols -> side list, patch phase
+                        if (lane == 0)
+                            defer_push2(J, tile, (unsigned long long)(g0 + sj), tl0 + vj,
+                                        ej == (int)BEYOND ? 0u : (uint32_t)lj, fj, def_head, def_tail);
+                        def_head = __shfl_sync(FULL, def_head, 0);
+                        def_tail = __shfl_sync(FULL, def_tail, 0);
+                        n_def++;
+                        total = 0;
+                    } else if (bj != 0) {
+                        n_miss++;
+                        if (lane == j && M.cache_ok && total >= 1u && total <= (uint32_t)CACHE_IDS &&
+                            len <= CACHE2_KEY_MAX) {  // the owner still holds the key
+                            const int32_t* src = ws.ids + (rbase + (int)vj);
+                            int32_t t5[CACHE_IDS];
+                            bool fits = true;  // ids are packed as signed 21-bit fields
+#pragma unroll
+                            for (int z = 0; z < CACHE_IDS; ++z) {
+                                t5[z] = (uint32_t)z < total ? src[z] : 0;
+                                fits = fits && t5[z] >= -(1 << 20) && t5[z] < (1 << 20);
+                            }
+                            if (fits) {
+                                uint32_t pw[4];
+                                val_pack(t5, total, pw);
+                                if (keyed) {
+                                    cache_insert(J, key, pw);
+                                } else {
+                                    uint32_t k32[8];
+                                    build_key32(ws.text, sm.kmask32, s, len, first, k32);
+                                    cache2_insert(J, k32, pw);
+                                }
+                            }
+                        }
+                    }
+                    if (lane > j) extra += total;
+                    extra_all += total;
+                }
+                // ---- ids of the part's hits (their positions are final now) ----
+                if ((pmask >> lane) & 1u) {
+                    int32_t* const p = ws.ids + (rbase + (int)(off + extra));
+                    if (c > 0) p[0] = sext21(w[0]);
+                    if (c > 1) p[1] = sext21(w[1]);
+                    if (c > 2) p[2] = sext21(w[2]);
+                    if (c > 3) p[3] = sext21(w[3]);
+                    if (c > 4) p[4] = val_id4(w);
+                }
+                __syncwarp();
+            }
+            if (tile_docs && active && dsb) {
                 const unsigned long long gpos = (unsigned long long)(g0 + s);
                 unsigned long long d = dfirst;
                 while (d < J.ndocs && J.doc_off[d] < gpos) ++d;
-                while (d < J.ndocs && J.doc_off[d] == gpos) J.tok_off[d++] = flushed + run + off;
+                while (d < J.ndocs && J.doc_off[d] == gpos) J.tok_off[d++] = tl0 + off + extra;
             }
-            run += H;
+            run = (uint32_t)(rbase + (int)(H + extra_all));
+        }
+
+        // ---- the tile's ids are complete: publish the count, learn the base, let the ids go ----
+        const unsigned long long cnt = (unsigned long long)flushed + run;
+        if (!have_base) {
+            if (lane == 0) st_relaxed_u64(J.status + tile, ST_AGG | cnt);
+            base = lookback(J.status, tile);
+            have_base = true;
+        }
+        if (lane == 0) st_relaxed_u64(J.status + tile, ST_PFX | (base + cnt));
+        if (run) flush();
+        // documents starting in this tile hold tile-local positions: make them global (pre-patch) ones
+        __syncwarp();
+        if (base && tile_docs && dfirst != NODOC) {
+            const unsigned long long tile_end = ((unsigned long long)tile + 1) * OWN;
+            for (unsigned long long d = (unsigned long long)dfirst + lane;; d += 32) {
+                const bool in = d < J.ndocs && J.doc_off[d] < tile_end && J.doc_off[d] < J.nbytes;
+                if (in) J.tok_off[d] += base;
+                if (!__all_sync(FULL, in)) break;
+            }
+        }
+        if (lane == 0) {
+            st_pre += n;
+            st_miss += n_miss;
+            st_def += n_def;
+        }
+        if (tile == J.ntiles - 1) {
+            // the last tile closes the offsets: empty documents at the very end of the text and entry n_docs
+            const unsigned long long total = base + cnt;
+            if (lane == 0) J.ctr->total_ids = total;
+            unsigned long long a = 0, b = J.ndocs;  // first document starting at / behind the end of the text
+            while (a < b) {
+                const unsigned long long mid = (a + b) >> 1;
+                if (J.doc_off[mid] < J.nbytes) a = mid + 1;
+                else b = mid;
+            }
+            for (unsigned long long d = a + lane; d <= J.ndocs; d += 32) J.tok_off[d] = total;
         }
         tile = __shfl_sync(FULL, next_tile, 0);
+    }
+    // ---- statistics ----
+    if (lane == 0) {
+        Counters* c = J.ctr;
+        if (st_pre) atomicAdd(&c->st_pretokens, st_pre);
+        if (st_pre - st_miss - st_def) atomicAdd(&c->st_hits, st_pre - st_miss - st_def);
+        if (st_def) atomicAdd(&c->st_block, st_def);
+        if (st_miss) atomicAdd(&c->st_warp, st_miss);
     }
 }
 
