@@ -155,7 +155,7 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     dm.cache_ok = (m->max_value < (1 << 20)) ? 1 : 0;  // ids are packed as signed 21-bit fields
     dm.kmax = m->max_sym_per_char ? m->max_sym_per_char : 1;
     dm.miss_len_max = MAXW;
-    dm.first_extra = 0;
+    dm.first_extra = m->has_prefix ? (m->n_prefix_syms > m->n_prefix_alone ? m->n_prefix_syms : m->n_prefix_alone) : 0u;
     CU(ctx, upload(d, m->sym_off, 257, &dm.sym_off));
     CU(ctx, upload(d, m->sym_pool, m->sym_off[256], &dm.sym_pool));
     uint32_t byte1[256];
@@ -192,8 +192,13 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     CU(ctx, cudaMalloc(&d->cut, sizeof(CutRanges)));
 
     int per_sm = 0, sms = 0;
-    if (m->has_prefix) CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile2_kernel<true>, NT, 0));
-    else CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile2_kernel<false>, NT, 0));
+    // the warps' shared-memory slices outgrow the 48 KB a kernel gets without asking
+    CU(ctx, cudaFuncSetAttribute(tile2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSm2)));
+    CU(ctx, cudaFuncSetAttribute(tile2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSm2)));
+    if (m->has_prefix)
+        CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile2_kernel<true>, NT2, sizeof(TileSm2)));
+    else
+        CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile2_kernel<false>, NT2, sizeof(TileSm2)));
     CU(ctx, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
     if (per_sm < 1) per_sm = 1;
     d->sms = sms;
@@ -349,9 +354,15 @@ static cudaError_t grow(T** p, size_t* cap, size_t need) {
 }
 
 /* the pieces of a flight's tile buffer */
+static size_t tile_groups(uint32_t ntiles) { return ((size_t)ntiles + GRP - 1) / GRP; }
+static size_t tilebuf_words(uint32_t ntiles) { return 2 * (size_t)ntiles + 4 * tile_groups(ntiles) + 4 * ((size_t)ntiles + 1) + 4; }
 static void job_tile_arrays(Job* J, hut_flight* f, uint32_t ntiles) {
+    const size_t ng = tile_groups(ntiles);
     J->status = reinterpret_cast<unsigned long long*>(f->tilebuf);
-    J->first_doc = f->tilebuf + 2 * (size_t)ntiles;
+    J->grp_st = J->status + ntiles;
+    J->grp_acc = J->grp_st + ng;
+    J->cnt0 = reinterpret_cast<uint32_t*>(J->grp_acc + ng);  // grp_st | grp_acc | cnt0 are zeroed by one memset
+    J->first_doc = J->cnt0 + ((size_t)ntiles + 1);
     J->tot = J->first_doc + ((size_t)ntiles + 1);
     J->def_first = J->tot + ((size_t)ntiles + 1);
 }
@@ -378,7 +389,7 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     }
     const uint32_t nblocks = (ntiles + SCAN_BLK - 1) / SCAN_BLK;
     if (def_want < (size_t)ntiles / 8 + 65536) def_want = (size_t)ntiles / 8 + 65536;
-    CU(ctx, grow(&f->tilebuf, &f->tilebuf_cap, 5 * ((size_t)ntiles + 1) + 4));
+    CU(ctx, grow(&f->tilebuf, &f->tilebuf_cap, tilebuf_words(ntiles)));
     CU(ctx, grow(&f->bsum, &f->bsum_cap, (size_t)nblocks));
     CU(ctx, grow(&f->def, &f->def_cap, def_want));
     Job J;
@@ -409,16 +420,16 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     J.big_cap = d->big_cap;
     J.big_slots = d->big_slots;
     CU(ctx, cudaEventRecord(f->ev[0], st));
-    // look-back words = 0 ("nothing known"), first_doc = NODOC: one memset each
-    CU(ctx, cudaMemsetAsync(J.status, 0, (size_t)ntiles * sizeof(unsigned long long), st));
+    // scan state = 0 ("nothing known"), first_doc = NODOC: one memset each
+    CU(ctx, cudaMemsetAsync(J.grp_st, 0, 2 * tile_groups(ntiles) * sizeof(unsigned long long) + ((size_t)ntiles + 1) * sizeof(uint32_t), st));
     CU(ctx, cudaMemsetAsync(J.first_doc, 0xFF, ((size_t)ntiles + 1) * sizeof(uint32_t), st));
     init_kernel<<<1, 32, 0, st>>>(J);
     if (n_docs) doc_kernel<<<(unsigned)((n_docs + 255) / 256), 256, 0, st>>>(J);
     CU(ctx, cudaEventRecord(f->ev[1], st));
-    const uint32_t want = (ntiles + WPB - 1) / WPB;
+    const uint32_t want = (ntiles + WPB2 - 1) / WPB2;
     const uint32_t tile_grid = want < (uint32_t)d->grid ? want : (uint32_t)d->grid;
-    if (d->dm.has_prefix) tile2_kernel<true><<<tile_grid, NT, 0, st>>>(d->dm, J);
-    else tile2_kernel<false><<<tile_grid, NT, 0, st>>>(d->dm, J);
+    if (d->dm.has_prefix) tile2_kernel<true><<<tile_grid, NT2, sizeof(TileSm2), st>>>(d->dm, J);
+    else tile2_kernel<false><<<tile_grid, NT2, sizeof(TileSm2), st>>>(d->dm, J);
     CU(ctx, cudaEventRecord(f->ev[2], st));
     CU(ctx, cudaEventRecord(f->ev[3], st));
     CU(ctx, cudaGetLastError());
@@ -489,6 +500,17 @@ static int finish_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, uint64_t n_docs
                               (uint64_t*)J.tok_off, st, (size_t)c->n_def + (size_t)c->n_def / 8 + 1024);
         if (rc != HUT_STATUS_OK) return rc;
     }
+#ifdef HUT_TIMING
+    fprintf(stderr, "hut timing (Mcycles summed over warps): stage %.1f classify %.1f rounds_hit %.1f rounds_miss %.1f "
+            "publish %.1f finalize %.1f closer %.1f looptop %.1f\n", c->tm[0] / 1e6, c->tm[1] / 1e6, c->tm[2] / 1e6,
+            c->tm[3] / 1e6, c->tm[4] / 1e6, c->tm[5] / 1e6, c->tm[6] / 1e6, c->tm[7] / 1e6);
+    fprintf(stderr, "hut timing: blocked %.1f Mcycles, wmerge_one %.1f, merge_lane (lane-cycles) %.1f\nhut hist log2(cycles):", c->tw[0] / 1e6,
+            c->tw[2] / 1e6, c->tw[3] / 1e6);
+    for (int i = 8; i < 30; ++i) fprintf(stderr, " %d:%u", i, c->hist[i]);
+    fprintf(stderr, "\nhut misses/tile:");
+    for (int i = 0; i < 32; ++i) fprintf(stderr, " %u", c->hmiss[i]);
+    fprintf(stderr, "\n");
+#endif
     float ms_all = 0, ms_main = 0, ms_patch = 0;
     cudaEventElapsedTime(&ms_all, f->ev[0], f->ev[3]);
     cudaEventElapsedTime(&ms_main, f->ev[1], f->ev[2]);

@@ -100,6 +100,12 @@ struct Counters {
     unsigned long long long_total; // ids of all deferred pretokens (scan2_kernel)
     unsigned long long st_pretokens, st_hits, st_warp, st_block, st_big, st_cut;
     unsigned int pool_lock[32];
+#ifdef HUT_TIMING
+    unsigned long long tm[8];      // cycles per phase of tile2_kernel, summed over warps (build switch, not shipped)
+    unsigned long long tw[4];      // cycles blocked in tile_base, calls blocked, cycles in wmerge_one, cycles in merge_lane rounds
+    unsigned int hist[32];         // tiles by log2(cycles of their rounds)
+    unsigned int hmiss[32];        // tiles by number of misses (clamped to 31)
+#endif
     CutEvent events[MAX_EVENTS];
 };
 
@@ -136,7 +142,10 @@ struct Job {
     unsigned long long out_cap;
     unsigned long long* tok_off;
     uint32_t ntiles;
-    unsigned long long* status;  // [ntiles] look-back word per tile: flag (bits 62..63) | id count / inclusive prefix
+    unsigned long long* status;  // [ntiles] inclusive id prefix per tile (pre-patch), written when the tile's ids leave
+    uint32_t* cnt0;              // [ntiles] id count + 1 per tile, 0 = not known yet            (two-level scan,
+    unsigned long long* grp_acc; // [ngroups] tiles done << 40 | ids of the group so far          hut_tile2.cuh)
+    unsigned long long* grp_st;  // [ngroups] look-back word per group: flag (bits 62..63) | total / inclusive prefix
     uint32_t* first_doc;         // [ntiles + 1]
     Counters* ctr;
     CacheSlot* cache;

@@ -18,6 +18,11 @@ __global__ void init_kernel(Job J) {
         c->long_total = 0;
         c->st_pretokens = c->st_hits = c->st_warp = c->st_block = c->st_big = c->st_cut = 0;
         for (int i = 0; i < 32; ++i) c->pool_lock[i] = 0;
+#ifdef HUT_TIMING
+        for (int i = 0; i < 8; ++i) c->tm[i] = 0;
+        for (int i = 0; i < 4; ++i) c->tw[i] = 0;
+        for (int i = 0; i < 32; ++i) c->hist[i] = c->hmiss[i] = 0;
+#endif
     }
 }
 
@@ -240,9 +245,9 @@ __global__ void __launch_bounds__(1024) scan2_kernel(Job J) {
 }
 
 // ids produced by the tiles before t, not counting deferred pretokens (tile2_kernel left the inclusive prefixes in
-// the look-back words); shift(t) = deferred ids before tile t
+// J.status); shift(t) = deferred ids before tile t
 __device__ __forceinline__ unsigned long long pre_base(const Job& J, unsigned long long t) {
-    return t ? (J.status[t - 1] & ST_MASK) : 0ull;
+    return t ? J.status[t - 1] : 0ull;
 }
 __device__ __forceinline__ unsigned long long tile_shift(const Job& J, unsigned long long t) {
     return J.bsum[t / SCAN_BLK] + J.tot[t];
@@ -278,7 +283,7 @@ __global__ void __launch_bounds__(256, 8) patch_kernel(const Job J) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t gw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), nw = gridDim.x * (blockDim.x >> 5);
     for (uint32_t tile = gw; tile < J.ntiles; tile += nw) {
-        const unsigned long long b0 = pre_base(J, tile), b1 = J.status[tile] & ST_MASK;
+        const unsigned long long b0 = pre_base(J, tile), b1 = J.status[tile];
         const uint32_t ns = (uint32_t)(b1 - b0);
         unsigned long long o = b0 + tile_shift(J, tile);
         const int32_t* src = J.pre + b0;
@@ -314,7 +319,7 @@ __global__ void patch_doc_kernel(const Job J) {
     if (d > J.ndocs) return;
     const unsigned long long pos = d < J.ndocs ? J.doc_off[d] : J.nbytes;
     if (d == J.ndocs || pos >= J.nbytes) {
-        const unsigned long long total = (J.status[J.ntiles - 1] & ST_MASK) + J.ctr->long_total;
+        const unsigned long long total = J.status[J.ntiles - 1] + J.ctr->long_total;
         J.tok_off[d] = total;
         if (d == J.ndocs) J.ctr->total_ids = total;
         return;
