@@ -27,13 +27,13 @@ struct hut_flight {
     Job job;
     Counters* ctr;       // device counters
     Counters* h_ctr;     // pinned mirror of the device counters, copied at the end of the launch
-    uint32_t* tilebuf;   // status (uint64 per tile) | first_doc | tot | def_first (ntiles + 1 uint32 each)
+    uint32_t* tilebuf;   // cnt | tot | first_doc | def_first (ntiles + 1 uint32 each) | slot_off (uint64 each)
     size_t tilebuf_cap;
     unsigned long long* bsum;
     size_t bsum_cap;
     DefEntry* def;
     size_t def_cap;
-    cudaEvent_t ev[4];   // start, before / after tile2_kernel, end
+    cudaEvent_t ev[4];   // start, before / after tile_kernel, end
     cudaEvent_t done;    // counters are in h_ctr
 };
 
@@ -73,7 +73,10 @@ struct hut_dev {
     unsigned long long big_slot_words;
     uint32_t big_cap, big_slots;
     int grid, long_grid, sms;
-    // grow-only temporaries of the patch phase (shards with long pretokens) and of the document cuts
+    uint32_t stride, slot_extra;
+    // grow-only temporaries shared by the device's flights (they run one after the other on the device's stream)
+    int32_t* stage;
+    size_t stage_cap;
     int32_t* long_ids;
     size_t long_cap;
     int32_t* tmp_ids;
@@ -192,18 +195,17 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     CU(ctx, cudaMalloc(&d->cut, sizeof(CutRanges)));
 
     int per_sm = 0, sms = 0;
-    // the warps' shared-memory slices outgrow the 48 KB a kernel gets without asking
-    CU(ctx, cudaFuncSetAttribute(tile2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSm2)));
-    CU(ctx, cudaFuncSetAttribute(tile2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSm2)));
-    if (m->has_prefix)
-        CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile2_kernel<true>, NT2, sizeof(TileSm2)));
-    else
-        CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile2_kernel<false>, NT2, sizeof(TileSm2)));
+    if (m->has_prefix) CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile_kernel<true>, NT, 0));
+    else CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile_kernel<false>, NT, 0));
     CU(ctx, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
     if (per_sm < 1) per_sm = 1;
     d->sms = sms;
     d->grid = per_sm * sms;
     d->long_grid = 2 * sms;
+    // ids a 960-byte tile can produce: one per symbol of the pretokens STARTING in it (the last one may run up to
+    // MAXW - 1 bytes past the tile) + the prefix ids of every document starting in it
+    d->stride = (uint32_t)(OWN + MAXW) * dm.kmax;
+    d->slot_extra = m->has_prefix ? m->n_prefix_syms + m->n_prefix_alone : 0u;
     d->med_cap = 4096u * dm.kmax + m->n_prefix_syms + 64;
     d->cta_scratch_words = 5ull * d->med_cap + 8;  // U, MG, NX, PV + tournament-tree levels
     CU(ctx, cudaMalloc(&d->cta_scratch, d->cta_scratch_words * sizeof(uint32_t) * d->long_grid));
@@ -226,6 +228,7 @@ static void dev_free(hut_dev* d) {
     cudaFree(d->cut);
     cudaFree(d->cta_scratch);
     cudaFree(d->big_pool);
+    cudaFree(d->stage);
     cudaFree(d->long_ids);
     cudaFree(d->tmp_ids);
     for (int b = 0; b < 2; ++b) {
@@ -354,25 +357,10 @@ static cudaError_t grow(T** p, size_t* cap, size_t need) {
 }
 
 /* the pieces of a flight's tile buffer */
-static size_t tile_groups(uint32_t ntiles) { return ((size_t)ntiles + GRP - 1) / GRP; }
-static size_t tilebuf_words(uint32_t ntiles) { return 2 * (size_t)ntiles + 4 * tile_groups(ntiles) + 4 * ((size_t)ntiles + 1) + 4; }
-static void job_tile_arrays(Job* J, hut_flight* f, uint32_t ntiles) {
-    const size_t ng = tile_groups(ntiles);
-    J->status = reinterpret_cast<unsigned long long*>(f->tilebuf);
-    J->grp_st = J->status + ntiles;
-    J->grp_acc = J->grp_st + ng;
-    J->cnt0 = reinterpret_cast<uint32_t*>(J->grp_acc + ng);  // grp_st | grp_acc | cnt0 are zeroed by one memset
-    J->first_doc = J->cnt0 + ((size_t)ntiles + 1);
-    J->tot = J->first_doc + ((size_t)ntiles + 1);
-    J->def_first = J->tot + ((size_t)ntiles + 1);
-}
-
-/* launches the kernel pipeline for one resident shard on `st`; the device must be current.  Common path: two small
- * kernels + tile2_kernel, which leaves the ids at their final position; the patch phase for long pretokens is started
- * by finish_shard when the counters ask for it. */
+/* launches the kernel pipeline for one resident shard on `st`; the device must be current */
 static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* d_bytes, uint64_t n_bytes,
                         const uint64_t* d_doc_offsets, uint64_t n_docs, int32_t* d_ids, uint64_t ids_capacity,
-                        uint64_t* d_tok_offsets, cudaStream_t st, size_t def_want) {
+                        uint64_t* d_tok_offsets, cudaStream_t st, size_t def_want, size_t long_want) {
     if (n_docs >= 0xFFFFFFF0ull) return set_err(ctx, HUT_STATUS_ARG, "%s", "too many documents in one shard");
     if ((uintptr_t)d_bytes & 15) return set_err(ctx, HUT_STATUS_ARG, "%s", "device text buffer must be 16-byte aligned");
     const uint64_t ntiles64 = (n_bytes + OWN - 1) / OWN;
@@ -389,9 +377,13 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     }
     const uint32_t nblocks = (ntiles + SCAN_BLK - 1) / SCAN_BLK;
     if (def_want < (size_t)ntiles / 8 + 65536) def_want = (size_t)ntiles / 8 + 65536;
-    CU(ctx, grow(&f->tilebuf, &f->tilebuf_cap, tilebuf_words(ntiles)));
+    if (long_want < (size_t)n_bytes / 16 + (1u << 20)) long_want = (size_t)n_bytes / 16 + (1u << 20);
+    const bool pfx = d->dm.has_prefix != 0;
+    CU(ctx, grow(&d->stage, &d->stage_cap, (size_t)ntiles * d->stride + (size_t)n_docs * d->slot_extra + 64));
+    CU(ctx, grow(&f->tilebuf, &f->tilebuf_cap, 6 * ((size_t)ntiles + 1) + 4));
     CU(ctx, grow(&f->bsum, &f->bsum_cap, (size_t)nblocks));
     CU(ctx, grow(&f->def, &f->def_cap, def_want));
+    CU(ctx, grow(&d->long_ids, &d->long_cap, long_want));
     Job J;
     memset(&J, 0, sizeof J);
     J.text = d_bytes;
@@ -402,11 +394,20 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     J.out_cap = ids_capacity;
     J.tok_off = (unsigned long long*)d_tok_offsets;
     J.ntiles = ntiles;
-    job_tile_arrays(&J, f, ntiles);
+    J.stride = d->stride;
+    J.slot_extra = d->slot_extra;
+    J.slot_off = reinterpret_cast<unsigned long long*>(f->tilebuf + 4 * ((size_t)ntiles + 1));  // 16-byte aligned
+    J.stage = d->stage;
+    J.cnt = f->tilebuf;
+    J.tot = J.cnt + ((size_t)ntiles + 1);
+    J.first_doc = J.tot + ((size_t)ntiles + 1);
+    J.def_first = J.first_doc + ((size_t)ntiles + 1);
     J.bsum = f->bsum;
     J.nblocks = nblocks;
     J.def = f->def;
     J.def_cap = f->def_cap > 0xFFFFFFF0ull ? 0xFFFFFFF0u : (uint32_t)f->def_cap;
+    J.long_ids = d->long_ids;
+    J.long_cap = d->long_cap;
     J.ctr = f->ctr;
     J.cache = d->cache;
     J.cache_bits = d->cache_bits;
@@ -420,20 +421,27 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     J.big_cap = d->big_cap;
     J.big_slots = d->big_slots;
     CU(ctx, cudaEventRecord(f->ev[0], st));
-    // scan state = 0 ("nothing known"), first_doc = NODOC: one memset each
-    CU(ctx, cudaMemsetAsync(J.grp_st, 0, 2 * tile_groups(ntiles) * sizeof(unsigned long long) + ((size_t)ntiles + 1) * sizeof(uint32_t), st));
     CU(ctx, cudaMemsetAsync(J.first_doc, 0xFF, ((size_t)ntiles + 1) * sizeof(uint32_t), st));
     init_kernel<<<1, 32, 0, st>>>(J);
     if (n_docs) doc_kernel<<<(unsigned)((n_docs + 255) / 256), 256, 0, st>>>(J);
+    if (pfx)
+        slot_docs_kernel<<<(unsigned)(((size_t)ntiles + 1 + 255) / 256), 256, 0, st>>>(
+            J, reinterpret_cast<unsigned long long*>(f->tilebuf + 4 * ((size_t)ntiles + 1)));
     CU(ctx, cudaEventRecord(f->ev[1], st));
-    const uint32_t want = (ntiles + WPB2 - 1) / WPB2;
+    const uint32_t want = (ntiles + WPB - 1) / WPB;
     const uint32_t tile_grid = want < (uint32_t)d->grid ? want : (uint32_t)d->grid;
-    if (d->dm.has_prefix) tile2_kernel<true><<<tile_grid, NT2, sizeof(TileSm2), st>>>(d->dm, J);
-    else tile2_kernel<false><<<tile_grid, NT2, sizeof(TileSm2), st>>>(d->dm, J);
+    if (pfx) tile_kernel<true><<<tile_grid, NT, 0, st>>>(d->dm, J);
+    else tile_kernel<false><<<tile_grid, NT, 0, st>>>(d->dm, J);
     CU(ctx, cudaEventRecord(f->ev[2], st));
+    long_kernel<<<d->long_grid, LNT, 0, st>>>(d->dm, J);
+    scan1_kernel<<<nblocks, 1024, 0, st>>>(J);
+    scan2_kernel<<<1, 1024, 0, st>>>(J);
+    const uint32_t cgrid = (ntiles + 7) / 8;
+    compact_kernel<<<cgrid < (uint32_t)d->sms * 8u ? cgrid : (uint32_t)d->sms * 8u, 256, 0, st>>>(J);
+    fixdoc_kernel<<<(unsigned)((n_docs + 1 + 255) / 256), 256, 0, st>>>(J);
     CU(ctx, cudaEventRecord(f->ev[3], st));
     CU(ctx, cudaGetLastError());
-    d->stats.kernel_launches += n_docs ? 3 : 2;
+    d->stats.kernel_launches += 6 + (n_docs ? 1 : 0) + (pfx ? 1 : 0);
     f->job = J;
     CU(ctx, cudaMemcpyAsync(f->h_ctr, f->ctr, offsetof(Counters, events), cudaMemcpyDeviceToHost, st));
     CU(ctx, cudaEventRecord(f->done, st));
@@ -442,104 +450,47 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
 
 static void stats_begin(hut_dev* d) { memset(&d->stats, 0, sizeof d->stats); }
 
-/* Patch phase of a shard that holds pretokens of more than 32 bytes / symbols (rare in ordinary text): long_kernel
- * merges them, the ids behind each of them move right to make room and the deferred ids are spliced in.  Runs on the
- * flight's own state, so chunks queued behind it are not disturbed. */
-static int patch_phase(hut_ctx* ctx, hut_dev* d, hut_flight* f, cudaStream_t st, float* ms_out) {
-    Job J = f->job;
-    const Counters* c = f->h_ctr;
-    const uint64_t total_pre = c->total_ids;
-    size_t long_want = (size_t)(J.nbytes / 16) + (1u << 20);
-    cudaEvent_t e0 = f->ev[0], e1 = f->ev[3];  // the main launch's events have been read already
-    CU(ctx, cudaEventRecord(e0, st));
-    for (int attempt = 0;; ++attempt) {
-        CU(ctx, grow(&d->long_ids, &d->long_cap, long_want));
-        J.long_ids = d->long_ids;
-        J.long_cap = d->long_cap;
-        CU(ctx, cudaMemsetAsync(J.tot, 0, ((size_t)J.ntiles + 1) * sizeof(uint32_t), st));
-        CU(ctx, cudaMemsetAsync(J.def_first, 0xFF, ((size_t)J.ntiles + 1) * sizeof(uint32_t), st));
-        long_reset_kernel<<<1, 32, 0, st>>>(J);
-        long_kernel<<<d->long_grid, LNT, 0, st>>>(d->dm, J);
-        CU(ctx, cudaMemcpyAsync(f->h_ctr, f->ctr, offsetof(Counters, events), cudaMemcpyDeviceToHost, st));
-        CU(ctx, cudaStreamSynchronize(st));
-        d->stats.kernel_launches += 2;
-        if (!(c->flags & FLAG_LONG_CAP) || attempt == 3) break;
-        long_want = (size_t)c->long_used + (size_t)c->long_used / 8 + 4096;  // the bump pointer kept counting
-    }
-    if (c->flags & (FLAG_LONG_CAP | FLAG_BIG_CAP)) return HUT_STATUS_OK;  // reported by the caller
-    CU(ctx, grow(&d->tmp_ids, &d->tmp_ids_cap, (size_t)total_pre + 1));
-    if (total_pre)
-        CU(ctx, cudaMemcpyAsync(d->tmp_ids, J.out, total_pre * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
-    J.pre = d->tmp_ids;
-    scan1_kernel<<<J.nblocks, 1024, 0, st>>>(J);
-    scan2_kernel<<<1, 1024, 0, st>>>(J);
-    const uint32_t cgrid = (J.ntiles + 7) / 8;
-    patch_kernel<<<cgrid < (uint32_t)d->sms * 8u ? cgrid : (uint32_t)d->sms * 8u, 256, 0, st>>>(J);
-    patch_doc_kernel<<<(unsigned)((J.ndocs + 1 + 255) / 256), 256, 0, st>>>(J);
-    CU(ctx, cudaGetLastError());
-    CU(ctx, cudaEventRecord(e1, st));
-    CU(ctx, cudaMemcpyAsync(f->h_ctr, f->ctr, offsetof(Counters, events), cudaMemcpyDeviceToHost, st));
-    CU(ctx, cudaStreamSynchronize(st));
-    d->stats.kernel_launches += 4;
-    f->job = J;
-    cudaEventElapsedTime(ms_out, e0, e1);
-    return HUT_STATUS_OK;
-}
-
-/* waits for the flight's counters: runs the patch phase if the shard has long pretokens, applies document cuts,
+/* waits for the flight's counters: re-runs with larger side buffers if they overflowed, applies document cuts,
  * accumulates stats */
 static int finish_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, uint64_t n_docs, int32_t* d_ids,
                         uint64_t* d_tok_offsets, uint64_t* n_ids_out, cudaStream_t st) {
     const Counters* c = f->h_ctr;
     for (int attempt = 0;; ++attempt) {
         CU(ctx, cudaEventSynchronize(f->done));
-        if (!(c->flags & FLAG_DEF_CAP) || attempt == 3) break;
-        // rare: very many long pretokens.  The counter kept counting, so it states the need.
+        if (!(c->flags & (FLAG_DEF_CAP | FLAG_LONG_CAP)) || attempt == 4) break;
+        // rare: many / very long deferred pretokens.  The counters kept counting, so they state the need.  The staging
+        // area and the id buffer for long pretokens are shared by the device's flights: drain the stream first.
+        CU(ctx, cudaStreamSynchronize(st));
         const Job J = f->job;
+        const size_t def_want = (size_t)c->n_def + (size_t)c->n_def / 8 + 1024;
+        const size_t long_want = (size_t)c->long_used + (size_t)c->long_used / 8 + 4096;
         int rc = launch_shard(ctx, d, f, J.text, J.nbytes, (const uint64_t*)J.doc_off, J.ndocs, J.out, J.out_cap,
-                              (uint64_t*)J.tok_off, st, (size_t)c->n_def + (size_t)c->n_def / 8 + 1024);
+                              (uint64_t*)J.tok_off, st, def_want, long_want);
         if (rc != HUT_STATUS_OK) return rc;
     }
-#ifdef HUT_TIMING
-    fprintf(stderr, "hut timing (Mcycles summed over warps): stage %.1f classify %.1f rounds_hit %.1f rounds_miss %.1f "
-            "publish %.1f finalize %.1f closer %.1f looptop %.1f\n", c->tm[0] / 1e6, c->tm[1] / 1e6, c->tm[2] / 1e6,
-            c->tm[3] / 1e6, c->tm[4] / 1e6, c->tm[5] / 1e6, c->tm[6] / 1e6, c->tm[7] / 1e6);
-    fprintf(stderr, "hut timing: blocked %.1f Mcycles, wmerge_one %.1f, merge_lane (lane-cycles) %.1f\nhut hist log2(cycles):", c->tw[0] / 1e6,
-            c->tw[2] / 1e6, c->tw[3] / 1e6);
-    for (int i = 8; i < 30; ++i) fprintf(stderr, " %d:%u", i, c->hist[i]);
-    fprintf(stderr, "\nhut misses/tile:");
-    for (int i = 0; i < 32; ++i) fprintf(stderr, " %u", c->hmiss[i]);
-    fprintf(stderr, "\n");
-#endif
-    float ms_all = 0, ms_main = 0, ms_patch = 0;
+    float ms_all = 0, ms_main = 0;
     cudaEventElapsedTime(&ms_all, f->ev[0], f->ev[3]);
     cudaEventElapsedTime(&ms_main, f->ev[1], f->ev[2]);
     d->stats.pretokens += c->st_pretokens;
     d->stats.cache_hits += c->st_hits;
     d->stats.warp_merges += c->st_warp;
     d->stats.block_merges += c->st_block;
-    if (c->flags & FLAG_DEF_CAP)
-        return set_err(ctx, HUT_STATUS_MEMORY, "%s", "the list of long pretokens could not be sized");
-    if (c->flags & FLAG_OUT_CAP) return set_err(ctx, HUT_STATUS_CAPACITY, "%s", "output id buffer too small");
-    if (c->flags & FLAG_NUL)
-        return set_err(ctx, HUT_STATUS_VALUE, "%s", "document contains a 0x00 byte (cut documents at NUL before calling)");
-    if (c->n_def && f->job.ntiles) {
-        int rc = patch_phase(ctx, d, f, st, &ms_patch);
-        if (rc != HUT_STATUS_OK) return rc;
-        d->stats.big_merges += c->st_big;
-    }
-    d->stats.kernel_ms += ms_all + ms_patch;
+    d->stats.big_merges += c->st_big;
+    d->stats.kernel_ms += ms_all;
     d->stats.main_kernel_ms += ms_main;
     uint64_t total = c->total_ids;
     if (c->flags & FLAG_OUT_CAP) return set_err(ctx, HUT_STATUS_CAPACITY, "%s", "output id buffer too small");
     if (c->flags & FLAG_BIG_CAP)
         return set_err(ctx, HUT_STATUS_UNSUPPORTED, "%s", "a pretoken exceeds the configured max_pretoken working area");
-    if (c->flags & FLAG_LONG_CAP)
+    if (c->flags & (FLAG_DEF_CAP | FLAG_LONG_CAP))
         return set_err(ctx, HUT_STATUS_MEMORY, "%s", "side buffers for long pretokens could not be sized");
     if (c->flags & FLAG_EVENTS)
         return set_err(ctx, HUT_STATUS_UNSUPPORTED, "%s", "too many over-long pretokens in one call");
+    if (c->flags & FLAG_NUL)
+        return set_err(ctx, HUT_STATUS_VALUE, "%s", "document contains a 0x00 byte (cut documents at NUL before calling)");
     if (c->n_events) {
-        // reference-compatible cut (core.c:402-407,503): drop the rest of each affected document
+        // reference-compatible cut (core.c:402-407,503): drop the rest of each affected document.  The events sit in
+        // this flight's own counters, so chunks queued behind it have not touched them.
         CU(ctx, grow(&d->tmp_ids, &d->tmp_ids_cap, (size_t)total + 1));
         CU(ctx, cudaMemcpyAsync(d->tmp_ids, d_ids, total * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
         cut_prepare_kernel<<<1, 1, 0, st>>>(f->job, d->cut);
@@ -568,7 +519,7 @@ extern "C" int hut_encode_device(hut_ctx* ctx, int dev_index, const uint8_t* d_b
     cudaStream_t st = stream ? (cudaStream_t)stream : d->stream;
     stats_begin(d);
     hut_flight* f = &d->fl[0];
-    int rc = launch_shard(ctx, d, f, d_bytes, n_bytes, d_doc_offsets, n_docs, d_ids, ids_capacity, d_tok_offsets, st, 0);
+    int rc = launch_shard(ctx, d, f, d_bytes, n_bytes, d_doc_offsets, n_docs, d_ids, ids_capacity, d_tok_offsets, st, 0, 0);
     if (rc != HUT_STATUS_OK) return rc;
     return finish_shard(ctx, d, f, n_docs, d_ids, d_tok_offsets, n_ids_out, st);
 }
@@ -667,7 +618,7 @@ static int chunk_issue(hut_ctx* ctx, const uint8_t* bytes, const uint64_t* doc_o
     CU(ctx, cudaStreamWaitEvent(d->stream, c->ev_in, 0));
     TRACE(p, 2, d->stream);
     const int rc = launch_shard(ctx, d, &d->fl[p->buf], c->d_text, nb, (const uint64_t*)c->d_off, nd, c->d_ids,
-                                c->d_ids_cap, (uint64_t*)c->d_tok, d->stream, 0);
+                                c->d_ids_cap, (uint64_t*)c->d_tok, d->stream, 0, 0);
     if (rc == HUT_STATUS_OK) TRACE(p, 3, d->stream);
     return rc;
 }

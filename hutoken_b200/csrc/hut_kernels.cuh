@@ -1,19 +1,28 @@
 /* sm_100a device code of the BPE encode engine, part 1: data layout, PTX helpers, table probes, the
  * unique-pretoken cache and the block-cooperative merge of long pretokens.  Included only by hut_engine.cu (through
- * hut_tile2.cuh / hut_pipeline.cuh).
+ * hut_tile.cuh / hut_pipeline.cuh).
  *
- * Pipeline per shard, all on one stream, no host round trip on the common path:
+ * Pipeline per shard (hut_pipeline.cuh), all on one stream, no host round trip, no inter-CTA waiting:
  *
  *   doc_kernel      one thread per document: first document starting in each 960-byte tile
- *   tile2_kernel    (hut_tile2.cuh) the whole hot path in ONE pass: parser (parser.c:24-88), byte encoder
- *                   (pretokenizer.c:102-168), unique-pretoken cache, merge loop (core.c:66-209, queue.c), device-wide
- *                   scan of the id counts by decoupled look-back, ids written once at their final position
+ *   tile_kernel     (hut_tile.cuh) WARP per tile, tiles claimed from an atomic ticket, no block barrier:
+ *                   TMA bulk copy of the tile (+ 32-byte halos) into the warp's shared-memory slice; bit-sliced class
+ *                   masks + local start rule (hut_bitslice.h)           <- parser_next_token (parser.c:24-88)
+ *                   lane-per-pretoken probe of the unique-pretoken cache (32-byte slots, one L2 sector per probe)
+ *                                                       <- (no equivalent: the reference re-merges every occurrence)
+ *                   cache misses are merged right there: a few by the whole warp one after the other (one symbol per
+ *                   lane), many (cold cache) by one lane each, all at once
+ *                                                       <- bpe_encode_arena_string (core.c:66-209), MinPQ (queue.c),
+ *                                                          get_pair_rank_from_strings (core.c:700-722), hashmap.c
+ *                   ids -> the tile's slot of the staging buffer, dense and in order; per-tile counts
+ *   long_kernel     pretokens > 32 bytes / symbols: block-cooperative merge (rare)
+ *   scan kernels    exclusive scan of the per-tile id counts      <- IntVector growth (vector.c:41-55)
+ *   compact_kernel  staging slots -> dense int32 ids, coalesced   <- list building (lib.c:699-715, 810-860)
+ *   fixdoc_kernel   per-document id offsets
  *
- * and, only when a shard holds pretokens of more than 32 bytes / symbols (the host sees the flag with the counters):
- *
- *   long_kernel     CTA per deferred pretoken: block-cooperative merge
- *   scan kernels    exclusive scan of the deferred ids per tile
- *   patch kernels   ids shift right by the deferred ids before them, which are spliced in; document offsets follow
+ * (A single-pass variant -- ids kept in shared memory until a decoupled look-back delivers the tile's base -- was
+ * built and measured in round 2 and is in the history: the in-order hand-over of bases stalls warps behind every
+ * slow tile and the shared memory it needs leaves the SM without L1; see profiles/README.md.)
  *
  * Algorithmic HBM traffic of the path: B_in + 4*T + 8*(N_docs+1) bytes.
  */
@@ -35,7 +44,10 @@ constexpr int SPAN = 1024;            // chunks 0..31; chunk 31 is the look-ahea
 constexpr int LOADB = SPAN + 16;      // bytes staged per tile (16 more: look-ahead of the halo's last chars)
 constexpr int TEXTB = LOADB + 16;     // shared bytes reserved (unaligned 20-byte key reads stay inside)
 constexpr int TRUST = SPAN - 3;       // boundaries at span positions >= TRUST lack their look-ahead
-constexpr int WPB = 8;                // warps per CTA (they never synchronise with each other)
+#ifndef HUT_WPB
+#define HUT_WPB 8
+#endif
+constexpr int WPB = HUT_WPB;          // warps per CTA (they never synchronise with each other)
 constexpr int NT = WPB * 32;
 constexpr int MAXW = 32;              // longest pretoken (bytes) / most symbols handled inside tile_kernel
 constexpr int CACHE_KEY_MAX = 15;     // longest pretoken (bytes) the cache keys on
@@ -46,6 +58,11 @@ constexpr int MAX_EVENTS = 1024;
 constexpr int SCAN_BLK = 4096;        // tiles per scan block
 constexpr int LNT = 128;              // threads per CTA of long_kernel
 constexpr int LNW = LNT / 32;
+constexpr int MISS_SMALL = 32;        // most initial symbols of a cache miss tile_kernel merges itself (one lane each)
+constexpr int32_t HOLE = (int32_t)0x80000000;  // staging filler behind the ids of a cache miss merged later
+constexpr uint32_t CNT_CHAIN = 0x80000000u;    // cnt[tile] flag: the tile has pretokens deferred to long_kernel
+constexpr uint32_t CNT_HOLES = 0x40000000u;    // cnt[tile] flag: the tile's slot holds holes (misses merged later)
+constexpr uint32_t CNT_MASK = 0x3FFFFFFFu;
 constexpr uint32_t NONE = HUT_UNIT_MASK;
 constexpr uint32_t RAWCHAR = 0xFFFFFFFEu;
 constexpr uint32_t ENDLINK = 0xFFFFFFFFu;
@@ -78,13 +95,12 @@ struct CutEvent {  // a document cut at an over-long pretoken (core.c:402-407, 5
     unsigned long long pos;        // byte position of the pretoken
 };
 
-struct DefEntry {  // a pretoken tile2_kernel hands to long_kernel
+struct DefEntry {  // a pretoken tile_kernel hands to long_kernel
     unsigned long long pos;   // global byte position of its first byte
     uint32_t tile;
-    uint32_t local_off;       // ids of its tile that precede it (pre-patch positions)
+    uint32_t local_off;       // ids of its tile that precede it in the staging slot
     uint32_t len;             // bytes, 0 = unknown (runs past the halo)
-    uint32_t flags;           // bit 0: first pretoken of its document, bit 1: cut (set by long_kernel), bit 2: first
-                              // entry of its tile's chain
+    uint32_t flags;           // bit 0: first pretoken of its document, bit 1: cut (set by long_kernel)
     uint32_t count;           // ids produced (long_kernel)
     uint32_t pad;
     unsigned long long ids_off;  // into long_ids
@@ -94,18 +110,11 @@ struct Counters {
     unsigned int flags;
     unsigned int n_events;
     unsigned int n_def;
-    unsigned int ticket;           // next tile to hand out (tile2_kernel)
-    unsigned long long total_ids;  // ids of the shard (pre-patch after tile2_kernel, final after the patch phase)
+    unsigned int ticket;           // next tile to hand out (tile_kernel)
+    unsigned long long total_ids;
     unsigned long long long_used;  // bump pointer into long_ids
-    unsigned long long long_total; // ids of all deferred pretokens (scan2_kernel)
     unsigned long long st_pretokens, st_hits, st_warp, st_block, st_big, st_cut;
     unsigned int pool_lock[32];
-#ifdef HUT_TIMING
-    unsigned long long tm[8];      // cycles per phase of tile2_kernel, summed over warps (build switch, not shipped)
-    unsigned long long tw[4];      // cycles blocked in tile_base, calls blocked, cycles in wmerge_one, cycles in merge_lane rounds
-    unsigned int hist[32];         // tiles by log2(cycles of their rounds)
-    unsigned int hmiss[32];        // tiles by number of misses (clamped to 31)
-#endif
     CutEvent events[MAX_EVENTS];
 };
 
@@ -142,26 +151,25 @@ struct Job {
     unsigned long long out_cap;
     unsigned long long* tok_off;
     uint32_t ntiles;
-    unsigned long long* status;  // [ntiles] inclusive id prefix per tile (pre-patch), written when the tile's ids leave
-    uint32_t* cnt0;              // [ntiles] id count + 1 per tile, 0 = not known yet            (two-level scan,
-    unsigned long long* grp_acc; // [ngroups] tiles done << 40 | ids of the group so far          hut_tile2.cuh)
-    unsigned long long* grp_st;  // [ngroups] look-back word per group: flag (bits 62..63) | total / inclusive prefix
-    uint32_t* first_doc;         // [ntiles + 1]
+    uint32_t stride;           // ids per staging slot of a tile in which no document starts
+    uint32_t slot_extra;       // more ids per document starting in the tile (prefix symbols / ids); 0 = no prefix
+    const unsigned long long* slot_off;  // [ntiles + 1] start of each tile's slot: t * stride + docs_before(t) * slot_extra
+    int32_t* stage;
+    uint32_t* cnt;             // [ntiles] entries used in the slot (CNT_MASK) | CNT_CHAIN | CNT_HOLES
+    uint32_t* tot;             // [ntiles] ids of the tile incl. deferred ones; after scan1: exclusive in-block prefix
+    unsigned long long* bsum;  // [nblocks] block sums; after scan2: exclusive prefix
+    uint32_t nblocks;
+    uint32_t* first_doc;       // [ntiles + 1]
+    uint32_t* def_first;       // [ntiles] index of the tile's first DefEntry (valid if CNT_CHAIN)
+    DefEntry* def;
+    uint32_t def_cap;
+    int32_t* long_ids;
+    unsigned long long long_cap;
     Counters* ctr;
     CacheSlot* cache;
     uint32_t cache_bits;
     CacheSlot2* cache2;
     uint32_t cache2_bits;
-    DefEntry* def;
-    uint32_t def_cap;
-    // ---- patch phase (only when the shard has deferred pretokens) ----
-    const int32_t* pre;          // copy of the pre-patch ids
-    uint32_t* tot;               // [ntiles] deferred ids per tile; after scan1: exclusive in-block prefix
-    uint32_t* def_first;         // [ntiles] index of the tile's first DefEntry
-    unsigned long long* bsum;    // [nblocks] block sums; after scan2: exclusive prefix
-    uint32_t nblocks;
-    int32_t* long_ids;
-    unsigned long long long_cap;
     // long_kernel working areas (global memory, L2 resident)
     uint32_t* cta_scratch;
     unsigned long long cta_scratch_words;  // per CTA
@@ -171,6 +179,12 @@ struct Job {
     uint32_t big_cap;  // symbols per big array
     uint32_t big_slots;
 };
+
+// staging slot of a tile: room for one id per symbol of the pretokens starting in it, plus the prefix ids of the
+// documents starting in it (so a prefix model does not pay the prefix room on every tile)
+__device__ __forceinline__ int32_t* stage_slot(const Job& J, unsigned long long tile) {
+    return J.stage + (J.slot_extra ? __ldg(J.slot_off + tile) : tile * J.stride);  // the table exists for prefix models only
+}
 
 // ------------------------------------------------------------------------------------------------
 // small PTX helpers (mbarrier + 1-D TMA bulk copy)
@@ -510,6 +524,127 @@ __device__ __forceinline__ uint32_t char_symbols(const DevModel& M, const uint32
     *pool_begin = lo;
     if (hi - lo == 1) *first = __ldg(M.sym_pool + lo);
     return hi - lo;
+}
+
+// ------------------------------------------------------------------------------------------------
+// lane-per-pretoken merge.  ONE LANE runs the whole merge loop of one pretoken of at most S symbols (arrays in
+// local memory, which the hardware interleaves by lane): per merge one scan for the leftmost minimal rank -- the
+// (rank, left index) order of the reference's heap (queue.c:162-164) -- one shift to close the gap and two pair-table
+// probes (issued together) for the new neighbours.  Replaces bpe_encode_arena_string (core.c:66-209) for the
+// pretokens the cache has not seen; 32 independent pretokens per warp keep the probe latency overlapped.
+// The ids go into the `room` entries tile_kernel reserved at dst (the rest of the room becomes HOLEs) and, when the
+// pretoken is cacheable, into the cache.  Returns room - ids written.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+
+template <int S>
+__device__ __forceinline__ uint32_t merge_entry(const DevModel& M, const Job& J, const uint32_t* byte1,
+                                                unsigned long long pos, uint32_t len, uint32_t first, uint32_t room,
+                                                int32_t* dst) {
+    uint32_t U[S], MG[S];
+    auto at = [&](unsigned long long p) -> uint32_t { return (uint32_t)__ldg(J.text + p); };
+    const uint32_t b0 = at(pos);
+    const bool with_prefix = first && b0 != ' ';
+    const bool alone_first = first && b0 == ' ';
+    const uint32_t npfx = with_prefix ? M.n_prefix_syms : 0u;
+    const uint32_t nal = alone_first ? M.n_prefix_alone : 0u;
+    // ---- initial symbols (A.3) + the cache key ----
+    uint32_t m = 0;
+    for (uint32_t k = 0; k < npfx; ++k) U[m++] = M.prefix_syms[k];
+    unsigned long long k0 = 0, k1 = 0, k2 = 0, k3 = 0;
+    for (uint32_t p = 0; p < len; ++p) {
+        uint32_t unit = M.inert, pb = 0;
+        const uint32_t cnt = char_symbols(M, byte1, at, pos + p, pos, pos + len, &unit, &pb);
+        if (cnt == 1) U[m++] = unit;
+        else
+            for (uint32_t k = 0; k < cnt; ++k) U[m++] = __ldg(M.sym_pool + pb + k);
+        const unsigned long long b = at(pos + p);
+        if (p < 8) k0 |= b << (8 * p);
+        else if (p < 16) k1 |= b << (8 * (p - 8));
+        else if (S > 16 && p < 24) k2 |= b << (8 * (p - 16));
+        else if (S > 16 && p < 31) k3 |= b << (8 * (p - 24));
+    }
+    // ---- merge loop (A.4).  The first slot of every initial pair is prefetched so that the probes overlap.
+    // Symbols never move: a merged-away symbol is cleared in `alive` and neighbours are found with bit scans, so the
+    // array index of the scans is the same in every lane (coalesced local memory) ----
+    const uint32_t m0 = m;
+    for (uint32_t k = 0; k + 1 < m0; ++k) {
+        const uint32_t l = U[k], r = U[k + 1];
+        if (l < M.inert && r < M.inert) prefetch_l1(M.pair_tab + hut_pair_hash(l, r, M.pair_mask));
+    }
+    for (uint32_t k = 0; k < m0; ++k) MG[k] = k + 1 < m0 ? pair_probe(M, U[k], U[k + 1]) : NONE;
+    unsigned long long alive = m0 >= 64 ? ~0ull : ((1ull << m0) - 1ull);
+    for (;;) {
+        uint32_t best = 0xFFFFFFFFu, j = 0, mu = NONE;
+        for (uint32_t k = 0; k + 1 < m0; ++k) {
+            const uint32_t mg = MG[k];
+            const uint32_t rk = rank_of_unit(M, mg);
+            if (rk < best) {
+                best = rk;
+                j = k;
+                mu = mg;
+            }
+        }
+        if (best == 0xFFFFFFFFu) break;
+        const uint32_t r = j + 1 + (uint32_t)(__ffsll((long long)(alive >> (j + 1))) - 1);  // right partner of j
+        alive &= ~(1ull << r);
+        U[j] = mu;
+        MG[r] = NONE;
+        const unsigned long long below = alive & ((1ull << j) - 1ull), above = alive >> (r + 1);
+        const int l = below ? 63 - __clzll((long long)below) : -1;
+        const int r2 = above ? (int)(r + 1) + (__ffsll((long long)above) - 1) : -1;
+        const uint32_t ul = l >= 0 ? U[l] : NONE, ur = r2 >= 0 ? U[r2] : NONE;
+        uint32_t ml, mr;
+        pair_probe2(M, ul, mu, ur, &ml, &mr);
+        if (l >= 0) MG[l] = ml;
+        MG[j] = mr;  // NONE when j is the last symbol now
+    }
+    // ---- ids into the reserved room, HOLEs behind them ----
+    const uint32_t total = nal + (uint32_t)__popcll(alive);  // <= room by construction (tile_kernel reserves the worst case)
+    int32_t t5[CACHE_IDS] = {0, 0, 0, 0, 0};
+    {
+        uint32_t k = 0;
+        for (; k < nal; ++k) {
+            const int32_t id = M.prefix_alone[k];
+#pragma unroll
+            for (int z = 0; z < CACHE_IDS; ++z)
+                if (k == (uint32_t)z) t5[z] = id;
+            dst[k] = id;
+        }
+        for (uint32_t i = 0; i < m0; ++i) {
+            if (!((alive >> i) & 1ull)) continue;
+            const int32_t id = id_of_unit(M, U[i]);
+#pragma unroll
+            for (int z = 0; z < CACHE_IDS; ++z)
+                if (k == (uint32_t)z) t5[z] = id;
+            dst[k++] = id;
+        }
+        for (; k < room; ++k) dst[k] = HOLE;
+    }
+    if (M.cache_ok && total >= 1 && total <= (uint32_t)CACHE_IDS) {
+        uint32_t pw[4];
+        val_pack(t5, total, pw);
+        if (len <= (uint32_t)CACHE_KEY_MAX) {
+            uint32_t key[4];
+            key[0] = (uint32_t)k0;
+            key[1] = (uint32_t)(k0 >> 32);
+            key[2] = (uint32_t)k1;
+            key[3] = ((uint32_t)(k1 >> 32) & 0x00FFFFFFu) | ((0x80u | (first << 4) | len) << 24);
+            cache_insert(J, key, pw);
+        } else if (S > 16 && len <= (uint32_t)CACHE2_KEY_MAX) {
+            uint32_t key[8];
+            key[0] = (uint32_t)k0;
+            key[1] = (uint32_t)(k0 >> 32);
+            key[2] = (uint32_t)k1;
+            key[3] = (uint32_t)(k1 >> 32);
+            key[4] = (uint32_t)k2;
+            key[5] = (uint32_t)(k2 >> 32);
+            key[6] = (uint32_t)k3;
+            key[7] = (uint32_t)(k3 >> 32) | ((0x80u | (first << 5) | len) << 24);
+            cache2_insert(J, key, pw);
+        }
+    }
+    return room - total;
 }
 
 // ------------------------------------------------------------------------------------------------

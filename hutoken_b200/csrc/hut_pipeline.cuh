@@ -1,8 +1,8 @@
-/* sm_100a device code of the BPE encode engine, part 3: the small kernels around tile2_kernel and the patch phase
- * for shards that hold long pretokens (see hut_kernels.cuh for the overview).  Included only by hut_engine.cu. */
+/* sm_100a device code of the BPE encode engine, part 3: the small kernels around tile_kernel (see hut_kernels.cuh for
+ * the overview).  Included only by hut_engine.cu. */
 #pragma once
 
-#include "hut_tile2.cuh"
+#include "hut_tile.cuh"
 
 namespace hut {
 
@@ -15,14 +15,8 @@ __global__ void init_kernel(Job J) {
         c->ticket = 0;
         c->total_ids = 0;
         c->long_used = 0;
-        c->long_total = 0;
         c->st_pretokens = c->st_hits = c->st_warp = c->st_block = c->st_big = c->st_cut = 0;
         for (int i = 0; i < 32; ++i) c->pool_lock[i] = 0;
-#ifdef HUT_TIMING
-        for (int i = 0; i < 8; ++i) c->tm[i] = 0;
-        for (int i = 0; i < 4; ++i) c->tw[i] = 0;
-        for (int i = 0; i < 32; ++i) c->hist[i] = c->hmiss[i] = 0;
-#endif
     }
 }
 
@@ -36,17 +30,22 @@ __global__ void doc_kernel(Job J) {
     if (d == 0 || J.doc_off[d - 1] / OWN != t) J.first_doc[t] = (uint32_t)d;
 }
 
-// before long_kernel runs (again): nothing of an earlier attempt may be left
-__global__ void long_reset_kernel(Job J) {
-    if (threadIdx.x == 0 && blockIdx.x == 0) {
-        Counters* c = J.ctr;
-        c->flags &= ~(unsigned)FLAG_LONG_CAP;
-        c->n_events = 0;
-        c->long_used = 0;
-        c->long_total = 0;
-        c->st_big = 0;
-        for (int i = 0; i < 32; ++i) c->pool_lock[i] = 0;
+// start of every tile's staging slot: tile * stride, plus slot_extra ids for each document starting before the tile
+// (lower bound of the tile's first byte in doc_off) for a prefix model; see stage_slot()
+__global__ void slot_docs_kernel(Job J, unsigned long long* out) {
+    const unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t > J.ntiles) return;
+    unsigned long long a = 0;
+    if (J.slot_extra) {
+        const unsigned long long pos = t * OWN;
+        unsigned long long b = J.ndocs;
+        while (a < b) {
+            const unsigned long long mid = (a + b) >> 1;
+            if (J.doc_off[mid] < pos) a = mid + 1;
+            else b = mid;
+        }
     }
+    out[t] = t * J.stride + a * J.slot_extra;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -97,7 +96,6 @@ __global__ void __launch_bounds__(LNT) long_kernel(const DevModel M, const Job J
                 if (tid == 0) {
                     E->flags |= 2u;
                     E->count = 0;
-                    if (E->flags & 4u) J.def_first[E->tile] = e;
                 }
             } else {
                 set_flag(J, FLAG_BIG_CAP);
@@ -155,7 +153,6 @@ __global__ void __launch_bounds__(LNT) long_kernel(const DevModel M, const Job J
             E->count = cnt;
             E->ids_off = off;
             atomicAdd(&J.tot[E->tile], cnt);
-            if (E->flags & 4u) J.def_first[E->tile] = e;
             if (big) {
                 __threadfence();
                 atomicExch(&J.ctr->pool_lock[sm.slot], 0u);
@@ -166,7 +163,7 @@ __global__ void __launch_bounds__(LNT) long_kernel(const DevModel M, const Job J
 }
 
 // ------------------------------------------------------------------------------------------------
-// exclusive scan of the deferred ids per tile (patch phase): scan1 per block of SCAN_BLK tiles, scan2 over the block sums
+// exclusive scan of the per-tile id counts: scan1 per block of SCAN_BLK tiles, scan2 over the block sums
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(1024) scan1_kernel(Job J) {
     __shared__ uint32_t wsum[32];
@@ -241,15 +238,10 @@ __global__ void __launch_bounds__(1024) scan2_kernel(Job J) {
         if (tid == 1023) carry_s = excl + v;
         __syncthreads();
     }
-    if (tid == 0) J.ctr->long_total = carry_s;
+    if (tid == 0) J.ctr->total_ids = carry_s;
 }
 
-// ids produced by the tiles before t, not counting deferred pretokens (tile2_kernel left the inclusive prefixes in
-// J.status); shift(t) = deferred ids before tile t
-__device__ __forceinline__ unsigned long long pre_base(const Job& J, unsigned long long t) {
-    return t ? J.status[t - 1] : 0ull;
-}
-__device__ __forceinline__ unsigned long long tile_shift(const Job& J, unsigned long long t) {
+__device__ __forceinline__ unsigned long long tile_base(const Job& J, unsigned long long t) {
     return J.bsum[t / SCAN_BLK] + J.tot[t];
 }
 
@@ -276,22 +268,107 @@ __device__ __forceinline__ void copy_ids(const Job& J, const int32_t* src, unsig
 }
 
 
-// Patch phase, warp per tile: the tile's pre-patch ids (a copy, J.pre) move to their final position, which lies
-// tile_shift(t) further right, and the ids of the tile's deferred pretokens are spliced in where they belong.  A
-// deferred pretoken over the reference's limit instead records a cut event (core.c:402-407,503).
-__global__ void __launch_bounds__(256, 8) patch_kernel(const Job J) {
+// warp copy of the non-HOLE entries of src[0 .. n) to the dense output at position o; returns how many there were.
+// Four 128-byte loads are in flight per step.
+__device__ __forceinline__ uint32_t copy_ids_filtered(const Job& J, const int32_t* src, unsigned long long o, uint32_t n) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t lt = (1u << lane) - 1u;
+    uint32_t kept = 0;
+    for (uint32_t base = 0; base < n; base += 128) {
+        int32_t v[4];
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            const uint32_t i = base + 32 * g + lane;
+            v[g] = i < n ? ld_stream_s32(src + i) : HOLE;
+        }
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            const bool keep = v[g] != HOLE;
+            const uint32_t mask = __ballot_sync(0xFFFFFFFFu, keep);
+            if (keep) {
+                const unsigned long long at = o + kept + __popc(mask & lt);
+                if (at < J.out_cap) st_stream_s32(J.out + at, v[g]);
+                else set_flag(J, FLAG_OUT_CAP);
+            }
+            kept += __popc(mask);
+        }
+    }
+    return kept;
+}
+
+// The same for a whole tile whose slot holds HOLEs, and the documents starting in the tile get their final id offset
+// on the way: tile_kernel left the slot position of their first pretoken in tok_off, which is translated to the
+// number of ids kept before it.
+__device__ __forceinline__ void compact_tile_holes(const Job& J, uint32_t tile, const int32_t* src, unsigned long long o,
+                                                   uint32_t n) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t lt = (1u << lane) - 1u;
+    const unsigned long long tile_end = ((unsigned long long)tile + 1) * OWN;
+    unsigned long long d = J.first_doc[tile];
+    uint32_t so = 0xFFFFFFFFu;  // slot position of document d's first pretoken; none left: 0xFFFFFFFF
+    auto load_doc = [&]() {
+        so = 0xFFFFFFFFu;
+        if (d != NODOC && d < J.ndocs) {
+            const unsigned long long pos = J.doc_off[d];
+            if (pos < tile_end && pos < J.nbytes) so = (uint32_t)J.tok_off[d];
+        }
+    };
+    load_doc();
+    uint32_t kept = 0;
+    for (uint32_t base = 0; base < n; base += 128) {
+        int32_t v[4];
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            const uint32_t i = base + 32 * g + lane;
+            v[g] = i < n ? ld_stream_s32(src + i) : HOLE;
+        }
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            const uint32_t gbase = base + 32 * g;
+            const bool keep = v[g] != HOLE;
+            const uint32_t mask = __ballot_sync(0xFFFFFFFFu, keep);
+            while (so < gbase + 32) {  // warp-uniform
+                if (lane == 0) J.tok_off[d] = o + kept + __popc(mask & ((1u << (so - gbase)) - 1u));
+                ++d;
+                load_doc();
+            }
+            if (keep) {
+                const unsigned long long at = o + kept + __popc(mask & lt);
+                if (at < J.out_cap) st_stream_s32(J.out + at, v[g]);
+                else set_flag(J, FLAG_OUT_CAP);
+            }
+            kept += __popc(mask);
+        }
+    }
+    while (so != 0xFFFFFFFFu) {  // documents starting behind the last entry of the slot
+        if (lane == 0) J.tok_off[d] = o + kept;
+        ++d;
+        load_doc();
+    }
+}
+
+// staging slots -> dense ids (warp per tile); drops the HOLEs left by deferred cache misses and splices in the ids
+// of the pretokens long_kernel merged
+__global__ void __launch_bounds__(256, 8) compact_kernel(const Job J) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t gw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), nw = gridDim.x * (blockDim.x >> 5);
     for (uint32_t tile = gw; tile < J.ntiles; tile += nw) {
-        const unsigned long long b0 = pre_base(J, tile), b1 = J.status[tile];
-        const uint32_t ns = (uint32_t)(b1 - b0);
-        unsigned long long o = b0 + tile_shift(J, tile);
-        const int32_t* src = J.pre + b0;
+        const uint32_t c = J.cnt[tile];
+        const uint32_t ns = c & CNT_MASK;
+        unsigned long long o = tile_base(J, tile);
+        const int32_t* src = stage_slot(J, tile);
+        if (!(c & (CNT_CHAIN | CNT_HOLES))) {
+            copy_ids(J, src, o, ns);
+            continue;
+        }
+        if (!(c & CNT_CHAIN)) {
+            compact_tile_holes(J, tile, src, o, ns);
+            continue;
+        }
         uint32_t prev = 0;
         for (uint32_t idx = J.def_first[tile]; idx != NODOC;) {
             const DefEntry E = J.def[idx];
-            copy_ids(J, src + prev, o, E.local_off - prev);
-            o += E.local_off - prev;
+            o += copy_ids_filtered(J, src + prev, o, E.local_off - prev);
             prev = E.local_off;
             if (E.flags & 2u) {  // reference-compatible cut: everything from here to the end of the document goes
                 if (lane == 0) {
@@ -309,25 +386,34 @@ __global__ void __launch_bounds__(256, 8) patch_kernel(const Job J) {
             }
             idx = E.pad;
         }
-        copy_ids(J, src + prev, o, ns - prev);
+        copy_ids_filtered(J, src + prev, o, ns - prev);
     }
 }
 
-// Patch phase, thread per document: pre-patch id offset -> final one (deferred ids before the document are added)
-__global__ void patch_doc_kernel(const Job J) {
+// tile-local document offsets -> global ones
+__global__ void fixdoc_kernel(const Job J) {
     const unsigned long long d = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (d > J.ndocs) return;
+    const unsigned long long total = J.ctr->total_ids;
     const unsigned long long pos = d < J.ndocs ? J.doc_off[d] : J.nbytes;
     if (d == J.ndocs || pos >= J.nbytes) {
-        const unsigned long long total = J.status[J.ntiles - 1] + J.ctr->long_total;
         J.tok_off[d] = total;
-        if (d == J.ndocs) J.ctr->total_ids = total;
         return;
     }
     const unsigned long long t = pos / OWN;
-    unsigned long long v = J.tok_off[d] + tile_shift(J, t);
-    for (uint32_t idx = J.def_first[t]; idx != NODOC; idx = J.def[idx].pad)
-        if (J.def[idx].pos < pos) v += J.def[idx].count;
+    const uint32_t c = J.cnt[t];
+    if ((c & (CNT_HOLES | CNT_CHAIN)) == CNT_HOLES) return;  // compact_kernel has translated these already
+    unsigned long long v = J.tok_off[d];  // entries of the tile's slot before the document
+    if (c & CNT_HOLES) {
+        const int32_t* src = stage_slot(J, t);
+        uint32_t h = 0;
+        for (uint32_t i = 0; i < (uint32_t)v; ++i) h += src[i] == HOLE;
+        v -= h;
+    }
+    v += tile_base(J, t);
+    if (c & CNT_CHAIN)
+        for (uint32_t idx = J.def_first[t]; idx != NODOC; idx = J.def[idx].pad)
+            if (J.def[idx].pos < pos) v += J.def[idx].count;
     J.tok_off[d] = v;
 }
 
