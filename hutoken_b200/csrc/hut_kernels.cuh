@@ -381,6 +381,27 @@ __device__ __forceinline__ bool cache_lookup(const Job& J, const uint32_t x[4], 
     return false;
 }
 
+// the probes after the first one (tile_kernel issues the first probe of several pretokens together)
+__device__ __forceinline__ bool cache_lookup_from(const Job& J, const uint32_t x[4], uint32_t w[4], uint32_t i,
+                                                  int probes) {
+    const uint32_t mask = (1u << J.cache_bits) - 1;
+#pragma unroll 1
+    for (int p = 0; p < probes; ++p) {
+        uint4 a, b;
+        ld_slot256(J.cache + i, a, b);
+        if ((a.x | a.y) == 0) return false;
+        if (a.x == x[0] && a.y == x[1] && a.z == x[2] && a.w == x[3]) {
+            w[0] = b.x;
+            w[1] = b.y;
+            w[2] = b.z;
+            w[3] = b.w;
+            return val_count(b.x) != 0;
+        }
+        i = (i + 1) & mask;
+    }
+    return false;
+}
+
 // ---- second cache: keys of 16..31 text bytes ----
 __device__ __forceinline__ void build_key32(const uint8_t* text, const uint4* kmask32, int s, int len, uint32_t first,
                                             uint32_t x[8]) {

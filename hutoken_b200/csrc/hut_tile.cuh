@@ -7,6 +7,9 @@
 #ifndef HUT_TILE_CTAS
 #define HUT_TILE_CTAS 4  // resident CTAs per SM the tile kernel is compiled for (64 registers per thread)
 #endif
+#ifndef HUT_PPL
+#define HUT_PPL 1        // pretokens a lane handles per round of the tile kernel (measured: 2 or 3 probes in flight per lane are slower, 6.2 / 9.0 ms against 3.8: the scattered 32-byte loads already saturate the L1TEX pipe)
+#endif
 
 namespace hut {
 
@@ -26,6 +29,8 @@ struct __align__(16) WarpSm {
     uint32_t def_head, def_tail;  // chain of the tile's pretokens handed to long_kernel
     uint32_t st_pre, st_miss, st_def, st_pad;  // statistics of this warp
 };
+
+constexpr int PPL = HUT_PPL;
 
 struct TileSm {
     uint4 kmask[16];            // kmask[len]: byte masks of a 16-byte key holding len text bytes
@@ -221,6 +226,7 @@ __global__ void __launch_bounds__(NT, HUT_TILE_CTAS) tile_kernel(const __grid_co
     int lane;  // read once from the special register (kept from being recomputed from %tid inside the loops)
     asm volatile("mov.u32 %0, %%laneid;" : "=r"(lane));
     const uint32_t FULL = 0xFFFFFFFFu;
+    const uint32_t lt_mask = (1u << lane) - 1u;
     WarpSm& ws = sm.w[warp];
 
     for (int i = tid; i < 256; i += NT) sm.byte1[i] = M.byte1[i];
@@ -359,53 +365,109 @@ __global__ void __launch_bounds__(NT, HUT_TILE_CTAS) tile_kernel(const __grid_co
         }
         __syncwarp();
         int32_t* const slot = J.stage + (PFX ? slot_o : (unsigned long long)tile * J.stride);
-        for (uint32_t r0 = 0; r0 < n; r0 += 32) {
-            const uint32_t q = r0 + lane;
-            const bool active = q < n;
-            const int s = active ? ws.pstart[q] : BACK;
-            const int e = active ? ws.pstart[q + 1] : BACK;
-            const int len = e - s;                       // > MAXW when the end lies beyond the halo (BEYOND)
-            const bool keyed = len <= CACHE_KEY_MAX;
-            uint32_t dsb = 0;
-            if (tile_docs) dsb = (ws.dsm[s >> 5] >> (s & 31)) & 1u;
-            const uint32_t first = PFX ? dsb : 0u;
-            uint32_t key[4], w[4] = {0u, 0u, 0u, 0u};
-            const uint32_t b0 = build_key(ws.text, sm.kmask, s, keyed ? len : 0, first, key);
-            bool hit = false;
+        for (uint32_t r0 = 0; r0 < n; r0 += 32 * PPL) {
+            // PPL pretokens per lane and round (lane + 32 * h): their cache probes are in flight together
+            int s[PPL], e[PPL];
+            bool active[PPL], keyed[PPL], hit[PPL];
+            uint32_t dsb[PPL], b0[PPL], key[PPL][4], w[PPL][4], slot_i[PPL];
+            uint4 sa[PPL], sb[PPL];
+            bool unkeyed = false;
+#pragma unroll
+            for (int h = 0; h < PPL; ++h) {
+                const uint32_t q = r0 + 32u * h + lane;
+                active[h] = q < n;
+                s[h] = active[h] ? ws.pstart[q] : BACK;
+                e[h] = active[h] ? ws.pstart[q + 1] : BACK;
+                const int len = e[h] - s[h];             // > MAXW when the end lies beyond the halo (BEYOND)
+                keyed[h] = len <= CACHE_KEY_MAX;
+                unkeyed = unkeyed || !keyed[h];
+                dsb[h] = 0;
+                if (tile_docs) dsb[h] = (ws.dsm[s[h] >> 5] >> (s[h] & 31)) & 1u;
+                b0[h] = build_key(ws.text, sm.kmask, s[h], keyed[h] ? len : 0, PFX ? dsb[h] : 0u, key[h]);
+                slot_i[h] = cache_hash(key[h], J.cache_bits);
+                hit[h] = false;
+#pragma unroll
+                for (int z = 0; z < 4; ++z) w[h][z] = 0u;
+            }
+#pragma unroll
+            for (int h = 0; h < PPL; ++h) {
+                sa[h] = make_uint4(0u, 0u, 0u, 0u);
+#ifdef HUT_EXP_NOPROBE  // timing experiment only: every keyed pretoken "hits" with one id, no load is issued
+                if (active[h] && keyed[h]) {
+                    sa[h] = make_uint4(key[h][0], key[h][1], key[h][2], key[h][3]);
+                    sb[h] = make_uint4((1u << 21) | (slot_i[h] & 0xFFFFu), 0u, 0u, 0u);
+                }
+#else
+                if (active[h] && keyed[h] && M.cache_ok) ld_slot256(J.cache + slot_i[h], sa[h], sb[h]);
+#endif
+            }
             // pretokens of 16..31 bytes (rare): second cache, 32-byte keys
-            if (__any_sync(FULL, !keyed)) {
-                if (active && !keyed && len <= CACHE2_KEY_MAX && M.cache_ok) {
-                    uint32_t k32[8];
-                    build_key32(ws.text, sm.kmask32, s, len, first, k32);
-                    hit = cache2_lookup(J, k32, w);
+            if (__any_sync(FULL, unkeyed)) {
+#pragma unroll
+                for (int h = 0; h < PPL; ++h) {
+                    const int len = e[h] - s[h];
+                    if (active[h] && !keyed[h] && len <= CACHE2_KEY_MAX && M.cache_ok) {
+                        uint32_t k32[8];
+                        build_key32(ws.text, sm.kmask32, s[h], len, PFX ? dsb[h] : 0u, k32);
+                        hit[h] = cache2_lookup(J, k32, w[h]);
+                    }
                 }
             }
-            if (active && keyed && M.cache_ok) hit = cache_lookup(J, key, w);
-            // ---- counts of the hits -> offsets inside the tile's slot ----
-            // state of the lane's pretoken: 0 nothing / hit, 2 cache miss merged by this warp (batches of 32), 3 long
-            // pretoken -> long_kernel.  A miss reserves room for its worst case (one id per symbol + prefix ids).
-            uint32_t c = hit ? val_count(w[0]) : 0u;
-            uint32_t state = 0;
-            if (active && !hit && b0 != 0) {  // b0 == 0: a NUL in the text, the call fails (FLAG_NUL)
-                const bool lng = (uint32_t)len > M.miss_len_max ||
-                                 (uint32_t)len * M.kmax + (first ? M.n_prefix_syms : 0u) > (uint32_t)MISS_SMALL;
-                state = lng ? 3u : 2u;
-                if (!lng) c = (uint32_t)len * M.kmax + (first ? M.first_extra : 0u);
-            }
-            uint32_t inc = c;
+            uint32_t c[PPL];
+            bool need = false;
 #pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const uint32_t t = __shfl_up_sync(FULL, inc, d);
-                if (lane >= d) inc += t;
+            for (int h = 0; h < PPL; ++h) {
+                if ((sa[h].x | sa[h].y) != 0u) {  // an empty slot (or no probe at all) is a miss
+                    if (sa[h].x == key[h][0] && sa[h].y == key[h][1] && sa[h].z == key[h][2] && sa[h].w == key[h][3]) {
+                        w[h][0] = sb[h].x, w[h][1] = sb[h].y, w[h][2] = sb[h].z, w[h][3] = sb[h].w;
+                        hit[h] = val_count(sb[h].x) != 0u;
+                    } else {
+                        hit[h] = cache_lookup_from(J, key[h], w[h], (slot_i[h] + 1u) & ((1u << J.cache_bits) - 1u), CACHE_PROBES - 1);
+                    }
+                }
+                c[h] = hit[h] ? val_count(w[h][0]) : 0u;
+                need = need || (active[h] && !hit[h]);
             }
-            const uint32_t round_total = __shfl_sync(FULL, inc, 31);
-            const uint32_t off = run + inc - c;          // position of this lane's ids (or room) in the tile's slot
-            if (hit) put_hit_ids(slot + off, c, w);
-            // everything below up to the per-document offsets concerns pretokens the cache did not answer: one vote
-            // decides for the whole round
-            if (__any_sync(FULL, state != 0)) rare_round(M, J, sm, ws, tile, s, e, first, c, off, state);
-            if (tile_docs && active && dsb) doc_offsets_at(J, (unsigned long long)(g0 + s), dfirst, off);
-            run += round_total;
+            if (!__any_sync(FULL, need)) {
+                // ---- every pretoken of the round was answered by the cache: counts are 0..5, so three ballots scan them ----
+#pragma unroll
+                for (int h = 0; h < PPL; ++h) {
+                    const uint32_t m0 = __ballot_sync(FULL, c[h] & 1u), m1 = __ballot_sync(FULL, c[h] & 2u),
+                                   m2 = __ballot_sync(FULL, c[h] & 4u);
+                    const uint32_t off = run + __popc(m0 & lt_mask) + 2u * __popc(m1 & lt_mask) + 4u * __popc(m2 & lt_mask);
+                    if (hit[h]) put_hit_ids(slot + off, c[h], w[h]);
+                    if (tile_docs && active[h] && dsb[h]) doc_offsets_at(J, (unsigned long long)(g0 + s[h]), dfirst, off);
+                    run += __popc(m0) + 2u * __popc(m1) + 4u * __popc(m2);
+                }
+                continue;
+            }
+            // ---- some pretokens were not answered.  state of a lane's pretoken: 0 nothing / hit, 2 cache miss merged by
+            // this warp (batches of 32), 3 long pretoken -> long_kernel.  A miss reserves room for its worst case (one
+            // id per symbol + prefix ids). ----
+#pragma unroll
+            for (int h = 0; h < PPL; ++h) {
+                const int len = e[h] - s[h];
+                const uint32_t first = PFX ? dsb[h] : 0u;
+                uint32_t state = 0, cc = c[h];
+                if (active[h] && !hit[h] && b0[h] != 0) {  // b0 == 0: a NUL in the text, the call fails (FLAG_NUL)
+                    const bool lng = (uint32_t)len > M.miss_len_max ||
+                                     (uint32_t)len * M.kmax + (first ? M.n_prefix_syms : 0u) > (uint32_t)MISS_SMALL;
+                    state = lng ? 3u : 2u;
+                    if (!lng) cc = (uint32_t)len * M.kmax + (first ? M.first_extra : 0u);
+                }
+                uint32_t inc = cc;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const uint32_t t = __shfl_up_sync(FULL, inc, d);
+                    if (lane >= d) inc += t;
+                }
+                const uint32_t round_total = __shfl_sync(FULL, inc, 31);
+                const uint32_t off = run + inc - cc;     // position of this lane's ids (or room) in the tile's slot
+                if (hit[h]) put_hit_ids(slot + off, cc, w[h]);
+                if (__any_sync(FULL, state != 0)) rare_round(M, J, sm, ws, tile, s[h], e[h], first, cc, off, state);
+                if (tile_docs && active[h] && dsb[h]) doc_offsets_at(J, (unsigned long long)(g0 + s[h]), dfirst, off);
+                run += round_total;
+            }
         }
         if (lane == 0) {
             const uint32_t def_head = ws.def_head;
