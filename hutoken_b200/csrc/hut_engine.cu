@@ -155,6 +155,7 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     dm.byte_mode = m->is_byte_encoder;
     dm.multi_sym = m->max_sym_per_char > 1;
     dm.has_prefix = m->has_prefix;
+    dm.monotone = m->monotone;
     dm.cache_ok = (m->max_value < (1 << 20)) ? 1 : 0;  // ids are packed as signed 21-bit fields
     dm.kmax = m->max_sym_per_char ? m->max_sym_per_char : 1;
     dm.miss_len_max = MAXW;
@@ -209,13 +210,13 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     d->med_cap = 4096u * dm.kmax + m->n_prefix_syms + 64;
     d->cta_scratch_words = 5ull * d->med_cap + 8;  // U, MG, NX, PV + tournament-tree levels
     CU(ctx, cudaMalloc(&d->cta_scratch, d->cta_scratch_words * sizeof(uint32_t) * d->long_grid));
-    d->big_slots = ctx->opt.big_slots ? ctx->opt.big_slots : (ctx->opt.max_pretoken > (64ull << 20) ? 2 : 8);
-    if (d->big_slots > 32) d->big_slots = 32;
+    // working areas for pretokens of more than med_cap symbols (huge_kernel): allocated when the first one shows up
+    d->big_slots = 0;
+    d->big_pool = nullptr;
     unsigned long long bc = dm.limit * dm.kmax + m->n_prefix_syms + 64;
     if (bc > 0xFFFFFFF0ull) return set_err(ctx, HUT_STATUS_ARG, "%s", "max_pretoken too large");
     d->big_cap = (uint32_t)bc;
-    d->big_slot_words = 5ull * d->big_cap + 8;
-    CU(ctx, cudaMalloc(&d->big_pool, d->big_slot_words * sizeof(uint32_t) * d->big_slots));
+    d->big_slot_words = 7ull * d->big_cap + d->big_cap / 4 + 4096;  // U, MG, NX, PV, tree, lists of the cooperative rounds
     return HUT_STATUS_OK;
 }
 
@@ -434,6 +435,7 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     else tile_kernel<false><<<tile_grid, NT, 0, st>>>(d->dm, J);
     CU(ctx, cudaEventRecord(f->ev[2], st));
     long_kernel<<<d->long_grid, LNT, 0, st>>>(d->dm, J);
+    if (d->big_slots) huge_kernel<<<d->big_slots, HNT, 0, st>>>(d->dm, J);
     scan1_kernel<<<nblocks, 1024, 0, st>>>(J);
     scan2_kernel<<<1, 1024, 0, st>>>(J);
     const uint32_t cgrid = (ntiles + 7) / 8;
@@ -457,10 +459,16 @@ static int finish_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, uint64_t n_docs
     const Counters* c = f->h_ctr;
     for (int attempt = 0;; ++attempt) {
         CU(ctx, cudaEventSynchronize(f->done));
-        if (!(c->flags & (FLAG_DEF_CAP | FLAG_LONG_CAP)) || attempt == 4) break;
+        if (!(c->flags & (FLAG_DEF_CAP | FLAG_LONG_CAP | FLAG_BIG_NEED)) || attempt == 4) break;
         // rare: many / very long deferred pretokens.  The counters kept counting, so they state the need.  The staging
         // area and the id buffer for long pretokens are shared by the device's flights: drain the stream first.
         CU(ctx, cudaStreamSynchronize(st));
+        if ((c->flags & FLAG_BIG_NEED) && !d->big_pool) {
+            uint32_t slots = ctx->opt.big_slots ? ctx->opt.big_slots : (ctx->opt.max_pretoken > (64ull << 20) ? 2 : 8);
+            if (slots > 32) slots = 32;
+            CU(ctx, cudaMalloc(&d->big_pool, d->big_slot_words * sizeof(uint32_t) * slots));
+            d->big_slots = slots;
+        }
         const Job J = f->job;
         const size_t def_want = (size_t)c->n_def + (size_t)c->n_def / 8 + 1024;
         const size_t long_want = (size_t)c->long_used + (size_t)c->long_used / 8 + 4096;
@@ -482,7 +490,7 @@ static int finish_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, uint64_t n_docs
     if (c->flags & FLAG_OUT_CAP) return set_err(ctx, HUT_STATUS_CAPACITY, "%s", "output id buffer too small");
     if (c->flags & FLAG_BIG_CAP)
         return set_err(ctx, HUT_STATUS_UNSUPPORTED, "%s", "a pretoken exceeds the configured max_pretoken working area");
-    if (c->flags & (FLAG_DEF_CAP | FLAG_LONG_CAP))
+    if (c->flags & (FLAG_DEF_CAP | FLAG_LONG_CAP | FLAG_BIG_NEED))
         return set_err(ctx, HUT_STATUS_MEMORY, "%s", "side buffers for long pretokens could not be sized");
     if (c->flags & FLAG_EVENTS)
         return set_err(ctx, HUT_STATUS_UNSUPPORTED, "%s", "too many over-long pretokens in one call");

@@ -56,8 +56,9 @@ constexpr int CACHE_PROBES = 8;
 constexpr int CACHE_IDS = 5;          // most ids a cache value holds
 constexpr int MAX_EVENTS = 1024;
 constexpr int SCAN_BLK = 4096;        // tiles per scan block
-constexpr int LNT = 128;              // threads per CTA of long_kernel
-constexpr int LNW = LNT / 32;
+constexpr int LNT = 128;              // threads per CTA of long_kernel (pretokens of up to med_cap symbols)
+constexpr int HNT = 1024;             // threads per CTA of huge_kernel (longer ones: cooperative rounds)
+constexpr int LMAXW = 32;             // most warps a CTA of the long path has
 constexpr int MISS_SMALL = 32;        // most initial symbols of a cache miss tile_kernel merges itself (one lane each)
 constexpr int32_t HOLE = (int32_t)0x80000000;  // staging filler behind the ids of a cache miss merged later
 constexpr uint32_t CNT_CHAIN = 0x80000000u;    // cnt[tile] flag: the tile has pretokens deferred to long_kernel
@@ -75,7 +76,8 @@ enum : uint32_t {
     FLAG_BIG_CAP = 4u,    // pretoken longer than the configured working area (no-limit mode)
     FLAG_EVENTS = 8u,     // more over-long pretokens than MAX_EVENTS
     FLAG_DEF_CAP = 16u,   // deferred-pretoken list full   (host retries with a larger one)
-    FLAG_LONG_CAP = 32u   // ids of deferred pretokens do not fit (host retries with a larger buffer)
+    FLAG_LONG_CAP = 32u,  // ids of deferred pretokens do not fit (host retries with a larger buffer)
+    FLAG_BIG_NEED = 64u   // a pretoken needs a working area of the big pool, which does not exist yet (host retries)
 };
 
 struct __align__(16) CacheSlot {  // 32 bytes = one L2 sector
@@ -114,7 +116,6 @@ struct Counters {
     unsigned long long total_ids;
     unsigned long long long_used;  // bump pointer into long_ids
     unsigned long long st_pretokens, st_hits, st_warp, st_block, st_big, st_cut;
-    unsigned int pool_lock[32];
     CutEvent events[MAX_EVENTS];
 };
 
@@ -125,6 +126,7 @@ struct DevModel {
     const int32_t* rank_of;
     uint32_t n_vocab, n_units, inert;
     int distinct_values, identity_ids, byte_mode, multi_sym, has_prefix, cache_ok;
+    int monotone;              // every pair containing a merged token ranks above that token (hut_model.c)
     const uint32_t* sym_off;   // [257]
     const uint32_t* sym_pool;
     const uint32_t* byte1;     // [256] the single unit of a byte / replaced lead byte; RAWCHAR; NONE = use the pool
@@ -669,7 +671,7 @@ __device__ __forceinline__ uint32_t merge_entry(const DevModel& M, const Job& J,
 }
 
 // ------------------------------------------------------------------------------------------------
-// long_kernel helpers: one CTA (LNT threads) per deferred pretoken
+// long_kernel / huge_kernel helpers: one CTA (blockDim.x threads) per deferred pretoken
 // ------------------------------------------------------------------------------------------------
 constexpr int TREE_SM_KEYS = 1024 + 32 + 8;  // tournament-tree levels of up to 1024 keys stay in shared memory
 constexpr int TREE_MAX_LEVELS = 7;           // 32^7 positions
@@ -677,12 +679,13 @@ constexpr int TREE_MAX_LEVELS = 7;           // 32^7 positions
 struct LongSm {
     unsigned long long tree[TREE_SM_KEYS];
     uint32_t byte1[256];
-    unsigned long long red64[LNW];
-    uint32_t red32[LNW];
+    unsigned long long red64[LMAXW];
+    uint32_t red32[LMAXW];
     unsigned long long found;
     unsigned long long doc_end;
     unsigned long long ids_off;
     uint32_t slot;
+    uint32_t na, nb, nd, chain;  // cooperative rounds: list lengths, "a chain was too long to walk" flag
 };
 
 // block-wide exclusive scan of one uint32 per thread; returns exclusive prefix, *total = sum
@@ -698,8 +701,8 @@ __device__ __forceinline__ uint32_t block_scan_excl(LongSm& sm, uint32_t v, uint
     if (lane == 31) sm.red32[warp] = inc;
     __syncthreads();
     uint32_t wbase = 0, tot = 0;
-#pragma unroll
-    for (int w = 0; w < LNW; ++w) {
+    const int nwarps = blockDim.x >> 5;
+    for (int w = 0; w < nwarps; ++w) {
         uint32_t s = sm.red32[w];
         if (w < warp) wbase += s;
         tot += s;
@@ -719,8 +722,8 @@ __device__ __forceinline__ unsigned long long block_min64(LongSm& sm, unsigned l
     if ((threadIdx.x & 31) == 0) sm.red64[threadIdx.x >> 5] = v;
     __syncthreads();
     unsigned long long r = sm.red64[0];
-#pragma unroll
-    for (int w = 1; w < LNW; ++w) r = sm.red64[w] < r ? sm.red64[w] : r;
+    const int nwarps = blockDim.x >> 5;
+    for (int w = 1; w < nwarps; ++w) r = sm.red64[w] < r ? sm.red64[w] : r;
     return r;
 }
 
@@ -767,22 +770,33 @@ __device__ unsigned long long find_run_end(const Job& J, LongSm& sm, unsigned lo
         __syncthreads();
         unsigned long long f = sm.found;
         if (f != ~0ull) return f;
-        p0 += LNT;
+        p0 += blockDim.x;
         if (p0 > stop) return p0;
     }
 }
 
 // ------------------------------------------------------------------------------------------------
 // block-cooperative merge of one pretoken [gs, ge) with its symbol arrays in global memory (L2):
-// U unit, MG merged unit of pair (i, next(i)), NX / PV linked list, T tournament-tree levels.  One merge per round,
-// the pair with the smallest (rank, index) -- the same order as the reference heap -- read from the tree's root.
+// U unit, MG merged unit of pair (i, next(i)), NX / PV linked list, T tournament-tree levels (fan-out 32) over the
+// keys (rank << 32 | position): the next merge of the reference -- the pair with the smallest (rank, left index),
+// queue.c:162-164 -- is the tree's root.
+//   X == nullptr : one merge per step, applied by one lane, the touched tree groups refreshed by its warp.
+//   X != nullptr (huge_kernel; the model's ranks are monotone: every pair containing a merged token ranks above it,
+//     checked at hut_create): the order "smallest rank first, leftmost first" then applies ALL pairs of the current
+//     minimum rank before anything else, and the pairs they create rank higher.  So a round takes the minimum rank r
+//     from the root, walks the tree down to every position whose pair has rank r (all warps, level by level), drops
+//     every second one of a chain of overlapping occurrences (the leftmost wins, core.c:111-176), applies the rest at
+//     once, re-probes the new neighbour pairs and refreshes the touched tree groups level by level.  A round of one or
+//     two occurrences is cheaper done by the single-lane step, which therefore goes first (up to 4 pops).
 // cta_merge_run leaves the survivors in U (dead = ENDLINK) and returns their number (+ the ids emitted alone
 // before the first pretoken); 0xFFFFFFFF if the symbol count exceeds cap.  cta_merge_emit writes the ids.
 // ------------------------------------------------------------------------------------------------
 __device__ uint32_t cta_merge_run(const DevModel& M, const Job& J, LongSm& sm, unsigned long long gs,
                                   unsigned long long ge, bool with_prefix, bool alone_first, uint32_t* U, uint32_t* MG,
-                                  uint32_t* NX, uint32_t* PV, unsigned long long* T, uint32_t cap, uint32_t* m_out) {
+                                  uint32_t* NX, uint32_t* PV, unsigned long long* T, uint32_t cap, uint32_t* m_out,
+                                  uint32_t* X) {
     const uint32_t tid = threadIdx.x;
+    const uint32_t LNT = blockDim.x, LNW = blockDim.x >> 5;
     auto at = [&](unsigned long long p) -> uint32_t { return (uint32_t)__ldg(J.text + p); };
     const unsigned long long len = ge - gs;
     const unsigned long long chunk = (len + LNT - 1) / LNT;
@@ -869,62 +883,255 @@ __device__ uint32_t cta_merge_run(const DevModel& M, const Job& J, LongSm& sm, u
         }
         __syncthreads();
     }
-    if (warp == 0) {
-        const int top = nl - 1;
+    const int top = nl - 1;
+    // one merge: the pair at position i (the tree's root).  Called by warp 0; lane 0 applies it, the warp refreshes
+    // the (at most three) touched groups of every level.
+    auto pop_one = [&](uint32_t i) {
+        uint32_t p = ENDLINK, j = ENDLINK;
+        if (lane == 0) {
+            j = NX[i];
+            U[i] = MG[i];
+            U[j] = ENDLINK;  // dead
+            MG[j] = NONE;
+            const uint32_t nj = NX[j];
+            NX[i] = nj;
+            if (nj != ENDLINK) PV[nj] = i;
+            p = PV[i];
+            if (p != ENDLINK) MG[p] = pair_probe(M, U[p], U[i]);
+            MG[i] = (nj != ENDLINK) ? pair_probe(M, U[i], U[nj]) : NONE;
+        }
+        p = __shfl_sync(0xFFFFFFFFu, p, 0);
+        j = __shfl_sync(0xFFFFFFFFu, j, 0);
+        __syncwarp();
+        uint32_t a0 = i >> 5, a1 = j >> 5, a2 = p != ENDLINK ? p >> 5 : a0;
+        {
+            unsigned long long k = warp_min(pos_key(a0 * 32u + lane));
+            if (lane == 0) lv[0][a0] = k;
+            if (a1 != a0) {
+                k = warp_min(pos_key(a1 * 32u + lane));
+                if (lane == 0) lv[0][a1] = k;
+            }
+            if (a2 != a0 && a2 != a1) {
+                k = warp_min(pos_key(a2 * 32u + lane));
+                if (lane == 0) lv[0][a2] = k;
+            }
+        }
+        __syncwarp();
+        for (int l = 1; l <= top; ++l) {
+            a0 >>= 5;
+            a1 >>= 5;
+            a2 >>= 5;
+            const unsigned long long* below = lv[l - 1];
+            const uint32_t nb = lcnt[l - 1];
+            uint32_t c = a0 * 32u + lane;
+            unsigned long long k = warp_min(c < nb ? below[c] : ~0ull);
+            if (lane == 0) lv[l][a0] = k;
+            if (a1 != a0) {
+                c = a1 * 32u + lane;
+                k = warp_min(c < nb ? below[c] : ~0ull);
+                if (lane == 0) lv[l][a1] = k;
+            }
+            if (a2 != a0 && a2 != a1) {
+                c = a2 * 32u + lane;
+                k = warp_min(c < nb ? below[c] : ~0ull);
+                if (lane == 0) lv[l][a2] = k;
+            }
+            __syncwarp();
+        }
+    };
+    auto root = [&]() -> unsigned long long { return *reinterpret_cast<volatile unsigned long long*>(lv[top]); };
+    if (X == nullptr) {
+        if (warp == 0)
+            for (;;) {
+                const unsigned long long best = root();
+                if (best == ~0ull) break;
+                pop_one((uint32_t)best);
+            }
+    } else {
+        // scratch behind the tree: two position / group lists, the dirty-group list and one dirty bitmap per level
+        uint32_t* LA = X;
+        uint32_t* LB = LA + cap;
+        uint32_t* STAMP = LB + cap;              // per position: the last round that selected it
+        uint32_t* DL = STAMP + cap;              // <= lcnt[0] groups
+        uint32_t* BM = DL + (cap / 32u + 64u);   // bitmaps of all levels, one after the other
+        uint32_t bm_off[TREE_MAX_LEVELS];
+        {
+            uint32_t o = 0;
+            for (int l = 0; l < nl; ++l) {
+                bm_off[l] = o;
+                o += (lcnt[l] + 31u) / 32u + 1u;
+            }
+            for (uint32_t i = tid; i < o; i += LNT) BM[i] = 0u;
+            for (uint32_t i = tid; i < m; i += LNT) STAMP[i] = 0u;
+        }
+        const uint32_t lt = (1u << lane) - 1u;
+        uint32_t round = 0;
+        uint32_t stretch = 64;  // single-lane steps after a round that could not be applied at once (doubles up to 64 Ki
+                                // while that keeps happening: a model whose ranks are far from monotone stays serial)
         for (;;) {
-            const unsigned long long best = *reinterpret_cast<volatile unsigned long long*>(lv[top]);
+            ++round;
+            __syncthreads();
+            unsigned long long best = root();
             if (best == ~0ull) break;
-            const uint32_t i = (uint32_t)best;
-            uint32_t p = ENDLINK, j = ENDLINK;
-            if (lane == 0) {
-                j = NX[i];
-                U[i] = MG[i];
+            const uint32_t rmin = (uint32_t)(best >> 32);
+            // ---- a handful of occurrences: the single-lane step ----
+            if (warp == 0) {
+                for (int it = 0; it < 4; ++it) {
+                    const unsigned long long b = root();
+                    if (b == ~0ull || (uint32_t)(b >> 32) != rmin) break;
+                    pop_one((uint32_t)b);
+                }
+            }
+            __syncthreads();
+            best = root();
+            if (best == ~0ull) break;
+            if ((uint32_t)(best >> 32) != rmin) continue;
+            // ---- many: every position whose pair has rank rmin, found by walking the tree down, all warps ----
+            if (tid == 0) {
+                LA[0] = 0u;
+                sm.na = 1u;
+                sm.chain = 0u;
+            }
+            __syncthreads();
+            for (int l = top; l >= 0; --l) {
+                if (tid == 0) sm.nb = 0u;
+                __syncthreads();
+                const uint32_t na = sm.na;
+                for (uint32_t k = warp; k < na; k += LNW) {
+                    const uint32_t c = LA[k] * 32u + lane;
+                    unsigned long long key;
+                    if (l > 0) key = c < lcnt[l - 1] ? lv[l - 1][c] : ~0ull;
+                    else key = pos_key(c);
+                    const bool mine = (uint32_t)(key >> 32) == rmin;
+                    const uint32_t hm = __ballot_sync(0xFFFFFFFFu, mine);
+                    if (hm) {
+                        uint32_t base = 0;
+                        if (lane == 0) base = atomicAdd(&sm.nb, (uint32_t)__popc(hm));
+                        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                        if (mine) LB[base + __popc(hm & lt)] = c;
+                    }
+                }
+                __syncthreads();
+                if (tid == 0) sm.na = sm.nb;
+                uint32_t* t = LA;
+                LA = LB;
+                LB = t;
+                __syncthreads();
+            }
+            const uint32_t np = sm.na;  // LA[0 .. np): the positions
+            // ---- overlapping occurrences (x, x, x: pairs at p and next(p)): the leftmost wins, so of a chain every
+            // second one stays.  A position is dropped iff the number of chain members left of it is odd. ----
+            for (uint32_t k = tid; k < np; k += LNT) {
+                const uint32_t p = LA[k];
+                uint32_t q = PV[p], steps = 0;
+                while (q != ENDLINK && steps < 64u) {
+                    const uint32_t mg = MG[q];
+                    if (mg == NONE || rank_of_unit(M, mg) != rmin) break;
+                    ++steps;
+                    q = PV[q];
+                }
+                if (steps >= 64u) sm.chain = 1u;
+                if (steps & 1u) LA[k] = ENDLINK;  // dropped
+            }
+            __syncthreads();
+            // ---- is it safe to apply them all at once?  Going left to right, the single-lane order would create for
+            // each of them the pairs (left neighbour, merged) and (merged, right neighbour); if all of these rank above
+            // rmin, none of them is touched before the round's last merge and the result is the same.  With monotone
+            // ranks that always holds; otherwise it is checked here (the left neighbour is the merged unit of the
+            // occurrence before it when that one ends right before this one). ----
+            if (!M.monotone && !sm.chain) {
+                for (uint32_t k = tid; k < np; k += LNT) {
+                    const uint32_t p = LA[k];
+                    if (p != ENDLINK) STAMP[p] = round;
+                }
+                __syncthreads();
+                for (uint32_t k = tid; k < np; k += LNT) {
+                    const uint32_t p = LA[k];
+                    if (p == ENDLINK) continue;
+                    const uint32_t mu = MG[p];
+                    const uint32_t nj = NX[NX[p]];
+                    const uint32_t right = nj != ENDLINK ? U[nj] : NONE;
+                    uint32_t left = NONE;
+                    const uint32_t pv = PV[p];
+                    if (pv != ENDLINK) {
+                        const uint32_t pp = PV[pv];
+                        left = (pp != ENDLINK && STAMP[pp] == round) ? MG[pp] : U[pv];
+                    }
+                    uint32_t ml, mr;
+                    pair_probe2(M, left, mu, right, &ml, &mr);
+                    if (rank_of_unit(M, ml) <= rmin || rank_of_unit(M, mr) <= rmin) sm.chain = 1u;
+                }
+                __syncthreads();
+            }
+            if (sm.chain) {
+                // a very long chain (e.g. a run of one letter) or a pair that would jump the queue: a stretch of exact
+                // single-lane steps, then the next round looks again
+                if (warp == 0)
+                    for (uint32_t it = 0; it < stretch; ++it) {
+                        const unsigned long long b = root();
+                        if (b == ~0ull) break;
+                        pop_one((uint32_t)b);
+                    }
+                if (stretch < 65536u) stretch *= 2u;
+                continue;
+            }
+            stretch = 64;
+            // ---- apply all at once (no two of them share a symbol) ----
+            for (uint32_t k = tid; k < np; k += LNT) {
+                const uint32_t p = LA[k];
+                if (p == ENDLINK) continue;
+                const uint32_t j = NX[p];
+                U[p] = MG[p];
                 U[j] = ENDLINK;  // dead
                 MG[j] = NONE;
                 const uint32_t nj = NX[j];
-                NX[i] = nj;
-                if (nj != ENDLINK) PV[nj] = i;
-                p = PV[i];
-                if (p != ENDLINK) MG[p] = pair_probe(M, U[p], U[i]);
-                MG[i] = (nj != ENDLINK) ? pair_probe(M, U[i], U[nj]) : NONE;
+                NX[p] = nj;
+                if (nj != ENDLINK) PV[nj] = p;
+                LB[k] = j;
             }
-            p = __shfl_sync(0xFFFFFFFFu, p, 0);
-            j = __shfl_sync(0xFFFFFFFFu, j, 0);
-            __syncwarp();
-            uint32_t a0 = i >> 5, a1 = j >> 5, a2 = p != ENDLINK ? p >> 5 : a0;
-            {
-                unsigned long long k = warp_min(pos_key(a0 * 32u + lane));
-                if (lane == 0) lv[0][a0] = k;
-                if (a1 != a0) {
-                    k = warp_min(pos_key(a1 * 32u + lane));
-                    if (lane == 0) lv[0][a1] = k;
-                }
-                if (a2 != a0 && a2 != a1) {
-                    k = warp_min(pos_key(a2 * 32u + lane));
-                    if (lane == 0) lv[0][a2] = k;
+            if (tid == 0) sm.nd = 0u;
+            __syncthreads();
+            // ---- new neighbour pairs (both ends may have changed in this round, so this comes after the barrier);
+            // the leaf groups of everything touched become dirty ----
+            auto dirty = [&](int l, uint32_t g) {
+                const uint32_t old = atomicOr(&BM[bm_off[l] + (g >> 5)], 1u << (g & 31u));
+                if (!(old & (1u << (g & 31u)))) DL[atomicAdd(&sm.nd, 1u)] = g;
+            };
+            for (uint32_t k = tid; k < np; k += LNT) {
+                const uint32_t p = LA[k];
+                if (p == ENDLINK) continue;
+                const uint32_t nj = NX[p], pp = PV[p];
+                MG[p] = nj != ENDLINK ? pair_probe(M, U[p], U[nj]) : NONE;
+                dirty(0, p >> 5);
+                dirty(0, LB[k] >> 5);
+                if (pp != ENDLINK) {
+                    MG[pp] = pair_probe(M, U[pp], U[p]);  // the same value if pp merged in this round too
+                    dirty(0, pp >> 5);
                 }
             }
-            __syncwarp();
-            for (int l = 1; l <= top; ++l) {
-                a0 >>= 5;
-                a1 >>= 5;
-                a2 >>= 5;
-                const unsigned long long* below = lv[l - 1];
-                const uint32_t nb = lcnt[l - 1];
-                uint32_t c = a0 * 32u + lane;
-                unsigned long long k = warp_min(c < nb ? below[c] : ~0ull);
-                if (lane == 0) lv[l][a0] = k;
-                if (a1 != a0) {
-                    c = a1 * 32u + lane;
-                    k = warp_min(c < nb ? below[c] : ~0ull);
-                    if (lane == 0) lv[l][a1] = k;
+            __syncthreads();
+            // ---- refresh the tree, level by level, dirty groups only ----
+            for (int l = 0; l <= top; ++l) {
+                const uint32_t nd = sm.nd;
+                // the dirty groups of this level move to LA (the position list is not needed any more)
+                for (uint32_t k = tid; k < nd; k += LNT) LA[k] = DL[k];
+                __syncthreads();
+                if (tid == 0) sm.nd = 0u;
+                __syncthreads();
+                for (uint32_t k = warp; k < nd; k += LNW) {
+                    const uint32_t g = LA[k];
+                    const uint32_t c = g * 32u + lane;
+                    unsigned long long key;
+                    if (l > 0) key = c < lcnt[l - 1] ? lv[l - 1][c] : ~0ull;
+                    else key = pos_key(c);
+                    key = warp_min(key);
+                    if (lane == 0) {
+                        lv[l][g] = key;
+                        BM[bm_off[l] + (g >> 5)] = 0u;  // cleared as a word: every group of the word is in the list
+                        if (l < top) dirty(l + 1, g >> 5);
+                    }
                 }
-                if (a2 != a0 && a2 != a1) {
-                    c = a2 * 32u + lane;
-                    k = warp_min(c < nb ? below[c] : ~0ull);
-                    if (lane == 0) lv[l][a2] = k;
-                }
-                __syncwarp();
+                __syncthreads();
             }
         }
     }
@@ -940,6 +1147,7 @@ __device__ uint32_t cta_merge_run(const DevModel& M, const Job& J, LongSm& sm, u
 __device__ void cta_merge_emit(const DevModel& M, LongSm& sm, const uint32_t* U, uint32_t m, bool alone_first,
                                int32_t* dst) {
     const uint32_t tid = threadIdx.x;
+    const uint32_t LNT = blockDim.x;
     const uint32_t chunk2 = (m + LNT - 1) / LNT;
     uint32_t i0 = chunk2 * tid, i1 = i0 + chunk2;
     if (i0 > m) i0 = m;

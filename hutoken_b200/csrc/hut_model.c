@@ -716,7 +716,9 @@ static int cmp_rule_rank(const void* a, const void* b) {
     return (x->rank > y->rank) - (x->rank < y->rank);
 }
 
-/* open-addressing table from the builder's packed (L,R,M) entries */
+static int compute_monotone(hut_model* m);
+
+/* open-addressing table from the builder's packed (L,R,M) entries (rank_of is final when this is called) */
 static int build_pair_tab(hut_model* m, const builder* b) {
     free(m->pair_tab);
     m->pair_count = 0;
@@ -742,6 +744,27 @@ static int build_pair_tab(hut_model* m, const builder* b) {
             m->pair_count++;
         }
     }
+    return compute_monotone(m);
+}
+
+/* monotone ranks (hut_model.h): rank(M) > rank(L), rank(R) for every pair (L, R) -> M whose L / R is itself produced
+ * by some pair */
+static int compute_monotone(hut_model* m) {
+    uint8_t* produced = calloc((size_t)m->n_units + 2, 1);
+    if (!produced) return 0;
+    for (uint32_t i = 0; i < m->pair_cap; ++i)
+        if (m->pair_tab[i] != HUT_PAIR_EMPTY) produced[m->pair_tab[i] & HUT_UNIT_MASK] = 1;
+    int mono = 1;
+    for (uint32_t i = 0; i < m->pair_cap && mono; ++i) {
+        const uint64_t e = m->pair_tab[i];
+        if (e == HUT_PAIR_EMPTY) continue;
+        const uint32_t l = (uint32_t)(e >> 42) & HUT_UNIT_MASK, r = (uint32_t)(e >> 21) & HUT_UNIT_MASK,
+                       mg = (uint32_t)e & HUT_UNIT_MASK;
+        const int32_t rk = m->rank_of[mg];
+        if ((produced[l] && m->rank_of[l] >= rk) || (produced[r] && m->rank_of[r] >= rk)) mono = 0;
+    }
+    free(produced);
+    m->monotone = mono;
     return 1;
 }
 

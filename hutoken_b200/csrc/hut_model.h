@@ -52,6 +52,10 @@ typedef struct hut_model {
     int distinct_values;       /* 1: no two strings share a value => unit order == rank order */
     int identity_ids;          /* 1: out_id[u] == u for all vocab units */
     int32_t max_value;
+    int monotone;              /* 1: every pair (L, R) -> M ranks above L and above R whenever those are themselves the
+                                  product of a pair (true for any vocabulary grown by BPE training).  Then "smallest
+                                  rank first, leftmost first" (core.c:111-176, queue.c:162-164) applies all pairs of
+                                  the current minimum rank before anything else: huge_kernel's cooperative rounds. */
 
     /* ---- pair table: (L,R) -> M.  slot = L << 42 | R << 21 | M ; empty = all ones -------------- */
     uint64_t* pair_tab;

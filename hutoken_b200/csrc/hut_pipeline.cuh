@@ -16,7 +16,6 @@ __global__ void init_kernel(Job J) {
         c->total_ids = 0;
         c->long_used = 0;
         c->st_pretokens = c->st_hits = c->st_warp = c->st_block = c->st_big = c->st_cut = 0;
-        for (int i = 0; i < 32; ++i) c->pool_lock[i] = 0;
     }
 }
 
@@ -49,22 +48,28 @@ __global__ void slot_docs_kernel(Job J, unsigned long long* out) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// long_kernel: one CTA per deferred pretoken (longer than 32 bytes / symbols, or running past the tile's halo)
+// long_kernel / huge_kernel: one CTA per deferred pretoken (longer than 32 bytes / symbols, or running past the
+// tile's halo).  long_kernel (128 threads) merges those of up to med_cap symbols in its CTA's own scratch area and
+// leaves the longer ones (DefEntry flag 8) to huge_kernel (1024 threads, one working area of the big pool per CTA),
+// which runs cooperative rounds when the model's ranks are monotone (cta_merge_run).
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(LNT) long_kernel(const DevModel M, const Job J) {
-    __shared__ LongSm sm;
+template <bool HUGE>
+__device__ __forceinline__ void long_entries(const DevModel& M, const Job& J, LongSm& sm) {
     const uint32_t tid = threadIdx.x;
-    for (uint32_t i = tid; i < 256; i += LNT) sm.byte1[i] = M.byte1[i];
+    for (uint32_t i = tid; i < 256; i += blockDim.x) sm.byte1[i] = M.byte1[i];
     __syncthreads();
     uint32_t n = J.ctr->n_def;
     if (n > J.def_cap) n = J.def_cap;
-    uint32_t* const scratch = J.cta_scratch + (unsigned long long)blockIdx.x * J.cta_scratch_words;
+    uint32_t* const scratch = HUGE ? J.big_pool + (unsigned long long)blockIdx.x * J.big_slot_words
+                                   : J.cta_scratch + (unsigned long long)blockIdx.x * J.cta_scratch_words;
+    const uint32_t cap = HUGE ? J.big_cap : J.med_cap;
     unsigned long long n_big = 0;
     for (uint32_t e = blockIdx.x; e < n; e += gridDim.x) {
         DefEntry* E = J.def + e;
+        __syncthreads();
+        if (HUGE && !(E->flags & 8u)) continue;  // uniform: every thread reads the same word
         const unsigned long long gs = E->pos;
         const bool first = (E->flags & 1u) != 0;
-        __syncthreads();
         if (tid == 0) {  // end of the document containing gs: first doc_off > gs
             unsigned long long a = 0, b = J.ndocs + 1;
             while (a < b) {
@@ -102,38 +107,29 @@ __global__ void __launch_bounds__(LNT) long_kernel(const DevModel M, const Job J
             }
             continue;
         }
-        const unsigned long long bound = (ge - gs) * M.kmax + M.n_prefix_syms;
-        const bool big = bound > J.med_cap;
-        uint32_t *U, *MG, *NX, *PV, cap;
-        if (!big) {
-            U = scratch;
-            MG = U + J.med_cap;
-            NX = MG + J.med_cap;
-            PV = NX + J.med_cap;
-            cap = J.med_cap;
-        } else {
-            if (tid == 0) {
-                uint32_t slot = blockIdx.x % J.big_slots;
-                for (;;) {
-                    if (atomicCAS(&J.ctr->pool_lock[slot], 0u, 1u) == 0u) break;
-                    slot = (slot + 1) % J.big_slots;
-                    __nanosleep(200);
+        if (!HUGE) {
+            const unsigned long long bound = (ge - gs) * M.kmax + M.n_prefix_syms;
+            if (bound > J.med_cap) {  // huge_kernel's; it is told the length found here (< 2^32: limit * kmax fits)
+                __syncthreads();
+                if (tid == 0) {
+                    E->len = (uint32_t)(ge - gs);
+                    E->flags |= 8u;
+                    if (J.big_slots == 0) set_flag(J, FLAG_BIG_NEED);  // the host allocates the pool and runs the shard again
                 }
-                sm.slot = slot;
+                continue;
             }
-            __syncthreads();
-            U = J.big_pool + (unsigned long long)sm.slot * J.big_slot_words;
-            MG = U + J.big_cap;
-            NX = MG + J.big_cap;
-            PV = NX + J.big_cap;
-            cap = J.big_cap;
-            n_big++;
         }
-        // tournament-tree levels behind the four arrays (8-byte aligned; the areas hold 5 * cap + 8 words)
+        uint32_t* U = scratch;
+        uint32_t* MG = U + cap;
+        uint32_t* NX = MG + cap;
+        uint32_t* PV = NX + cap;
+        // tournament-tree levels behind the four arrays (8-byte aligned; cap / 8 words are plenty), then -- huge_kernel
+        // with a monotone model only -- the lists of the cooperative rounds
         unsigned long long* T = reinterpret_cast<unsigned long long*>(
             (reinterpret_cast<uintptr_t>(PV + cap) + 7u) & ~(uintptr_t)7u);
+        uint32_t* X = (HUGE && M.monotone) ? reinterpret_cast<uint32_t*>(T) + (cap / 8u + 64u) : nullptr;
         uint32_t m = 0;
-        uint32_t cnt = cta_merge_run(M, J, sm, gs, ge, with_prefix, alone_first, U, MG, NX, PV, T, cap, &m);
+        uint32_t cnt = cta_merge_run(M, J, sm, gs, ge, with_prefix, alone_first, U, MG, NX, PV, T, cap, &m, X);
         if (cnt == 0xFFFFFFFFu) {
             set_flag(J, FLAG_BIG_CAP);
             cnt = 0;
@@ -153,13 +149,21 @@ __global__ void __launch_bounds__(LNT) long_kernel(const DevModel M, const Job J
             E->count = cnt;
             E->ids_off = off;
             atomicAdd(&J.tot[E->tile], cnt);
-            if (big) {
-                __threadfence();
-                atomicExch(&J.ctr->pool_lock[sm.slot], 0u);
-            }
         }
+        if (HUGE) n_big++;
     }
     if (tid == 0 && n_big) atomicAdd(&J.ctr->st_big, n_big);
+}
+
+__global__ void __launch_bounds__(LNT) long_kernel(const DevModel M, const Job J) {
+    __shared__ LongSm sm;
+    long_entries<false>(M, J, sm);
+}
+
+__global__ void __launch_bounds__(HNT, 1) huge_kernel(const DevModel M, const Job J) {
+    __shared__ LongSm sm;
+    if (J.ctr->flags & FLAG_BIG_NEED) return;  // no pool yet
+    long_entries<true>(M, J, sm);
 }
 
 // ------------------------------------------------------------------------------------------------

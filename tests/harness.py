@@ -77,10 +77,10 @@ class HostModel:
         return out[:n].tobytes()
 
     def info(self):
-        out = np.zeros(8, dtype=np.uint32)
+        out = np.zeros(9, dtype=np.uint32)
         lib().harness_info(self._h, out.ctypes.data)
         keys = ["n_vocab", "n_units", "pair_count", "pair_cap", "distinct_values", "identity_ids",
-                "max_sym_per_char", "vocab_lines"]
+                "max_sym_per_char", "vocab_lines", "monotone"]
         return dict(zip(keys, out.tolist()))
 
     def close(self):

@@ -185,6 +185,7 @@ void harness_info(const hut_model* m, uint32_t* out) {
     out[5] = (uint32_t)m->identity_ids;
     out[6] = m->max_sym_per_char;
     out[7] = m->vocab_lines;
+    out[8] = (uint32_t)m->monotone;
 }
 
 /* ---- bit-sliced classifier (hut_bitslice.h), chunk by chunk the way the warp lanes run it ---- */
