@@ -52,6 +52,9 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-decode", action="store_true", help="skip the decode leg (ids -> text on the device)")
     ap.add_argument("--check", action="store_true", help="also verify a sample of the output against the oracle")
+    ap.add_argument("--no-workloads", action="store_true", help="skip the short runs of the other configs (workloads object)")
+    ap.add_argument("--no-latency", action="store_true", help="skip the per-call latency leg (latency object)")
+    ap.add_argument("--llama-mb", type=int, default=10240, help="configs[2] corpus in all, MiB (split over the ranks)")
     return ap.parse_args()
 
 
@@ -304,7 +307,61 @@ def _device_equal(torch, ptr, d_text, n, dev):
     return bool(torch.equal(got, d_text[:n]))
 
 
+def heavy_tail(data, offs, seed, frac=0.05):
+    """Splices long single-class runs into a corpus so that the rarely taken paths get real work: about `frac` of the
+    bytes end up in pretokens of 16..31 bytes (second cache) and of 40..4000 bytes (long_kernel): long words, digit
+    runs, hex / base64-like blobs with one character class.  Returns (data, offs) with the same documents, grown."""
+    rng = np.random.default_rng(seed)
+    nd = len(offs) - 1
+    total = int(offs[-1])
+    budget = int(total * frac)
+    lens = []
+    while budget > 0:
+        n = int(rng.integers(16, 32)) if rng.random() < 0.85 else int(min(4000, max(40, rng.lognormal(5.3, 1.0))))
+        lens.append(n)
+        budget -= n + 1
+    lens = np.array(lens, dtype=np.int64)
+    where = np.sort(rng.integers(0, nd, size=len(lens)))  # run k is appended to document where[k]
+    alph = [np.frombuffer(b"abcdefghijklmnopqrstuvwxyz", np.uint8), np.frombuffer(b"0123456789", np.uint8),
+            np.frombuffer(b"ABCDEFGHIJKLMNOPQRSTUVWXYZabcdefghijklmnopqrstuvwxyz", np.uint8)]
+    kinds = rng.integers(0, 3, size=len(lens))
+    out = np.empty(total + int(lens.sum()) + len(lens) + 64, dtype=np.uint8)
+    new_offs = np.empty(nd + 1, dtype=np.uint64)
+    at, k = 0, 0
+    for d in range(nd):
+        new_offs[d] = at
+        lo, hi = int(offs[d]), int(offs[d + 1])
+        out[at:at + hi - lo] = data[lo:hi]
+        at += hi - lo
+        while k < len(lens) and where[k] == d:
+            out[at] = 0x20
+            a = alph[kinds[k]]
+            out[at + 1:at + 1 + lens[k]] = a[rng.integers(0, len(a), size=lens[k])]
+            at += 1 + int(lens[k])
+            k += 1
+    new_offs[nd] = at
+    out[at:at + 64] = 0
+    return out[:at + 64], new_offs
+
+
+def long_run_docs(seed, sizes):
+    """configs[4] shape: documents holding one single-class run of the given sizes inside normal text."""
+    import synth
+    rng = np.random.default_rng(seed)
+    base, boffs = synth.corpus(seed, 64 << 10)
+    filler = base[:int(boffs[4])].tobytes()
+    docs = []
+    letters = np.frombuffer(b"abcdefghijklmnopqrstuvwxyz", np.uint8)
+    for n in sizes:
+        run = letters[rng.integers(0, 26, size=n)].tobytes()
+        docs.append(filler[:300] + b" " + run + b" " + filler[300:600])
+    offs = np.zeros(len(docs) + 1, dtype=np.uint64)
+    offs[1:] = np.cumsum([len(d) for d in docs])
+    return np.frombuffer(b"".join(docs) + b"\0" * 64, dtype=np.uint8), offs
+
+
 def run_ours(args):
+    import hashlib
     import torch
     import torch.distributed as dist
     import synth
@@ -321,56 +378,112 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
     lib = capi.load_library()
-    v, s = synth.PATHS[args.model]
-    eng = capi.Engine(v, s, devices=[local], chunk_mb=args.chunk_mb, **synth.MODEL_KW[args.model])
-
-    # ---- this rank's documents (pinned host memory: the e2e leg copies from it) ----
-    t0 = time.time()
-    data, offs, nbytes = make_corpus(2 + rank, args.mb << 20, args.special_every,
-                                     pinned_alloc=lambda n: pinned_u8(lib, n))
-    ndocs = len(offs) - 1
-    gen_s = time.time() - t0
-
-    d_text = torch.empty(nbytes + 64, dtype=torch.uint8, device=dev)
-    d_text.copy_(torch.from_numpy(data[:nbytes + 64]), non_blocking=False)
-    d_offs = torch.from_numpy(offs.astype(np.int64)).to(dev)
-    ids_cap = nbytes + 4096  # byte mode, one symbol per byte: T <= B_in
-    if args.model.startswith("llama"):
-        ids_cap = nbytes + 8 * ndocs + 4096
-    d_ids = torch.empty(ids_cap, dtype=torch.int32, device=dev)
-    d_tok = torch.empty(ndocs + 1, dtype=torch.int64, device=dev)
     stream = torch.cuda.current_stream(dev)
     sh = stream.cuda_stream
+    peak, peak_src = measured_peak()
+    check_bytes = 8 << 20
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    def step_device():
-        eng.cache_reset()
-        return eng.encode_device(0, d_text.data_ptr(), nbytes, d_offs.data_ptr(), ndocs, d_ids.data_ptr(), ids_cap,
-                                 d_tok.data_ptr(), stream=sh)
+    def make_engine(model, **kw):
+        v, s = synth.PATHS[model]
+        return capi.Engine(v, s, devices=[local], chunk_mb=args.chunk_mb, **synth.MODEL_KW[model], **kw)
 
-    # ---- device-resident leg: `value` ----
-    n_ids = 0
-    for _ in range(args.warmup):
-        n_ids = step_device()
+    def make_oracle(model, **kw):
+        from oracle import oracle as O
+        v, s = synth.PATHS[model]
+        return O.Oracle(v, s, **synth.MODEL_KW[model], **kw)
+
+    def device_leg(eng, model, data, offs, nbytes, steps, warmup, sync_all):
+        """`value` leg: text and offsets resident in HBM, ids stay there (hut_encode_device).  CUDA events on the launch
+        stream; the pretoken cache is reset inside every step."""
+        ndocs = len(offs) - 1
+        d_text = torch.empty(nbytes + 64, dtype=torch.uint8, device=dev)
+        d_text.copy_(torch.from_numpy(data[:nbytes + 64]), non_blocking=False)
+        d_offs = torch.from_numpy(offs.astype(np.int64)).to(dev)
+        ids_cap = nbytes + 4096  # byte mode, one symbol per byte: T <= B_in
+        if model.startswith("llama"):
+            ids_cap = nbytes + 8 * ndocs + 4096
+        d_ids = torch.empty(ids_cap, dtype=torch.int32, device=dev)
+        d_tok = torch.empty(ndocs + 1, dtype=torch.int64, device=dev)
+
+        def step():
+            eng.cache_reset()
+            return eng.encode_device(0, d_text.data_ptr(), nbytes, d_offs.data_ptr(), ndocs, d_ids.data_ptr(), ids_cap,
+                                     d_tok.data_ptr(), stream=sh)
+
+        n_ids = 0
+        for _ in range(warmup):
+            n_ids = step()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        main_ms, launches, st = [], 0, None
+        if sync_all:
+            barrier()
+        else:
+            torch.cuda.synchronize(dev)
+        e0.record(stream)
+        for _ in range(steps):
+            n_ids = step()
+            st = eng.stats()
+            main_ms.append(st["main_kernel_ms"])
+            launches += int(st["kernel_launches"])
+        e1.record(stream)
+        if sync_all:
+            barrier()
+        else:
+            torch.cuda.synchronize(dev)
+        return {"ms": e0.elapsed_time(e1) / steps, "main_ms": float(np.mean(main_ms)), "n_ids": int(n_ids),
+                "launches": launches, "stats": st, "d_text": d_text, "d_ids": d_ids, "d_tok": d_tok, "ndocs": ndocs}
+
+    def parity(orc, data, offs, leg, limit):
+        """ids + offsets of the first `limit` bytes against the oracle: (equal, sha256 of the engine's id prefix, probe stats)"""
+        nd = int(np.searchsorted(offs, np.uint64(limit), side="right")) - 1
+        nd = max(1, min(nd, len(offs) - 1))
+        before = orc.stats()
+        oids, otok = orc.encode_packed(data[:int(offs[nd]) + 1], offs[:nd + 1])
+        after = orc.stats()
+        got = leg["d_ids"][:len(oids)].cpu().numpy()
+        gtok = leg["d_tok"][:nd + 1].cpu().numpy().astype(np.uint64)
+        ok = bool(len(got) == len(oids) and np.array_equal(got, oids) and np.array_equal(gtok, otok))
+        probes = {k: after[k] - before[k] for k in ("pretokens", "symbols", "tokens", "probes")}
+        probes["bytes"] = int(offs[nd])
+        return ok, hashlib.sha256(got.tobytes()).hexdigest(), probes
+
+    def summarize(leg, nbytes, probes=None):
+        algo = nbytes + 4 * leg["n_ids"] + 8 * (leg["ndocs"] + 1)
+        out = {"value": nbytes / (leg["ms"] * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": leg["ms"],
+               "tokens_per_s": leg["n_ids"] / (leg["ms"] * 1e-3), "bytes": int(nbytes), "docs": int(leg["ndocs"]),
+               "roofline": {"kernel": "hut::tile_kernel", "kernel_ms": leg["main_ms"],
+                            "achieved": algo / (leg["main_ms"] * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                            "frac": algo / (leg["main_ms"] * 1e-3) / 1e9 / peak,
+                            "frac_whole_step": algo / (leg["ms"] * 1e-3) / 1e9 / peak,
+                            "algorithmic_bytes_per_launch": int(algo)},
+               "stats_last_step": {k: leg["stats"][k] for k in ("pretokens", "cache_hits", "warp_merges", "block_merges",
+                                                                "big_merges", "cut_documents")}}
+        if probes and probes["bytes"]:
+            # SURVEY 8(d) secondary figure: lookups the ALGORITHM needs (no dedup credit), 8 B per (key, value) slot,
+            # counted by the oracle on the parity prefix and scaled to the shard by bytes
+            p_total = probes["probes"] * (nbytes / probes["bytes"])
+            out["roofline"]["bytes_incl_probes"] = int(algo + 8 * p_total)
+            out["roofline"]["probes_per_input_byte"] = probes["probes"] / probes["bytes"]
+        return out
+
+    # =============================== headline workload: configs[1] (or --model / --mb) ===============================
+    eng = make_engine(args.model)
+    t0 = time.time()
+    data, offs, nbytes = make_corpus(2 + rank, args.mb << 20, args.special_every,
+                                     pinned_alloc=lambda n: pinned_u8(lib, n))
+    ndocs = len(offs) - 1
+    gen_s = time.time() - t0
     clocks = ClockSampler(local)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    main_ms, launches = [], 0
-    barrier()
     clocks.start()
-    e0.record(stream)
-    for _ in range(args.steps):
-        n_ids = step_device()
-        st = eng.stats()
-        main_ms.append(st["main_kernel_ms"])
-        launches += int(st["kernel_launches"])
-    e1.record(stream)
-    barrier()
+    leg = device_leg(eng, args.model, data, offs, nbytes, args.steps, args.warmup, sync_all=True)
     clk = clocks.stop()
-    dev_ms = e0.elapsed_time(e1) / args.steps
+    dev_ms, n_ids, launches, st = leg["ms"], leg["n_ids"], leg["launches"], leg["stats"]
+    d_text, d_ids, d_tok = leg["d_text"], leg["d_ids"], leg["d_tok"]
 
     # ---- end-to-end leg through the host-buffer C-ABI call: H2D text + kernels + D2H ids every step ----
     e2e_ms = None
@@ -414,7 +527,16 @@ def run_ours(args):
         except ValueError as e:  # ids the vocabulary cannot print (-1): nothing to decode
             dec = {"value": None, "note": str(e)}
 
-    # ---- max over ranks / whole-job sums (hutoken_b200/dist.py; covered on CPU by tests/test_dist_cpu.py) ----
+    # ---- id check of THIS rank's shard (every rank, so the scaling runs carry one per GPU) ----
+    check_ok, check_sha, probes = None, None, None
+    if args.check or world > 1 or not args.no_workloads:
+        orc = make_oracle(args.model)
+        check_ok, check_sha, probes = parity(orc, data, offs, leg, check_bytes)
+        orc.close()
+        if not check_ok:
+            raise SystemExit(f"bench.py: rank {rank}: GPU ids differ from the oracle on the first {check_bytes} bytes")
+
+    # ---- max over ranks / whole-job sums ----
     from hutoken_b200 import dist as D
 
     def allmax(x):
@@ -428,28 +550,65 @@ def run_ours(args):
     total_ids = allsum(float(n_ids))
     e2e_ms_max = allmax(e2e_ms) if e2e_ms is not None else None
     launches_total = int(allsum(float(launches)))
+    checks_ok = int(allsum(1.0 if check_ok else 0.0)) if check_ok is not None else None
+    head = summarize(leg, nbytes, probes)
+    del d_text, d_ids, d_tok, leg
+    torch.cuda.empty_cache()
 
-    if args.check:
-        from oracle import oracle as O
-        orc = O.Oracle(v, s, **synth.MODEL_KW[args.model])
-        nd = int(np.searchsorted(offs, np.uint64(8 << 20), side="right")) - 1
-        oids, otok = orc.encode_packed(data[:int(offs[nd]) + 1], offs[:nd + 1])
-        got = d_ids[:len(oids)].cpu().numpy()
-        assert np.array_equal(got, oids), "bench --check: GPU ids differ from the oracle"
-        assert np.array_equal(d_tok[:nd + 1].cpu().numpy().astype(np.uint64), otok)
+    # =============================== the other configs, one short run each (same JSON line) ===============================
+    workloads = {}
+    if not args.no_workloads:
+        def extra(name, model, data_x, offs_x, eng_x, orc_kw, steps, limit, note):
+            nb = int(offs_x[-1])
+            lg = device_leg(eng_x, model, data_x, offs_x, nb, steps, 1, sync_all=False)
+            orc_x = make_oracle(model, **orc_kw)
+            ok, sha, pr = parity(orc_x, data_x, offs_x, lg, limit)
+            orc_x.close()
+            w = summarize(lg, nb, pr)
+            w["parity"] = {"equal_to_oracle": ok, "prefix_bytes": int(pr["bytes"]), "sha256_int32_ids": sha}
+            w["config"] = note
+            ms_all = allmax(lg["ms"])
+            w["whole_job_value"] = allsum(float(nb)) / (ms_all * 1e-3) / 1e6
+            workloads[name] = w
+            del lg
+            torch.cuda.empty_cache()
+
+        # configs[2]: Llama-shaped 32k vocab, 10 GiB in all, split over the ranks (so the scaling run yields the
+        # strong-scaling curve north_star asks for)
+        if args.model != "llama":
+            mb2 = max(64, args.llama_mb // world)
+            eng2 = make_engine("llama")
+            d2, o2, nb2 = make_corpus(300 + rank, mb2 << 20, 0, pinned_alloc=lambda n: pinned_u8(lib, n))
+            extra("configs[2] llama_10GiB_total", "llama", d2, o2, eng2, {}, 2, check_bytes,
+                  f"Llama/PULI-LlumiX-shaped 32K vocab (prefix U+2581, plain mode), {mb2} MiB on this rank = "
+                  f"{mb2 * world} MiB over {world} rank(s) (strong scaling)")
+            eng2.close()
+            lib.hut_host_free(d2.ctypes.data)
+            del d2, o2
+        # configs[3]: a special byte / multibyte character every ~200 bytes
+        d3, o3, nb3 = make_corpus(400 + rank, 256 << 20, 200, pinned_alloc=None)
+        extra("configs[3] special_every_200", args.model, d3, o3, eng, {}, 3, check_bytes,
+              "configs[1] model, one replaced byte / multibyte character every ~200 bytes, 256 MiB per rank")
+        # heavy tail: 5 % of the bytes in pretokens of 16..31 and 40..4000 bytes (second cache, long_kernel)
+        d5, o5 = heavy_tail(d3[:(96 << 20)], o3[:int(np.searchsorted(o3, np.uint64(96 << 20), side="right"))], 500 + rank)
+        extra("heavy_tail_mix", args.model, d5, o5, eng, {}, 3, check_bytes,
+              "configs[1] model, 96 MiB + 5 % of the bytes spliced in as single-class runs of 16..31 / 40..4000 bytes")
+        del d3, o3, d5, o5
+        # configs[4]: long single-class runs really merged (opt-in no-limit mode; the reference cuts such documents)
+        eng4 = make_engine(args.model, max_pretoken=32 << 20)
+        d4, o4 = long_run_docs(600 + rank, [16 << 10, 64 << 10, (256 << 10) - 8, (256 << 10) + 8, 1 << 20])
+        extra("configs[4] long_runs_no_limit", args.model, d4, o4, eng4, {"no_limit": True}, 1, 1 << 30,
+              "5 documents holding one letters-only run of 16 Ki / 64 Ki / 256 Ki - 8 / 256 Ki + 8 / 1 Mi bytes, "
+              "max_pretoken = 32 MiB (no cut), checked in full against the oracle's no-limit mode")
+        eng4.close()
+        del d4, o4
+
+    # =============================== latency of the drop-in calls (rank 0) ===============================
+    latency = None
+    if rank == 0 and not args.no_latency:
+        latency = measure_latency(args.model)
 
     if rank == 0:
-        peak, peak_src = measured_peak()
-        k_ms = float(np.mean(main_ms))
-        algo = nbytes + 4 * n_ids + 8 * (ndocs + 1)
-        achieved = algo / (k_ms * 1e-3) / 1e9
-        traffic = None
-        try:  # DRAM bytes of the dominant kernel from the committed ncu capture of this very workload
-            tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["tile_kernel"]
-            if args.model == "gpt2" and args.mb == 1024 and args.special_every == 0:
-                traffic = int(tj["dram_bytes_read"] + tj["dram_bytes_write"])
-        except Exception:
-            pass
         line = {
             "metric": METRIC, "value": total_bytes / (dev_ms_max * 1e-3) / 1e6, "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms_max, "higher_is_better": True,
@@ -460,14 +619,17 @@ def run_ours(args):
             "bytes_per_gpu": int(nbytes), "docs_per_gpu": int(ndocs),
             "gpu_launches": launches_total,
             "clocks": clk,
-            "roofline": {"bound": "hbm", "kernel": "hut::tile_kernel (+ miss_kernel)", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": int(algo), "kernel_ms": k_ms,
-                         "kernel_share_of_step": k_ms / dev_ms},
-            "stats_last_step": {k: st[k] for k in ("pretokens", "cache_hits", "warp_merges", "block_merges",
-                                                   "big_merges")},
+            "roofline": dict(head["roofline"], bound="hbm", traffic=ncu_traffic(args), peak_source=peak_src,
+                             kernel_share_of_step=head["roofline"]["kernel_ms"] / dev_ms),
+            "stats_last_step": head["stats_last_step"],
+            "check": None if checks_ok is None else {"ranks_equal_to_oracle": checks_ok, "ranks": world,
+                                                     "prefix_bytes": check_bytes, "sha256_rank0": check_sha},
             "corpus_gen_s": gen_s,
         }
+        if workloads:
+            line["workloads"] = workloads
+        if latency is not None:
+            line["latency"] = latency
         if dec is not None:
             line["decode"] = dec
         if e2e_ms_max is not None:
@@ -495,6 +657,92 @@ def run_ours(args):
         dist.barrier()
         dist.destroy_process_group()
     eng.close()
+
+
+def ncu_traffic(args):
+    """DRAM bytes of the dominant kernel from the committed ncu capture of this very workload (per launch), else None"""
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["tile_kernel"]
+        if args.model == "gpt2" and args.mb == 1024 and args.special_every == 0:
+            return int(tj["dram_bytes_read"] + tj["dram_bytes_write"])
+    except Exception:
+        pass
+    return None
+
+
+def measure_latency(model):
+    """The reference's own per-call bound (tests/test_tokenizer.py:107-130: mean encode(sentence1) < 1 ms over 10 000
+    calls, the same for decode(encode(..))), through the drop-in Python surface, with the unmodified reference beside
+    it; plus the list API (one PyLong per id) on a 64 MB sample beside the packed call."""
+    import synth
+    import hutoken_b200 as hutoken
+    v, s = synth.PATHS[model]
+    kw = synth.MODEL_KW[model]
+    sentence1 = "How can the net amount of entropy of the universe be massively decreased?"
+    out = {"sentence_bytes": len(sentence1), "calls": 10000}
+
+    def timed(fn, n):
+        ts = np.empty(n)
+        for i in range(n):
+            t0 = time.perf_counter()
+            fn()
+            ts[i] = time.perf_counter() - t0
+        return {"mean_us": float(ts.mean() * 1e6), "p50_us": float(np.percentile(ts, 50) * 1e6),
+                "p99_us": float(np.percentile(ts, 99) * 1e6)}
+
+    hutoken.initialize(v, s, prefix=kw["prefix"], is_byte_encoder=kw["is_byte_encoder"])
+    ids = hutoken.encode(sentence1)
+    for _ in range(200):
+        hutoken.encode(sentence1)
+    out["encode"] = timed(lambda: hutoken.encode(sentence1), 10000)
+    try:
+        hutoken.decode(ids)
+        out["decode_of_encode"] = timed(lambda: hutoken.decode(hutoken.encode(sentence1)), 10000)
+    except Exception as e:  # a vocabulary that cannot print every id
+        out["decode_of_encode"] = {"note": str(e)}
+    # list API vs packed API on the same 64 MB of documents
+    data, offs = synth.corpus(77, 64 << 20)
+    docs = [d.decode("utf-8") for d in synth.docs_of(data, offs)]
+    hutoken.batch_encode(docs[:64], 1)
+    t0 = time.perf_counter()
+    res = hutoken.batch_encode(docs, 1)
+    t_list = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    pid, ptok = hutoken.batch_encode_packed(data[:int(offs[-1])], offs)
+    t_packed = time.perf_counter() - t0
+    nb = int(offs[-1])
+    out["batch_encode_list_api"] = {"value": nb / t_list / 1e6, "unit": UNIT, "seconds": t_list, "bytes": nb,
+                                    "ids": int(sum(len(r) for r in res)),
+                                    "note": "hutoken.batch_encode(list of str): two UTF-8 passes + one PyLong per id"}
+    out["batch_encode_packed_api"] = {"value": nb / t_packed / 1e6, "unit": UNIT, "seconds": t_packed,
+                                      "ids": int(len(pid))}
+    # the unmodified reference on the same calls
+    try:
+        from oracle import oracle as O
+        ref = O.load_ref()
+        if ref is not None:
+            ref.initialize(v, s, kw["prefix"], kw["is_byte_encoder"])
+            for _ in range(200):
+                ref.encode(sentence1)
+            r = {"encode": timed(lambda: ref.encode(sentence1), 10000)}
+            try:
+                rids = ref.encode(sentence1)
+                ref.decode(rids)
+                r["decode_of_encode"] = timed(lambda: ref.decode(ref.encode(sentence1)), 10000)
+            except Exception as e:
+                r["decode_of_encode"] = {"note": str(e)}
+            nthreads = host_threads()
+            sub = docs[:len(docs) // 8]
+            nbs = sum(len(d.encode("utf-8")) for d in sub)
+            t0 = time.perf_counter()
+            ref.batch_encode(sub, nthreads)
+            dt = time.perf_counter() - t0
+            r["batch_encode_list_api"] = {"value": nbs / dt / 1e6, "unit": UNIT, "seconds": dt, "bytes": nbs,
+                                          "threads": nthreads}
+            out["reference"] = r
+    except Exception as e:
+        out["reference"] = {"note": f"{type(e).__name__}: {e}"}
+    return out
 
 
 def main():

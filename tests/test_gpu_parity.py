@@ -163,6 +163,38 @@ def test_no_limit_long_runs(name):
     assert_same(ids, tok, oids, otok, f"no-limit at the limit {name}")
 
 
+@pytest.mark.parametrize("name", ["gpt2_small", "llama_small"])
+def test_no_limit_cooperative_rounds(name):
+    """huge_kernel's cooperative rounds (all pairs of the minimum rank applied at once): a merges-file model has
+    monotone ranks (every rule's parts are made by earlier rules), so every round of a long run takes that path.
+    Runs of random letters, digits, one letter (a single chain of overlapping pairs) and a two-letter pattern, merged
+    in no-limit mode and compared with the oracle (merge order: core.c:211-337, queue.c:162-164)."""
+    import subprocess
+    import sys
+    import os
+    from hutoken_b200 import capi
+    from oracle import oracle as O
+    from common import ROOT
+    v, s = synth.PATHS[name]
+    mp = os.path.join(tempfile.mkdtemp(), name + ".merges.txt")
+    subprocess.run([sys.executable, os.path.join(ROOT, "tools", "make_merges.py"), v, mp], check=True,
+                   stdout=subprocess.DEVNULL)
+    kw = synth.MODEL_KW[name]
+    eng = capi.Engine(v, s, merges_path=mp, max_pretoken=8 << 20, **kw)
+    orc = O.Oracle(v, s, merges_path=mp, no_limit=True, **kw)
+    rng = random.Random(5)
+    docs = ["go " + "".join(rng.choices("abcdefghijklmnopqrstuvwxyz", k=n)) + " end" for n in (5000, 300000, 2 << 20)]
+    docs += ["".join(rng.choices("0123456789", k=700000)), "a" * 70000 + " " + "ab" * 40000 + " " + "aab" * 30000,
+             "é" * 20000, "x"]
+    data, offs = pack(docs)
+    ids, tok = eng.encode_packed(data, offs)
+    oids, otok = orc.encode_packed(data, offs)
+    assert_same(ids, tok, oids, otok, f"cooperative rounds {name}")
+    assert eng.stats()["big_merges"] >= 5
+    eng.close()
+    orc.close()
+
+
 def test_one_context_over_distinct_devices():
     """hut_create over ALL distinct GPUs of the box (the product's own multi-GPU entry, HUTOKEN_B200_DEVICES):
     chunks dealt round-robin to physically different devices.  Skipped on a one-GPU box."""

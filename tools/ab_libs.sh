@@ -15,8 +15,8 @@ except Exception as e:
 PY
 }
 for v in "$@"; do
-    HUTOKEN_B200_LIB=$PWD/hutoken_b200/exp_$v.so timeout -s KILL 300 python bench.py --no-cpu-baseline --no-e2e --no-decode $AB_CHECK $AB_ARGS > gpurun_out/exp_$v.json 2> gpurun_out/exp_$v.err
+    HUTOKEN_B200_LIB=$PWD/hutoken_b200/exp_$v.so timeout -s KILL 300 python bench.py --no-cpu-baseline --no-e2e --no-decode --no-workloads --no-latency $AB_CHECK $AB_ARGS > gpurun_out/exp_$v.json 2> gpurun_out/exp_$v.err
     line "$v" gpurun_out/exp_$v.json
 done
-timeout -s KILL 300 python bench.py --no-cpu-baseline --no-e2e --no-decode --check $AB_ARGS > gpurun_out/exp_base.json 2> gpurun_out/exp_base.err
+timeout -s KILL 300 python bench.py --no-cpu-baseline --no-e2e --no-decode --no-workloads --no-latency --check $AB_ARGS > gpurun_out/exp_base.json 2> gpurun_out/exp_base.err
 line shipped gpurun_out/exp_base.json
