@@ -83,6 +83,12 @@ struct hut_dev {
     size_t tmp_ids_cap;
     hut_flight fl[2];
     hut_chunkbuf cb[2];
+    // small-batch path (small_kernel): pinned buffers the device reads / writes directly
+    uint8_t* sm_text;
+    unsigned long long* sm_off;
+    Counters* sm_ctr;            // only the head (before events) is used
+    volatile unsigned int* sm_done;
+    unsigned int sm_seq;
     hut_stats stats;
 };
 
@@ -202,7 +208,13 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     if (per_sm < 1) per_sm = 1;
     d->sms = sms;
     d->grid = per_sm * sms;
-    d->long_grid = 2 * sms;
+    {   // long_kernel walks its pretokens one merge at a time: many small CTAs in flight hide that latency
+        int per = 0;
+        CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, long_kernel, LNT, 0));
+        if (per < 1) per = 1;
+        if (per > 8) per = 8;
+        d->long_grid = per * sms;
+    }
     // ids a 960-byte tile can produce: one per symbol of the pretokens STARTING in it (the last one may run up to
     // MAXW - 1 bytes past the tile) + the prefix ids of every document starting in it
     d->stride = (uint32_t)(OWN + MAXW) * dm.kmax;
@@ -250,6 +262,10 @@ static void dev_free(hut_dev* d) {
             if (d->fl[b].ev[i]) cudaEventDestroy(d->fl[b].ev[i]);
         if (d->fl[b].done) cudaEventDestroy(d->fl[b].done);
     }
+    cudaFreeHost(d->sm_text);
+    cudaFreeHost(d->sm_off);
+    cudaFreeHost(d->sm_ctr);
+    cudaFreeHost((void*)d->sm_done);
     if (d->stream) cudaStreamDestroy(d->stream);
     if (d->s_in) cudaStreamDestroy(d->s_in);
     if (d->s_out) cudaStreamDestroy(d->s_out);
@@ -670,6 +686,96 @@ static int chunk_complete(hut_ctx* ctx, chunk_plan* p, uint64_t id_base, uint64_
     return HUT_STATUS_OK;
 }
 
+/* ---- small batches: one launch of one CTA, no copies (small_kernel in hut_pipeline.cuh) -------------------------- */
+#define SMALL_MAX_BYTES ((uint64_t)SMALL_MAX_TILES * OWN)
+#define SMALL_MAX_DOCS 2048u
+#define HUT_SMALL_RETRY (-1) /* the general path has to do it */
+
+static int encode_small(hut_ctx* ctx, const uint8_t* bytes, const uint64_t* doc_offsets, uint64_t n_docs,
+                        hut_result* result) {
+    hut_dev* d = &ctx->dev[0];
+    hut_flight* f = &d->fl[0];
+    const uint64_t b0 = doc_offsets[0], nb = doc_offsets[n_docs] - b0;
+    CU(ctx, cudaSetDevice(d->device));
+    if (!d->sm_text) {
+        CU(ctx, cudaMallocHost(&d->sm_text, SMALL_MAX_BYTES + 256));
+        CU(ctx, cudaMallocHost(&d->sm_off, (SMALL_MAX_DOCS + 2) * sizeof(unsigned long long)));
+        CU(ctx, cudaMallocHost(&d->sm_ctr, offsetof(Counters, events)));
+        CU(ctx, cudaMallocHost((void**)&d->sm_done, 64));
+        *d->sm_done = 0;
+        d->sm_seq = 0;
+    }
+    const uint32_t ntiles = (uint32_t)((nb + OWN - 1) / OWN);
+    const uint64_t worst = nb * d->dm.kmax + n_docs * (uint64_t)(d->dm.n_prefix_syms + d->dm.n_prefix_alone) + 64;
+    {
+        cudaError_t e = grow_host(&ctx->h_ids, &ctx->h_ids_cap, (size_t)worst, false);
+        if (e == cudaSuccess) e = grow_host(&ctx->h_tok, &ctx->h_tok_cap, (size_t)n_docs + 1, false);
+        if (e != cudaSuccess) return set_err(ctx, HUT_STATUS_CUDA, "CUDA error: %s", cudaGetErrorString(e));
+    }
+    CU(ctx, grow(&d->stage, &d->stage_cap, (size_t)ntiles * d->stride + (size_t)n_docs * d->slot_extra + 64));
+    CU(ctx, grow(&f->tilebuf, &f->tilebuf_cap, 6 * ((size_t)ntiles + 1) + 4));
+    CU(ctx, grow(&f->bsum, &f->bsum_cap, 1));
+    CU(ctx, grow(&f->def, &f->def_cap, 1024));
+    memcpy(d->sm_text, bytes + b0, nb);
+    memset(d->sm_text + nb, 0, 128);
+    for (uint64_t i = 0; i <= n_docs; ++i) d->sm_off[i] = doc_offsets[i] - b0;
+    Job J;
+    memset(&J, 0, sizeof J);
+    J.text = d->sm_text;
+    J.nbytes = nb;
+    J.doc_off = d->sm_off;
+    J.ndocs = n_docs;
+    J.out = ctx->h_ids;
+    J.out_cap = ctx->h_ids_cap;
+    J.tok_off = ctx->h_tok;
+    J.ntiles = ntiles;
+    J.stride = d->stride;
+    J.slot_extra = d->slot_extra;
+    J.slot_off = reinterpret_cast<unsigned long long*>(f->tilebuf + 4 * ((size_t)ntiles + 1));
+    J.stage = d->stage;
+    J.cnt = f->tilebuf;
+    J.tot = J.cnt + ((size_t)ntiles + 1);
+    J.first_doc = J.tot + ((size_t)ntiles + 1);
+    J.def_first = J.first_doc + ((size_t)ntiles + 1);
+    J.bsum = f->bsum;
+    J.nblocks = 1;
+    J.def = f->def;
+    J.def_cap = (uint32_t)f->def_cap;
+    J.ctr = f->ctr;
+    J.cache = d->cache;
+    J.cache_bits = d->cache_bits;
+    J.cache2 = d->cache2;
+    J.cache2_bits = d->cache2_bits;
+    const unsigned int seq = ++d->sm_seq;
+    if (d->dm.has_prefix) small_kernel<true><<<1, NT, 0, d->stream>>>(d->dm, J, d->sm_ctr, d->sm_done, seq);
+    else small_kernel<false><<<1, NT, 0, d->stream>>>(d->dm, J, d->sm_ctr, d->sm_done, seq);
+    CU(ctx, cudaGetLastError());
+    // the kernel writes `done` last (after a system-wide fence): spinning on it is cheaper than a stream synchronize
+    for (unsigned spins = 0; *d->sm_done != seq; ++spins) {
+        if ((spins & 0xFFFFu) == 0xFFFFu) {
+            cudaError_t e = cudaStreamQuery(d->stream);
+            if (e != cudaSuccess && e != cudaErrorNotReady)
+                return set_err(ctx, HUT_STATUS_CUDA, "CUDA error: %s", cudaGetErrorString(e));
+            if (e == cudaSuccess && *d->sm_done != seq)
+                return set_err(ctx, HUT_STATUS_CUDA, "%s", "small_kernel ended without reporting");
+        }
+    }
+    const Counters* c = d->sm_ctr;
+    if (c->flags & SMALL_FALLBACK) return HUT_SMALL_RETRY;
+    stats_begin(d);
+    d->stats.pretokens = c->st_pretokens;
+    d->stats.cache_hits = c->st_hits;
+    d->stats.warp_merges = c->st_warp;
+    d->stats.kernel_launches = 1;
+    if (c->flags & FLAG_NUL)
+        return set_err(ctx, HUT_STATUS_VALUE, "%s", "document contains a 0x00 byte (cut documents at NUL before calling)");
+    result->ids = ctx->h_ids;
+    result->tok_offsets = (const uint64_t*)ctx->h_tok;
+    result->n_ids = c->total_ids;
+    result->n_docs = n_docs;
+    return HUT_STATUS_OK;
+}
+
 extern "C" int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64_t* doc_offsets, uint64_t n_docs,
                                 hut_result* result) {
     if (!ctx) return HUT_STATUS_STATE;
@@ -679,6 +785,10 @@ extern "C" int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64
     for (uint64_t i = 0; i < n_docs; ++i)  // decreasing offsets would underflow every byte count below
         if (doc_offsets[i] > doc_offsets[i + 1]) return set_err(ctx, HUT_STATUS_ARG, "%s", "doc_offsets must be non-decreasing");
     const uint64_t total_bytes = doc_offsets[n_docs] - doc_offsets[0];
+    if (total_bytes && total_bytes <= SMALL_MAX_BYTES && n_docs <= SMALL_MAX_DOCS && !getenv("HUTOKEN_B200_NO_SMALL")) {
+        const int rc = encode_small(ctx, bytes, doc_offsets, n_docs, result);
+        if (rc != HUT_SMALL_RETRY) return rc;
+    }
     // ---- plan: contiguous document ranges balanced by bytes (hut_plan_shards), dealt round-robin to the devices;
     //      every device works on two chunks at a time: upload of chunk k+1 | kernels of chunk k | download of k-1 ----
     const int ndev = ctx->ndev;

@@ -20,19 +20,18 @@ __global__ void init_kernel(Job J) {
 }
 
 // first_doc[t] = first document starting inside tile t (pre-set to NODOC)
-__global__ void doc_kernel(Job J) {
-    const unsigned long long d = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void doc_first(const Job& J, unsigned long long d) {
     if (d >= J.ndocs) return;
     const unsigned long long pos = J.doc_off[d];
     if (pos >= J.nbytes) return;
     const unsigned long long t = pos / OWN;
     if (d == 0 || J.doc_off[d - 1] / OWN != t) J.first_doc[t] = (uint32_t)d;
 }
+__global__ void doc_kernel(Job J) { doc_first(J, (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x); }
 
 // start of every tile's staging slot: tile * stride, plus slot_extra ids for each document starting before the tile
 // (lower bound of the tile's first byte in doc_off) for a prefix model; see stage_slot()
-__global__ void slot_docs_kernel(Job J, unsigned long long* out) {
-    const unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void slot_docs(const Job& J, unsigned long long* out, unsigned long long t) {
     if (t > J.ntiles) return;
     unsigned long long a = 0;
     if (J.slot_extra) {
@@ -45,6 +44,9 @@ __global__ void slot_docs_kernel(Job J, unsigned long long* out) {
         }
     }
     out[t] = t * J.stride + a * J.slot_extra;
+}
+__global__ void slot_docs_kernel(Job J, unsigned long long* out) {
+    slot_docs(J, out, (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -353,9 +355,8 @@ __device__ __forceinline__ void compact_tile_holes(const Job& J, uint32_t tile, 
 
 // staging slots -> dense ids (warp per tile); drops the HOLEs left by deferred cache misses and splices in the ids
 // of the pretokens long_kernel merged
-__global__ void __launch_bounds__(256, 8) compact_kernel(const Job J) {
+__device__ __forceinline__ void compact_tiles(const Job& J, const uint32_t gw, const uint32_t nw) {
     const uint32_t lane = threadIdx.x & 31;
-    const uint32_t gw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), nw = gridDim.x * (blockDim.x >> 5);
     for (uint32_t tile = gw; tile < J.ntiles; tile += nw) {
         const uint32_t c = J.cnt[tile];
         const uint32_t ns = c & CNT_MASK;
@@ -394,9 +395,12 @@ __global__ void __launch_bounds__(256, 8) compact_kernel(const Job J) {
     }
 }
 
+__global__ void __launch_bounds__(256, 8) compact_kernel(const Job J) {
+    compact_tiles(J, blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), gridDim.x * (blockDim.x >> 5));
+}
+
 // tile-local document offsets -> global ones
-__global__ void fixdoc_kernel(const Job J) {
-    const unsigned long long d = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void fixdoc_doc(const Job& J, unsigned long long d) {
     if (d > J.ndocs) return;
     const unsigned long long total = J.ctr->total_ids;
     const unsigned long long pos = d < J.ndocs ? J.doc_off[d] : J.nbytes;
@@ -419,6 +423,68 @@ __global__ void fixdoc_kernel(const Job J) {
         for (uint32_t idx = J.def_first[t]; idx != NODOC; idx = J.def[idx].pad)
             if (J.def[idx].pos < pos) v += J.def[idx].count;
     J.tok_off[d] = v;
+}
+__global__ void fixdoc_kernel(const Job J) { fixdoc_doc(J, (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x); }
+
+// ------------------------------------------------------------------------------------------------
+// small_kernel: the whole pipeline for a SMALL batch (a sentence, a handful of short documents) in ONE launch of one
+// CTA -- what hutoken.encode(text) costs is launch latency, not throughput (the reference's own check of this path is a
+// per-call bound, tests/test_tokenizer.py:107-130).  Text, offsets, ids and counters live in pinned host memory the
+// device reads and writes directly, so there is no copy either; the host waits on `done`.  Anything the one CTA does
+// not do itself (pretokens handed to long_kernel) makes it give up: the host then takes the general path.
+// ------------------------------------------------------------------------------------------------
+constexpr uint32_t SMALL_MAX_TILES = 72;  // 69 120 bytes
+constexpr uint32_t SMALL_FALLBACK = 0x80000000u;
+
+template <bool PFX>
+__global__ void __launch_bounds__(NT, 1) small_kernel(const __grid_constant__ DevModel M, const __grid_constant__ Job J,
+                                                      Counters* h_ctr, volatile unsigned int* done, unsigned int seq) {
+    __shared__ TileSm sm;
+    const uint32_t tid = threadIdx.x;
+    if (tid == 0) {
+        Counters* c = J.ctr;
+        c->flags = 0;
+        c->n_events = 0;
+        c->n_def = 0;
+        c->total_ids = 0;
+        c->long_used = 0;
+        c->st_pretokens = c->st_hits = c->st_warp = c->st_block = c->st_big = c->st_cut = 0;
+    }
+    for (uint32_t t = tid; t <= J.ntiles; t += NT) J.first_doc[t] = NODOC;
+    __syncthreads();
+    for (unsigned long long d = tid; d < J.ndocs; d += NT) doc_first(J, d);
+    if (PFX)
+        for (uint32_t t = tid; t <= J.ntiles; t += NT) slot_docs(J, const_cast<unsigned long long*>(J.slot_off), t);
+    __syncthreads();
+    tile_body<PFX>(M, J, sm, tid >> 5, WPB);
+    __syncthreads();
+    const bool give_up = J.ctr->n_def != 0 || (J.ctr->flags & ~(unsigned)FLAG_NUL) != 0;
+    if (!give_up) {
+        if (tid == 0) {  // exclusive scan of the (few) per-tile id counts, in place like scan1 / scan2
+            unsigned long long run = 0;
+            for (uint32_t t = 0; t < J.ntiles; ++t) {
+                const uint32_t v = J.tot[t];
+                J.tot[t] = (uint32_t)run;
+                run += v;
+            }
+            J.bsum[0] = 0;
+            J.ctr->total_ids = run;
+        }
+        __syncthreads();
+        compact_tiles(J, tid >> 5, WPB);
+        for (unsigned long long d = tid; d <= J.ndocs; d += NT) fixdoc_doc(J, d);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        const Counters* c = J.ctr;
+        h_ctr->flags = c->flags | (give_up ? SMALL_FALLBACK : 0u);
+        h_ctr->total_ids = c->total_ids;
+        h_ctr->st_pretokens = c->st_pretokens;
+        h_ctr->st_hits = c->st_hits;
+        h_ctr->st_warp = c->st_warp;
+        __threadfence_system();
+        *done = seq;
+    }
 }
 
 // ------------------------------------------------------------------------------------------------

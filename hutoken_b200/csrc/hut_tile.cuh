@@ -219,9 +219,7 @@ __device__ __forceinline__ void rare_round(const DevModel& M, const Job& J, Tile
 // PFX: the model has a prefix (first pretoken of a document keyed apart and merged with the prefix symbols; staging
 // slots of uneven size read from J.slot_off); without one the slot of a tile is tile * stride.
 template <bool PFX>
-__global__ void __launch_bounds__(NT, HUT_TILE_CTAS) tile_kernel(const __grid_constant__ DevModel M,
-                                                                 const __grid_constant__ Job J) {
-    __shared__ TileSm sm;
+__device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileSm& sm, const uint32_t gw, const uint32_t nw) {
     const int tid = threadIdx.x, warp = tid >> 5;
     int lane;  // read once from the special register (kept from being recomputed from %tid inside the loops)
     asm volatile("mov.u32 %0, %%laneid;" : "=r"(lane));
@@ -248,7 +246,6 @@ __global__ void __launch_bounds__(NT, HUT_TILE_CTAS) tile_kernel(const __grid_co
     uint32_t parity = 0;
     if (lane == 0) ws.qn = ws.st_pre = ws.st_miss = ws.st_def = 0;
     __syncwarp();
-    const uint32_t gw = blockIdx.x * WPB + warp, nw = gridDim.x * WPB;
 
     for (uint32_t tile = gw; tile < J.ntiles; tile += nw) {
         unsigned long long slot_o = 0;
@@ -495,6 +492,13 @@ __global__ void __launch_bounds__(NT, HUT_TILE_CTAS) tile_kernel(const __grid_co
         if (st_def) atomicAdd(&c->st_block, st_def);
         if (st_miss) atomicAdd(&c->st_warp, st_miss);
     }
+}
+
+template <bool PFX>
+__global__ void __launch_bounds__(NT, HUT_TILE_CTAS) tile_kernel(const __grid_constant__ DevModel M,
+                                                                 const __grid_constant__ Job J) {
+    __shared__ TileSm sm;
+    tile_body<PFX>(M, J, sm, blockIdx.x * WPB + (threadIdx.x >> 5), gridDim.x * WPB);
 }
 
 }  // namespace hut
