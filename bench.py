@@ -537,7 +537,7 @@ def run_ours(args):
             raise SystemExit(f"bench.py: rank {rank}: GPU ids differ from the oracle on the first {check_bytes} bytes")
 
     # ---- max over ranks / whole-job sums ----
-    from hutoken_b200 import dist as D
+    import dist_torch as D  # tools/dist_torch.py: torch.distributed plumbing (the product package imports no PyTorch)
 
     def allmax(x):
         return D.all_reduce_scalar(x, "max", dev)

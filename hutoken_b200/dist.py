@@ -3,8 +3,8 @@ per-shard results become one global result.
 
 Replaces the reference's mutex-guarded "next document" counter shared by worker threads (taskqueue.c:16-35,
 lib.c:779-794).  Shards are independent, so nothing crosses ranks on the data path; the only exchange is one
-integer per rank (its id count) to rebase the per-shard offsets.  torch.distributed is plumbing
-here (gloo on CPU, nccl on GPUs); no tensor of ids ever goes through it unless the caller asks for a gather.
+integer per rank (its id count) to rebase the per-shard offsets.  Nothing here imports PyTorch: the
+torch.distributed plumbing of the bench and of the multi-process tests lives in tools/dist_torch.py.
 """
 from __future__ import annotations
 
@@ -55,35 +55,3 @@ def rebase_offsets(shard_tok_offsets, shard_n_ids):
         base += int(n)
     out.append(np.array([base], dtype=np.uint64))
     return np.concatenate(out)
-
-
-def all_reduce_scalar(x, op="max", device=None):
-    """max / sum of one float over all ranks (the bench's max-over-ranks timing and whole-job totals)."""
-    import torch
-    import torch.distributed as dist
-    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
-        return float(x)
-    t = torch.tensor([float(x)], dtype=torch.float64, device=device if device is not None else "cpu")
-    dist.all_reduce(t, op=dist.ReduceOp.MAX if op == "max" else dist.ReduceOp.SUM)
-    return float(t.item())
-
-
-def gather_counts(n_ids, device=None):
-    """Every rank's id count, on every rank: the only data-dependent value shards have to exchange."""
-    import torch
-    import torch.distributed as dist
-    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
-        return [int(n_ids)]
-    t = torch.tensor([int(n_ids)], dtype=torch.int64, device=device if device is not None else "cpu")
-    outs = [torch.zeros_like(t) for _ in range(dist.get_world_size())]
-    dist.all_gather(outs, t)
-    return [int(o.item()) for o in outs]
-
-
-def global_offsets(local_tok_offsets, n_ids, device=None):
-    """This rank's token offsets rebased into the whole job's id space (+ the job's total id count)."""
-    import torch.distributed as dist
-    counts = gather_counts(n_ids, device)
-    rank = dist.get_rank() if (dist.is_available() and dist.is_initialized()) else 0
-    base = sum(counts[:rank])
-    return np.asarray(local_tok_offsets, dtype=np.uint64) + np.uint64(base), sum(counts)

@@ -60,10 +60,11 @@ def _worker(rank, world, port, name, seed, q):
         orc = oracle_for(name)
         sdata, soffs, first_doc = D.local_shard(data, offs, rank, world)
         ids, tok = orc.encode_packed(np.concatenate([sdata, np.zeros(16, np.uint8)]), soffs)
-        gtok, total = D.global_offsets(tok, len(ids))
+        import dist_torch as DT
+        gtok, total = DT.global_offsets(tok, len(ids))
         # the bench's reductions: max-over-ranks of a time, sum of the units
-        tmax = D.all_reduce_scalar(1.0 + rank, "max")
-        bsum = D.all_reduce_scalar(float(len(sdata)), "sum")
+        tmax = DT.all_reduce_scalar(1.0 + rank, "max")
+        bsum = DT.all_reduce_scalar(float(len(sdata)), "sum")
         q.put((rank, first_doc, ids, gtok, total, tmax, bsum))
     finally:
         dist.barrier()
