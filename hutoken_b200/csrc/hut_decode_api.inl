@@ -58,14 +58,33 @@ static void dec_free(hut_decstate* s) {
     free(s);
 }
 
+static int dec_init_tables(hut_ctx* ctx, hut_decstate* s);
+
+/* decode-side device state, created by the first hut_decode_* call.  A failure half way leaves nothing behind: the
+ * tables uploaded so far are released (they are the newest entries of the device's allocation list) and the next call
+ * starts again from scratch. */
 static int dec_init(hut_ctx* ctx) {
     if (ctx->dec && ctx->dec->ready) return HUT_STATUS_OK;
     hut_dev* d = &ctx->dev[0];
-    const hut_model* m = ctx->model;
     CU(ctx, cudaSetDevice(d->device));
     if (!ctx->dec) ctx->dec = (hut_decstate*)calloc(1, sizeof(hut_decstate));
     if (!ctx->dec) return set_err(ctx, HUT_STATUS_MEMORY, "%s", "out of memory");
     hut_decstate* s = ctx->dec;
+    const int first = d->nalloc;
+    const int rc = dec_init_tables(ctx, s);
+    if (rc != HUT_STATUS_OK) {
+        while (d->nalloc > first) cudaFree(d->allocs[--d->nalloc]);
+        cudaFree(s->d_bad);
+        if (s->ev[0]) cudaEventDestroy(s->ev[0]);
+        if (s->ev[1]) cudaEventDestroy(s->ev[1]);
+        memset(s, 0, sizeof *s);
+    }
+    return rc;
+}
+
+static int dec_init_tables(hut_ctx* ctx, hut_decstate* s) {
+    hut_dev* d = &ctx->dev[0];
+    const hut_model* m = ctx->model;
     DecModel& D = s->dm;
     CU(ctx, upload(d, m->dec_off, (size_t)m->vocab_lines + 1, &D.dec_off));
     CU(ctx, upload(d, m->dec_len, (size_t)m->vocab_lines, &D.dec_len));

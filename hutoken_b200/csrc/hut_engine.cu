@@ -123,10 +123,11 @@ static int set_err(hut_ctx* ctx, int status, const char* fmt, const char* a) {
 template <class T>
 static cudaError_t upload(hut_dev* d, const T* src, size_t n, const T** out) {
     T* p = nullptr;
+    if (d->nalloc >= (int)(sizeof d->allocs / sizeof d->allocs[0])) return cudaErrorMemoryAllocation;  // list full
     cudaError_t e = cudaMalloc(&p, (n ? n : 1) * sizeof(T));
     if (e != cudaSuccess) return e;
-    if (n) e = cudaMemcpy(p, src, n * sizeof(T), cudaMemcpyHostToDevice);
     d->allocs[d->nalloc++] = p;
+    if (n) e = cudaMemcpy(p, src, n * sizeof(T), cudaMemcpyHostToDevice);
     *out = p;
     return e;
 }
@@ -210,7 +211,8 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     d->grid = per_sm * sms;
     {   // long_kernel walks its pretokens one merge at a time: many small CTAs in flight hide that latency
         int per = 0;
-        CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, long_kernel, LNT, 0));
+        CU(ctx, cudaFuncSetAttribute(long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(4 * LSM_CAP * sizeof(uint32_t))));
+        CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, long_kernel, LNT, 4 * LSM_CAP * sizeof(uint32_t)));
         if (per < 1) per = 1;
         if (per > 8) per = 8;
         d->long_grid = per * sms;
@@ -450,7 +452,7 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     if (pfx) tile_kernel<true><<<tile_grid, NT, 0, st>>>(d->dm, J);
     else tile_kernel<false><<<tile_grid, NT, 0, st>>>(d->dm, J);
     CU(ctx, cudaEventRecord(f->ev[2], st));
-    long_kernel<<<d->long_grid, LNT, 0, st>>>(d->dm, J);
+    long_kernel<<<d->long_grid, LNT, 4 * LSM_CAP * sizeof(uint32_t), st>>>(d->dm, J);
     if (d->big_slots) huge_kernel<<<d->big_slots, HNT, 0, st>>>(d->dm, J);
     scan1_kernel<<<nblocks, 1024, 0, st>>>(J);
     scan2_kernel<<<1, 1024, 0, st>>>(J);

@@ -56,7 +56,9 @@ constexpr int CACHE_PROBES = 8;
 constexpr int CACHE_IDS = 5;          // most ids a cache value holds
 constexpr int MAX_EVENTS = 1024;
 constexpr int SCAN_BLK = 4096;        // tiles per scan block
-constexpr int LNT = 128;              // threads per CTA of long_kernel (pretokens of up to med_cap symbols)
+constexpr int LNT = 128;              // threads per CTA of long_kernel (pretokens of up to med_cap symbols); measured on the
+                                      // heavy-tail mix: 8 CTAs of 128 per SM 8.6 ms, 16 of 32 10.1 ms, 2 of 128 13.2 ms
+constexpr int LSM_CAP = 4096;         // symbols of a pretoken whose working arrays long_kernel keeps in shared memory
 constexpr int HNT = 1024;             // threads per CTA of huge_kernel (longer ones: cooperative rounds)
 constexpr int LMAXW = 32;             // most warps a CTA of the long path has
 constexpr int MISS_SMALL = 32;        // most initial symbols of a cache miss tile_kernel merges itself (one lane each)

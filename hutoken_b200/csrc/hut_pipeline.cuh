@@ -64,7 +64,8 @@ __device__ __forceinline__ void long_entries(const DevModel& M, const Job& J, Lo
     if (n > J.def_cap) n = J.def_cap;
     uint32_t* const scratch = HUGE ? J.big_pool + (unsigned long long)blockIdx.x * J.big_slot_words
                                    : J.cta_scratch + (unsigned long long)blockIdx.x * J.cta_scratch_words;
-    const uint32_t cap = HUGE ? J.big_cap : J.med_cap;
+    const uint32_t cap_g = HUGE ? J.big_cap : J.med_cap;
+    extern __shared__ __align__(16) uint32_t long_dyn[];  // long_kernel: 4 * LSM_CAP words
     unsigned long long n_big = 0;
     for (uint32_t e = blockIdx.x; e < n; e += gridDim.x) {
         DefEntry* E = J.def + e;
@@ -121,7 +122,11 @@ __device__ __forceinline__ void long_entries(const DevModel& M, const Job& J, Lo
                 continue;
             }
         }
-        uint32_t* U = scratch;
+        // a pretoken of up to LSM_CAP symbols (most of them) has its arrays and its whole tree in shared memory: every
+        // merge is a chain of a dozen dependent accesses, so their latency is what it costs
+        const bool in_sm = !HUGE && (ge - gs) * M.kmax + M.n_prefix_syms <= (unsigned long long)LSM_CAP;
+        const uint32_t cap = in_sm ? (uint32_t)LSM_CAP : cap_g;
+        uint32_t* U = in_sm ? long_dyn : scratch;
         uint32_t* MG = U + cap;
         uint32_t* NX = MG + cap;
         uint32_t* PV = NX + cap;

@@ -24,20 +24,22 @@ def _ext():
 
 
 def initialize(model_or_path, *args, **kwargs):
-    """initialize(vocab_path, special_chars_path, prefix=None, is_byte_encoder=False, token_id=-1, pattern=None)"""
+    """initialize(vocab_path, special_chars_path, prefix=None, is_byte_encoder=False, token_id=-1, pattern=None,
+    merges_file=None).  merges_file (keyword, or the 7th positional argument after the vocab path like the
+    reference's hub branch passes it, hutoken.py:112) switches to id-keyed ranks (core.c:211-337)."""
     ext = _ext()
     if not os.path.isfile(model_or_path):
         raise ValueError(f"'{model_or_path}' is not a vocab file; Hugging Face model names are not supported "
                          "by the B200 engine (no network): convert the tokenizer to hutoken's vocab format first.")
     special_chars_file = args[0] if args else kwargs.get("special_file_path")
-    merges_file = args[6] if len(args) > 6 else None
+    merges_file = args[6] if len(args) > 6 else kwargs.get("merges_file", kwargs.get("merges_file_path"))
     if special_chars_file and not os.path.isfile(special_chars_file):
         raise ValueError(f"Special characters file '{special_chars_file}' does not exist.")
     if merges_file and not os.path.isfile(merges_file):
         raise ValueError(f"The provided merges file '{merges_file}' does not exist.")
     return ext.initialize(model_or_path, special_chars_file, kwargs.get("prefix"),
                           kwargs.get("is_byte_encoder", False), kwargs.get("token_id", -1),
-                          kwargs.get("pattern"))
+                          kwargs.get("pattern"), merges_file)
 
 
 def encode(text):

@@ -5,7 +5,7 @@
  * map, explicit binary heap on malloc'd storage, no arena, no VLAs), same observable results inside the
  * reference's defined domain.  Reference citations (matyasosvath/hutoken @ 2d23def) are given per function.
  *
- * Pinning: tests/test_oracle_vs_ref.py runs this file against the UNMODIFIED reference compiled into
+ * Pinning: tests/test_oracle_golden.py runs this file against the UNMODIFIED reference compiled into
  * oracle/_ref on randomised inputs, and tests/golden/ holds vectors produced by that reference.
  */
 #define _GNU_SOURCE

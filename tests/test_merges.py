@@ -200,6 +200,10 @@ def test_gpu_merges_python_surface():
     orc = _oracle(name)
     texts = ["hello world", " árvíztűrő tükörfúrógép 123", "x\n\ny"]
     assert [ext.encode(t) for t in texts] == orc.batch_encode(texts)
+    # the Python shim forwards merges_file too (keyword here; the reference's hub branch passes it positionally)
+    import hutoken_b200 as hutoken
+    hutoken.initialize(v, s, is_byte_encoder=True, merges_file=synth.MERGES[name])
+    assert [hutoken.encode(t) for t in texts] == orc.batch_encode(texts)
     assert ext.batch_encode(texts, 4) == orc.batch_encode(texts)
     with pytest.raises(FileNotFoundError, match="Could not open merges file."):
         ext.initialize(v, s, None, True, merges_file_path="/nonexistent/merges.txt")
