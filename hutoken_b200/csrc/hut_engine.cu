@@ -494,6 +494,11 @@ static int finish_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, uint64_t n_docs
                               (uint64_t*)J.tok_off, st, def_want, long_want);
         if (rc != HUT_STATUS_OK) return rc;
     }
+#ifdef HUT_LONGSTAT
+    if (c->st_big)
+        fprintf(stderr, "hut longstat: rounds at once %llu (prefix only %llu), merges applied at once %llu, stretches %llu\n",
+                c->lp[0], c->lp[3], c->lp[2], c->lp[1]);
+#endif
     float ms_all = 0, ms_main = 0;
     cudaEventElapsedTime(&ms_all, f->ev[0], f->ev[3]);
     cudaEventElapsedTime(&ms_main, f->ev[1], f->ev[2]);

@@ -118,6 +118,10 @@ struct Counters {
     unsigned long long total_ids;
     unsigned long long long_used;  // bump pointer into long_ids
     unsigned long long st_pretokens, st_hits, st_warp, st_block, st_big, st_cut;
+#ifdef HUT_LONGSTAT
+    unsigned long long lp[4];      // huge_kernel: rounds applied at once, rounds replaced by a stretch, merges applied at
+                                   // once, rounds that applied a prefix only (build switch, not shipped)
+#endif
     CutEvent events[MAX_EVENTS];
 };
 
@@ -688,6 +692,7 @@ struct LongSm {
     unsigned long long ids_off;
     uint32_t slot;
     uint32_t na, nb, nd, chain;  // cooperative rounds: list lengths, "a chain was too long to walk" flag
+    uint32_t first_bad, nkeep;   // leftmost occurrence whose merge would create a pair that jumps the queue; applied ones
 };
 
 // block-wide exclusive scan of one uint32 per thread; returns exclusive prefix, *total = sum
@@ -891,16 +896,22 @@ __device__ uint32_t cta_merge_run(const DevModel& M, const Job& J, LongSm& sm, u
     auto pop_one = [&](uint32_t i) {
         uint32_t p = ENDLINK, j = ENDLINK;
         if (lane == 0) {
+            // loads first, as few in a row as the links allow (every one of them is an L2 round trip), then the stores
             j = NX[i];
-            U[i] = MG[i];
+            const uint32_t mi = MG[i];
+            p = PV[i];
+            const uint32_t nj = NX[j];
+            const uint32_t up = p != ENDLINK ? U[p] : NONE;
+            const uint32_t unj = nj != ENDLINK ? U[nj] : NONE;
+            U[i] = mi;
             U[j] = ENDLINK;  // dead
             MG[j] = NONE;
-            const uint32_t nj = NX[j];
             NX[i] = nj;
             if (nj != ENDLINK) PV[nj] = i;
-            p = PV[i];
-            if (p != ENDLINK) MG[p] = pair_probe(M, U[p], U[i]);
-            MG[i] = (nj != ENDLINK) ? pair_probe(M, U[i], U[nj]) : NONE;
+            uint32_t ml, mr;
+            pair_probe2(M, up, mi, unj, &ml, &mr);  // both new neighbour pairs, probed together
+            if (p != ENDLINK) MG[p] = ml;
+            MG[i] = mr;  // NONE when i is the last symbol now
         }
         p = __shfl_sync(0xFFFFFFFFu, p, 0);
         j = __shfl_sync(0xFFFFFFFFu, j, 0);
@@ -993,6 +1004,8 @@ __device__ uint32_t cta_merge_run(const DevModel& M, const Job& J, LongSm& sm, u
                 LA[0] = 0u;
                 sm.na = 1u;
                 sm.chain = 0u;
+                sm.first_bad = ENDLINK;
+                sm.nkeep = 0u;
             }
             __syncthreads();
             for (int l = top; l >= 0; --l) {
@@ -1036,11 +1049,13 @@ __device__ uint32_t cta_merge_run(const DevModel& M, const Job& J, LongSm& sm, u
                 if (steps & 1u) LA[k] = ENDLINK;  // dropped
             }
             __syncthreads();
-            // ---- is it safe to apply them all at once?  Going left to right, the single-lane order would create for
-            // each of them the pairs (left neighbour, merged) and (merged, right neighbour); if all of these rank above
-            // rmin, none of them is touched before the round's last merge and the result is the same.  With monotone
-            // ranks that always holds; otherwise it is checked here (the left neighbour is the merged unit of the
-            // occurrence before it when that one ends right before this one). ----
+            // ---- which of them can be applied at once?  Going left to right, the single-lane order would create for
+            // each of them the pairs (left neighbour, merged) and (merged, right neighbour); as long as these rank above
+            // rmin nothing else is touched before the next occurrence is merged, so the result is the same.  With
+            // monotone ranks that always holds; otherwise it is checked here (the left neighbour is the merged unit of
+            // the occurrence before it when that one ends right before this one) and the round applies only the
+            // occurrences LEFT of the first one that fails -- a prefix of the reference's own order -- and then hands
+            // that one to the single-lane step. ----
             if (!M.monotone && !sm.chain) {
                 for (uint32_t k = tid; k < np; k += LNT) {
                     const uint32_t p = LA[k];
@@ -1061,13 +1076,27 @@ __device__ uint32_t cta_merge_run(const DevModel& M, const Job& J, LongSm& sm, u
                     }
                     uint32_t ml, mr;
                     pair_probe2(M, left, mu, right, &ml, &mr);
-                    if (rank_of_unit(M, ml) <= rmin || rank_of_unit(M, mr) <= rmin) sm.chain = 1u;
+                    if (rank_of_unit(M, ml) <= rmin || rank_of_unit(M, mr) <= rmin) atomicMin(&sm.first_bad, p);
                 }
                 __syncthreads();
+                const uint32_t fb = sm.first_bad;
+                if (fb != ENDLINK) {
+                    uint32_t kept = 0;
+                    for (uint32_t k = tid; k < np; k += LNT) {
+                        const uint32_t p = LA[k];
+                        if (p == ENDLINK) continue;
+                        if (p >= fb) LA[k] = ENDLINK;
+                        else ++kept;
+                    }
+                    if (kept) atomicAdd(&sm.nkeep, kept);
+                    __syncthreads();
+                }
             }
-            if (sm.chain) {
-                // a very long chain (e.g. a run of one letter) or a pair that would jump the queue: a stretch of exact
-                // single-lane steps, then the next round looks again
+            const bool partial = sm.first_bad != ENDLINK;
+            const uint32_t nkeep = sm.nkeep;
+            if (sm.chain || (partial && nkeep == 0u)) {
+                // a very long chain (e.g. a run of one letter), or the leftmost occurrence itself would create a pair
+                // that jumps the queue: a stretch of exact single-lane steps, then the next round looks again
                 if (warp == 0)
                     for (uint32_t it = 0; it < stretch; ++it) {
                         const unsigned long long b = root();
@@ -1075,9 +1104,19 @@ __device__ uint32_t cta_merge_run(const DevModel& M, const Job& J, LongSm& sm, u
                         pop_one((uint32_t)b);
                     }
                 if (stretch < 65536u) stretch *= 2u;
+#ifdef HUT_LONGSTAT
+                if (tid == 0) atomicAdd(&J.ctr->lp[1], 1ull);
+#endif
                 continue;
             }
-            stretch = 64;
+            if (!partial || nkeep >= 32u) stretch = 64;
+#ifdef HUT_LONGSTAT
+            if (tid == 0) {
+                atomicAdd(&J.ctr->lp[0], 1ull);
+                atomicAdd(&J.ctr->lp[2], (unsigned long long)(partial ? nkeep : np));
+                if (partial) atomicAdd(&J.ctr->lp[3], 1ull);
+            }
+#endif
             // ---- apply all at once (no two of them share a symbol) ----
             for (uint32_t k = tid; k < np; k += LNT) {
                 const uint32_t p = LA[k];
@@ -1134,6 +1173,10 @@ __device__ uint32_t cta_merge_run(const DevModel& M, const Job& J, LongSm& sm, u
                     }
                 }
                 __syncthreads();
+            }
+            if (partial && warp == 0) {  // the occurrence that failed the check is the root now: the single-lane step
+                const unsigned long long b = root();
+                if (b != ~0ull && (uint32_t)(b >> 32) == rmin) pop_one((uint32_t)b);
             }
         }
     }

@@ -16,6 +16,9 @@ __global__ void init_kernel(Job J) {
         c->total_ids = 0;
         c->long_used = 0;
         c->st_pretokens = c->st_hits = c->st_warp = c->st_block = c->st_big = c->st_cut = 0;
+#ifdef HUT_LONGSTAT
+        c->lp[0] = c->lp[1] = c->lp[2] = c->lp[3] = 0;
+#endif
     }
 }
 
@@ -131,10 +134,10 @@ __device__ __forceinline__ void long_entries(const DevModel& M, const Job& J, Lo
         uint32_t* NX = MG + cap;
         uint32_t* PV = NX + cap;
         // tournament-tree levels behind the four arrays (8-byte aligned; cap / 8 words are plenty), then -- huge_kernel
-        // with a monotone model only -- the lists of the cooperative rounds
+        // only -- the lists of the cooperative rounds
         unsigned long long* T = reinterpret_cast<unsigned long long*>(
             (reinterpret_cast<uintptr_t>(PV + cap) + 7u) & ~(uintptr_t)7u);
-        uint32_t* X = (HUGE && M.monotone) ? reinterpret_cast<uint32_t*>(T) + (cap / 8u + 64u) : nullptr;
+        uint32_t* X = HUGE ? reinterpret_cast<uint32_t*>(T) + (cap / 8u + 64u) : nullptr;
         uint32_t m = 0;
         uint32_t cnt = cta_merge_run(M, J, sm, gs, ge, with_prefix, alone_first, U, MG, NX, PV, T, cap, &m, X);
         if (cnt == 0xFFFFFFFFu) {

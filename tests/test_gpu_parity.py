@@ -195,6 +195,34 @@ def test_no_limit_cooperative_rounds(name):
     orc.close()
 
 
+@pytest.mark.parametrize("byte_mode", [True, False])
+def test_no_limit_rounds_on_adversarial_ranks(byte_mode):
+    """huge_kernel on random vocabularies whose ranks are NOT monotone (a merge may create a pair that ranks below the
+    round's rank): the rounds must notice (the check of the created pairs), apply only the occurrences left of the
+    first offender and hand that one to the single-lane step.  Long runs over the models' small alphabets, string-keyed
+    ranks and merges-file ranks, against the oracle's no-limit mode."""
+    from hutoken_b200 import capi
+    from oracle import oracle as O
+    import os
+    tmp = tempfile.mkdtemp()
+    for seed in range(10):
+        rng = random.Random(4000 + seed)
+        v, s, kw = F.random_model(rng, tmp, byte_mode, f"h{seed}")
+        mp = F.random_merges(rng, v, os.path.join(tmp, f"h{seed}_merges.txt")) if seed % 2 else None
+        eng = capi.Engine(v, s, merges_path=mp, max_pretoken=4 << 20, **kw)
+        orc = O.Oracle(v, s, merges_path=mp, no_limit=True, **kw)
+        docs = []
+        for n, alpha in ((6000, F.ALPHA_PLAIN[:5]), (30000, F.ALPHA_PLAIN), (9000, ["a", "b"]), (20000, F.DIGITS[:4])):
+            docs.append("x " + "".join(rng.choice(alpha) for _ in range(n)) + " y")
+        data, offs = pack(docs)
+        ids, tok = eng.encode_packed(data, offs)
+        oids, otok = orc.encode_packed(data, offs)
+        assert_same(ids, tok, oids, otok, f"adversarial ranks seed {seed} byte_mode {byte_mode} merges {bool(mp)}")
+        assert eng.stats()["big_merges"] >= 3
+        eng.close()
+        orc.close()
+
+
 def test_one_context_over_distinct_devices():
     """hut_create over ALL distinct GPUs of the box (the product's own multi-GPU entry, HUTOKEN_B200_DEVICES):
     chunks dealt round-robin to physically different devices.  Skipped on a one-GPU box."""
