@@ -596,9 +596,9 @@ def run_ours(args):
         del d3, o3, d5, o5
         # configs[4]: long single-class runs really merged (opt-in no-limit mode; the reference cuts such documents)
         eng4 = make_engine(args.model, max_pretoken=32 << 20)
-        d4, o4 = long_run_docs(600 + rank, [16 << 10, 64 << 10, (256 << 10) - 8, (256 << 10) + 8, 1 << 20])
+        d4, o4 = long_run_docs(600 + rank, [16 << 10, 64 << 10, (256 << 10) - 8, (256 << 10) + 8, 16 << 20])
         extra("configs[4] long_runs_no_limit", args.model, d4, o4, eng4, {"no_limit": True}, 1, 1 << 30,
-              "5 documents holding one letters-only run of 16 Ki / 64 Ki / 256 Ki - 8 / 256 Ki + 8 / 1 Mi bytes, "
+              "5 documents holding one letters-only run of 16 Ki / 64 Ki / 256 Ki - 8 / 256 Ki + 8 / 16 Mi bytes (SURVEY 8(d) C5), "
               "max_pretoken = 32 MiB (no cut), checked in full against the oracle's no-limit mode")
         eng4.close()
         del d4, o4
