@@ -160,7 +160,6 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     dm.distinct_values = m->distinct_values;
     dm.identity_ids = m->identity_ids;
     dm.byte_mode = m->is_byte_encoder;
-    dm.multi_sym = m->max_sym_per_char > 1;
     dm.has_prefix = m->has_prefix;
     dm.monotone = m->monotone;
     dm.cache_ok = (m->max_value < (1 << 20)) ? 1 : 0;  // ids are packed as signed 21-bit fields

@@ -5,20 +5,21 @@
  * Pipeline per shard (hut_pipeline.cuh), all on one stream, no host round trip, no inter-CTA waiting:
  *
  *   doc_kernel      one thread per document: first document starting in each 960-byte tile
- *   tile_kernel     (hut_tile.cuh) WARP per tile, tiles claimed from an atomic ticket, no block barrier:
+ *   tile_kernel     (hut_tile.cuh) persistent, WARP per tile, no block barrier:
  *                   TMA bulk copy of the tile (+ 32-byte halos) into the warp's shared-memory slice; bit-sliced class
  *                   masks + local start rule (hut_bitslice.h)           <- parser_next_token (parser.c:24-88)
  *                   lane-per-pretoken probe of the unique-pretoken cache (32-byte slots, one L2 sector per probe)
  *                                                       <- (no equivalent: the reference re-merges every occurrence)
- *                   cache misses are merged right there: a few by the whole warp one after the other (one symbol per
- *                   lane), many (cold cache) by one lane each, all at once
- *                                                       <- bpe_encode_arena_string (core.c:66-209), MinPQ (queue.c),
+ *                   cache misses reserve room in the slot and are merged 32 at a time, one pretoken per lane
+ *                   (merge_entry)                       <- bpe_encode_arena_string (core.c:66-209), MinPQ (queue.c),
  *                                                          get_pair_rank_from_strings (core.c:700-722), hashmap.c
- *                   ids -> the tile's slot of the staging buffer, dense and in order; per-tile counts
- *   long_kernel     pretokens > 32 bytes / symbols: block-cooperative merge (rare)
+ *                   ids -> the tile's slot of the staging buffer, in order; per-tile counts
+ *   long_kernel     pretokens of 33 .. 4160 symbols: one CTA each, tournament tree over (rank, position)
+ *   huge_kernel     longer ones: cooperative rounds (all pairs of the minimum rank at once, checked per round)
  *   scan kernels    exclusive scan of the per-tile id counts      <- IntVector growth (vector.c:41-55)
  *   compact_kernel  staging slots -> dense int32 ids, coalesced   <- list building (lib.c:699-715, 810-860)
  *   fixdoc_kernel   per-document id offsets
+ *   small_kernel    all of the above in one launch of one CTA for a small batch (hutoken.encode of a sentence)
  *
  * (A single-pass variant -- ids kept in shared memory until a decoupled look-back delivers the tile's base -- was
  * built and measured in round 2 and is in the history: the in-order hand-over of bases stalls warps behind every
@@ -131,7 +132,7 @@ struct DevModel {
     const int32_t* out_id;
     const int32_t* rank_of;
     uint32_t n_vocab, n_units, inert;
-    int distinct_values, identity_ids, byte_mode, multi_sym, has_prefix, cache_ok;
+    int distinct_values, identity_ids, byte_mode, has_prefix, cache_ok;
     int monotone;              // every pair containing a merged token ranks above that token (hut_model.c)
     const uint32_t* sym_off;   // [257]
     const uint32_t* sym_pool;
@@ -144,7 +145,7 @@ struct DevModel {
     const int32_t* prefix_alone;
     uint32_t n_prefix_alone;
     uint32_t kmax;
-    uint32_t miss_len_max;     // longest pretoken (bytes) whose symbols fit one lane of miss_kernel
+    uint32_t miss_len_max;     // longest pretoken (bytes) tile_kernel merges itself (batches of 32, one per lane)
     uint32_t first_extra;      // extra ids the first pretoken of a document can produce (prefix symbols / ids)
     unsigned long long limit;  // longest pretoken merged; beyond: cut (compat) or error (no-limit)
     int compat_cut;
