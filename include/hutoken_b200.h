@@ -50,7 +50,8 @@ typedef struct hut_options {
     uint64_t max_pretoken;     /* 0 = reference-compatible: a document is cut at its first pretoken longer than
                                   262144 bytes (core.c:27-28,402-407,503).  Otherwise: no cut; pretokens up to this
                                   many bytes are merged (block-cooperative path), longer ones are an error. */
-    uint32_t big_slots;        /* working areas for pretokens that outgrow a tile; 0 = default */
+    uint32_t big_slots;        /* working areas (= CTAs of huge_kernel) for pretokens of more than 4160 symbols; 0 = default
+                                  (8; 2 when max_pretoken > 64 MiB).  Allocated when the first such pretoken shows up. */
     uint32_t chunk_mb;         /* hut_encode_batch streams the batch through the devices in chunks of about this many
                                   MiB so that upload, kernels and download overlap; 0 = default (32) */
 } hut_options;
@@ -76,7 +77,8 @@ typedef struct hut_result {
  * like the reference's strdup (lib.c:772).  The batch is cut into contiguous document ranges balanced by bytes
  * (hut_plan_shards) which are dealt round-robin to the context's devices and streamed through them (upload of one
  * chunk overlaps the kernels of the previous and the download of the one before); there is no inter-device
- * communication.  The result lives in
+ * communication.  A small batch (<= 69 120 bytes, <= 2 048 documents: every single sentence) takes one kernel launch on
+ * pinned host buffers instead (no copies).  The result lives in
  * pinned host memory owned by the context and stays valid until the next call on this context. */
 int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64_t* doc_offsets, uint64_t n_docs,
                      hut_result* result);
