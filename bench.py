@@ -523,7 +523,7 @@ def run_ours(args):
                 same = _device_equal(torch, t_ptr, d_text, nbytes, dev)
             dec = {"value": n_text / (dms * 1e-3) / 1e6, "unit": "decoded MB/s (ids resident in HBM)", "ms_per_step": dms,
                    "kernel_ms": dst["kernel_ms"], "gpu_launches_per_step": int(dst["kernel_launches"]),
-                   "text_bytes": int(n_text), "round_trip_equals_input": same}
+                   "text_bytes": int(n_text), "round_trip_equals_input": same, "path": dst.get("path")}
         except ValueError as e:  # ids the vocabulary cannot print (-1): nothing to decode
             dec = {"value": None, "note": str(e)}
 

@@ -54,7 +54,8 @@ class Stats(C.Structure):
 
 EXPORTS = ["hut_create", "hut_destroy", "hut_last_error", "hut_encode_batch", "hut_encode_device",
            "hut_cache_reset", "hut_host_alloc", "hut_host_free", "hut_get_stats", "hut_vocab_lines",
-           "hut_device_count", "hut_plan_shards", "hut_decode_batch", "hut_decode_device", "hut_decode_stats"]
+           "hut_device_count", "hut_plan_shards", "hut_decode_batch", "hut_decode_device", "hut_decode_stats",
+           "hut_decode_path"]
 
 _lib = None
 
@@ -80,6 +81,8 @@ def load_library():
     lib.hut_decode_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64,
                                       C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.c_void_p]
     lib.hut_decode_stats.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
+    lib.hut_decode_path.argtypes = [C.c_void_p]
+    lib.hut_decode_path.restype = C.c_int
     lib.hut_cache_reset.argtypes = [C.c_void_p]
     lib.hut_host_alloc.restype = C.c_void_p
     lib.hut_host_alloc.argtypes = [C.c_size_t]
@@ -191,7 +194,8 @@ class Engine:
     def decode_stats(self):
         ms, n = C.c_double(), C.c_uint64()
         self._lib.hut_decode_stats(self._h, C.byref(ms), C.byref(n))
-        return {"kernel_ms": ms.value, "kernel_launches": n.value}
+        path = {0: None, 1: "token-wise", 2: "general"}[self._lib.hut_decode_path(self._h)]
+        return {"kernel_ms": ms.value, "kernel_launches": n.value, "path": path}
 
     def cache_reset(self):
         self._check(self._lib.hut_cache_reset(self._h))

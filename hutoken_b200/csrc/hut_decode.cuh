@@ -35,7 +35,19 @@ struct DecModel {
     const uint8_t* prefix;
     uint32_t prefix_len;
     int byte_mode;
+    // ---- token-wise path (below): the decoded bytes of every token, worked out once per model ----
+    const uint8_t* trie_kids;  // [trie_nodes] node has children
+    const uint8_t* t_len8;     // [vocab_lines] decoded length; 255: look at t_meta (long, missing or not independent)
+    const uint32_t* t_meta;    // [vocab_lines] T_* flags | bytes the prefix stands for << 24 | decoded length
+    const uint4* t_slot;       // [vocab_lines] the first 15 decoded bytes, byte 15 = length (255: t_pool)
+    const uint32_t* t_off;     // [vocab_lines + 1] offsets into t_pool
+    const uint8_t* t_pool;
 };
+
+constexpr uint32_t T_MISSING = 1u << 31;       // no vocab line carries the id
+constexpr uint32_t T_UNSAFE = 1u << 30;        // the scan of the token alone can differ from its scan inside a text
+constexpr uint32_t T_UNSAFE_START = 1u << 29;  // ... when it is the first token of a document (prefix stripping)
+constexpr uint32_t T_PS_SHIFT = 24, T_PS_MASK = 31u, T_LEN_MASK = 0xFFFFFFu;
 
 constexpr int DEC_TILE = 1024;   // raw bytes per tile
 constexpr int DEC_LOOK = 32;     // look-ahead: the longest replacement is 26 bytes (32-byte line buffer, lib.c:483)
@@ -649,6 +661,339 @@ __global__ void dec_pack_kernel(unsigned long long ndocs, const unsigned long lo
                                __funnelshift_r(r3, r4, sh));
         }
         for (unsigned long long i = head + (nwords << 4) + lane; i < n; i += 32) dst[i] = src[i];
+    }
+}
+
+// ================================================================================================
+// Token-wise path.  pretokenizer_decode (pretokenizer.c:197-296) scans the concatenated token strings greedily; the
+// scan of a text is the scan of its tokens one after the other whenever no step straddles a token boundary, i.e.
+// when, scanning each token ALONE, (a) every character is complete inside the token and (b) no walk down the
+// replacement trie reaches the end of the token at a node that still has children (inside a text it would go on
+// into the next token).  Every token of a GPT-2 / Llama style vocabulary is like that, so the decoded bytes of each
+// token are worked out once per model (dec2_token_kernel, which restates the same scan for one token) and decoding
+// becomes: lengths per sub-block of 256 ids -> scan -> copy of the tokens' decoded bytes to their final place, with
+// text_off read off the same scan.  The prefix is stripped from the first token of a document by skipping the bytes
+// its characters stand for.  A batch that uses a token without the property (T_UNSAFE / T_UNSAFE_START) goes
+// through the general kernels above instead, so the results are the same by construction.
+// ================================================================================================
+__global__ void dec2_kids_kernel(const unsigned long long* edge, uint32_t cap, uint8_t* kids) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < cap; i += gridDim.x * blockDim.x) {
+        const unsigned long long e = edge[i];
+        if (e != HUT_TRIE_EMPTY) kids[(uint32_t)(e >> 32) >> 8] = 1;
+    }
+}
+
+// Thread per vocab line.  EMIT == false: t_meta[t] (flags, prefix bytes, decoded length).  EMIT == true: the decoded
+// bytes at pool + off[t].
+template <bool EMIT>
+__global__ void dec2_token_kernel(DecModel D, const uint8_t* kids, uint32_t* meta, const uint32_t* off, uint8_t* pool) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= D.vocab_lines) return;
+    const uint32_t len = D.dec_len[t];
+    if (len == HUT_DEC_MISSING) {
+        if (!EMIT) meta[t] = T_MISSING;
+        return;
+    }
+    const uint8_t* const R = D.dec_pool + D.dec_off[t];
+    uint8_t* const out = EMIT ? pool + off[t] : nullptr;
+    auto B = [&](uint32_t i) -> uint32_t { return i < len ? (uint32_t)R[i] : 0u; };
+    bool with_prefix = D.prefix_len && len >= D.prefix_len;
+    if (with_prefix)
+        for (uint32_t k = 0; k < D.prefix_len; ++k) with_prefix = with_prefix && R[k] == D.prefix[k];
+    bool part_of_prefix = D.prefix_len && len < D.prefix_len;  // the prefix could continue in the next token
+    if (part_of_prefix)
+        for (uint32_t k = 0; k < len; ++k) part_of_prefix = part_of_prefix && R[k] == D.prefix[k];
+    constexpr uint32_t NONE = 0xFFFFFFFFu;
+    uint32_t p = 0, em = 0, ps = NONE;
+    bool unsafe = false;
+    while (p < len) {
+        if (with_prefix && p == D.prefix_len) ps = em;
+        const uint32_t b0 = R[p];
+        uint32_t step = 0, outb = 0, q = p + 1;
+        uint32_t node = D.root_child[b0];
+        while (node) {  // longest replacement starting here
+            const int o = D.trie_out[node];
+            if (o >= 0) {
+                step = D.trie_depth[node];
+                outb = (uint32_t)o;
+            }
+            if (q >= len) {
+                if (kids[node]) unsafe = true;  // (b)
+                break;
+            }
+            node = trie_child(D.trie_edge, D.trie_mask, node, R[q]);
+            ++q;
+        }
+        if (step) {
+            if (EMIT) out[em] = (uint8_t)outb;
+            em += 1;
+        } else {
+            const uint32_t b1 = B(p + 1), b2 = B(p + 2), b3 = B(p + 3);
+            uint32_t cl, cp;
+            if (b0 < 0x80) { cl = 1; cp = b0; }
+            else if ((b0 & 0xE0) == 0xC0) { cl = 2; cp = ((b0 & 0x1F) << 6) | (b1 & 0x3F); }
+            else if ((b0 & 0xF0) == 0xE0) { cl = 3; cp = ((b0 & 0x0F) << 12) | ((b1 & 0x3F) << 6) | (b2 & 0x3F); }
+            else if ((b0 & 0xF8) == 0xF0) { cl = 4; cp = ((b0 & 0x07) << 18) | ((b1 & 0x3F) << 12) | ((b2 & 0x3F) << 6) | (b3 & 0x3F); }
+            else { cl = 1; cp = 0xFFFD; }
+            if (p + cl > len) {  // (a)
+                unsafe = true;
+                cl = len - p;
+            }
+            step = cl;
+            if (D.byte_mode) {
+                if (EMIT) out[em] = (uint8_t)(cp < 256 ? cp : (uint32_t)'?');  // pretokenizer.c:247-254
+                em += 1;
+            } else {  // pretokenizer.c:283-287
+                if (EMIT)
+                    for (uint32_t k = 0; k < cl; ++k) out[em + k] = R[p + k];
+                em += cl;
+            }
+        }
+        p += step;
+    }
+    if (EMIT) return;
+    if (with_prefix && p == D.prefix_len) ps = em;  // the token is the prefix
+    uint32_t m = em & T_LEN_MASK;
+    if (unsafe || em > T_LEN_MASK) m |= T_UNSAFE;
+    if (part_of_prefix || (with_prefix && (ps == NONE || ps > T_PS_MASK))) m |= T_UNSAFE_START;
+    else if (with_prefix) m |= ps << T_PS_SHIFT;
+    meta[t] = m;
+}
+
+__device__ __forceinline__ unsigned long long dec2_lower_bound(const unsigned long long* a, unsigned long long cnt,
+                                                               unsigned long long v) {
+    unsigned long long lo = 0, hi = cnt;
+    while (lo < hi) {
+        const unsigned long long m = (lo + hi) >> 1;
+        if (__ldg(a + m) < v) lo = m + 1;
+        else hi = m;
+    }
+    return lo;
+}
+
+__device__ __forceinline__ void dec2_load_ids(const int32_t* ids, unsigned long long i0, unsigned long long n,
+                                              int32_t (&id)[8]) {
+    if (i0 + 8 <= n && (reinterpret_cast<uintptr_t>(ids) & 15u) == 0) {
+        const int4 a = __ldg(reinterpret_cast<const int4*>(ids + i0)), b = __ldg(reinterpret_cast<const int4*>(ids + i0) + 1);
+        id[0] = a.x; id[1] = a.y; id[2] = a.z; id[3] = a.w;
+        id[4] = b.x; id[5] = b.y; id[6] = b.z; id[7] = b.w;
+    } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) id[k] = i0 + k < n ? ids[i0 + k] : 0;
+    }
+}
+
+// Warp per sub-block of DEC_SUB ids: decoded bytes of the sub-block.  bad[0]: an id outside the vocabulary
+// (core.c:520-531); bad[1]: the batch needs the general kernels.  PFX: the bytes the prefix stands for come off the
+// first token of every document that starts in the sub-block.
+template <bool PFX>
+__global__ void __launch_bounds__(256) dec2_sub_kernel(DecModel D, const int32_t* ids, unsigned long long n,
+                                                       const unsigned long long* tok_off, unsigned long long ndocs,
+                                                       uint32_t* sub_len, unsigned int* bad) {
+    const int lane = threadIdx.x & 31;
+    const unsigned long long blk = (unsigned long long)blockIdx.x * 8u + (threadIdx.x >> 5);
+    if (blk == 0 && lane == 0 && (tok_off[0] != 0 || tok_off[ndocs] != n)) atomicExch(bad + 1, 1u);  // ids outside every document
+    const unsigned long long b0 = blk * DEC_SUB;
+    if (b0 >= n) return;
+    const unsigned long long i0 = b0 + (unsigned long long)lane * 8u;
+    int32_t id[8];
+    dec2_load_ids(ids, i0, n, id);
+    uint32_t l[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) l[k] = (i0 + k < n && (uint32_t)id[k] < D.vocab_lines) ? __ldg(D.t_len8 + id[k]) : 256u;
+    uint32_t sum = 0;
+    unsigned int flag = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        if (i0 + k >= n) continue;
+        if (l[k] < 255u) {
+            sum += l[k];
+        } else if (l[k] == 256u) {
+            flag |= 1u;
+        } else {
+            const uint32_t m = __ldg(D.t_meta + id[k]);
+            flag |= (m & T_MISSING ? 1u : 0u) | (m & T_UNSAFE ? 2u : 0u);
+            sum += m & T_LEN_MASK;
+        }
+    }
+    if (PFX) {
+        const unsigned long long b1 = b0 + DEC_SUB < n ? b0 + DEC_SUB : n;
+        for (unsigned long long base = dec2_lower_bound(tok_off, ndocs, b0);; base += 32) {
+            const unsigned long long d = base + lane;
+            bool in = d < ndocs;
+            unsigned long long t = 0;
+            if (in) {
+                t = __ldg(tok_off + d);
+                in = t < b1;
+            }
+            if (in && __ldg(tok_off + d + 1) > t) {
+                const int32_t f = ids[t];
+                if ((uint32_t)f < D.vocab_lines) {
+                    const uint32_t m = __ldg(D.t_meta + f);
+                    if (m & T_UNSAFE_START) flag |= 2u;
+                    sum -= (m >> T_PS_SHIFT) & T_PS_MASK;
+                }
+            }
+            if (!__all_sync(0xFFFFFFFFu, in)) break;
+        }
+    }
+    if (flag & 1u) atomicExch(bad, 1u);
+    if (flag & 2u) atomicExch(bad + 1, 1u);
+#pragma unroll
+    for (int d = 16; d; d >>= 1) sum += __shfl_xor_sync(0xFFFFFFFFu, sum, d);
+    if (lane == 0) sub_len[blk] = sum;
+}
+
+// Warp per sub-block (n / DEC_SUB + 1 of them: document boundaries at the very end belong to the last one).  Every
+// lane takes 8 consecutive ids and loads their 16-byte slots at once, the warp scans the lengths, the bytes are put
+// together in shared memory at the 16-byte phase of their destination and leave in 16-byte stores; text_off of the
+// documents that start inside the sub-block comes from the same scan.
+constexpr int G2_WARPS = 8;
+constexpr int G2_STAGE = 2048;  // bytes of one sub-block that fit the staging buffer; larger ones are written directly
+
+struct G2Warp {
+    uint4 stage[(G2_STAGE + 48) / 16];
+    uint32_t off[DEC_SUB + 4];   // exclusive scan of the lengths inside the sub-block, [DEC_SUB] = total
+    uint32_t skip[DEC_SUB / 4];  // PFX: bytes dropped from the front of each token (one byte per id)
+};
+
+__device__ __forceinline__ void dec2_put4(uint8_t* p, uint32_t w, uint32_t cnt) {
+    p[0] = (uint8_t)w;
+    if (cnt > 1) p[1] = (uint8_t)(w >> 8);
+    if (cnt > 2) p[2] = (uint8_t)(w >> 16);
+    if (cnt > 3) p[3] = (uint8_t)(w >> 24);
+}
+
+template <bool PFX>
+__global__ void __launch_bounds__(G2_WARPS * 32) dec2_gather_kernel(DecModel D, const int32_t* ids, unsigned long long n,
+                                                                    const unsigned long long* tok_off,
+                                                                    unsigned long long ndocs,
+                                                                    const unsigned long long* sub_off, uint8_t* text,
+                                                                    unsigned long long* text_off) {
+    __shared__ G2Warp sm[G2_WARPS];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned long long blk = (unsigned long long)blockIdx.x * G2_WARPS + warp;
+    if (blk > n / DEC_SUB) return;  // warps never synchronise with each other
+    G2Warp& W = sm[warp];
+    const unsigned long long b0 = blk * DEC_SUB, i0 = b0 + (unsigned long long)lane * 8u;
+    int32_t id[8];
+    dec2_load_ids(ids, i0, n, id);
+    uint4 s[8];
+    uint32_t l[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const bool ok = i0 + k < n && (uint32_t)id[k] < D.vocab_lines;
+        s[k] = ok ? __ldg(D.t_slot + id[k]) : make_uint4(0u, 0u, 0u, 0u);
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        l[k] = s[k].w >> 24;
+        if (l[k] == 255u) l[k] = __ldg(D.t_meta + id[k]) & T_LEN_MASK;
+    }
+    const unsigned long long d_lo = dec2_lower_bound(tok_off, ndocs, b0);
+    uint32_t sk[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) sk[k] = 0;
+    if (PFX) {
+        W.skip[lane * 2] = 0;
+        W.skip[lane * 2 + 1] = 0;
+        __syncwarp();
+        const unsigned long long b1 = b0 + DEC_SUB < n ? b0 + DEC_SUB : n;
+        for (unsigned long long base = d_lo;; base += 32) {
+            const unsigned long long d = base + lane;
+            bool in = d < ndocs;
+            unsigned long long t = 0;
+            if (in) {
+                t = __ldg(tok_off + d);
+                in = t < b1;
+            }
+            if (in && __ldg(tok_off + d + 1) > t) {
+                const int32_t f = ids[t];
+                if ((uint32_t)f < D.vocab_lines)
+                    reinterpret_cast<uint8_t*>(W.skip)[t - b0] = (uint8_t)((__ldg(D.t_meta + f) >> T_PS_SHIFT) & T_PS_MASK);
+            }
+            if (!__all_sync(0xFFFFFFFFu, in)) break;
+        }
+        __syncwarp();
+        const uint32_t w0 = W.skip[lane * 2], w1 = W.skip[lane * 2 + 1];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            sk[k] = ((k < 4 ? w0 : w1) >> ((k & 3) * 8)) & 0xFFu;
+            l[k] -= sk[k];
+        }
+    }
+    uint32_t mine = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) mine += l[k];
+    uint32_t inc = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+        if (lane >= d) inc += t;
+    }
+    const uint32_t total = __shfl_sync(0xFFFFFFFFu, inc, 31), before = inc - mine;
+    {
+        uint32_t run = before;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            W.off[lane * 8 + k] = run;
+            run += l[k];
+        }
+        if (lane == 31) W.off[DEC_SUB] = run;
+    }
+    __syncwarp();
+    const unsigned long long g0 = __ldg(sub_off + blk);
+    for (unsigned long long base = d_lo;; base += 32) {  // documents (and the end mark) that start in this sub-block
+        const unsigned long long d = base + lane;
+        bool in = d <= ndocs;
+        unsigned long long t = 0;
+        if (in) {
+            t = __ldg(tok_off + d);
+            in = t < b0 + DEC_SUB;
+        }
+        if (in) text_off[d] = g0 + W.off[t - b0];
+        if (!__all_sync(0xFFFFFFFFu, in)) break;
+    }
+    uint8_t* const gdst = text + g0;
+    const bool staged = total <= (uint32_t)G2_STAGE;
+    const uint32_t ph = (uint32_t)(reinterpret_cast<uintptr_t>(gdst) & 15u);
+    uint8_t* sp = staged ? reinterpret_cast<uint8_t*>(W.stage) + ph + before : gdst + before;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const uint32_t L = l[k];
+        if (!L) continue;
+        if (L + sk[k] <= 15u) {
+            uint4 v = s[k];
+            if (PFX)
+                for (uint32_t c = 0; c < sk[k]; ++c) {
+                    v.x = __funnelshift_r(v.x, v.y, 8);
+                    v.y = __funnelshift_r(v.y, v.z, 8);
+                    v.z = __funnelshift_r(v.z, v.w, 8);
+                    v.w >>= 8;
+                }
+            dec2_put4(sp, v.x, L);
+            if (L > 4) dec2_put4(sp + 4, v.y, L - 4);
+            if (L > 8) dec2_put4(sp + 8, v.z, L - 8);
+            if (L > 12) dec2_put4(sp + 12, v.w, L - 12);
+        } else {
+            const uint8_t* src = D.t_pool + __ldg(D.t_off + id[k]) + sk[k];
+            for (uint32_t c = 0; c < L; ++c) sp[c] = __ldg(src + c);
+        }
+        sp += L;
+    }
+    if (!staged) return;
+    __syncwarp();
+    const uint32_t end = ph + total;
+    const uint8_t* const sb = reinterpret_cast<const uint8_t*>(W.stage);
+    uint8_t* const gb = gdst - ph;  // 16-byte aligned
+    for (uint32_t w = lane; w * 16u < end; w += 32) {
+        const uint32_t lo = w * 16u, hi = lo + 16u;
+        if (lo >= ph && hi <= end) {
+            reinterpret_cast<uint4*>(gb)[w] = W.stage[w];
+        } else {
+            const uint32_t a = lo > ph ? lo : ph, b = hi < end ? hi : end;
+            for (uint32_t q = a; q < b; ++q) gb[q] = sb[q];
+        }
     }
 }
 

@@ -35,6 +35,8 @@ struct hut_decstate {
     cudaEvent_t ev[2];
     float last_ms;
     unsigned last_launches;
+    int token_wise;  /* the per-token tables exist and HUTOKEN_B200_DECODE=general is not set */
+    int last_path;   /* 1: token-wise kernels, 2: general kernels */
 };
 
 static void dec_free(hut_decstate* s) {
@@ -59,6 +61,7 @@ static void dec_free(hut_decstate* s) {
 }
 
 static int dec_init_tables(hut_ctx* ctx, hut_decstate* s);
+static int dec_init_token_tables(hut_ctx* ctx, hut_decstate* s);
 
 /* decode-side device state, created by the first hut_decode_* call.  A failure half way leaves nothing behind: the
  * tables uploaded so far are released (they are the newest entries of the device's allocation list) and the next call
@@ -82,6 +85,56 @@ static int dec_init(hut_ctx* ctx) {
     return rc;
 }
 
+/* Decoded bytes of every token (hut_decode.cuh, token-wise path): lengths and flags first, offsets by a host scan,
+ * then the bytes; the 16-byte slots and the one-byte lengths are put together on the host. */
+static int dec_init_token_tables(hut_ctx* ctx, hut_decstate* s) {
+    hut_dev* d = &ctx->dev[0];
+    DecModel& D = s->dm;
+    const uint32_t V = D.vocab_lines;
+    uint8_t* kids = nullptr;
+    CU(ctx, dev_alloc(d, (void**)&kids, (size_t)D.trie_nodes + 1));
+    CU(ctx, cudaMemset(kids, 0, (size_t)D.trie_nodes + 1));
+    if (D.trie_mask != 0xFFFFFFFFu) dec2_kids_kernel<<<64, 256, 0, d->stream>>>(D.trie_edge, D.trie_mask + 1, kids);
+    D.trie_kids = kids;
+    uint32_t *meta = nullptr, *off = nullptr;
+    CU(ctx, dev_alloc(d, (void**)&meta, ((size_t)V + 1) * sizeof(uint32_t)));
+    CU(ctx, dev_alloc(d, (void**)&off, ((size_t)V + 1) * sizeof(uint32_t)));
+    const unsigned grid = (V + 127) / 128;
+    if (V) dec2_token_kernel<false><<<grid, 128, 0, d->stream>>>(D, kids, meta, nullptr, nullptr);
+    std::vector<uint32_t> h_meta((size_t)V + 1), h_off((size_t)V + 1);
+    CU(ctx, cudaMemcpyAsync(h_meta.data(), meta, (size_t)V * sizeof(uint32_t), cudaMemcpyDeviceToHost, d->stream));
+    CU(ctx, cudaStreamSynchronize(d->stream));
+    unsigned long long total = 0;
+    for (uint32_t t = 0; t < V; ++t) {
+        h_off[t] = (uint32_t)total;
+        total += h_meta[t] & T_LEN_MASK;
+    }
+    h_off[V] = (uint32_t)total;
+    if (total > 0xFFFFFF00ull) return set_err(ctx, HUT_STATUS_MEMORY, "%s", "decoded vocabulary too large");
+    uint8_t* pool = nullptr;
+    CU(ctx, dev_alloc(d, (void**)&pool, (size_t)total + 16));
+    CU(ctx, cudaMemsetAsync(pool, 0, (size_t)total + 16, d->stream));
+    CU(ctx, cudaMemcpyAsync(off, h_off.data(), ((size_t)V + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, d->stream));
+    if (V) dec2_token_kernel<true><<<grid, 128, 0, d->stream>>>(D, kids, nullptr, off, pool);
+    std::vector<uint8_t> h_pool((size_t)total + 16), h_len8((size_t)V + 1), h_slot(((size_t)V + 1) * 16);
+    CU(ctx, cudaMemcpyAsync(h_pool.data(), pool, (size_t)total + 16, cudaMemcpyDeviceToHost, d->stream));
+    CU(ctx, cudaStreamSynchronize(d->stream));
+    CU(ctx, cudaGetLastError());
+    for (uint32_t t = 0; t < V; ++t) {
+        const uint32_t m = h_meta[t], len = m & T_LEN_MASK;
+        h_len8[t] = (uint8_t)((m & (T_MISSING | T_UNSAFE)) || len >= 255u ? 255u : len);
+        uint8_t* slot = &h_slot[(size_t)t * 16];
+        for (uint32_t k = 0; k < 15 && k < len; ++k) slot[k] = h_pool[h_off[t] + k];
+        slot[15] = (uint8_t)(len <= 15u ? len : 255u);
+    }
+    CU(ctx, upload(d, (const uint8_t*)h_len8.data(), (size_t)V + 1, &D.t_len8));
+    CU(ctx, upload(d, reinterpret_cast<const uint4*>(h_slot.data()), (size_t)V + 1, &D.t_slot));
+    D.t_meta = meta;
+    D.t_off = off;
+    D.t_pool = pool;
+    return HUT_STATUS_OK;
+}
+
 static int dec_init_tables(hut_ctx* ctx, hut_decstate* s) {
     hut_dev* d = &ctx->dev[0];
     const hut_model* m = ctx->model;
@@ -99,9 +152,13 @@ static int dec_init_tables(hut_ctx* ctx, hut_decstate* s) {
     CU(ctx, upload(d, m->prefix_bytes, m->prefix_len, &D.prefix));
     D.prefix_len = m->prefix_len;
     D.byte_mode = m->is_byte_encoder;
-    CU(ctx, cudaMalloc(&s->d_bad, sizeof(unsigned int)));
+    CU(ctx, cudaMalloc(&s->d_bad, 2 * sizeof(unsigned int)));
     CU(ctx, cudaEventCreate(&s->ev[0]));
     CU(ctx, cudaEventCreate(&s->ev[1]));
+    const int rc = dec_init_token_tables(ctx, s);
+    if (rc != HUT_STATUS_OK) return rc;
+    const char* mode = getenv("HUTOKEN_B200_DECODE"); /* "general": keep to the general kernels (tests compare the two) */
+    s->token_wise = !(mode && !strcmp(mode, "general"));
     s->ready = 1;
     return HUT_STATUS_OK;
 }
@@ -135,7 +192,42 @@ static int dec_run(hut_ctx* ctx, const int32_t* d_ids, unsigned long long n_ids,
     CU(ctx, grow(&s->d_doc_len, &s->d_doc_len_cap, (size_t)n_docs + 1));
     CU(ctx, grow(&s->d_text_off, &s->d_text_off_cap, (size_t)n_docs + 2));
     CU(ctx, cudaEventRecord(s->ev[0], st));
-    CU(ctx, cudaMemsetAsync(s->d_bad, 0, sizeof(unsigned int), st));
+    CU(ctx, cudaMemsetAsync(s->d_bad, 0, 2 * sizeof(unsigned int), st));
+    if (s->token_wise && n_ids && n_docs) {
+        /* token-wise kernels: lengths -> scan -> bytes and text_off in one pass; one synchronisation */
+        const bool pfx = D.prefix_len != 0;
+        const unsigned g1 = (unsigned)((nsub + 7) / 8);
+        if (pfx) dec2_sub_kernel<true><<<g1, 256, 0, st>>>(D, d_ids, n_ids, d_tok, n_docs, s->d_sub_len, s->d_bad);
+        else dec2_sub_kernel<false><<<g1, 256, 0, st>>>(D, d_ids, n_ids, d_tok, n_docs, s->d_sub_len, s->d_bad);
+        s->last_launches++;
+        int rc2 = dec_scan(ctx, s, s->d_sub_len, nsub, s->d_sub_off, st);
+        if (rc2 != HUT_STATUS_OK) return rc2;
+        unsigned long long total = 0;
+        unsigned int bad2[2] = {0, 0};
+        CU(ctx, cudaMemcpyAsync(&total, s->d_sub_off + nsub, sizeof total, cudaMemcpyDeviceToHost, st));
+        CU(ctx, cudaMemcpyAsync(bad2, s->d_bad, sizeof bad2, cudaMemcpyDeviceToHost, st));
+        CU(ctx, cudaStreamSynchronize(st));
+        if (bad2[0]) /* core.c:522-530 */
+            return set_err(ctx, HUT_STATUS_VALUE, "%s", "Element must be non-negative and less than vocab size.");
+        if (!bad2[1]) {
+            CU(ctx, grow(&s->d_text, &s->d_text_cap, (size_t)total + 16));
+            const unsigned g2 = (unsigned)((n_ids / DEC_SUB + 1 + G2_WARPS - 1) / G2_WARPS);
+            if (pfx)
+                dec2_gather_kernel<true><<<g2, G2_WARPS * 32, 0, st>>>(D, d_ids, n_ids, d_tok, n_docs, s->d_sub_off,
+                                                                       s->d_text, s->d_text_off);
+            else
+                dec2_gather_kernel<false><<<g2, G2_WARPS * 32, 0, st>>>(D, d_ids, n_ids, d_tok, n_docs, s->d_sub_off,
+                                                                        s->d_text, s->d_text_off);
+            s->last_launches++;
+            CU(ctx, cudaEventRecord(s->ev[1], st));
+            CU(ctx, cudaGetLastError());
+            s->last_path = 1;
+            *n_text = total;
+            return HUT_STATUS_OK;
+        }
+        CU(ctx, cudaMemsetAsync(s->d_bad, 0, 2 * sizeof(unsigned int), st));
+    }
+    s->last_path = 2;
     if (nsub) {
         dec_sub_kernel<<<(unsigned)((nsub + 7) / 8), 256, 0, st>>>(D, d_ids, n_ids, s->d_sub_len, s->d_bad);
         s->last_launches++;
@@ -245,3 +337,5 @@ extern "C" int hut_decode_stats(const hut_ctx* ctx, double* kernel_ms, uint64_t*
     if (kernel_launches) *kernel_launches = ctx->dec->last_launches;
     return HUT_STATUS_OK;
 }
+
+extern "C" int hut_decode_path(const hut_ctx* ctx) { return ctx && ctx->dec ? ctx->dec->last_path : 0; }

@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include "../../include/hutoken_b200.h"
 #include "hut_model.h"
@@ -59,7 +60,7 @@ struct hut_dev {
     cudaStream_t stream;        // kernels
     cudaStream_t s_in, s_out;   // H2D / D2H copies of the host-buffer API
     DevModel dm;
-    void* allocs[48];
+    void* allocs[64];
     int nalloc;
     CacheSlot* cache;
     uint32_t cache_bits;
@@ -129,6 +130,14 @@ static cudaError_t upload(hut_dev* d, const T* src, size_t n, const T** out) {
     d->allocs[d->nalloc++] = p;
     if (n) e = cudaMemcpy(p, src, n * sizeof(T), cudaMemcpyHostToDevice);
     *out = p;
+    return e;
+}
+
+/* uninitialised device memory on the device's allocation list */
+static cudaError_t dev_alloc(hut_dev* d, void** out, size_t bytes) {
+    if (d->nalloc >= (int)(sizeof d->allocs / sizeof d->allocs[0])) return cudaErrorMemoryAllocation;  // list full
+    cudaError_t e = cudaMalloc(out, bytes ? bytes : 1);
+    if (e == cudaSuccess) d->allocs[d->nalloc++] = *out;
     return e;
 }
 

@@ -123,6 +123,13 @@ int hut_decode_device(hut_ctx* ctx, const int32_t* d_ids, uint64_t n_ids, const 
 /* device time (CUDA events on the launch stream) and kernel count of the last decode call */
 int hut_decode_stats(const hut_ctx* ctx, double* kernel_ms, uint64_t* kernel_launches);
 
+/* Which kernels the last decode call ran: 1 = token-wise (every token of the batch decodes independently of its
+ * neighbours: lengths, scan, one copy pass), 2 = general (greedy scan of the concatenated token strings, tile by
+ * tile; taken when a token ends inside a special-chars pattern or inside a character), 0 = no call yet.  Both
+ * produce the bytes of pretokenizer_decode (pretokenizer.c:197-296).  HUTOKEN_B200_DECODE=general in the environment
+ * keeps a context to the general kernels. */
+int hut_decode_path(const hut_ctx* ctx);
+
 /* Drops the unique-pretoken cache of every device (it otherwise persists across calls). */
 int hut_cache_reset(hut_ctx* ctx);
 

@@ -175,7 +175,7 @@ def test_gpu_decode_golden(name):
     got = eng.batch_decode_bytes([c["ids"] for c in ok])
     for g, c in zip(got, ok):
         assert g.split(b"\0", 1)[0] == bytes.fromhex(c["text_hex"])
-    assert eng.decode_stats()["kernel_launches"] >= 8
+    assert eng.decode_stats()["kernel_launches"] >= 5
 
 
 @pytest.mark.gpu
@@ -216,6 +216,7 @@ def test_gpu_decode_corpus_round_trip(name):
 def test_gpu_decode_fuzz_models(byte_mode):
     from hutoken_b200 import capi
     tmp = tempfile.mkdtemp()
+    paths = {"token-wise": 0, "general": 0, None: 0}
     for seed in range(30):
         rng = random.Random(7000 + seed)
         v, s, kw = F.random_model(rng, tmp, byte_mode, f"gd{seed}")
@@ -234,10 +235,64 @@ def test_gpu_decode_fuzz_models(byte_mode):
         got = eng.batch_decode_bytes(lists)
         for x, g in zip(lists, got):
             assert g == orc.decode_bytes(x), (seed, kw, x)
+        # one list per call: a batch without a boundary-straddling token takes the token-wise kernels
+        for x in lists[:40]:
+            assert eng.batch_decode_bytes([x])[0] == orc.decode_bytes(x), (seed, kw, x)
+            paths[eng.decode_stats()["path"]] += 1
         with pytest.raises(ValueError, match="less than vocab size"):
             eng.batch_decode_bytes([[0], [n_lines]])
         eng.close()
         orc.close()
+    assert paths["token-wise"] > 50 and paths["general"] > 10, paths
+
+
+def _general_engine(v, s, **kw):
+    """An engine kept to the general decode kernels (the switch is read when the decode state is created)."""
+    from hutoken_b200 import capi
+    eng = capi.Engine(v, s, **kw)
+    os.environ["HUTOKEN_B200_DECODE"] = "general"
+    try:
+        eng.batch_decode_bytes([[]])
+    finally:
+        del os.environ["HUTOKEN_B200_DECODE"]
+    return eng
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", MODELS)
+def test_gpu_decode_token_wise_equals_general(name):
+    """The two sets of decode kernels on the same ids: documents of every size from empty to thousands of sub-blocks,
+    offsets that put document starts on, before and after sub-block boundaries, prefix stripping on every document."""
+    from common import engine_for
+    eng, orc = engine_for(name), oracle_for(name)
+    v, s = synth.PATHS[name]
+    gen = _general_engine(v, s, **synth.MODEL_KW[name])
+    data, offs = synth.corpus(67, 1 << 20, special_every=150)
+    ids, _ = eng.encode_packed(data, offs)
+    ids = ids[ids >= 0]
+    rng = np.random.default_rng(5)
+    for shape in ("one", "tiny", "ragged", "aligned"):
+        n = len(ids)
+        if shape == "one":
+            cuts = np.array([], dtype=np.int64)
+        elif shape == "tiny":
+            n = 40000
+            cuts = np.sort(rng.integers(0, n + 1, size=12000))  # many empty documents, most sub-blocks start several
+        elif shape == "ragged":
+            cuts = np.sort(rng.integers(0, n + 1, size=300))
+        else:
+            cuts = np.arange(256, n, 256 * 7)
+        tok = np.concatenate([[0], cuts, [n]]).astype(np.uint64)
+        a_text, a_off = eng.decode_packed(ids[:n], tok)
+        assert eng.decode_stats()["path"] == "token-wise", (name, shape)
+        b_text, b_off = gen.decode_packed(ids[:n], tok)
+        assert gen.decode_stats()["path"] == "general"
+        assert np.array_equal(a_off, b_off), (name, shape)
+        assert a_text[:int(a_off[-1])].tobytes() == b_text[:int(b_off[-1])].tobytes(), (name, shape)
+        for d in rng.integers(0, len(tok) - 1, size=20):
+            got = a_text[int(a_off[d]):int(a_off[d + 1])].tobytes()
+            assert got == orc.decode_bytes(ids[int(tok[d]):int(tok[d + 1])]), (name, shape, d)
+    gen.close()
 
 
 @pytest.mark.gpu
