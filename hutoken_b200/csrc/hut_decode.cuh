@@ -760,15 +760,16 @@ __global__ void dec2_token_kernel(DecModel D, const uint8_t* kids, uint32_t* met
     meta[t] = m;
 }
 
-__device__ __forceinline__ unsigned long long dec2_lower_bound(const unsigned long long* a, unsigned long long cnt,
-                                                               unsigned long long v) {
-    unsigned long long lo = 0, hi = cnt;
-    while (lo < hi) {
-        const unsigned long long m = (lo + hi) >> 1;
-        if (__ldg(a + m) < v) lo = m + 1;
-        else hi = m;
-    }
-    return lo;
+// first_doc[b] = the first entry d of tok_off[0..ndocs] with tok_off[d] / DEC_SUB == b (0xFFFFFFFF, set beforehand: no
+// document starts in the sub-block).  tok_off does not decrease, so exactly one entry per sub-block writes.
+constexpr uint32_t DEC2_NO_DOC = 0xFFFFFFFFu;
+
+__global__ void __launch_bounds__(256) dec2_first_doc_kernel(const unsigned long long* tok_off, unsigned long long ndocs,
+                                                             uint32_t* first_doc) {
+    const unsigned long long d = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (d > ndocs) return;
+    const unsigned long long b = __ldg(tok_off + d) / DEC_SUB;
+    if (d == 0 || __ldg(tok_off + d - 1) / DEC_SUB != b) first_doc[b] = (uint32_t)d;
 }
 
 __device__ __forceinline__ void dec2_load_ids(const int32_t* ids, unsigned long long i0, unsigned long long n,
@@ -789,7 +790,8 @@ __device__ __forceinline__ void dec2_load_ids(const int32_t* ids, unsigned long 
 template <bool PFX>
 __global__ void __launch_bounds__(256) dec2_sub_kernel(DecModel D, const int32_t* ids, unsigned long long n,
                                                        const unsigned long long* tok_off, unsigned long long ndocs,
-                                                       uint32_t* sub_len, unsigned int* bad) {
+                                                       const uint32_t* first_doc, uint32_t* sub_len,
+                                                       unsigned int* bad) {
     const int lane = threadIdx.x & 31;
     const unsigned long long blk = (unsigned long long)blockIdx.x * 8u + (threadIdx.x >> 5);
     if (blk == 0 && lane == 0 && (tok_off[0] != 0 || tok_off[ndocs] != n)) atomicExch(bad + 1, 1u);  // ids outside every document
@@ -818,7 +820,8 @@ __global__ void __launch_bounds__(256) dec2_sub_kernel(DecModel D, const int32_t
     }
     if (PFX) {
         const unsigned long long b1 = b0 + DEC_SUB < n ? b0 + DEC_SUB : n;
-        for (unsigned long long base = dec2_lower_bound(tok_off, ndocs, b0);; base += 32) {
+        const uint32_t d_lo = __ldg(first_doc + blk);
+        for (unsigned long long base = d_lo; d_lo != DEC2_NO_DOC; base += 32) {
             const unsigned long long d = base + lane;
             bool in = d < ndocs;
             unsigned long long t = 0;
@@ -849,6 +852,9 @@ __global__ void __launch_bounds__(256) dec2_sub_kernel(DecModel D, const int32_t
 // together in shared memory at the 16-byte phase of their destination and leave in 16-byte stores; text_off of the
 // documents that start inside the sub-block comes from the same scan.
 constexpr int G2_WARPS = 8;
+#ifndef G2_CTAS
+#define G2_CTAS 4
+#endif
 constexpr int G2_STAGE = 2048;  // bytes of one sub-block that fit the staging buffer; larger ones are written directly
 
 struct G2Warp {
@@ -865,9 +871,10 @@ __device__ __forceinline__ void dec2_put4(uint8_t* p, uint32_t w, uint32_t cnt) 
 }
 
 template <bool PFX>
-__global__ void __launch_bounds__(G2_WARPS * 32) dec2_gather_kernel(DecModel D, const int32_t* ids, unsigned long long n,
+__global__ void __launch_bounds__(G2_WARPS * 32, G2_CTAS) dec2_gather_kernel(DecModel D, const int32_t* ids, unsigned long long n,
                                                                     const unsigned long long* tok_off,
                                                                     unsigned long long ndocs,
+                                                                    const uint32_t* first_doc,
                                                                     const unsigned long long* sub_off, uint8_t* text,
                                                                     unsigned long long* text_off) {
     __shared__ G2Warp sm[G2_WARPS];
@@ -890,7 +897,7 @@ __global__ void __launch_bounds__(G2_WARPS * 32) dec2_gather_kernel(DecModel D, 
         l[k] = s[k].w >> 24;
         if (l[k] == 255u) l[k] = __ldg(D.t_meta + id[k]) & T_LEN_MASK;
     }
-    const unsigned long long d_lo = dec2_lower_bound(tok_off, ndocs, b0);
+    const uint32_t d_lo = __ldg(first_doc + blk);
     uint32_t sk[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) sk[k] = 0;
@@ -899,7 +906,7 @@ __global__ void __launch_bounds__(G2_WARPS * 32) dec2_gather_kernel(DecModel D, 
         W.skip[lane * 2 + 1] = 0;
         __syncwarp();
         const unsigned long long b1 = b0 + DEC_SUB < n ? b0 + DEC_SUB : n;
-        for (unsigned long long base = d_lo;; base += 32) {
+        for (unsigned long long base = d_lo; d_lo != DEC2_NO_DOC; base += 32) {
             const unsigned long long d = base + lane;
             bool in = d < ndocs;
             unsigned long long t = 0;
@@ -932,7 +939,8 @@ __global__ void __launch_bounds__(G2_WARPS * 32) dec2_gather_kernel(DecModel D, 
         if (lane >= d) inc += t;
     }
     const uint32_t total = __shfl_sync(0xFFFFFFFFu, inc, 31), before = inc - mine;
-    {
+    const unsigned long long g0 = __ldg(sub_off + blk);
+    if (d_lo != DEC2_NO_DOC) {
         uint32_t run = before;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
@@ -940,10 +948,9 @@ __global__ void __launch_bounds__(G2_WARPS * 32) dec2_gather_kernel(DecModel D, 
             run += l[k];
         }
         if (lane == 31) W.off[DEC_SUB] = run;
+        __syncwarp();
     }
-    __syncwarp();
-    const unsigned long long g0 = __ldg(sub_off + blk);
-    for (unsigned long long base = d_lo;; base += 32) {  // documents (and the end mark) that start in this sub-block
+    for (unsigned long long base = d_lo; d_lo != DEC2_NO_DOC; base += 32) {  // documents (and the end mark) that start here
         const unsigned long long d = base + lane;
         bool in = d <= ndocs;
         unsigned long long t = 0;
@@ -990,9 +997,17 @@ __global__ void __launch_bounds__(G2_WARPS * 32) dec2_gather_kernel(DecModel D, 
         const uint32_t lo = w * 16u, hi = lo + 16u;
         if (lo >= ph && hi <= end) {
             reinterpret_cast<uint4*>(gb)[w] = W.stage[w];
-        } else {
-            const uint32_t a = lo > ph ? lo : ph, b = hi < end ? hi : end;
-            for (uint32_t q = a; q < b; ++q) gb[q] = sb[q];
+        } else {  // a 16-byte word shared with the neighbouring sub-block: whole 32-bit words, then single bytes
+#pragma unroll
+            for (uint32_t j = 0; j < 4; ++j) {
+                const uint32_t l4 = lo + 4u * j, h4 = l4 + 4u;
+                if (l4 >= ph && h4 <= end) {
+                    reinterpret_cast<uint32_t*>(gb)[l4 >> 2] = reinterpret_cast<const uint32_t*>(sb)[l4 >> 2];
+                } else {
+                    const uint32_t a = l4 > ph ? l4 : ph, b = h4 < end ? h4 : end;
+                    for (uint32_t q = a; q < b; ++q) gb[q] = sb[q];
+                }
+            }
         }
     }
 }

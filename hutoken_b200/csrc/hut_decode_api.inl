@@ -28,6 +28,8 @@ struct hut_decstate {
     uint8_t* d_text;
     size_t d_text_cap;
     unsigned int* d_bad;
+    uint32_t* d_first_doc;  /* token-wise path: first document that starts in each sub-block */
+    size_t d_first_doc_cap;
     uint8_t* h_text;
     size_t h_text_cap;
     unsigned long long* h_text_off;
@@ -53,6 +55,7 @@ static void dec_free(hut_decstate* s) {
     cudaFree(s->d_text_off);
     cudaFree(s->d_text);
     cudaFree(s->d_bad);
+    cudaFree(s->d_first_doc);
     cudaFreeHost(s->h_text);
     cudaFreeHost(s->h_text_off);
     if (s->ev[0]) cudaEventDestroy(s->ev[0]);
@@ -193,13 +196,19 @@ static int dec_run(hut_ctx* ctx, const int32_t* d_ids, unsigned long long n_ids,
     CU(ctx, grow(&s->d_text_off, &s->d_text_off_cap, (size_t)n_docs + 2));
     CU(ctx, cudaEventRecord(s->ev[0], st));
     CU(ctx, cudaMemsetAsync(s->d_bad, 0, 2 * sizeof(unsigned int), st));
-    if (s->token_wise && n_ids && n_docs) {
+    if (s->token_wise && n_ids && n_docs && n_docs < 0xFFFFFFF0ull) {
         /* token-wise kernels: lengths -> scan -> bytes and text_off in one pass; one synchronisation */
         const bool pfx = D.prefix_len != 0;
         const unsigned g1 = (unsigned)((nsub + 7) / 8);
-        if (pfx) dec2_sub_kernel<true><<<g1, 256, 0, st>>>(D, d_ids, n_ids, d_tok, n_docs, s->d_sub_len, s->d_bad);
-        else dec2_sub_kernel<false><<<g1, 256, 0, st>>>(D, d_ids, n_ids, d_tok, n_docs, s->d_sub_len, s->d_bad);
-        s->last_launches++;
+        const size_t nfirst = (size_t)(n_ids / DEC_SUB + 1);
+        CU(ctx, grow(&s->d_first_doc, &s->d_first_doc_cap, nfirst));
+        CU(ctx, cudaMemsetAsync(s->d_first_doc, 0xFF, nfirst * sizeof(uint32_t), st));
+        dec2_first_doc_kernel<<<(unsigned)(n_docs / 256 + 1), 256, 0, st>>>(d_tok, n_docs, s->d_first_doc);
+        if (pfx)
+            dec2_sub_kernel<true><<<g1, 256, 0, st>>>(D, d_ids, n_ids, d_tok, n_docs, s->d_first_doc, s->d_sub_len, s->d_bad);
+        else
+            dec2_sub_kernel<false><<<g1, 256, 0, st>>>(D, d_ids, n_ids, d_tok, n_docs, s->d_first_doc, s->d_sub_len, s->d_bad);
+        s->last_launches += 2;
         int rc2 = dec_scan(ctx, s, s->d_sub_len, nsub, s->d_sub_off, st);
         if (rc2 != HUT_STATUS_OK) return rc2;
         unsigned long long total = 0;
@@ -213,11 +222,11 @@ static int dec_run(hut_ctx* ctx, const int32_t* d_ids, unsigned long long n_ids,
             CU(ctx, grow(&s->d_text, &s->d_text_cap, (size_t)total + 16));
             const unsigned g2 = (unsigned)((n_ids / DEC_SUB + 1 + G2_WARPS - 1) / G2_WARPS);
             if (pfx)
-                dec2_gather_kernel<true><<<g2, G2_WARPS * 32, 0, st>>>(D, d_ids, n_ids, d_tok, n_docs, s->d_sub_off,
-                                                                       s->d_text, s->d_text_off);
+                dec2_gather_kernel<true><<<g2, G2_WARPS * 32, 0, st>>>(D, d_ids, n_ids, d_tok, n_docs, s->d_first_doc,
+                                                                       s->d_sub_off, s->d_text, s->d_text_off);
             else
-                dec2_gather_kernel<false><<<g2, G2_WARPS * 32, 0, st>>>(D, d_ids, n_ids, d_tok, n_docs, s->d_sub_off,
-                                                                        s->d_text, s->d_text_off);
+                dec2_gather_kernel<false><<<g2, G2_WARPS * 32, 0, st>>>(D, d_ids, n_ids, d_tok, n_docs, s->d_first_doc,
+                                                                        s->d_sub_off, s->d_text, s->d_text_off);
             s->last_launches++;
             CU(ctx, cudaEventRecord(s->ev[1], st));
             CU(ctx, cudaGetLastError());
