@@ -47,7 +47,9 @@ struct DecModel {
 constexpr uint32_t T_MISSING = 1u << 31;       // no vocab line carries the id
 constexpr uint32_t T_UNSAFE = 1u << 30;        // the scan of the token alone can differ from its scan inside a text
 constexpr uint32_t T_UNSAFE_START = 1u << 29;  // ... when it is the first token of a document (prefix stripping)
-constexpr uint32_t T_PS_SHIFT = 24, T_PS_MASK = 31u, T_LEN_MASK = 0xFFFFFFu;
+constexpr uint32_t T_PS_SHIFT = 24, T_PS_MASK = 31u, T_LEN_MASK = 0x7FFFFFu;
+constexpr uint32_t T_SOFT = 1u << 23;  // with T_UNSAFE: only because a trie walk reaches the end of the token; whether it
+                                       // goes on to a longer replacement is looked up in the tokens that follow
 
 constexpr int DEC_TILE = 1024;   // raw bytes per tile
 constexpr int DEC_LOOK = 32;     // look-ahead: the longest replacement is 26 bytes (32-byte line buffer, lib.c:483)
@@ -705,7 +707,7 @@ __global__ void dec2_token_kernel(DecModel D, const uint8_t* kids, uint32_t* met
         for (uint32_t k = 0; k < len; ++k) part_of_prefix = part_of_prefix && R[k] == D.prefix[k];
     constexpr uint32_t NONE = 0xFFFFFFFFu;
     uint32_t p = 0, em = 0, ps = NONE;
-    bool unsafe = false;
+    bool unsafe = false, soft = false;
     while (p < len) {
         if (with_prefix && p == D.prefix_len) ps = em;
         const uint32_t b0 = R[p];
@@ -718,7 +720,7 @@ __global__ void dec2_token_kernel(DecModel D, const uint8_t* kids, uint32_t* met
                 outb = (uint32_t)o;
             }
             if (q >= len) {
-                if (kids[node]) unsafe = true;  // (b)
+                if (kids[node]) soft = true;  // (b)
                 break;
             }
             node = trie_child(D.trie_edge, D.trie_mask, node, R[q]);
@@ -755,6 +757,7 @@ __global__ void dec2_token_kernel(DecModel D, const uint8_t* kids, uint32_t* met
     if (with_prefix && p == D.prefix_len) ps = em;  // the token is the prefix
     uint32_t m = em & T_LEN_MASK;
     if (unsafe || em > T_LEN_MASK) m |= T_UNSAFE;
+    else if (soft) m |= T_UNSAFE | T_SOFT;
     if (part_of_prefix || (with_prefix && (ps == NONE || ps > T_PS_MASK))) m |= T_UNSAFE_START;
     else if (with_prefix) m |= ps << T_PS_SHIFT;
     meta[t] = m;
@@ -772,6 +775,68 @@ __global__ void __launch_bounds__(256) dec2_first_doc_kernel(const unsigned long
     if (d == 0 || __ldg(tok_off + d - 1) / DEC_SUB != b) first_doc[b] = (uint32_t)d;
 }
 
+// Token ids[i] is T_SOFT: scanning it alone, some walk down the trie stops at the end of the token with children left.
+// Inside the document the walk goes on into the following tokens; the token still decodes as it does alone unless
+// that finds a longer replacement.  Rare (a token that ends like the beginning of a special-chars pattern).
+__device__ __noinline__ bool dec2_context_ok(const DecModel& D, const int32_t* ids, unsigned long long i,
+                                             const unsigned long long* tok_off, unsigned long long ndocs) {
+    unsigned long long lo = 0, hi = ndocs;  // first entry of tok_off beyond i = end of the token's document
+    while (lo < hi) {
+        const unsigned long long m = (lo + hi) >> 1;
+        if (__ldg(tok_off + m) <= i) lo = m + 1;
+        else hi = m;
+    }
+    const unsigned long long doc_end = __ldg(tok_off + lo);
+    const int32_t id = ids[i];
+    const uint32_t len = __ldg(D.dec_len + id);
+    const uint8_t* const R = D.dec_pool + __ldg(D.dec_off + id);
+    uint32_t p = 0;
+    while (p < len) {
+        const uint32_t b0 = R[p];
+        uint32_t node = D.root_child[b0], step = 0, q = p + 1;
+        while (node) {
+            if (D.trie_out[node] >= 0) step = D.trie_depth[node];
+            if (q >= len) break;
+            node = trie_child(D.trie_edge, D.trie_mask, node, R[q]);
+            ++q;
+        }
+        if (node && D.trie_kids[node]) {  // on into the document
+            unsigned long long j = i + 1;
+            const uint8_t* src = nullptr;
+            uint32_t c = 0, l2 = 0;
+            for (;;) {
+                while (c >= l2 && j < doc_end) {
+                    const int32_t id2 = ids[j++];
+                    l2 = (uint32_t)id2 < D.vocab_lines ? __ldg(D.dec_len + id2) : (uint32_t)HUT_DEC_MISSING;
+                    if (l2 == HUT_DEC_MISSING) return false;  // bad[0] is raised by the warp that owns the id
+                    src = D.dec_pool + __ldg(D.dec_off + id2);
+                    c = 0;
+                }
+                if (c >= l2) break;  // end of the document
+                node = trie_child(D.trie_edge, D.trie_mask, node, src[c++]);
+                if (!node) break;
+                if (D.trie_out[node] >= 0) return false;
+            }
+        }
+        if (!step) step = b0 < 0x80 ? 1u : (b0 & 0xE0) == 0xC0 ? 2u : (b0 & 0xF0) == 0xE0 ? 3u : (b0 & 0xF8) == 0xF0 ? 4u : 1u;
+        p += step;
+    }
+    return true;
+}
+
+// Only for batches in which dec2_sub_kernel met T_SOFT tokens: each of them against the tokens that follow it.
+__global__ void __launch_bounds__(256) dec2_soft_kernel(DecModel D, const int32_t* ids, unsigned long long n,
+                                                        const unsigned long long* tok_off, unsigned long long ndocs,
+                                                        unsigned int* bad) {
+    const unsigned long long step = (unsigned long long)gridDim.x * blockDim.x;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += step) {
+        const int32_t t = ids[i];
+        if ((uint32_t)t >= D.vocab_lines || __ldg(D.t_len8 + t) != 255u) continue;
+        const uint32_t m = __ldg(D.t_meta + t);
+        if ((m & T_UNSAFE) && (m & T_SOFT) && !dec2_context_ok(D, ids, i, tok_off, ndocs)) atomicExch(bad + 1, 1u);
+    }
+}
+
 __device__ __forceinline__ void dec2_load_ids(const int32_t* ids, unsigned long long i0, unsigned long long n,
                                               int32_t (&id)[8]) {
     if (i0 + 8 <= n && (reinterpret_cast<uintptr_t>(ids) & 15u) == 0) {
@@ -785,7 +850,7 @@ __device__ __forceinline__ void dec2_load_ids(const int32_t* ids, unsigned long 
 }
 
 // Warp per sub-block of DEC_SUB ids: decoded bytes of the sub-block.  bad[0]: an id outside the vocabulary
-// (core.c:520-531); bad[1]: the batch needs the general kernels.  PFX: the bytes the prefix stands for come off the
+// (core.c:520-531); bad[1]: the batch needs the general kernels; bad[2]: T_SOFT tokens seen.  PFX: the bytes the prefix stands for come off the
 // first token of every document that starts in the sub-block.
 template <bool PFX>
 __global__ void __launch_bounds__(256) dec2_sub_kernel(DecModel D, const int32_t* ids, unsigned long long n,
@@ -814,7 +879,8 @@ __global__ void __launch_bounds__(256) dec2_sub_kernel(DecModel D, const int32_t
             flag |= 1u;
         } else {
             const uint32_t m = __ldg(D.t_meta + id[k]);
-            flag |= (m & T_MISSING ? 1u : 0u) | (m & T_UNSAFE ? 2u : 0u);
+            if (m & T_MISSING) flag |= 1u;
+            if (m & T_UNSAFE) flag |= m & T_SOFT ? 4u : 2u;
             sum += m & T_LEN_MASK;
         }
     }
@@ -842,6 +908,7 @@ __global__ void __launch_bounds__(256) dec2_sub_kernel(DecModel D, const int32_t
     }
     if (flag & 1u) atomicExch(bad, 1u);
     if (flag & 2u) atomicExch(bad + 1, 1u);
+    if (flag & 4u) atomicExch(bad + 2, 1u);  // dec2_soft_kernel decides
 #pragma unroll
     for (int d = 16; d; d >>= 1) sum += __shfl_xor_sync(0xFFFFFFFFu, sum, d);
     if (lane == 0) sub_len[blk] = sum;

@@ -155,7 +155,7 @@ static int dec_init_tables(hut_ctx* ctx, hut_decstate* s) {
     CU(ctx, upload(d, m->prefix_bytes, m->prefix_len, &D.prefix));
     D.prefix_len = m->prefix_len;
     D.byte_mode = m->is_byte_encoder;
-    CU(ctx, cudaMalloc(&s->d_bad, 2 * sizeof(unsigned int)));
+    CU(ctx, cudaMalloc(&s->d_bad, 4 * sizeof(unsigned int)));
     CU(ctx, cudaEventCreate(&s->ev[0]));
     CU(ctx, cudaEventCreate(&s->ev[1]));
     const int rc = dec_init_token_tables(ctx, s);
@@ -195,7 +195,7 @@ static int dec_run(hut_ctx* ctx, const int32_t* d_ids, unsigned long long n_ids,
     CU(ctx, grow(&s->d_doc_len, &s->d_doc_len_cap, (size_t)n_docs + 1));
     CU(ctx, grow(&s->d_text_off, &s->d_text_off_cap, (size_t)n_docs + 2));
     CU(ctx, cudaEventRecord(s->ev[0], st));
-    CU(ctx, cudaMemsetAsync(s->d_bad, 0, 2 * sizeof(unsigned int), st));
+    CU(ctx, cudaMemsetAsync(s->d_bad, 0, 4 * sizeof(unsigned int), st));
     if (s->token_wise && n_ids && n_docs && n_docs < 0xFFFFFFF0ull) {
         /* token-wise kernels: lengths -> scan -> bytes and text_off in one pass; one synchronisation */
         const bool pfx = D.prefix_len != 0;
@@ -212,12 +212,18 @@ static int dec_run(hut_ctx* ctx, const int32_t* d_ids, unsigned long long n_ids,
         int rc2 = dec_scan(ctx, s, s->d_sub_len, nsub, s->d_sub_off, st);
         if (rc2 != HUT_STATUS_OK) return rc2;
         unsigned long long total = 0;
-        unsigned int bad2[2] = {0, 0};
+        unsigned int bad2[3] = {0, 0, 0};
         CU(ctx, cudaMemcpyAsync(&total, s->d_sub_off + nsub, sizeof total, cudaMemcpyDeviceToHost, st));
         CU(ctx, cudaMemcpyAsync(bad2, s->d_bad, sizeof bad2, cudaMemcpyDeviceToHost, st));
         CU(ctx, cudaStreamSynchronize(st));
         if (bad2[0]) /* core.c:522-530 */
             return set_err(ctx, HUT_STATUS_VALUE, "%s", "Element must be non-negative and less than vocab size.");
+        if (!bad2[1] && bad2[2]) { /* tokens that end like the beginning of a pattern: looked at in their context */
+            dec2_soft_kernel<<<(unsigned)d->sms * 8, 256, 0, st>>>(D, d_ids, n_ids, d_tok, n_docs, s->d_bad);
+            s->last_launches++;
+            CU(ctx, cudaMemcpyAsync(bad2, s->d_bad, sizeof bad2, cudaMemcpyDeviceToHost, st));
+            CU(ctx, cudaStreamSynchronize(st));
+        }
         if (!bad2[1]) {
             CU(ctx, grow(&s->d_text, &s->d_text_cap, (size_t)total + 16));
             const unsigned g2 = (unsigned)((n_ids / DEC_SUB + 1 + G2_WARPS - 1) / G2_WARPS);
@@ -234,7 +240,7 @@ static int dec_run(hut_ctx* ctx, const int32_t* d_ids, unsigned long long n_ids,
             *n_text = total;
             return HUT_STATUS_OK;
         }
-        CU(ctx, cudaMemsetAsync(s->d_bad, 0, 2 * sizeof(unsigned int), st));
+        CU(ctx, cudaMemsetAsync(s->d_bad, 0, 4 * sizeof(unsigned int), st));
     }
     s->last_path = 2;
     if (nsub) {

@@ -296,6 +296,39 @@ def test_gpu_decode_token_wise_equals_general(name):
 
 
 @pytest.mark.gpu
+def test_gpu_decode_tokens_that_end_inside_a_pattern():
+    """Llama-style table (`<0xHH>` patterns): a token ending in '<' decodes alone unless the following tokens spell a
+    pattern with it -- inside one document only.  Path and bytes against the oracle."""
+    from hutoken_b200 import capi
+    tmp = tempfile.mkdtemp()
+    toks = [b"a", b"<", b"0", b"x", b"A", b">", b"<0", b"\xE2\x96\x81", b"b<", b"x0A>", b"\xE2\x96\x81<0x0", b"A>b",
+            b"<0x0A>", b"<0x", b"\xE2\x96"]
+    v = os.path.join(tmp, "pat.vocab.txt")
+    synth.write_vocab(v, [(t, i) for i, t in enumerate(toks)])
+    s = synth.PATHS["llama_small"][1]
+    kw = dict(prefix="\u2581", is_byte_encoder=False)
+    eng, orc = capi.Engine(v, s, **kw), O.Oracle(v, s, **kw)
+    T = {t: i for i, t in enumerate(toks)}
+    cases = [
+        ([[T[b"b<"], T[b"a"]]], "token-wise"),                                   # the walk goes on and finds nothing
+        ([[T[b"<"], T[b"0"], T[b"x"], T[b"0"], T[b"A"], T[b">"]]], "general"),  # spelled across tokens
+        ([[T[b"a"], T[b"<0"]], [T[b"x0A>"], T[b"a"]]], "token-wise"),            # ... across two documents: no pattern
+        ([[T[b"a"], T[b"<0"], T[b"x0A>"]]], "general"),
+        ([[T[b"\xE2\x96\x81<0x0"], T[b"A>b"]]], "general"),                      # prefix + pattern over the boundary
+        ([[T[b"\xE2\x96\x81<0x0"], T[b"a"]], [T[b"<0x0A>"], T[b"<0x"]]], "token-wise"),
+        ([[T[b"<0x"], T[b"<0x"], T[b"0"], T[b"a"]] * 200], "token-wise"),
+        ([[T[b"a"], T[b"\xE2\x96"]]], "general"),                                # ends inside a character
+    ]
+    for lists, path in cases:
+        got = eng.batch_decode_bytes(lists)
+        assert eng.decode_stats()["path"] == path, (lists, path)
+        for x, g in zip(lists, got):
+            assert g == orc.decode_bytes(x), (x, g)
+    eng.close()
+    orc.close()
+
+
+@pytest.mark.gpu
 def test_gpu_decode_python_surface():
     """hutoken.decode / batch_decode with the reference's messages (lib.c:876-1085, hutoken.py:141-164)."""
     from hutoken_b200 import _hutoken as ext
