@@ -52,10 +52,12 @@ class Stats(C.Structure):
         return {k: getattr(self, k) for k, _ in self._fields_}
 
 
+NOALLOC_MAX_IDS = 1 << 24  # HUT_NOALLOC_MAX_IDS
+
 EXPORTS = ["hut_create", "hut_destroy", "hut_last_error", "hut_encode_batch", "hut_encode_device",
            "hut_cache_reset", "hut_host_alloc", "hut_host_free", "hut_get_stats", "hut_vocab_lines",
            "hut_device_count", "hut_plan_shards", "hut_decode_batch", "hut_decode_device", "hut_decode_stats",
-           "hut_decode_path"]
+           "hut_decode_path", "hut_decode_device_noalloc"]
 
 _lib = None
 
@@ -82,6 +84,8 @@ def load_library():
                                       C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.c_void_p]
     lib.hut_decode_stats.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
     lib.hut_decode_path.argtypes = [C.c_void_p]
+    lib.hut_decode_device_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p,
+                                              C.c_uint64, C.c_void_p, C.POINTER(C.c_uint64), C.c_void_p]
     lib.hut_decode_path.restype = C.c_int
     lib.hut_cache_reset.argtypes = [C.c_void_p]
     lib.hut_host_alloc.restype = C.c_void_p
@@ -190,6 +194,14 @@ class Engine:
         self._check(self._lib.hut_decode_device(self._h, d_ids, n_ids, d_tok, n_docs, C.byref(t), C.byref(o),
                                                 C.byref(n), stream))
         return t.value, o.value, int(n.value)
+
+    def decode_device_noalloc(self, d_ids, n_ids, d_tok, n_docs, d_text, text_cap, d_text_off, stream=None):
+        """hut_decode_device_noalloc: caller-owned device outputs, scratch in the library's static device array, no
+        allocation; at most NOALLOC_MAX_IDS ids.  Returns the text length."""
+        n = C.c_uint64()
+        self._check(self._lib.hut_decode_device_noalloc(self._h, d_ids, n_ids, d_tok, n_docs, d_text, text_cap,
+                                                        d_text_off, C.byref(n), stream))
+        return int(n.value)
 
     def decode_stats(self):
         ms, n = C.c_double(), C.c_uint64()

@@ -37,6 +37,7 @@ struct hut_decstate {
     cudaEvent_t ev[2];
     float last_ms;
     unsigned last_launches;
+    unsigned char* na_scratch; /* device address of g_noalloc_scratch on this context's decode device */
     int token_wise;  /* the per-token tables exist and HUTOKEN_B200_DECODE=general is not set */
     int last_path;   /* 1: token-wise kernels, 2: general kernels */
 };
@@ -160,6 +161,8 @@ static int dec_init_tables(hut_ctx* ctx, hut_decstate* s) {
     CU(ctx, cudaEventCreate(&s->ev[1]));
     const int rc = dec_init_token_tables(ctx, s);
     if (rc != HUT_STATUS_OK) return rc;
+    const int rc_na = noalloc_setup(ctx, &s->na_scratch);
+    if (rc_na != HUT_STATUS_OK) return rc_na;
     const char* mode = getenv("HUTOKEN_B200_DECODE"); /* "general": keep to the general kernels (tests compare the two) */
     s->token_wise = !(mode && !strcmp(mode, "general"));
     s->ready = 1;
@@ -354,3 +357,87 @@ extern "C" int hut_decode_stats(const hut_ctx* ctx, double* kernel_ms, uint64_t*
 }
 
 extern "C" int hut_decode_path(const hut_ctx* ctx) { return ctx && ctx->dec ? ctx->dec->last_path : 0; }
+
+/* See include/hutoken_b200.h.  The token-wise kernels of dec_run with their scratch in g_noalloc_scratch; no
+ * cudaMalloc / cudaFree / grow() on this path. */
+extern "C" int hut_decode_device_noalloc(hut_ctx* ctx, const int32_t* d_ids, uint64_t n_ids, const uint64_t* d_tok_offsets,
+                                         uint64_t n_docs, uint8_t* d_text, uint64_t text_cap, uint64_t* d_text_offsets,
+                                         uint64_t* n_bytes_out, void* stream) {
+    if (!ctx) return HUT_STATUS_STATE;
+    if (n_bytes_out) *n_bytes_out = 0;
+    hut_decstate* s = ctx->dec;
+    if (!s || !s->ready || !s->na_scratch)
+        return set_err(ctx, HUT_STATUS_STATE, "%s",
+                       "hut_decode_device_noalloc: decode tables not built yet; call another hut_decode_* function once first");
+    if (n_ids > NA_MAX_IDS)
+        return set_err(ctx, HUT_STATUS_ARG, "%s",
+                       "hut_decode_device_noalloc: at most 16777216 ids (HUT_NOALLOC_MAX_IDS) per call; split the batch or use "
+                       "hut_decode_device");
+    if (n_docs >= 0xFFFFFFF0ull) return set_err(ctx, HUT_STATUS_ARG, "%s", "hut_decode_device_noalloc: too many documents");
+    if (!d_tok_offsets || !d_text_offsets || (n_ids && (!d_ids || !d_text)))
+        return set_err(ctx, HUT_STATUS_ARG, "%s", "null argument");
+    hut_dev* d = &ctx->dev[0];
+    CU(ctx, cudaSetDevice(d->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : d->stream;
+    const DecModel& D = s->dm;
+    unsigned char* const base = s->na_scratch;
+    unsigned int* const bad = reinterpret_cast<unsigned int*>(base + NA_OFF_BAD);
+    uint32_t* const sub_len = reinterpret_cast<uint32_t*>(base + NA_OFF_SUB_LEN);
+    unsigned long long* const sub_off = reinterpret_cast<unsigned long long*>(base + NA_OFF_SUB_OFF);
+    uint32_t* const first_doc = reinterpret_cast<uint32_t*>(base + NA_OFF_FIRST_DOC);
+    unsigned long long* const bsum = reinterpret_cast<unsigned long long*>(base + NA_OFF_BSUM);
+    const unsigned long long* const tok = (const unsigned long long*)d_tok_offsets;
+    unsigned long long* const toff = (unsigned long long*)d_text_offsets;
+    if (!n_ids || !n_docs) { /* nothing to print: every document is empty */
+        if (!n_docs) {
+            CU(ctx, cudaMemsetAsync(toff, 0, sizeof(unsigned long long), st));
+        } else {
+            unsigned long long ends[2] = {0, 0};
+            CU(ctx, cudaMemcpyAsync(ends, tok + (n_docs - 1), 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+            CU(ctx, cudaStreamSynchronize(st));
+            if (ends[1] != 0) return set_err(ctx, HUT_STATUS_ARG, "%s", "d_tok_offsets must end at n_ids");
+            CU(ctx, cudaMemsetAsync(toff, 0, ((size_t)n_docs + 1) * sizeof(unsigned long long), st));
+        }
+        CU(ctx, cudaStreamSynchronize(st));
+        return HUT_STATUS_OK;
+    }
+    const bool pfx = D.prefix_len != 0;
+    const unsigned long long nsub = (n_ids + DEC_SUB - 1) / DEC_SUB;
+    const size_t nfirst = (size_t)(n_ids / DEC_SUB + 1);
+    /* the array keeps the previous call's contents: flags and the first-document table start from their empty values;
+     * sub_len / sub_off / bsum are written in full before they are read */
+    CU(ctx, cudaMemsetAsync(bad, 0, 4 * sizeof(unsigned int), st));
+    CU(ctx, cudaMemsetAsync(first_doc, 0xFF, nfirst * sizeof(uint32_t), st));
+    dec2_first_doc_kernel<<<(unsigned)(n_docs / 256 + 1), 256, 0, st>>>(tok, n_docs, first_doc);
+    const unsigned g1 = (unsigned)((nsub + 7) / 8);
+    if (pfx) dec2_sub_kernel<true><<<g1, 256, 0, st>>>(D, d_ids, n_ids, tok, n_docs, first_doc, sub_len, bad);
+    else dec2_sub_kernel<false><<<g1, 256, 0, st>>>(D, d_ids, n_ids, tok, n_docs, first_doc, sub_len, bad);
+    const unsigned nb = (unsigned)(nsub / SCAN_BLOCK + 1);
+    scan_sums_kernel<<<nb, SCAN_NT, 0, st>>>(sub_len, nsub, bsum);
+    scan_top_kernel<<<1, 1024, 0, st>>>(bsum, nb);
+    scan_apply_kernel<<<nb, SCAN_NT, 0, st>>>(sub_len, nsub, bsum, sub_off);
+    unsigned long long total = 0;
+    unsigned int flags[3] = {0, 0, 0};
+    CU(ctx, cudaMemcpyAsync(&total, sub_off + nsub, sizeof total, cudaMemcpyDeviceToHost, st));
+    CU(ctx, cudaMemcpyAsync(flags, bad, sizeof flags, cudaMemcpyDeviceToHost, st));
+    CU(ctx, cudaStreamSynchronize(st));
+    if (flags[0]) /* core.c:522-530 */
+        return set_err(ctx, HUT_STATUS_VALUE, "%s", "Element must be non-negative and less than vocab size.");
+    if (!flags[1] && flags[2]) {
+        dec2_soft_kernel<<<(unsigned)d->sms * 8, 256, 0, st>>>(D, d_ids, n_ids, tok, n_docs, bad);
+        CU(ctx, cudaMemcpyAsync(flags, bad, sizeof flags, cudaMemcpyDeviceToHost, st));
+        CU(ctx, cudaStreamSynchronize(st));
+    }
+    if (flags[1])
+        return set_err(ctx, HUT_STATUS_VALUE, "%s",
+                       "hut_decode_device_noalloc: this batch needs the general decode kernels (a token ends inside a character or "
+                       "a pattern, or d_tok_offsets does not span [0, n_ids]); use hut_decode_device");
+    if (n_bytes_out) *n_bytes_out = total;
+    if (total > text_cap) return set_err(ctx, HUT_STATUS_CAPACITY, "%s", "hut_decode_device_noalloc: text_cap too small");
+    const unsigned g2 = (unsigned)((n_ids / DEC_SUB + 1 + G2_WARPS - 1) / G2_WARPS);
+    if (pfx) dec2_gather_kernel<true><<<g2, G2_WARPS * 32, 0, st>>>(D, d_ids, n_ids, tok, n_docs, first_doc, sub_off, d_text, toff);
+    else dec2_gather_kernel<false><<<g2, G2_WARPS * 32, 0, st>>>(D, d_ids, n_ids, tok, n_docs, first_doc, sub_off, d_text, toff);
+    CU(ctx, cudaGetLastError());
+    CU(ctx, cudaStreamSynchronize(st));
+    return HUT_STATUS_OK;
+}

@@ -903,4 +903,29 @@ extern "C" int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64
     return HUT_STATUS_OK;
 }
 
+/* ---- scratch of hut_decode_device_noalloc (below): a file-scope device array instead of cudaMalloc'ed buffers.
+ * Every GPU that loads the library holds these HUT_NOALLOC_SCRATCH_BYTES (about 1 MiB) until the process exits.
+ * In host code `g_noalloc_scratch` is only a stand-in for the symbol: the address a kernel may use comes from
+ * cudaGetSymbolAddress, asked once per context with the context's decode device current (noalloc_setup). ---- */
+constexpr unsigned long long NA_MAX_IDS = HUT_NOALLOC_MAX_IDS;
+constexpr size_t NA_MAX_SUB = (size_t)(NA_MAX_IDS / DEC_SUB);
+constexpr size_t na_align(size_t x) { return (x + 255) & ~(size_t)255; }
+constexpr size_t NA_OFF_BAD = 0;                                                             /* 4 x unsigned int */
+constexpr size_t NA_OFF_SUB_LEN = na_align(NA_OFF_BAD + 16);                                 /* uint32[nsub + 1] */
+constexpr size_t NA_OFF_SUB_OFF = na_align(NA_OFF_SUB_LEN + 4 * (NA_MAX_SUB + 1));           /* uint64[nsub + 2] */
+constexpr size_t NA_OFF_FIRST_DOC = na_align(NA_OFF_SUB_OFF + 8 * (NA_MAX_SUB + 2));         /* uint32[n_ids / 256 + 1] */
+constexpr size_t NA_OFF_BSUM = na_align(NA_OFF_FIRST_DOC + 4 * (NA_MAX_SUB + 1));            /* uint64[scan blocks] */
+constexpr size_t NA_BYTES = na_align(NA_OFF_BSUM + 8 * (NA_MAX_SUB / SCAN_BLOCK + 2));
+static_assert(NA_BYTES <= HUT_NOALLOC_SCRATCH_BYTES, "scratch layout larger than the size the header states");
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[HUT_NOALLOC_SCRATCH_BYTES];
+
+/* decode set-up (dec_init_tables), device of the context current: device address of the array on THAT device */
+static int noalloc_setup(hut_ctx* ctx, unsigned char** out) {
+    void* p = nullptr;
+    CU(ctx, cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    *out = (unsigned char*)p;
+    return HUT_STATUS_OK;
+}
+
 #include "hut_decode_api.inl"

@@ -130,6 +130,28 @@ int hut_decode_stats(const hut_ctx* ctx, double* kernel_ms, uint64_t* kernel_lau
  * keeps a context to the general kernels. */
 int hut_decode_path(const hut_ctx* ctx);
 
+/* hut_decode_device for callers that must not allocate (code under CUDA graph capture set-up rules, tight serving
+ * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same token-wise kernels and the same bytes as hut_decode_device, but
+ *   - the caller owns the outputs: d_text (text_cap bytes) and d_text_offsets (n_docs + 1 entries), on the device;
+ *   - the scratch (lengths per 256 ids, their scan, first document per sub-block, flags) lives in a file-scope
+ *     device array of HUT_NOALLOC_SCRATCH_BYTES inside the library, which bounds a call to HUT_NOALLOC_MAX_IDS ids;
+ *     more ids -> HUT_STATUS_ARG ("... at most 16777216 ids ...");
+ *   - nothing is allocated or freed (no cudaMalloc / cudaFree / cudaMallocHost); the call synchronises `stream`
+ *     once to read the text length and the flags.
+ * The decode tables must exist: call any other hut_decode_* function once per context first (that call allocates);
+ * otherwise HUT_STATUS_STATE.  A batch the token-wise kernels cannot take (a token that ends inside a character or
+ * inside a special-chars pattern completed by its neighbours) is refused with HUT_STATUS_VALUE: use
+ * hut_decode_device for it.  text_cap too small -> HUT_STATUS_CAPACITY, *n_bytes_out = bytes needed, no text written.
+ * The array is shared by every call of the process on that GPU and keeps the last call's contents (what has to start
+ * from zero is cleared by each call): calls that overlap on the GPU -- two streams, two contexts, two threads --
+ * race on it; serialise them.  d_tok_offsets must start at 0 and end at n_ids. */
+#define HUT_NOALLOC_MAX_IDS (1ull << 24)
+#define HUT_NOALLOC_SCRATCH_BYTES (1026u << 10)
+int hut_decode_device_noalloc(hut_ctx* ctx, const int32_t* d_ids, uint64_t n_ids, const uint64_t* d_tok_offsets,
+                              uint64_t n_docs, uint8_t* d_text, uint64_t text_cap, uint64_t* d_text_offsets,
+                              uint64_t* n_bytes_out, void* stream);
+
 /* Drops the unique-pretoken cache of every device (it otherwise persists across calls). */
 int hut_cache_reset(hut_ctx* ctx);
 
