@@ -501,40 +501,64 @@ def run_ours(args):
         e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
 
     # ---- decode leg: the ids just produced, resident on the device, back to text ----
-    dec = None
-    if not args.no_decode:
+    def decode_once(eng_x, lg, tok_ptr, nd, steps):
+        """(ms per call, text length, text address, text_off address, stats) of hut_decode_device on ids left in HBM"""
+        n_text = 0
+        for _ in range(2):
+            eng_x.decode_device(lg["d_ids"].data_ptr(), lg["n_ids"], tok_ptr, nd, stream=sh)
+        d0, d1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(dev)
+        d0.record(stream)
+        for _ in range(steps):
+            t_ptr, o_ptr, n_text = eng_x.decode_device(lg["d_ids"].data_ptr(), lg["n_ids"], tok_ptr, nd, stream=sh)
+        d1.record(stream)
+        torch.cuda.synchronize(dev)
+        return d0.elapsed_time(d1) / steps, int(n_text), t_ptr, o_ptr, eng_x.decode_stats()
+
+    def decode_leg(eng_x, lg, nb, steps, orc_x=None):
+        """The batch as the encode leg left it, then the same ids as ONE document (the reference's own benchmark shape,
+        scripts/benchmark.py:52-56).  Checked against the input text where the round trip is exact, and against the
+        oracle's decode of the first documents when an oracle is given."""
         try:
-            n_text = 0
-            for _ in range(2):
-                _, _, n_text = eng.decode_device(d_ids.data_ptr(), n_ids, d_tok.data_ptr(), ndocs, stream=sh)
-            d0, d1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            dsteps = max(1, min(args.steps, 5))
-            torch.cuda.synchronize(dev)
-            d0.record(stream)
-            for _ in range(dsteps):
-                t_ptr, _, n_text = eng.decode_device(d_ids.data_ptr(), n_ids, d_tok.data_ptr(), ndocs, stream=sh)
-            d1.record(stream)
-            torch.cuda.synchronize(dev)
-            dms = d0.elapsed_time(d1) / dsteps
-            dst = eng.decode_stats()
+            nd = lg["ndocs"]
+            ms, n_text, t_ptr, o_ptr, dst = decode_once(eng_x, lg, lg["d_tok"].data_ptr(), nd, steps)
             # round trip: byte mode with a complete byte alphabet decodes back to the input exactly
-            same = None
-            if n_text == nbytes:
-                same = _device_equal(torch, t_ptr, d_text, nbytes, dev)
-            dec = {"value": n_text / (dms * 1e-3) / 1e6, "unit": "decoded MB/s (ids resident in HBM)", "ms_per_step": dms,
-                   "kernel_ms": dst["kernel_ms"], "gpu_launches_per_step": int(dst["kernel_launches"]),
-                   "text_bytes": int(n_text), "round_trip_equals_input": same, "path": dst.get("path")}
+            same = _device_equal(torch, t_ptr, lg["d_text"], nb, dev) if n_text == nb else None
+            oracle_ok = None
+            if orc_x is not None:
+                k = min(nd, 64)
+                tok_h = lg["d_tok"][:k + 1].cpu().numpy()
+                ids_h = lg["d_ids"][:int(tok_h[-1])].cpu().numpy()
+                toff = torch.as_tensor(_DevView(o_ptr, 8 * (k + 1)), device=dev).cpu().numpy().view(np.uint64)
+                text_h = torch.as_tensor(_DevView(t_ptr, max(1, int(toff[-1]))), device=dev).cpu().numpy()
+                oracle_ok = all(text_h[int(toff[d]):int(toff[d + 1])].tobytes() ==
+                                orc_x.decode_bytes(ids_h[int(tok_h[d]):int(tok_h[d + 1])]) for d in range(k))
+            one = torch.tensor([0, lg["n_ids"]], dtype=torch.int64, device=dev)
+            ms1, n1, _, _, dst1 = decode_once(eng_x, lg, one.data_ptr(), 1, steps)
+            return {"value": n_text / (ms * 1e-3) / 1e6, "unit": "decoded MB/s (ids resident in HBM)", "ms_per_step": ms,
+                    "kernel_ms": dst["kernel_ms"], "gpu_launches_per_step": int(dst["kernel_launches"]),
+                    "text_bytes": n_text, "round_trip_equals_input": same, "first_docs_equal_oracle": oracle_ok,
+                    "path": dst.get("path"),
+                    "single_document": {"value": n1 / (ms1 * 1e-3) / 1e6, "ms_per_step": ms1, "text_bytes": n1,
+                                        "path": dst1.get("path"), "ms_vs_batch": ms1 / ms}}
         except ValueError as e:  # ids the vocabulary cannot print (-1): nothing to decode
-            dec = {"value": None, "note": str(e)}
+            return {"value": None, "note": str(e)}
+
+    leg["n_ids"], leg["ndocs"] = n_ids, ndocs
+    dec = None
 
     # ---- id check of THIS rank's shard (every rank, so the scaling runs carry one per GPU) ----
     check_ok, check_sha, probes = None, None, None
     if args.check or world > 1 or not args.no_workloads:
         orc = make_oracle(args.model)
         check_ok, check_sha, probes = parity(orc, data, offs, leg, check_bytes)
+        if not args.no_decode:
+            dec = decode_leg(eng, leg, nbytes, max(1, min(args.steps, 5)), orc)
         orc.close()
         if not check_ok:
             raise SystemExit(f"bench.py: rank {rank}: GPU ids differ from the oracle on the first {check_bytes} bytes")
+    elif not args.no_decode:
+        dec = decode_leg(eng, leg, nbytes, max(1, min(args.steps, 5)))
 
     # ---- max over ranks / whole-job sums ----
     import dist_torch as D  # tools/dist_torch.py: torch.distributed plumbing (the product package imports no PyTorch)
@@ -558,13 +582,16 @@ def run_ours(args):
     # =============================== the other configs, one short run each (same JSON line) ===============================
     workloads = {}
     if not args.no_workloads:
-        def extra(name, model, data_x, offs_x, eng_x, orc_kw, steps, limit, note):
+        def extra(name, model, data_x, offs_x, eng_x, orc_kw, steps, limit, note, with_decode=False):
             nb = int(offs_x[-1])
             lg = device_leg(eng_x, model, data_x, offs_x, nb, steps, 1, sync_all=False)
             orc_x = make_oracle(model, **orc_kw)
             ok, sha, pr = parity(orc_x, data_x, offs_x, lg, limit)
+            dec_x = decode_leg(eng_x, lg, nb, 2, orc_x) if with_decode and not args.no_decode else None
             orc_x.close()
             w = summarize(lg, nb, pr)
+            if dec_x is not None:
+                w["decode"] = dec_x
             w["parity"] = {"equal_to_oracle": ok, "prefix_bytes": int(pr["bytes"]), "sha256_int32_ids": sha}
             w["config"] = note
             ms_all = allmax(lg["ms"])
@@ -581,14 +608,15 @@ def run_ours(args):
             d2, o2, nb2 = make_corpus(300 + rank, mb2 << 20, 0, pinned_alloc=lambda n: pinned_u8(lib, n))
             extra("configs[2] llama_10GiB_total", "llama", d2, o2, eng2, {}, 2, check_bytes,
                   f"Llama/PULI-LlumiX-shaped 32K vocab (prefix U+2581, plain mode), {mb2} MiB on this rank = "
-                  f"{mb2 * world} MiB over {world} rank(s) (strong scaling)")
+                  f"{mb2 * world} MiB over {world} rank(s) (strong scaling)", with_decode=True)
             eng2.close()
             lib.hut_host_free(d2.ctypes.data)
             del d2, o2
         # configs[3]: a special byte / multibyte character every ~200 bytes
         d3, o3, nb3 = make_corpus(400 + rank, 256 << 20, 200, pinned_alloc=None)
         extra("configs[3] special_every_200", args.model, d3, o3, eng, {}, 3, check_bytes,
-              "configs[1] model, one replaced byte / multibyte character every ~200 bytes, 256 MiB per rank")
+              "configs[1] model, one replaced byte / multibyte character every ~200 bytes, 256 MiB per rank",
+              with_decode=True)
         # heavy tail: 5 % of the bytes in pretokens of 16..31 and 40..4000 bytes (second cache, long_kernel)
         d5, o5 = heavy_tail(d3[:(96 << 20)], o3[:int(np.searchsorted(o3, np.uint64(96 << 20), side="right"))], 500 + rank)
         extra("heavy_tail_mix", args.model, d5, o5, eng, {}, 3, check_bytes,
