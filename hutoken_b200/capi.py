@@ -206,7 +206,7 @@ class Engine:
     def decode_stats(self):
         ms, n = C.c_double(), C.c_uint64()
         self._lib.hut_decode_stats(self._h, C.byref(ms), C.byref(n))
-        path = {0: None, 1: "token-wise", 2: "general"}[self._lib.hut_decode_path(self._h)]
+        path = {0: None, 1: "token-wise", 2: "general", 3: "token-wise, one launch"}[self._lib.hut_decode_path(self._h)]
         return {"kernel_ms": ms.value, "kernel_launches": n.value, "path": path}
 
     def cache_reset(self):

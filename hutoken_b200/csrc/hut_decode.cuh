@@ -1079,4 +1079,106 @@ __global__ void __launch_bounds__(G2_WARPS * 32, G2_CTAS) dec2_gather_kernel(Dec
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// One-launch path for a few ids (hutoken.decode of a sentence): one CTA does the whole token-wise pipeline on
+// pinned host buffers the device reads and writes directly (ids, tok_off in; text, text_off, header out) and raises
+// `done` last, after a system-wide fence; the host spins on it.  Anything it cannot finish -- an unsafe or soft
+// token, more text than the staging buffer -- is reported in hdr->flags and the call goes through dec_run.
+// ------------------------------------------------------------------------------------------------
+constexpr int DS_NT = 256;
+constexpr int DS_MAX_IDS = 2048;
+constexpr int DS_MAX_DOCS = 256;
+constexpr int DS_TEXT = 32768;  // decoded bytes staged in shared memory
+constexpr unsigned int DS_BAD_ID = 1u, DS_FALLBACK = 2u;
+
+struct DecSmallHdr {
+    unsigned long long total;
+    unsigned int flags;
+    unsigned int pad;
+};
+
+template <bool PFX>
+__global__ void __launch_bounds__(DS_NT, 1) dec_small_kernel(DecModel D, const int32_t* ids, uint32_t n,
+                                                             const unsigned long long* tok_off, uint32_t ndocs,
+                                                             uint8_t* text, unsigned long long* text_off,
+                                                             DecSmallHdr* hdr, volatile unsigned int* done,
+                                                             unsigned int seq) {
+    __shared__ uint4 stage[DS_TEXT / 16];
+    __shared__ uint32_t off[DS_MAX_IDS + 1];
+    __shared__ uint8_t skip[DS_MAX_IDS];
+    __shared__ unsigned long long scan_sm[32];
+    __shared__ unsigned long long tot;
+    const int tid = threadIdx.x;
+    constexpr int PER = DS_MAX_IDS / DS_NT;
+    unsigned int flags = 0;
+    if (PFX) {
+        for (int i = tid; i < DS_MAX_IDS; i += DS_NT) skip[i] = 0;
+        __syncthreads();
+        for (uint32_t d = tid; d < ndocs; d += DS_NT) {
+            const unsigned long long t = tok_off[d];
+            if (tok_off[d + 1] > t) {
+                const int32_t f = ids[t];
+                if ((uint32_t)f < D.vocab_lines) {
+                    const uint32_t m = __ldg(D.t_meta + f);
+                    if (m & T_UNSAFE_START) flags |= DS_FALLBACK;
+                    skip[t] = (uint8_t)((m >> T_PS_SHIFT) & T_PS_MASK);
+                }
+            }
+        }
+        __syncthreads();
+    }
+    int32_t id[PER];
+    uint32_t l[PER];
+    uint32_t mine = 0;
+#pragma unroll
+    for (int k = 0; k < PER; ++k) {
+        const uint32_t i = (uint32_t)tid * PER + k;
+        id[k] = i < n ? ids[i] : 0;
+        l[k] = 0;
+        if (i < n) {
+            if ((uint32_t)id[k] >= D.vocab_lines) {
+                flags |= DS_BAD_ID;
+            } else {
+                const uint32_t m = __ldg(D.t_meta + id[k]);
+                if (m & T_MISSING) flags |= DS_BAD_ID;
+                if (m & T_UNSAFE) flags |= DS_FALLBACK;
+                l[k] = (m & T_LEN_MASK) - (PFX ? (uint32_t)skip[i] : 0u);
+            }
+        }
+        mine += l[k];
+    }
+    const unsigned long long ex = block_exclusive_u64(mine, &tot, scan_sm);
+    const unsigned int any = (__syncthreads_or((int)(flags & DS_BAD_ID)) ? DS_BAD_ID : 0u) |
+                             (__syncthreads_or((int)(flags & DS_FALLBACK)) ? DS_FALLBACK : 0u);
+    const unsigned long long total = tot;
+    const bool give_up = (any & (DS_BAD_ID | DS_FALLBACK)) || total > (unsigned long long)DS_TEXT;
+    if (!give_up) {
+        uint32_t run = (uint32_t)ex;
+#pragma unroll
+        for (int k = 0; k < PER; ++k) {
+            const uint32_t i = (uint32_t)tid * PER + k;
+            if (i <= n) off[i] = run;
+            if (i < n && l[k]) {
+                const uint8_t* src = D.t_pool + __ldg(D.t_off + id[k]) + (PFX ? (uint32_t)skip[i] : 0u);
+                uint8_t* dst = reinterpret_cast<uint8_t*>(stage) + run;
+                for (uint32_t c = 0; c < l[k]; ++c) dst[c] = __ldg(src + c);
+            }
+            run += l[k];
+        }
+        if (tid == DS_NT - 1 && n == (uint32_t)DS_MAX_IDS) off[n] = run;
+        __syncthreads();
+        for (uint32_t d = tid; d <= ndocs; d += DS_NT) text_off[d] = off[tok_off[d]];
+        const uint32_t words = ((uint32_t)total + 15u) >> 4;  // the host buffer is 16-byte aligned with room to spare
+        for (uint32_t w = tid; w < words; w += DS_NT) reinterpret_cast<uint4*>(text)[w] = stage[w];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (tid == 0) {
+        hdr->total = total;
+        hdr->flags = (any & DS_BAD_ID) | (give_up && !(any & DS_BAD_ID) ? DS_FALLBACK : 0u);
+        __threadfence_system();
+        *done = seq;
+    }
+}
+
 }  // namespace hut

@@ -37,6 +37,14 @@ struct hut_decstate {
     cudaEvent_t ev[2];
     float last_ms;
     unsigned last_launches;
+    /* one-launch path (dec_small_kernel): pinned host buffers the kernel reads and writes directly */
+    int32_t* ds_ids;
+    unsigned long long* ds_tok;
+    uint8_t* ds_text;
+    unsigned long long* ds_toff;
+    DecSmallHdr* ds_hdr;
+    volatile unsigned int* ds_done;
+    unsigned int ds_seq;
     unsigned char* na_scratch; /* device address of g_noalloc_scratch on this context's decode device */
     int token_wise;  /* the per-token tables exist and HUTOKEN_B200_DECODE=general is not set */
     int last_path;   /* 1: token-wise kernels, 2: general kernels */
@@ -58,6 +66,12 @@ static void dec_free(hut_decstate* s) {
     cudaFree(s->d_bad);
     cudaFree(s->d_first_doc);
     cudaFreeHost(s->h_text);
+    cudaFreeHost(s->ds_ids);
+    cudaFreeHost(s->ds_tok);
+    cudaFreeHost(s->ds_text);
+    cudaFreeHost(s->ds_toff);
+    cudaFreeHost(s->ds_hdr);
+    cudaFreeHost((void*)s->ds_done);
     cudaFreeHost(s->h_text_off);
     if (s->ev[0]) cudaEventDestroy(s->ev[0]);
     if (s->ev[1]) cudaEventDestroy(s->ev[1]);
@@ -289,6 +303,58 @@ static int dec_run(hut_ctx* ctx, const int32_t* d_ids, unsigned long long n_ids,
     return HUT_STATUS_OK;
 }
 
+/* A few ids: one kernel launch on pinned host buffers, the host spins on the flag the kernel raises last.
+ * HUT_SMALL_RETRY: dec_run has to do it (a token that does not decode independently, or more text than fits). */
+static int decode_small(hut_ctx* ctx, const int32_t* ids, const uint64_t* tok_offsets, uint64_t n_docs,
+                        hut_text_result* result) {
+    hut_decstate* s = ctx->dec;
+    hut_dev* d = &ctx->dev[0];
+    const uint64_t base = tok_offsets[0], n = tok_offsets[n_docs] - base;
+    if (!s->ds_ids) {
+        CU(ctx, cudaMallocHost(&s->ds_ids, DS_MAX_IDS * sizeof(int32_t)));
+        CU(ctx, cudaMallocHost(&s->ds_tok, (DS_MAX_DOCS + 1) * sizeof(unsigned long long)));
+        CU(ctx, cudaMallocHost(&s->ds_text, DS_TEXT + 64));
+        CU(ctx, cudaMallocHost(&s->ds_toff, (DS_MAX_DOCS + 1) * sizeof(unsigned long long)));
+        CU(ctx, cudaMallocHost(&s->ds_hdr, sizeof(DecSmallHdr)));
+        CU(ctx, cudaMallocHost((void**)&s->ds_done, 64));
+        *s->ds_done = 0;
+        s->ds_seq = 0;
+    }
+    memcpy(s->ds_ids, ids + base, (size_t)n * sizeof(int32_t));
+    for (uint64_t i = 0; i <= n_docs; ++i) s->ds_tok[i] = tok_offsets[i] - base;
+    const unsigned int seq = ++s->ds_seq;
+    const DecModel& D = s->dm;
+    if (D.prefix_len)
+        dec_small_kernel<true><<<1, DS_NT, 0, d->stream>>>(D, s->ds_ids, (uint32_t)n, s->ds_tok, (uint32_t)n_docs, s->ds_text,
+                                                           s->ds_toff, s->ds_hdr, s->ds_done, seq);
+    else
+        dec_small_kernel<false><<<1, DS_NT, 0, d->stream>>>(D, s->ds_ids, (uint32_t)n, s->ds_tok, (uint32_t)n_docs, s->ds_text,
+                                                            s->ds_toff, s->ds_hdr, s->ds_done, seq);
+    CU(ctx, cudaGetLastError());
+    for (unsigned spins = 0; *s->ds_done != seq; ++spins) {
+        if ((spins & 0xFFFFu) == 0xFFFFu) {
+            cudaError_t e = cudaStreamQuery(d->stream);
+            if (e != cudaSuccess && e != cudaErrorNotReady)
+                return set_err(ctx, HUT_STATUS_CUDA, "CUDA error: %s", cudaGetErrorString(e));
+            if (e == cudaSuccess && *s->ds_done != seq)
+                return set_err(ctx, HUT_STATUS_CUDA, "%s", "dec_small_kernel ended without reporting");
+        }
+    }
+    if (s->ds_hdr->flags & DS_BAD_ID) /* core.c:522-530 */
+        return set_err(ctx, HUT_STATUS_VALUE, "%s", "Element must be non-negative and less than vocab size.");
+    if (s->ds_hdr->flags & DS_FALLBACK) return HUT_SMALL_RETRY;
+    const unsigned long long n_text = s->ds_hdr->total;
+    s->ds_text[n_text] = 0;
+    s->last_launches = 1;
+    s->last_ms = 0.0f;
+    s->last_path = 3;
+    result->text = s->ds_text;
+    result->text_offsets = (const uint64_t*)s->ds_toff;
+    result->n_bytes = n_text;
+    result->n_docs = n_docs;
+    return HUT_STATUS_OK;
+}
+
 extern "C" int hut_decode_batch(hut_ctx* ctx, const int32_t* ids, const uint64_t* tok_offsets, uint64_t n_docs,
                                 hut_text_result* result) {
     if (!ctx) return HUT_STATUS_STATE;
@@ -302,6 +368,11 @@ extern "C" int hut_decode_batch(hut_ctx* ctx, const int32_t* ids, const uint64_t
     for (uint64_t i = 0; i < n_docs; ++i)
         if (tok_offsets[i + 1] < tok_offsets[i]) return set_err(ctx, HUT_STATUS_ARG, "%s", "tok_offsets must not decrease");
     if (n_ids && !ids) return set_err(ctx, HUT_STATUS_ARG, "%s", "null argument");
+    if (s->token_wise && n_ids && n_ids <= (unsigned long long)DS_MAX_IDS && n_docs <= (uint64_t)DS_MAX_DOCS &&
+        !getenv("HUTOKEN_B200_NO_SMALL")) {
+        rc = decode_small(ctx, ids, tok_offsets, n_docs, result);
+        if (rc != HUT_SMALL_RETRY) return rc;
+    }
     cudaStream_t st = d->stream;
     CU(ctx, grow(&s->d_ids, &s->d_ids_cap, (size_t)n_ids + 1));
     CU(ctx, grow(&s->d_tok, &s->d_tok_cap, (size_t)n_docs + 1));

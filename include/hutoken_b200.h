@@ -125,7 +125,8 @@ int hut_decode_stats(const hut_ctx* ctx, double* kernel_ms, uint64_t* kernel_lau
 
 /* Which kernels the last decode call ran: 1 = token-wise (every token of the batch decodes independently of its
  * neighbours: lengths, scan, one copy pass), 2 = general (greedy scan of the concatenated token strings, tile by
- * tile; taken when a token ends inside a special-chars pattern or inside a character), 0 = no call yet.  Both
+ * tile; taken when a token ends inside a special-chars pattern or inside a character), 3 = token-wise in one kernel
+ * launch on pinned host buffers (hut_decode_batch of at most 2048 ids in at most 256 lists), 0 = no call yet.  All
  * produce the bytes of pretokenizer_decode (pretokenizer.c:197-296).  HUTOKEN_B200_DECODE=general in the environment
  * keeps a context to the general kernels. */
 int hut_decode_path(const hut_ctx* ctx);
