@@ -74,6 +74,7 @@ struct hut_dev {
     unsigned long long big_slot_words;
     uint32_t big_cap, big_slots;
     int grid, long_grid, sms;
+    int mid_grid[2];  /* resident one-warp CTAs of mid_kernel<1024> / <4096> */
     uint32_t stride, slot_extra;
     // grow-only temporaries shared by the device's flights (they run one after the other on the device's stream)
     int32_t* stage;
@@ -220,6 +221,12 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     {   // long_kernel walks its pretokens one merge at a time: many small CTAs in flight hide that latency
         int per = 0;
         CU(ctx, cudaFuncSetAttribute(long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(4 * LSM_CAP * sizeof(uint32_t))));
+        CU(ctx, cudaFuncSetAttribute(mid_kernel<4096>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(4 * 4096 * sizeof(uint32_t))));
+        int per1 = 0, per4 = 0;
+        CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per1, mid_kernel<1024>, 32, 4 * 1024 * sizeof(uint32_t)));
+        CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per4, mid_kernel<4096>, 32, 4 * 4096 * sizeof(uint32_t)));
+        d->mid_grid[0] = (per1 > 0 ? per1 : 1) * sms;
+        d->mid_grid[1] = (per4 > 0 ? per4 : 1) * sms;
         CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, long_kernel, LNT, 4 * LSM_CAP * sizeof(uint32_t)));
         if (per < 1) per = 1;
         if (per > 8) per = 8;
@@ -460,6 +467,9 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     if (pfx) tile_kernel<true><<<tile_grid, NT, 0, st>>>(d->dm, J);
     else tile_kernel<false><<<tile_grid, NT, 0, st>>>(d->dm, J);
     CU(ctx, cudaEventRecord(f->ev[2], st));
+    mid_kernel<1024><<<d->mid_grid[0], 32, 4 * 1024 * sizeof(uint32_t), st>>>(d->dm, J);
+    if (d->dm.inert < (1u << 20)) /* keys of rank << 12 | position in 32 bits */
+        mid_kernel<4096><<<d->mid_grid[1], 32, 4 * 4096 * sizeof(uint32_t), st>>>(d->dm, J);
     long_kernel<<<d->long_grid, LNT, 4 * LSM_CAP * sizeof(uint32_t), st>>>(d->dm, J);
     if (d->big_slots) huge_kernel<<<d->big_slots, HNT, 0, st>>>(d->dm, J);
     scan1_kernel<<<nblocks, 1024, 0, st>>>(J);
@@ -469,7 +479,7 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     fixdoc_kernel<<<(unsigned)((n_docs + 1 + 255) / 256), 256, 0, st>>>(J);
     CU(ctx, cudaEventRecord(f->ev[3], st));
     CU(ctx, cudaGetLastError());
-    d->stats.kernel_launches += 6 + (n_docs ? 1 : 0) + (pfx ? 1 : 0);
+    d->stats.kernel_launches += 7 + (d->dm.inert < (1u << 20) ? 1 : 0) + (n_docs ? 1 : 0) + (pfx ? 1 : 0);
     f->job = J;
     CU(ctx, cudaMemcpyAsync(f->h_ctr, f->ctr, offsetof(Counters, events), cudaMemcpyDeviceToHost, st));
     CU(ctx, cudaEventRecord(f->done, st));

@@ -115,7 +115,8 @@ struct Counters {
     unsigned int flags;
     unsigned int n_events;
     unsigned int n_def;
-    unsigned int ticket;           // next tile to hand out (tile_kernel)
+    unsigned int ticket;           // next deferred entry to hand out: mid_kernel<1024>
+    unsigned int ticket2, pad0;    // ... mid_kernel<4096>
     unsigned long long total_ids;
     unsigned long long long_used;  // bump pointer into long_ids
     unsigned long long st_pretokens, st_hits, st_warp, st_block, st_big, st_cut;
@@ -870,13 +871,14 @@ __device__ uint32_t cta_merge_run(const DevModel& M, const Job& J, LongSm& sm, u
         const uint32_t mg = MG[pos];
         return mg == NONE ? ~0ull : (((unsigned long long)rank_of_unit(M, mg) << 32) | pos);
     };
+    // minimum key of the warp.  Lane order is position order at every level (lane l of group g stands for position /
+    // child group g * 32 + l), so among equal ranks the lowest lane holds the smallest key: one hardware reduction
+    // of the ranks, one ballot, one shuffle instead of five 64-bit shuffle-and-compare steps.
     auto warp_min = [&](unsigned long long k) -> unsigned long long {
-#pragma unroll
-        for (int d = 16; d; d >>= 1) {
-            const unsigned long long o = __shfl_xor_sync(0xFFFFFFFFu, k, d);
-            k = o < k ? o : k;
-        }
-        return k;
+        const uint32_t r = (uint32_t)(k >> 32);
+        const uint32_t rm = __reduce_min_sync(0xFFFFFFFFu, r);
+        const uint32_t b = __ballot_sync(0xFFFFFFFFu, r == rm);
+        return __shfl_sync(0xFFFFFFFFu, k, __ffs(b) - 1);
     };
     for (uint32_t g = warp; g < lcnt[0]; g += LNW) {
         const unsigned long long k = warp_min(pos_key(g * 32u + lane));
@@ -918,16 +920,14 @@ __device__ uint32_t cta_merge_run(const DevModel& M, const Job& J, LongSm& sm, u
         j = __shfl_sync(0xFFFFFFFFu, j, 0);
         __syncwarp();
         uint32_t a0 = i >> 5, a1 = j >> 5, a2 = p != ENDLINK ? p >> 5 : a0;
-        {
-            unsigned long long k = warp_min(pos_key(a0 * 32u + lane));
-            if (lane == 0) lv[0][a0] = k;
-            if (a1 != a0) {
-                k = warp_min(pos_key(a1 * 32u + lane));
-                if (lane == 0) lv[0][a1] = k;
-            }
-            if (a2 != a0 && a2 != a1) {
-                k = warp_min(pos_key(a2 * 32u + lane));
-                if (lane == 0) lv[0][a2] = k;
+        {  // the three groups side by side (equal ones are simply done again: cheaper than a branch between them)
+            const unsigned long long k0 = pos_key(a0 * 32u + lane), k1 = pos_key(a1 * 32u + lane),
+                                     k2 = pos_key(a2 * 32u + lane);
+            const unsigned long long m0 = warp_min(k0), m1 = warp_min(k1), m2 = warp_min(k2);
+            if (lane == 0) {
+                lv[0][a0] = m0;
+                lv[0][a1] = m1;
+                lv[0][a2] = m2;
             }
         }
         __syncwarp();
@@ -937,18 +937,14 @@ __device__ uint32_t cta_merge_run(const DevModel& M, const Job& J, LongSm& sm, u
             a2 >>= 5;
             const unsigned long long* below = lv[l - 1];
             const uint32_t nb = lcnt[l - 1];
-            uint32_t c = a0 * 32u + lane;
-            unsigned long long k = warp_min(c < nb ? below[c] : ~0ull);
-            if (lane == 0) lv[l][a0] = k;
-            if (a1 != a0) {
-                c = a1 * 32u + lane;
-                k = warp_min(c < nb ? below[c] : ~0ull);
-                if (lane == 0) lv[l][a1] = k;
-            }
-            if (a2 != a0 && a2 != a1) {
-                c = a2 * 32u + lane;
-                k = warp_min(c < nb ? below[c] : ~0ull);
-                if (lane == 0) lv[l][a2] = k;
+            const uint32_t c0 = a0 * 32u + lane, c1 = a1 * 32u + lane, c2 = a2 * 32u + lane;
+            const unsigned long long k0 = c0 < nb ? below[c0] : ~0ull, k1 = c1 < nb ? below[c1] : ~0ull,
+                                     k2 = c2 < nb ? below[c2] : ~0ull;
+            const unsigned long long m0 = warp_min(k0), m1 = warp_min(k1), m2 = warp_min(k2);
+            if (lane == 0) {
+                lv[l][a0] = m0;
+                lv[l][a1] = m1;
+                lv[l][a2] = m2;
             }
             __syncwarp();
         }
@@ -1210,6 +1206,232 @@ __device__ void cta_merge_emit(const DevModel& M, LongSm& sm, const uint32_t* U,
         if (u != ENDLINK) dst[ob++] = id_of_unit(M, u);
     }
     __syncthreads();
+}
+
+// ------------------------------------------------------------------------------------------------
+// warp-cooperative merge of one pretoken of at most CAP symbols (mid_kernel): the same order as cta_merge_run --
+// the pair with the smallest (rank, left index) first, queue.c:162-164 -- without a tree.  Position q belongs to lane
+// q & 31; every lane keeps the minimum key (rank << log2 CAP | position) of its positions in a register, the next merge is
+// one hardware reduction over the 32 registers, and after a merge only the lanes that own the (at most three)
+// changed positions look at their positions again.  All lanes read the links of the merge themselves (broadcast reads
+// of shared memory), lanes 0 and 1 probe the two new neighbour pairs side by side, lane 0 stores.
+// W: 4 * CAP words of shared memory of this warp: unit, key, merged unit, links (next | previous << 16).
+// ------------------------------------------------------------------------------------------------
+constexpr uint32_t MID_END = 0xFFFFu;
+
+// First position >= from where the run of class `cls` ends (find_run_end for one warp); a value > stop once the scan
+// has passed `stop` without finding it.
+__device__ __forceinline__ unsigned long long warp_find_run_end(const Job& J, unsigned long long from,
+                                                                 unsigned long long lo, unsigned long long end,
+                                                                 uint32_t cls, unsigned long long stop) {
+    const uint32_t lane = threadIdx.x & 31u;
+    for (unsigned long long p0 = from;; p0 += 32) {
+        const unsigned long long p = p0 + lane;
+        bool bnd = true;  // the end of the document ends the run
+        if (p < end) {
+            const uint32_t c = gclass(J, p, lo, end);
+            bnd = (cls == HC_SPACE) ? (c != HC_SPACE) : (c != HC_CONT && c != cls);
+        }
+        const uint32_t mask = __ballot_sync(0xFFFFFFFFu, bnd);
+        if (mask) {
+            const unsigned long long f = p0 + (uint32_t)(__ffs(mask) - 1);
+            return f < end ? f : end;
+        }
+        if (p0 + 32 > stop) return p0 + 32;
+    }
+}
+
+// CAP: 1024 or 4096 symbols.  key = rank << log2(CAP) | position in 32 bits: CAP 4096 needs ranks below 2^20 (the
+// host launches that variant only then).  Every lane keeps one minimum per 1024 positions (32 of its own), so looking
+// at a changed position again costs 32 shared-memory loads whatever the capacity.
+// returns the number of ids (the survivors + the ids emitted alone before the first pretoken); 0xFFFFFFFF if the
+// pretoken has more than CAP symbols (nothing done).
+template <uint32_t CAP>
+__device__ __forceinline__ uint32_t warp_merge_count(const DevModel& M, const Job& J, const uint32_t* byte1,
+                                                     unsigned long long gs, unsigned long long ge, bool with_prefix,
+                                                     bool alone_first, uint32_t* W, uint32_t* m_out) {
+    constexpr uint32_t SUBS = CAP / 1024u;
+    constexpr uint32_t POSB = CAP == 1024u ? 10u : 12u;
+    static_assert(CAP == 1024u || CAP == 4096u, "capacities with a key layout");
+    const uint32_t FULL = 0xFFFFFFFFu;
+    const uint32_t lane = threadIdx.x & 31u;
+    uint32_t* const U = W;
+    uint32_t* const KEY = W + CAP;
+    uint32_t* const MGv = W + 2 * CAP;
+    uint32_t* const LK = W + 3 * CAP;
+    auto at = [&](unsigned long long p) -> uint32_t { return (uint32_t)__ldg(J.text + p); };
+    const uint32_t len = (uint32_t)(ge - gs);
+    const uint32_t chunk = (len + 31u) >> 5;
+    unsigned long long a = gs + (unsigned long long)chunk * lane, b = a + chunk;
+    if (a > ge) a = ge;
+    if (b > ge) b = ge;
+    uint32_t cnt = 0;
+    for (unsigned long long p = a; p < b; ++p) {
+        uint32_t f, pb;
+        cnt += char_symbols(M, byte1, at, p, gs, ge, &f, &pb);
+    }
+    uint32_t inc = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(FULL, inc, d);
+        if (lane >= d) inc += t;
+    }
+    const uint32_t npfx = with_prefix ? M.n_prefix_syms : 0u;
+    const uint32_t m = __shfl_sync(FULL, inc, 31) + npfx;
+    if (m > CAP) return 0xFFFFFFFFu;
+    for (uint32_t i = lane; i < npfx; i += 32) U[i] = M.prefix_syms[i];
+    uint32_t w = inc - cnt + npfx;
+    for (unsigned long long p = a; p < b; ++p) {
+        uint32_t f = M.inert, pb = 0;
+        const uint32_t c = char_symbols(M, byte1, at, p, gs, ge, &f, &pb);
+        if (c == 1) U[w++] = f;
+        else
+            for (uint32_t k = 0; k < c; ++k) U[w++] = __ldg(M.sym_pool + pb + k);
+    }
+    __syncwarp();
+    auto key_of = [&](uint32_t mg, uint32_t pos) -> uint32_t {
+        return mg == NONE ? 0xFFFFFFFFu : ((rank_of_unit(M, mg) << POSB) | pos);
+    };
+    uint32_t lmin[SUBS];
+#pragma unroll
+    for (uint32_t sb = 0; sb < SUBS; ++sb) lmin[sb] = 0xFFFFFFFFu;
+    for (uint32_t i = lane; i < m; i += 32) {
+        const uint32_t mg = (i + 1 < m) ? pair_probe(M, U[i], U[i + 1]) : NONE;
+        const uint32_t k = key_of(mg, i);
+        MGv[i] = mg;
+        KEY[i] = k;
+        LK[i] = ((i + 1 < m) ? i + 1 : MID_END) | ((i ? i - 1 : MID_END) << 16);
+#pragma unroll
+        for (uint32_t sb = 0; sb < SUBS; ++sb)
+            if ((i >> 10) == sb) lmin[sb] = k < lmin[sb] ? k : lmin[sb];
+    }
+    __syncwarp();
+    // A merge needs the two new neighbour pairs probed in the pair table: one or two L2 round trips, by far the longest
+    // part of a step.  So the probes are made ahead of time, 32 candidates at once: every lane probes for the best pair
+    // of its own positions as if it were merged now (s_*: the position, the three units it saw, the two results), then
+    // merges are applied in key order for as long as the best pair's lane holds a guess made from the units that are
+    // still there.  A lane whose positions changed guesses again in the next pass; the best pair of all is always
+    // freshly guessed at the start of a pass, so every pass applies at least one merge.
+    uint32_t s_i = 0xFFFFFFFFu, s_up = 0, s_mi = 0, s_unj = 0, s_ml = NONE, s_mr = NONE;
+    for (;;) {
+        uint32_t mine = lmin[0];
+#pragma unroll
+        for (uint32_t sb = 1; sb < SUBS; ++sb) mine = lmin[sb] < mine ? lmin[sb] : mine;
+        if (__reduce_min_sync(FULL, mine) == 0xFFFFFFFFu) break;
+        // ---- guesses ----
+        if (mine != 0xFFFFFFFFu) {
+            const uint32_t ci = mine & (CAP - 1u);
+            const uint32_t lk = LK[ci];
+            const uint32_t cj = lk & 0xFFFFu, cp = lk >> 16;
+            const uint32_t cmi = MGv[ci];
+            const uint32_t cnj = LK[cj] & 0xFFFFu;
+            const uint32_t cup = cp != MID_END ? U[cp] : NONE;
+            const uint32_t cunj = cnj != MID_END ? U[cnj] : NONE;
+            if (!(s_i == ci && s_up == cup && s_mi == cmi && s_unj == cunj)) {
+                pair_probe2(M, cup, cmi, cunj, &s_ml, &s_mr);
+                s_i = ci;
+                s_up = cup;
+                s_mi = cmi;
+                s_unj = cunj;
+            }
+        }
+        __syncwarp();
+        // ---- merges, in key order, while the guesses hold ----
+        for (;;) {
+            mine = lmin[0];
+#pragma unroll
+            for (uint32_t sb = 1; sb < SUBS; ++sb) mine = lmin[sb] < mine ? lmin[sb] : mine;
+            const uint32_t best = __reduce_min_sync(FULL, mine);
+            if (best == 0xFFFFFFFFu) break;
+            const uint32_t i = best & (CAP - 1u);
+            const uint32_t lki = LK[i];
+            const uint32_t j = lki & 0xFFFFu, p = lki >> 16;
+            const uint32_t mi = MGv[i];
+            const uint32_t nj = LK[j] & 0xFFFFu;
+            const uint32_t up = p != MID_END ? U[p] : NONE;
+            const uint32_t unj = nj != MID_END ? U[nj] : NONE;
+            const uint32_t owner = i & 31u;
+            const uint32_t kj = KEY[j], kp = p != MID_END ? KEY[p] : 0xFFFFFFFFu;  // before the merge
+            const bool good = s_i == i && s_up == up && s_mi == mi && s_unj == unj;  // meaningful on the owner
+            if (!__shfl_sync(FULL, (int)good, owner)) break;
+            const uint32_t ml = __shfl_sync(FULL, s_ml, owner), mr = __shfl_sync(FULL, s_mr, owner);
+            if (lane == 0) {
+                U[i] = mi;
+                U[j] = ENDLINK;  // dead
+                MGv[j] = NONE;
+                KEY[j] = 0xFFFFFFFFu;
+                LK[i] = nj | (p << 16);
+                if (nj != MID_END) LK[nj] = (LK[nj] & 0xFFFFu) | (i << 16);
+                if (p != MID_END) {
+                    MGv[p] = ml;
+                    KEY[p] = key_of(ml, p);
+                }
+                MGv[i] = mr;  // NONE when i is the last symbol now
+                KEY[i] = key_of(mr, i);
+            }
+            __syncwarp();
+            // the lanes that own i, j and p look at the 32 positions of theirs around the changed one again
+            uint32_t todo = 0;
+            if (lane == owner) todo |= 1u << (i >> 10);  // its minimum was this pair
+            if (lane == (j & 31u) && kj != 0xFFFFFFFFu) {  // j's pair is gone: matters only if it was the lane's minimum
+#pragma unroll
+                for (uint32_t t = 0; t < SUBS; ++t)
+                    if (t == (j >> 10) && lmin[t] == kj) todo |= 1u << t;
+            }
+            if (p != MID_END && lane == (p & 31u)) {
+                const uint32_t kn = KEY[p];
+#pragma unroll
+                for (uint32_t t = 0; t < SUBS; ++t)
+                    if (t == (p >> 10)) {
+                        if (kn <= lmin[t]) lmin[t] = kn;
+                        else if (lmin[t] == kp) todo |= 1u << t;
+                    }
+            }
+            while (todo) {
+                const uint32_t sb = (uint32_t)__ffs(todo) - 1u;
+                todo &= todo - 1u;
+                // all 32 loads in flight before the first compare: the step is a chain of latencies, not of instructions
+                uint32_t v[32];
+                const uint32_t q0 = (sb << 10) + lane;
+#pragma unroll
+                for (uint32_t r = 0; r < 32; ++r) {
+                    const uint32_t q = q0 + r * 32u;
+                    v[r] = q < m ? KEY[q] : 0xFFFFFFFFu;
+                }
+#pragma unroll
+                for (uint32_t h = 16; h; h >>= 1)
+#pragma unroll
+                    for (uint32_t r = 0; r < h; ++r) v[r] = v[r + h] < v[r] ? v[r + h] : v[r];
+#pragma unroll
+                for (uint32_t t = 0; t < SUBS; ++t)
+                    if (t == sb) lmin[t] = v[0];
+            }
+        }
+    }
+    __syncwarp();
+    *m_out = m;
+    uint32_t live = 0;
+    for (uint32_t q = lane; q < m; q += 32) live += (U[q] != ENDLINK);
+#pragma unroll
+    for (int d = 16; d; d >>= 1) live += __shfl_xor_sync(FULL, live, d);
+    return live + (alone_first ? M.n_prefix_alone : 0u);
+}
+
+// the ids of the survivors, in order (warp_merge_count left them in W)
+__device__ __forceinline__ void warp_merge_emit(const DevModel& M, const uint32_t* W, uint32_t m, bool alone_first,
+                                                int32_t* dst) {
+    const uint32_t FULL = 0xFFFFFFFFu;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t nal = alone_first ? M.n_prefix_alone : 0u;
+    for (uint32_t i = lane; i < nal; i += 32) dst[i] = M.prefix_alone[i];
+    uint32_t ob = nal;
+    for (uint32_t q0 = 0; q0 < m; q0 += 32) {  // 32 positions at a time, compacted by a ballot
+        const uint32_t q = q0 + lane;
+        const uint32_t u = q < m ? W[q] : ENDLINK;
+        const uint32_t mask = __ballot_sync(FULL, u != ENDLINK);
+        if (u != ENDLINK) dst[ob + __popc(mask & ((1u << lane) - 1u))] = id_of_unit(M, u);
+        ob += __popc(mask);
+    }
 }
 
 }  // namespace hut

@@ -13,6 +13,7 @@ __global__ void init_kernel(Job J) {
         c->n_events = 0;
         c->n_def = 0;
         c->ticket = 0;
+        c->ticket2 = 0;
         c->total_ids = 0;
         c->long_used = 0;
         c->st_pretokens = c->st_hits = c->st_warp = c->st_block = c->st_big = c->st_cut = 0;
@@ -74,6 +75,7 @@ __device__ __forceinline__ void long_entries(const DevModel& M, const Job& J, Lo
         DefEntry* E = J.def + e;
         __syncthreads();
         if (HUGE && !(E->flags & 8u)) continue;  // uniform: every thread reads the same word
+        if (!HUGE && (E->flags & 4u)) continue;  // done by mid_kernel
         const unsigned long long gs = E->pos;
         const bool first = (E->flags & 1u) != 0;
         if (tid == 0) {  // end of the document containing gs: first doc_off > gs
@@ -163,6 +165,85 @@ __device__ __forceinline__ void long_entries(const DevModel& M, const Job& J, Lo
         if (HUGE) n_big++;
     }
     if (tid == 0 && n_big) atomicAdd(&J.ctr->st_big, n_big);
+}
+
+// mid_kernel<CAP>: one WARP per deferred pretoken of at most CAP symbols (most of them: a long word, a number, a
+// blob of a few hundred bytes) -- warp_merge_count, arrays in shared memory (16 bytes per symbol), no tree.  A merge
+// is one dependent chain (reduction, links, one table probe, stores), so what counts is how many chains the GPU has
+// in flight and how long a step of one is: CAP 1024 runs 12 one-warp CTAs per SM, CAP 4096 three (long_kernel: three
+// four-warp CTAs of which one warp works, and a tree to refresh), each probing the pair table for 32 candidate merges
+// at once (warp_merge_count).  Entries are handed out by a ticket counter.  Where tile_kernel did not see the end of the
+// pretoken the warp finds it (and leaves the length in the entry for the kernels after it).  Entries finished here
+// carry flag 4; long_kernel takes the rest: more symbols than 4096, pretokens to be cut, ranks of 2^20 and above.
+template <uint32_t CAP>
+__global__ void __launch_bounds__(32) mid_kernel(const DevModel M, const Job J) {
+    __shared__ uint32_t byte1[256];
+    extern __shared__ __align__(16) uint32_t mid_dyn[];  // 4 * CAP words
+    uint32_t* const W = mid_dyn;
+    const uint32_t lane = threadIdx.x;
+    uint32_t n = J.ctr->n_def;
+    if (n > J.def_cap) n = J.def_cap;
+    if (blockIdx.x >= n) return;
+    for (uint32_t i = lane; i < 256; i += 32) byte1[i] = M.byte1[i];
+    __syncwarp();
+    unsigned int* const ticket = CAP == 1024u ? &J.ctr->ticket : &J.ctr->ticket2;
+    for (;;) {  // entries handed out one at a time: their lengths differ by two orders of magnitude
+        uint32_t e = 0;
+        if (lane == 0) e = atomicAdd(ticket, 1u);
+        e = __shfl_sync(0xFFFFFFFFu, e, 0);
+        if (e >= n) break;
+        DefEntry* E = J.def + e;
+        const uint32_t flags = E->flags;
+        if (flags & (4u | 16u)) continue;  // done by the smaller variant / known to be beyond this path
+        uint32_t len = E->len;
+        const unsigned long long gs = E->pos;
+        if (len == 0) {  // the end lies beyond what the tile had loaded: look for it, up to 4096 bytes on
+            unsigned long long a = 0, b = J.ndocs + 1;  // end of the document containing gs: first doc_off > gs
+            while (a < b) {
+                const unsigned long long mid = (a + b) >> 1;
+                if (J.doc_off[mid] <= gs) a = mid + 1;
+                else b = mid;
+            }
+            unsigned long long dend = a <= J.ndocs ? J.doc_off[a] : J.nbytes;
+            if (dend > J.nbytes) dend = J.nbytes;
+            uint32_t cls = gclass(J, gs, gs, dend);
+            if (cls == HC_SPACE) {
+                const uint32_t c1 = gclass(J, gs + 1, gs, dend);
+                if (c1 >= HC_ALPHA && c1 <= HC_OTHER) cls = c1;
+            }
+            const unsigned long long ge = warp_find_run_end(J, gs + 1, gs, dend, cls, gs + 4096u);
+            if (ge - gs > 4096u) {
+                if (lane == 0) E->flags = flags | 16u;
+                continue;
+            }
+            len = (uint32_t)(ge - gs);
+            if (lane == 0) E->len = len;
+        }
+        if (len > CAP || len > M.limit) continue;
+        const unsigned long long ge = gs + len;
+        const bool first = (flags & 1u) != 0;
+        const uint32_t b0 = __ldg(J.text + gs);
+        const bool with_prefix = first && b0 != ' ', alone_first = first && b0 == ' ';
+        uint32_t m = 0;
+        const uint32_t cnt = warp_merge_count<CAP>(M, J, byte1, gs, ge, with_prefix, alone_first, W, &m);
+        if (cnt == 0xFFFFFFFFu) continue;  // more than CAP symbols
+        unsigned long long off = 0;
+        if (lane == 0) off = atomicAdd(&J.ctr->long_used, (unsigned long long)cnt);
+        off = __shfl_sync(0xFFFFFFFFu, off, 0);
+        if (off + cnt > J.long_cap) {
+            set_flag(J, FLAG_LONG_CAP);  // the host grows long_ids and runs the shard again
+        } else if (cnt) {
+            warp_merge_emit(M, W, m, alone_first, J.long_ids + off);
+        }
+        __syncwarp();
+        if (lane == 0) {
+            E->count = cnt;
+            E->ids_off = off;
+            E->flags = flags | 4u;
+            atomicAdd(&J.tot[E->tile], cnt);
+        }
+        __syncwarp();
+    }
 }
 
 __global__ void __launch_bounds__(LNT) long_kernel(const DevModel M, const Job J) {
