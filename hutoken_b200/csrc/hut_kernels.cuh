@@ -341,15 +341,16 @@ __device__ __forceinline__ uint32_t build_key(const uint8_t* text, const uint4* 
     return x0 & 0xFFu;  // the first text byte
 }
 
-__device__ __forceinline__ uint32_t cache_hash(const uint32_t x[4], uint32_t bits) {
+__device__ __forceinline__ uint32_t cache_hash_raw(const uint32_t x[4]) {
     uint32_t h = x[0] * 0x9E3779B1u;
     h += x[1] * 0x85EBCA77u;
     h += x[2] * 0xC2B2AE3Du;
     h += x[3] * 0x27D4EB2Fu;
     h ^= h >> 15;
     h *= 0x2C1B3C6Du;
-    return h >> (32 - bits);
+    return h;
 }
+__device__ __forceinline__ uint32_t cache_hash(const uint32_t x[4], uint32_t bits) { return cache_hash_raw(x) >> (32 - bits); }
 
 __device__ __forceinline__ int32_t sext21(uint32_t w) {
     int32_t r;
@@ -568,11 +569,23 @@ __device__ __forceinline__ uint32_t char_symbols(const DevModel& M, const uint32
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 
+template <bool WIDE> struct AliveMask { using type = uint32_t; };
+template <> struct AliveMask<true> { using type = unsigned long long; };
+__device__ __forceinline__ int al_ffs(uint32_t x) { return __ffs((int)x); }
+__device__ __forceinline__ int al_ffs(unsigned long long x) { return __ffsll((long long)x); }
+__device__ __forceinline__ int al_top(uint32_t x) { return 31 - __clz((int)x); }
+__device__ __forceinline__ int al_top(unsigned long long x) { return 63 - __clzll((long long)x); }
+__device__ __forceinline__ int al_popc(uint32_t x) { return __popc(x); }
+__device__ __forceinline__ int al_popc(unsigned long long x) { return __popcll(x); }
+
 template <int S>
 __device__ __forceinline__ uint32_t merge_entry(const DevModel& M, const Job& J, const uint32_t* byte1,
                                                 unsigned long long pos, uint32_t len, uint32_t first, uint32_t room,
                                                 int32_t* dst) {
+    static_assert(S <= 64 && S % 4 == 0, "positions are packed into 6 bits of the scan keys, which are read four at a time");
+    using AL = typename AliveMask<(S > 32)>::type;  // one bit per initial symbol
     uint32_t U[S], MG[S];
+    __align__(16) uint32_t KEY[S];
     auto at = [&](unsigned long long p) -> uint32_t { return (uint32_t)__ldg(J.text + p); };
     const uint32_t b0 = at(pos);
     const bool with_prefix = first && b0 != ' ';
@@ -581,13 +594,16 @@ __device__ __forceinline__ uint32_t merge_entry(const DevModel& M, const Job& J,
     const uint32_t nal = alone_first ? M.n_prefix_alone : 0u;
     // ---- initial symbols (A.3) + the cache key ----
     uint32_t m = 0;
+#pragma unroll 1
     for (uint32_t k = 0; k < npfx; ++k) U[m++] = M.prefix_syms[k];
     unsigned long long k0 = 0, k1 = 0, k2 = 0, k3 = 0;
+#pragma unroll 1
     for (uint32_t p = 0; p < len; ++p) {
         uint32_t unit = M.inert, pb = 0;
         const uint32_t cnt = char_symbols(M, byte1, at, pos + p, pos, pos + len, &unit, &pb);
         if (cnt == 1) U[m++] = unit;
         else
+#pragma unroll 1
             for (uint32_t k = 0; k < cnt; ++k) U[m++] = __ldg(M.sym_pool + pb + k);
         const unsigned long long b = at(pos + p);
         if (p < 8) k0 |= b << (8 * p);
@@ -599,42 +615,56 @@ __device__ __forceinline__ uint32_t merge_entry(const DevModel& M, const Job& J,
     // Symbols never move: a merged-away symbol is cleared in `alive` and neighbours are found with bit scans, so the
     // array index of the scans is the same in every lane (coalesced local memory) ----
     const uint32_t m0 = m;
+#pragma unroll 1
     for (uint32_t k = 0; k + 1 < m0; ++k) {
         const uint32_t l = U[k], r = U[k + 1];
         if (l < M.inert && r < M.inert) prefetch_l1(M.pair_tab + hut_pair_hash(l, r, M.pair_mask));
     }
-    for (uint32_t k = 0; k < m0; ++k) MG[k] = k + 1 < m0 ? pair_probe(M, U[k], U[k + 1]) : NONE;
-    unsigned long long alive = m0 >= 64 ? ~0ull : ((1ull << m0) - 1ull);
+    // KEY[k] = rank of the pair starting at position k in bits 6.., k below (ranks are dense, < 2^21: hut_model.c), all
+    // ones if the pair does not merge: the minimum over KEY is the reference's next merge, leftmost among equal ranks
+    auto keyof = [&](uint32_t mg, uint32_t k) -> uint32_t { return mg == NONE ? 0xFFFFFFFFu : ((rank_of_unit(M, mg) << 6) | k); };
+#pragma unroll 1
+    for (uint32_t k = 0; k < m0; ++k) {
+        const uint32_t mg = k + 1 < m0 ? pair_probe(M, U[k], U[k + 1]) : NONE;
+        MG[k] = mg;
+        KEY[k] = keyof(mg, k);
+    }
+#pragma unroll 1
+    for (uint32_t k = m0; k < ((m0 + 3u) & ~3u); ++k) KEY[k] = 0xFFFFFFFFu;  // the scan reads groups of four
+    AL alive = m0 >= (uint32_t)(8 * sizeof(AL)) ? ~(AL)0 : (((AL)1 << m0) - (AL)1);
     for (;;) {
-        uint32_t best = 0xFFFFFFFFu, j = 0, mu = NONE;
-        for (uint32_t k = 0; k + 1 < m0; ++k) {
-            const uint32_t mg = MG[k];
-            const uint32_t rk = rank_of_unit(M, mg);
-            if (rk < best) {
-                best = rk;
-                j = k;
-                mu = mg;
-            }
+        uint32_t bk = 0xFFFFFFFFu;
+#pragma unroll 1
+        for (uint32_t k = 0; k < m0; k += 4) {
+            const uint4 v = *reinterpret_cast<const uint4*>(&KEY[k]);
+            bk = min(min(bk, v.x), min(min(v.y, v.z), v.w));
         }
-        if (best == 0xFFFFFFFFu) break;
-        const uint32_t r = j + 1 + (uint32_t)(__ffsll((long long)(alive >> (j + 1))) - 1);  // right partner of j
-        alive &= ~(1ull << r);
+        if (bk == 0xFFFFFFFFu) break;
+        const uint32_t j = bk & 63u, mu = MG[j];
+        const uint32_t r = j + 1 + (uint32_t)(al_ffs(alive >> (j + 1)) - 1);  // right partner of j
+        alive &= ~((AL)1 << r);
         U[j] = mu;
         MG[r] = NONE;
-        const unsigned long long below = alive & ((1ull << j) - 1ull), above = alive >> (r + 1);
-        const int l = below ? 63 - __clzll((long long)below) : -1;
-        const int r2 = above ? (int)(r + 1) + (__ffsll((long long)above) - 1) : -1;
+        KEY[r] = 0xFFFFFFFFu;
+        const AL below = alive & (((AL)1 << j) - (AL)1), above = r + 1 < (uint32_t)(8 * sizeof(AL)) ? (alive >> (r + 1)) : (AL)0;
+        const int l = below ? al_top(below) : -1;
+        const int r2 = above ? (int)(r + 1) + (al_ffs(above) - 1) : -1;
         const uint32_t ul = l >= 0 ? U[l] : NONE, ur = r2 >= 0 ? U[r2] : NONE;
         uint32_t ml, mr;
         pair_probe2(M, ul, mu, ur, &ml, &mr);
-        if (l >= 0) MG[l] = ml;
+        if (l >= 0) {
+            MG[l] = ml;
+            KEY[l] = keyof(ml, (uint32_t)l);
+        }
         MG[j] = mr;  // NONE when j is the last symbol now
+        KEY[j] = keyof(mr, j);
     }
     // ---- ids into the reserved room, HOLEs behind them ----
-    const uint32_t total = nal + (uint32_t)__popcll(alive);  // <= room by construction (tile_kernel reserves the worst case)
+    const uint32_t total = nal + (uint32_t)al_popc(alive);  // <= room by construction (tile_kernel reserves the worst case)
     int32_t t5[CACHE_IDS] = {0, 0, 0, 0, 0};
     {
         uint32_t k = 0;
+#pragma unroll 1
         for (; k < nal; ++k) {
             const int32_t id = M.prefix_alone[k];
 #pragma unroll
@@ -642,14 +672,16 @@ __device__ __forceinline__ uint32_t merge_entry(const DevModel& M, const Job& J,
                 if (k == (uint32_t)z) t5[z] = id;
             dst[k] = id;
         }
+#pragma unroll 1
         for (uint32_t i = 0; i < m0; ++i) {
-            if (!((alive >> i) & 1ull)) continue;
+            if (!((alive >> i) & (AL)1)) continue;
             const int32_t id = id_of_unit(M, U[i]);
 #pragma unroll
             for (int z = 0; z < CACHE_IDS; ++z)
                 if (k == (uint32_t)z) t5[z] = id;
             dst[k++] = id;
         }
+#pragma unroll 1
         for (; k < room; ++k) dst[k] = HOLE;
     }
     if (M.cache_ok && total >= 1 && total <= (uint32_t)CACHE_IDS) {

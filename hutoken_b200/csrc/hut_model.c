@@ -1174,10 +1174,13 @@ int hut_model_load(hut_model** out, const char* vocab_path, const char* special_
         rc = fail(msg, msglen, HUT_ERR_MEMORY, "out of memory");
         goto out;
     }
+    /* rank_of is a DENSE rank: vocab units are ordered by (value, bytes), so the index of the first unit carrying a
+     * value orders the units exactly as the values do (ties stay ties), and it fits the 21-bit unit range -- the merge
+     * loops pack it with a position into one 32-bit key.  Only the order of ranks is ever used (core.c:111-176). */
     for (uint32_t u = 0; u <= m->n_units; ++u) {
         int is_vocab = u < m->n_vocab;
         m->out_id[u] = is_vocab ? b.units.val[u] : -1;
-        m->rank_of[u] = is_vocab ? b.units.val[u] : INT_MAX;
+        m->rank_of[u] = !is_vocab ? INT_MAX : (u && b.units.val[u] == b.units.val[u - 1]) ? m->rank_of[u - 1] : (int32_t)u;
         if (u < m->n_units && m->unit_len[u] > m->max_unit_len) m->max_unit_len = m->unit_len[u];
     }
 

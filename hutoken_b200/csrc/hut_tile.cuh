@@ -11,19 +11,42 @@
 #define HUT_PPL 1        // pretokens a lane handles per round of the tile kernel (measured: 2 or 3 probes in flight per lane are slower, 6.2 / 9.0 ms against 3.8: the scattered 32-byte loads already saturate the L1TEX pipe)
 #endif
 
+#ifndef HUT_FRONT_BITS
+#define HUT_FRONT_BITS 0  // log2 of the entries of the CTA's front table (0 = none)
+#endif
+
 namespace hut {
 
+// Front table: a direct-mapped table in the CTA's (dynamic) shared memory, consulted before the pretoken cache in
+// global memory.  One 16-byte entry = the first 8 key bytes, then value word 0 (id 0 + count, bits 0..23) with the
+// key's meta byte in bits 24..31, then value word 1 -- so only pretokens of at most 8 bytes with at most 2 ids live
+// here.  Entries are copies of values read from the pretoken cache (never computed here), written and read with one
+// 128-bit shared-memory access per lane, and a later writer simply replaces the entry.
+constexpr int FRONT_BITS = HUT_FRONT_BITS;
+constexpr uint32_t FRONT_BYTES = FRONT_BITS ? (16u << FRONT_BITS) : 0u;
+
+// Cache misses are merged 32 at a time, one per lane, and a batch takes as long as its longest pretoken (the merge
+// loop is quadratic in the symbols).  They therefore wait in one queue per length class, so that the many short
+// ones (numbers, short rare words) are not held up by a long word in every batch.
+#ifndef HUT_MISS_CLASSES
+#define HUT_MISS_CLASSES 1
+#endif
+#ifndef HUT_MISS_SHORT
+#define HUT_MISS_SHORT 7
+#endif
+constexpr int MISS_CLASSES = HUT_MISS_CLASSES;
+constexpr int MISS_SHORT = HUT_MISS_SHORT;  // longest pretoken (bytes) of class 0
 
 // shared memory of ONE WARP of tile_kernel
 struct __align__(16) WarpSm {
     uint8_t text[TEXTB];        // span bytes: [tile_start - 32, tile_start + 992 + 16), then zero padding
     uint32_t dsm[CHUNK + 4];    // per chunk: document starts
     uint16_t pstart[SPAN + 8];  // span positions of the boundaries in chunks 1..31 (31 = halo), then the end sentinel
-    uint4 q[64];                // cache misses waiting for a full batch: pos_off (x, y), meta (z), tile (w)
+    uint4 q[MISS_CLASSES][64];  // cache misses waiting for a full batch, by length class: pos_off (x, y), meta (z), tile (w)
     unsigned long long mbar;
     // what only the rounds with cache misses / long pretokens touch lives here, not in registers (warp-uniform values,
     // written by lane 0 or by all lanes alike)
-    uint32_t qn;                // entries of q
+    uint32_t qn[MISS_CLASSES];  // entries of q[]
     uint32_t slack;             // room reserved for misses of the tile in work that stayed unused
     uint32_t holes;             // the tile in work has reserved room
     uint32_t def_head, def_tail;  // chain of the tile's pretokens handed to long_kernel
@@ -108,7 +131,11 @@ __device__ __forceinline__ void defer_push(const Job& J, uint32_t tile, unsigned
 
 // merges the first n (<= 32) queued cache misses, one per lane (merge_entry).  The room a pretoken of another tile
 // did not use is subtracted from that tile's count here; for the tile in progress it is returned (warp sum).
+#ifdef HUT_BATCH_NOINLINE
+__device__ __noinline__ uint32_t run_batch(const DevModel& M, const Job& J, const uint32_t* byte1, const uint4* q,
+#else
 __device__ __forceinline__ uint32_t run_batch(const DevModel& M, const Job& J, const uint32_t* byte1, const uint4* q,
+#endif
                                            uint32_t n, uint32_t cur_tile) {
     const uint32_t lane = threadIdx.x & 31;
     uint32_t slack = 0;
@@ -163,28 +190,34 @@ __device__ __forceinline__ void rare_round(const DevModel& M, const Job& J, Tile
         // ---- cache misses -> this warp's queue; every 32 of them -- of this tile and of earlier ones -- are
         // merged at once, one per lane (merge_entry), so that their table probes overlap; what a miss leaves
         // unused of its room stays behind as HOLEs, which compact_kernel drops ----
-        const uint32_t m2 = __ballot_sync(FULL, state == 2);
-        if (m2) {
-            uint32_t qn = ws.qn;
-            const unsigned long long po = (unsigned long long)(g0 + s) | ((unsigned long long)off << 40);
-            if (state == 2)
-                ws.q[qn + __popc(m2 & lt_mask)] = make_uint4((uint32_t)po, (uint32_t)(po >> 32),
-                                                             (uint32_t)len | (first << 8) | (c << 16), tile);
-            qn += __popc(m2);
-            __syncwarp();
+        if (__any_sync(FULL, state == 2)) {
             uint32_t slack = 0, nb = 0;
-            while (qn >= 32) {
-                slack += run_batch(M, J, sm.byte1, ws.q, 32, tile);
-                nb += 32;
-                uint4 t = make_uint4(0, 0, 0, 0);
-                if (lane + 32 < qn) t = ws.q[lane + 32];
+            const unsigned long long po = (unsigned long long)(g0 + s) | ((unsigned long long)off << 40);
+            const uint32_t mycls = (MISS_CLASSES > 1 && len > MISS_SHORT) ? 1u : 0u;
+#pragma unroll 1
+            for (uint32_t cls = 0; cls < (uint32_t)MISS_CLASSES; ++cls) {  // one copy of the merge code for all classes
+                const uint32_t m2 = __ballot_sync(FULL, state == 2 && mycls == cls);
+                if (!m2) continue;
+                uint4* const q = ws.q[cls];
+                uint32_t qn = ws.qn[cls];
+                if (state == 2 && mycls == cls)
+                    q[qn + __popc(m2 & lt_mask)] = make_uint4((uint32_t)po, (uint32_t)(po >> 32),
+                                                              (uint32_t)len | (first << 8) | (c << 16), tile);
+                qn += __popc(m2);
                 __syncwarp();
-                if (lane + 32 < qn) ws.q[lane] = t;
-                qn -= 32;
-                __syncwarp();
+                while (qn >= 32) {
+                    slack += run_batch(M, J, sm.byte1, q, 32, tile);
+                    nb += 32;
+                    uint4 t = make_uint4(0, 0, 0, 0);
+                    if (lane + 32 < qn) t = q[lane + 32];
+                    __syncwarp();
+                    if (lane + 32 < qn) q[lane] = t;
+                    qn -= 32;
+                    __syncwarp();
+                }
+                if (lane == 0) ws.qn[cls] = qn;
             }
             if (lane == 0) {
-                ws.qn = qn;
                 ws.holes = 1;
                 ws.slack += slack;
                 ws.st_miss += nb;
@@ -218,8 +251,9 @@ __device__ __forceinline__ void rare_round(const DevModel& M, const Job& J, Tile
 
 // PFX: the model has a prefix (first pretoken of a document keyed apart and merged with the prefix symbols; staging
 // slots of uneven size read from J.slot_off); without one the slot of a tile is tile * stride.
-template <bool PFX>
-__device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileSm& sm, const uint32_t gw, const uint32_t nw) {
+template <bool PFX, int FB>
+__device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileSm& sm, uint4* front, const uint32_t gw,
+                                          const uint32_t nw) {
     const int tid = threadIdx.x, warp = tid >> 5;
     int lane;  // read once from the special register (kept from being recomputed from %tid inside the loops)
     asm volatile("mov.u32 %0, %%laneid;" : "=r"(lane));
@@ -228,6 +262,8 @@ __device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileS
     WarpSm& ws = sm.w[warp];
 
     for (int i = tid; i < 256; i += NT) sm.byte1[i] = M.byte1[i];
+    if (FB)
+        for (int i = tid; i < (1 << FB); i += NT) front[i] = make_uint4(0u, 0u, 0u, 0u);
     if (tid < 16) {
         auto wm = [&](int rem) -> uint32_t { return rem >= 4 ? 0xFFFFFFFFu : (rem <= 0 ? 0u : ((1u << (8 * rem)) - 1u)); };
         sm.kmask[tid] = make_uint4(wm(tid), wm(tid - 4), wm(tid - 8), wm(tid - 12));
@@ -244,7 +280,10 @@ __device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileS
     __syncthreads();  // the only block-wide barrier: the tables above are read-only afterwards
 
     uint32_t parity = 0;
-    if (lane == 0) ws.qn = ws.st_pre = ws.st_miss = ws.st_def = 0;
+    if (lane == 0) {
+        ws.st_pre = ws.st_miss = ws.st_def = 0;
+        for (int cls = 0; cls < MISS_CLASSES; ++cls) ws.qn[cls] = 0;
+    }
     __syncwarp();
 
     for (uint32_t tile = gw; tile < J.ntiles; tile += nw) {
@@ -263,7 +302,9 @@ __device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileS
             mbar_expect_tx(&ws.mbar, body);
             tma_load_1d(ws.text + lo_li, J.text + lo, body, &ws.mbar);
         }
+#pragma unroll 1
         for (int li = lane; li < lo_li; li += 32) ws.text[li] = 0;
+#pragma unroll 1
         for (int li = lo_li + (int)body + lane; li < TEXTB; li += 32) ws.text[li] = li < hi_li ? J.text[g0 + li] : 0;
         ws.dsm[lane] = 0;
         if (lane < 4) ws.dsm[CHUNK + lane] = 0;
@@ -366,7 +407,8 @@ __device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileS
             // PPL pretokens per lane and round (lane + 32 * h): their cache probes are in flight together
             int s[PPL], e[PPL];
             bool active[PPL], keyed[PPL], hit[PPL];
-            uint32_t dsb[PPL], b0[PPL], key[PPL][4], w[PPL][4], slot_i[PPL];
+            uint32_t dsb[PPL], b0[PPL], key[PPL][4], w[PPL][4], slot_i[PPL], fidx[PPL];
+            bool fhit[PPL];
             uint4 sa[PPL], sb[PPL];
             bool unkeyed = false;
 #pragma unroll
@@ -381,10 +423,23 @@ __device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileS
                 dsb[h] = 0;
                 if (tile_docs) dsb[h] = (ws.dsm[s[h] >> 5] >> (s[h] & 31)) & 1u;
                 b0[h] = build_key(ws.text, sm.kmask, s[h], keyed[h] ? len : 0, PFX ? dsb[h] : 0u, key[h]);
-                slot_i[h] = cache_hash(key[h], J.cache_bits);
+                const uint32_t hraw = cache_hash_raw(key[h]);
+                slot_i[h] = hraw >> (32 - J.cache_bits);
                 hit[h] = false;
 #pragma unroll
                 for (int z = 0; z < 4; ++z) w[h][z] = 0u;
+                fhit[h] = false;
+                if (FB) {
+                    // an empty entry (all zero) never matches: the meta byte of a key is never zero
+                    fidx[h] = (hraw >> 7) & ((1u << FB) - 1u);
+                    const uint4 f = front[fidx[h]];
+                    fhit[h] = f.x == key[h][0] && f.y == key[h][1] && ((f.z ^ key[h][3]) >> 24) == 0u;
+                    if (fhit[h]) {
+                        w[h][0] = f.z & 0x00FFFFFFu;
+                        w[h][1] = f.w;
+                        hit[h] = true;
+                    }
+                }
             }
 #pragma unroll
             for (int h = 0; h < PPL; ++h) {
@@ -395,7 +450,7 @@ __device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileS
                     sb[h] = make_uint4((1u << 21) | (slot_i[h] & 0xFFFFu), 0u, 0u, 0u);
                 }
 #else
-                if (active[h] && keyed[h] && M.cache_ok) ld_slot256(J.cache + slot_i[h], sa[h], sb[h]);
+                if (active[h] && keyed[h] && M.cache_ok && !fhit[h]) ld_slot256(J.cache + slot_i[h], sa[h], sb[h]);
 #endif
             }
             // pretokens of 16..31 bytes (rare): second cache, 32-byte keys
@@ -423,6 +478,8 @@ __device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileS
                     }
                 }
                 c[h] = hit[h] ? val_count(w[h][0]) : 0u;
+                if (FB && hit[h] && !fhit[h] && c[h] <= 2u && e[h] - s[h] <= 8)
+                    front[fidx[h]] = make_uint4(key[h][0], key[h][1], (w[h][0] & 0x00FFFFFFu) | (key[h][3] & 0xFF000000u), w[h][1]);
                 need = need || (active[h] && !hit[h]);
             }
             if (!__any_sync(FULL, need)) {
@@ -476,12 +533,14 @@ __device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileS
     }
     // ---- the misses still queued ----
     __syncwarp();
-    {
-        const uint32_t qn = ws.qn;
+#pragma unroll 1
+    for (uint32_t cls = 0; cls < (uint32_t)MISS_CLASSES; ++cls) {
+        const uint32_t qn = ws.qn[cls];
         if (qn) {
-            run_batch(M, J, sm.byte1, ws.q, qn, NODOC);
+            run_batch(M, J, sm.byte1, ws.q[cls], qn, NODOC);
             if (lane == 0) ws.st_miss += qn;
         }
+        __syncwarp();
     }
     // ---- statistics (a warp sees fewer than 2^32 pretokens: 2 TB of text over >= 8 warps) ----
     if (lane == 0) {
@@ -498,7 +557,8 @@ template <bool PFX>
 __global__ void __launch_bounds__(NT, HUT_TILE_CTAS) tile_kernel(const __grid_constant__ DevModel M,
                                                                  const __grid_constant__ Job J) {
     __shared__ TileSm sm;
-    tile_body<PFX>(M, J, sm, blockIdx.x * WPB + (threadIdx.x >> 5), gridDim.x * WPB);
+    extern __shared__ __align__(16) uint4 front_dyn[];  // FRONT_BYTES of dynamic shared memory
+    tile_body<PFX, FRONT_BITS>(M, J, sm, front_dyn, blockIdx.x * WPB + (threadIdx.x >> 5), gridDim.x * WPB);
 }
 
 }  // namespace hut
