@@ -202,6 +202,7 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     dm.limit = ctx->opt.max_pretoken ? ctx->opt.max_pretoken : 262144ull;  // core.c:27-28
 
     d->cache_bits = ctx->opt.cache_log2_slots ? ctx->opt.cache_log2_slots : 22;
+    if (!ctx->opt.cache_log2_slots && getenv("HUTOKEN_B200_CACHE_LOG2")) d->cache_bits = (uint32_t)atoi(getenv("HUTOKEN_B200_CACHE_LOG2"));  // tuning sweeps
     if (d->cache_bits < 10) d->cache_bits = 10;
     if (d->cache_bits > 26) d->cache_bits = 26;
     CU(ctx, cudaMalloc(&d->cache, sizeof(CacheSlot) << d->cache_bits));
@@ -212,12 +213,8 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     CU(ctx, cudaMalloc(&d->cut, sizeof(CutRanges)));
 
     int per_sm = 0, sms = 0;
-    if (FRONT_BYTES) {
-        CU(ctx, cudaFuncSetAttribute(tile_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FRONT_BYTES));
-        CU(ctx, cudaFuncSetAttribute(tile_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FRONT_BYTES));
-    }
-    if (m->has_prefix) CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile_kernel<true>, NT, FRONT_BYTES));
-    else CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile_kernel<false>, NT, FRONT_BYTES));
+    if (m->has_prefix) CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile_kernel<true>, NT, 0));
+    else CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile_kernel<false>, NT, 0));
     CU(ctx, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
     if (per_sm < 1) per_sm = 1;
     d->sms = sms;
@@ -468,8 +465,8 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     CU(ctx, cudaEventRecord(f->ev[1], st));
     const uint32_t want = (ntiles + WPB - 1) / WPB;
     const uint32_t tile_grid = want < (uint32_t)d->grid ? want : (uint32_t)d->grid;
-    if (pfx) tile_kernel<true><<<tile_grid, NT, FRONT_BYTES, st>>>(d->dm, J);
-    else tile_kernel<false><<<tile_grid, NT, FRONT_BYTES, st>>>(d->dm, J);
+    if (pfx) tile_kernel<true><<<tile_grid, NT, 0, st>>>(d->dm, J);
+    else tile_kernel<false><<<tile_grid, NT, 0, st>>>(d->dm, J);
     CU(ctx, cudaEventRecord(f->ev[2], st));
     mid_kernel<1024><<<d->mid_grid[0], 32, 4 * 1024 * sizeof(uint32_t), st>>>(d->dm, J);
     if (d->dm.inert < (1u << 20)) /* keys of rank << 12 | position in 32 bits */

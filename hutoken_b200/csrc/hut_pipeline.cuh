@@ -545,7 +545,7 @@ __global__ void __launch_bounds__(NT, 1) small_kernel(const __grid_constant__ De
     if (PFX)
         for (uint32_t t = tid; t <= J.ntiles; t += NT) slot_docs(J, const_cast<unsigned long long*>(J.slot_off), t);
     __syncthreads();
-    tile_body<PFX, 0>(M, J, sm, nullptr, tid >> 5, WPB);
+    tile_body<PFX>(M, J, sm, tid >> 5, WPB);
     __syncthreads();
     const bool give_up = J.ctr->n_def != 0 || (J.ctr->flags & ~(unsigned)FLAG_NUL) != 0;
     if (!give_up) {

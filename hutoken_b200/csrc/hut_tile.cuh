@@ -7,23 +7,8 @@
 #ifndef HUT_TILE_CTAS
 #define HUT_TILE_CTAS 4  // resident CTAs per SM the tile kernel is compiled for (64 registers per thread)
 #endif
-#ifndef HUT_PPL
-#define HUT_PPL 1        // pretokens a lane handles per round of the tile kernel (measured: 2 or 3 probes in flight per lane are slower, 6.2 / 9.0 ms against 3.8: the scattered 32-byte loads already saturate the L1TEX pipe)
-#endif
-
-#ifndef HUT_FRONT_BITS
-#define HUT_FRONT_BITS 0  // log2 of the entries of the CTA's front table (0 = none)
-#endif
 
 namespace hut {
-
-// Front table: a direct-mapped table in the CTA's (dynamic) shared memory, consulted before the pretoken cache in
-// global memory.  One 16-byte entry = the first 8 key bytes, then value word 0 (id 0 + count, bits 0..23) with the
-// key's meta byte in bits 24..31, then value word 1 -- so only pretokens of at most 8 bytes with at most 2 ids live
-// here.  Entries are copies of values read from the pretoken cache (never computed here), written and read with one
-// 128-bit shared-memory access per lane, and a later writer simply replaces the entry.
-constexpr int FRONT_BITS = HUT_FRONT_BITS;
-constexpr uint32_t FRONT_BYTES = FRONT_BITS ? (16u << FRONT_BITS) : 0u;
 
 // Cache misses are merged 32 at a time, one per lane, and a batch takes as long as its longest pretoken (the merge
 // loop is quadratic in the symbols).  They therefore wait in one queue per length class, so that the many short
@@ -53,7 +38,6 @@ struct __align__(16) WarpSm {
     uint32_t st_pre, st_miss, st_def, st_pad;  // statistics of this warp
 };
 
-constexpr int PPL = HUT_PPL;
 
 struct TileSm {
     uint4 kmask[16];            // kmask[len]: byte masks of a 16-byte key holding len text bytes
@@ -251,19 +235,16 @@ __device__ __forceinline__ void rare_round(const DevModel& M, const Job& J, Tile
 
 // PFX: the model has a prefix (first pretoken of a document keyed apart and merged with the prefix symbols; staging
 // slots of uneven size read from J.slot_off); without one the slot of a tile is tile * stride.
-template <bool PFX, int FB>
-__device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileSm& sm, uint4* front, const uint32_t gw,
-                                          const uint32_t nw) {
+template <bool PFX>
+__device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileSm& sm, const uint32_t gw, const uint32_t nw) {
     const int tid = threadIdx.x, warp = tid >> 5;
     int lane;  // read once from the special register (kept from being recomputed from %tid inside the loops)
     asm volatile("mov.u32 %0, %%laneid;" : "=r"(lane));
     const uint32_t FULL = 0xFFFFFFFFu;
-    const uint32_t lt_mask = (1u << lane) - 1u;
+    const uint32_t le_mask = 0xFFFFFFFFu >> (31 - lane);  // lanes up to and including this one
     WarpSm& ws = sm.w[warp];
 
     for (int i = tid; i < 256; i += NT) sm.byte1[i] = M.byte1[i];
-    if (FB)
-        for (int i = tid; i < (1 << FB); i += NT) front[i] = make_uint4(0u, 0u, 0u, 0u);
     if (tid < 16) {
         auto wm = [&](int rem) -> uint32_t { return rem >= 4 ? 0xFFFFFFFFu : (rem <= 0 ? 0u : ((1u << (8 * rem)) - 1u)); };
         sm.kmask[tid] = make_uint4(wm(tid), wm(tid - 4), wm(tid - 8), wm(tid - 12));
@@ -279,6 +260,8 @@ __device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileS
     }
     __syncthreads();  // the only block-wide barrier: the tables above are read-only afterwards
 
+    const uint32_t hshift = 32u - J.cache_bits;
+    const uint32_t probe_len = M.cache_ok ? (uint32_t)CACHE_KEY_MAX : 0u;  // longest pretoken looked up in the cache
     uint32_t parity = 0;
     if (lane == 0) {
         ws.st_pre = ws.st_miss = ws.st_def = 0;
@@ -403,107 +386,68 @@ __device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileS
         }
         __syncwarp();
         int32_t* const slot = J.stage + (PFX ? slot_o : (unsigned long long)tile * J.stride);
-        for (uint32_t r0 = 0; r0 < n; r0 += 32 * PPL) {
-            // PPL pretokens per lane and round (lane + 32 * h): their cache probes are in flight together
-            int s[PPL], e[PPL];
-            bool active[PPL], keyed[PPL], hit[PPL];
-            uint32_t dsb[PPL], b0[PPL], key[PPL][4], w[PPL][4], slot_i[PPL], fidx[PPL];
-            bool fhit[PPL];
-            uint4 sa[PPL], sb[PPL];
-            bool unkeyed = false;
-#pragma unroll
-            for (int h = 0; h < PPL; ++h) {
-                const uint32_t q = r0 + 32u * h + lane;
-                active[h] = q < n;
-                s[h] = active[h] ? ws.pstart[q] : BACK;
-                e[h] = active[h] ? ws.pstart[q + 1] : BACK;
-                const int len = e[h] - s[h];             // > MAXW when the end lies beyond the halo (BEYOND)
-                keyed[h] = len <= CACHE_KEY_MAX;
-                unkeyed = unkeyed || !keyed[h];
-                dsb[h] = 0;
-                if (tile_docs) dsb[h] = (ws.dsm[s[h] >> 5] >> (s[h] & 31)) & 1u;
-                b0[h] = build_key(ws.text, sm.kmask, s[h], keyed[h] ? len : 0, PFX ? dsb[h] : 0u, key[h]);
-                const uint32_t hraw = cache_hash_raw(key[h]);
-                slot_i[h] = hraw >> (32 - J.cache_bits);
-                hit[h] = false;
-#pragma unroll
-                for (int z = 0; z < 4; ++z) w[h][z] = 0u;
-                fhit[h] = false;
-                if (FB) {
-                    // an empty entry (all zero) never matches: the meta byte of a key is never zero
-                    fidx[h] = (hraw >> 7) & ((1u << FB) - 1u);
-                    const uint4 f = front[fidx[h]];
-                    fhit[h] = f.x == key[h][0] && f.y == key[h][1] && ((f.z ^ key[h][3]) >> 24) == 0u;
-                    if (fhit[h]) {
-                        w[h][0] = f.z & 0x00FFFFFFu;
-                        w[h][1] = f.w;
-                        hit[h] = true;
-                    }
+        const uint32_t hmask = (1u << J.cache_bits) - 1u;
+        for (uint32_t r0 = 0; r0 < n; r0 += 32) {
+            // ---- one pretoken per lane: key -> one 32-byte probe of the pretoken cache.  The code from here to the
+            // `continue` of the all-answered case is the hot path of the engine and is kept short on purpose: the SM's
+            // instruction cache holds little more than this loop, the classifier and one copy of the merge code ----
+            const uint32_t q = r0 + lane;
+            const bool active = q < n;
+            int s = BACK, e = BACK;
+            if (active) {
+                s = ws.pstart[q];
+                e = ws.pstart[q + 1];
+            }
+            const int len = e - s;                   // > MAXW when the end lies beyond the halo (BEYOND); 0 on idle lanes
+            const bool keyed = len <= CACHE_KEY_MAX;
+            uint32_t dsb = 0;
+            if (tile_docs) dsb = (ws.dsm[s >> 5] >> (s & 31)) & 1u;
+            uint32_t key[4];
+            const uint32_t b0 = build_key(ws.text, sm.kmask, s, keyed ? len : 0, PFX ? dsb : 0u, key);
+            const uint32_t slot_i = cache_hash_raw(key) >> hshift;
+            // an idle lane, a long pretoken or a disabled cache ask for nothing: the slot then reads as all zero, which no
+            // key equals (the meta byte of a key is never zero)
+            uint4 sa = make_uint4(0u, 0u, 0u, 0u), sb = make_uint4(0u, 0u, 0u, 0u);
+            if (active && (uint32_t)len <= probe_len) ld_slot256(J.cache + slot_i, sa, sb);
+            bool hit = sa.x == key[0] && sa.y == key[1] && sa.z == key[2] && sa.w == key[3];
+            if (!hit && (sa.x | sa.y) != 0u) {       // the slot holds another pretoken: walk on (few lanes, few steps)
+                uint32_t i = slot_i;
+#pragma unroll 1
+                for (int p = 1; p < CACHE_PROBES; ++p) {
+                    i = (i + 1u) & hmask;
+                    ld_slot256(J.cache + i, sa, sb);
+                    if ((sa.x | sa.y) == 0u) break;
+                    hit = sa.x == key[0] && sa.y == key[1] && sa.z == key[2] && sa.w == key[3];
+                    if (hit) break;
                 }
             }
-#pragma unroll
-            for (int h = 0; h < PPL; ++h) {
-                sa[h] = make_uint4(0u, 0u, 0u, 0u);
-#ifdef HUT_EXP_NOPROBE  // timing experiment only: every keyed pretoken "hits" with one id, no load is issued
-                if (active[h] && keyed[h]) {
-                    sa[h] = make_uint4(key[h][0], key[h][1], key[h][2], key[h][3]);
-                    sb[h] = make_uint4((1u << 21) | (slot_i[h] & 0xFFFFu), 0u, 0u, 0u);
-                }
-#else
-                if (active[h] && keyed[h] && M.cache_ok && !fhit[h]) ld_slot256(J.cache + slot_i[h], sa[h], sb[h]);
-#endif
-            }
-            // pretokens of 16..31 bytes (rare): second cache, 32-byte keys
-            if (__any_sync(FULL, unkeyed)) {
-#pragma unroll
-                for (int h = 0; h < PPL; ++h) {
-                    const int len = e[h] - s[h];
-                    if (active[h] && !keyed[h] && len <= CACHE2_KEY_MAX && M.cache_ok) {
-                        uint32_t k32[8];
-                        build_key32(ws.text, sm.kmask32, s[h], len, PFX ? dsb[h] : 0u, k32);
-                        hit[h] = cache2_lookup(J, k32, w[h]);
-                    }
-                }
-            }
-            uint32_t c[PPL];
-            bool need = false;
-#pragma unroll
-            for (int h = 0; h < PPL; ++h) {
-                if ((sa[h].x | sa[h].y) != 0u) {  // an empty slot (or no probe at all) is a miss
-                    if (sa[h].x == key[h][0] && sa[h].y == key[h][1] && sa[h].z == key[h][2] && sa[h].w == key[h][3]) {
-                        w[h][0] = sb[h].x, w[h][1] = sb[h].y, w[h][2] = sb[h].z, w[h][3] = sb[h].w;
-                        hit[h] = val_count(sb[h].x) != 0u;
-                    } else {
-                        hit[h] = cache_lookup_from(J, key[h], w[h], (slot_i[h] + 1u) & ((1u << J.cache_bits) - 1u), CACHE_PROBES - 1);
-                    }
-                }
-                c[h] = hit[h] ? val_count(w[h][0]) : 0u;
-                if (FB && hit[h] && !fhit[h] && c[h] <= 2u && e[h] - s[h] <= 8)
-                    front[fidx[h]] = make_uint4(key[h][0], key[h][1], (w[h][0] & 0x00FFFFFFu) | (key[h][3] & 0xFF000000u), w[h][1]);
-                need = need || (active[h] && !hit[h]);
-            }
-            if (!__any_sync(FULL, need)) {
-                // ---- every pretoken of the round was answered by the cache: counts are 0..5, so three ballots scan them ----
-#pragma unroll
-                for (int h = 0; h < PPL; ++h) {
-                    const uint32_t m0 = __ballot_sync(FULL, c[h] & 1u), m1 = __ballot_sync(FULL, c[h] & 2u),
-                                   m2 = __ballot_sync(FULL, c[h] & 4u);
-                    const uint32_t off = run + __popc(m0 & lt_mask) + 2u * __popc(m1 & lt_mask) + 4u * __popc(m2 & lt_mask);
-                    if (hit[h]) put_hit_ids(slot + off, c[h], w[h]);
-                    if (tile_docs && active[h] && dsb[h]) doc_offsets_at(J, (unsigned long long)(g0 + s[h]), dfirst, off);
-                    run += __popc(m0) + 2u * __popc(m1) + 4u * __popc(m2);
-                }
+            uint32_t c = hit ? val_count(sb.x) : 0u;  // count 0: the value is still being written -> a miss
+            if (!__any_sync(FULL, active && c == 0u)) {
+                // ---- every pretoken of the round was answered by the cache: counts are 1..5, three ballots scan them ----
+                const uint32_t m0 = __ballot_sync(FULL, (c & 1u) != 0u), m1 = __ballot_sync(FULL, (c & 2u) != 0u),
+                               m2 = __ballot_sync(FULL, (c & 4u) != 0u);
+                const uint32_t incl = __popc(m0 & le_mask) + 2u * __popc(m1 & le_mask) + 4u * __popc(m2 & le_mask);
+                const uint32_t off = run + incl - c;
+                const uint32_t w[4] = {sb.x, sb.y, sb.z, sb.w};
+                if (c) put_hit_ids(slot + off, c, w);
+                if (tile_docs && active && dsb) doc_offsets_at(J, (unsigned long long)(g0 + s), dfirst, off);
+                run += __shfl_sync(FULL, incl, 31);
                 continue;
             }
-            // ---- some pretokens were not answered.  state of a lane's pretoken: 0 nothing / hit, 2 cache miss merged by
-            // this warp (batches of 32), 3 long pretoken -> long_kernel.  A miss reserves room for its worst case (one
-            // id per symbol + prefix ids). ----
-#pragma unroll
-            for (int h = 0; h < PPL; ++h) {
-                const int len = e[h] - s[h];
-                const uint32_t first = PFX ? dsb[h] : 0u;
-                uint32_t state = 0, cc = c[h];
-                if (active[h] && !hit[h] && b0[h] != 0) {  // b0 == 0: a NUL in the text, the call fails (FLAG_NUL)
+            // ---- some pretokens were not answered.  Pretokens of 16..31 bytes ask the second cache (32-byte keys) first ----
+            uint32_t w[4] = {sb.x, sb.y, sb.z, sb.w};
+            if (active && !keyed && len <= CACHE2_KEY_MAX && M.cache_ok) {
+                uint32_t k32[8];
+                build_key32(ws.text, sm.kmask32, s, len, PFX ? dsb : 0u, k32);
+                hit = cache2_lookup(J, k32, w);
+                c = hit ? val_count(w[0]) : 0u;
+            }
+            // state of a lane's pretoken: 0 nothing / answered, 2 cache miss merged by this warp (batches of 32), 3 long
+            // pretoken -> long_kernel.  A miss reserves room for its worst case (one id per symbol + prefix ids).
+            {
+                const uint32_t first = PFX ? dsb : 0u;
+                uint32_t state = 0, cc = c;
+                if (active && c == 0u && b0 != 0) {  // b0 == 0: a NUL in the text, the call fails (FLAG_NUL)
                     const bool lng = (uint32_t)len > M.miss_len_max ||
                                      (uint32_t)len * M.kmax + (first ? M.n_prefix_syms : 0u) > (uint32_t)MISS_SMALL;
                     state = lng ? 3u : 2u;
@@ -517,9 +461,9 @@ __device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileS
                 }
                 const uint32_t round_total = __shfl_sync(FULL, inc, 31);
                 const uint32_t off = run + inc - cc;     // position of this lane's ids (or room) in the tile's slot
-                if (hit[h]) put_hit_ids(slot + off, cc, w[h]);
-                if (__any_sync(FULL, state != 0)) rare_round(M, J, sm, ws, tile, s[h], e[h], first, cc, off, state);
-                if (tile_docs && active[h] && dsb[h]) doc_offsets_at(J, (unsigned long long)(g0 + s[h]), dfirst, off);
+                if (c) put_hit_ids(slot + off, c, w);
+                if (__any_sync(FULL, state != 0)) rare_round(M, J, sm, ws, tile, s, e, first, cc, off, state);
+                if (tile_docs && active && dsb) doc_offsets_at(J, (unsigned long long)(g0 + s), dfirst, off);
                 run += round_total;
             }
         }
@@ -557,8 +501,7 @@ template <bool PFX>
 __global__ void __launch_bounds__(NT, HUT_TILE_CTAS) tile_kernel(const __grid_constant__ DevModel M,
                                                                  const __grid_constant__ Job J) {
     __shared__ TileSm sm;
-    extern __shared__ __align__(16) uint4 front_dyn[];  // FRONT_BYTES of dynamic shared memory
-    tile_body<PFX, FRONT_BITS>(M, J, sm, front_dyn, blockIdx.x * WPB + (threadIdx.x >> 5), gridDim.x * WPB);
+    tile_body<PFX>(M, J, sm, blockIdx.x * WPB + (threadIdx.x >> 5), gridDim.x * WPB);
 }
 
 }  // namespace hut
