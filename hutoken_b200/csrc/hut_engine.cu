@@ -6,6 +6,7 @@
  * No CPU fallback: every id is produced by those kernels.
  */
 #include <cuda_runtime.h>
+#include <stdarg.h>
 
 #include <cstdio>
 #include <cstdlib>
@@ -113,6 +114,16 @@ struct hut_ctx {
 
 static int set_err(hut_ctx* ctx, int status, const char* fmt, const char* a) {
     if (ctx) snprintf(ctx->err, sizeof ctx->err, fmt, a);
+    return status;
+}
+static int set_errf(hut_ctx* ctx, int status, const char* fmt, ...) __attribute__((format(printf, 3, 4)));
+static int set_errf(hut_ctx* ctx, int status, const char* fmt, ...) {
+    if (ctx) {
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(ctx->err, sizeof ctx->err, fmt, ap);
+        va_end(ap);
+    }
     return status;
 }
 
@@ -533,7 +544,10 @@ static int finish_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, uint64_t n_docs
     if (c->flags & FLAG_BIG_CAP)
         return set_err(ctx, HUT_STATUS_UNSUPPORTED, "%s", "a pretoken exceeds the configured max_pretoken working area");
     if (c->flags & (FLAG_DEF_CAP | FLAG_LONG_CAP | FLAG_BIG_NEED))
-        return set_err(ctx, HUT_STATUS_MEMORY, "%s", "side buffers for long pretokens could not be sized");
+        return set_errf(ctx, HUT_STATUS_MEMORY,
+                       "side buffers for long pretokens still too small after 4 re-runs: %u deferred pretokens, %llu of their ids%s",
+                       c->n_def, (unsigned long long)c->long_used,
+                       (c->flags & FLAG_BIG_NEED) ? ", working area for pretokens beyond 4096 symbols missing" : "");
     if (c->flags & FLAG_EVENTS)
         return set_err(ctx, HUT_STATUS_UNSUPPORTED, "%s", "too many over-long pretokens in one call");
     if (c->flags & FLAG_NUL)
@@ -866,6 +880,34 @@ extern "C" int hut_encode_batch(hut_ctx* ctx, const uint8_t* bytes, const uint64
         if (e != cudaSuccess) return bail(set_err(ctx, HUT_STATUS_CUDA, "CUDA error: %s", cudaGetErrorString(e)));
     }
     for (int i = 0; i < ndev; ++i) stats_begin(&ctx->dev[i]);
+    // device buffers of every (device, buffer) pair sized once for the largest chunk it will see, before anything is
+    // queued: growing inside the loop would have to drain the device first (chunk_issue keeps that path as a net)
+    for (int i = 0; i < ndev; ++i)
+        for (int b = 0; b < 2; ++b) {
+            hut_dev* d = &ctx->dev[i];
+            hut_chunkbuf* c = &d->cb[b];
+            uint64_t nb = 0, nd = 0, worst = 0;
+            for (int k = 0; k < nch; ++k) {
+                if (plan[k].dev != i || plan[k].buf != b) continue;
+                const uint64_t kb = plan[k].byte_hi - plan[k].byte_lo, kd = plan[k].doc_hi - plan[k].doc_lo;
+                const uint64_t kw = kb * d->dm.kmax + kd * (uint64_t)(d->dm.n_prefix_syms + d->dm.n_prefix_alone) + 64;
+                nb = kb > nb ? kb : nb;
+                nd = kd > nd ? kd : nd;
+                worst = kw > worst ? kw : worst;
+            }
+            if (!worst) continue;
+            if (nb + 64 > c->d_text_cap || nd + 1 > c->d_off_cap || nd + 1 > c->d_tok_cap || worst > c->d_ids_cap) {
+                cudaError_t e = cudaSetDevice(d->device);
+                if (e == cudaSuccess) e = cudaDeviceSynchronize();
+                if (e == cudaSuccess) e = grow(&c->d_text, &c->d_text_cap, (size_t)nb + 64);
+                if (e == cudaSuccess) e = grow(&c->d_off, &c->d_off_cap, (size_t)nd + 1);
+                if (e == cudaSuccess) e = grow(&c->d_tok, &c->d_tok_cap, (size_t)nd + 1);
+                if (e == cudaSuccess) e = grow(&c->d_ids, &c->d_ids_cap, (size_t)worst);
+                if (e != cudaSuccess) return bail(set_errf(ctx, e == cudaErrorMemoryAllocation ? HUT_STATUS_MEMORY : HUT_STATUS_CUDA,
+                                                          "chunk buffers of %llu text bytes / %llu ids: %s",
+                                                          (unsigned long long)nb, (unsigned long long)worst, cudaGetErrorString(e)));
+            }
+        }
     const int depth = 2 * ndev;
     uint64_t id_base = 0, bytes_done = 0;
     for (int k = 0; k < nch + depth; ++k) {

@@ -116,7 +116,8 @@ struct Counters {
     unsigned int n_events;
     unsigned int n_def;
     unsigned int ticket;           // next deferred entry to hand out: mid_kernel<1024>
-    unsigned int ticket2, pad0;    // ... mid_kernel<4096>
+    unsigned int ticket2;          // ... mid_kernel<4096>
+    unsigned int tile_ticket;      // next tile to hand out: tile_kernel
     unsigned long long total_ids;
     unsigned long long long_used;  // bump pointer into long_ids
     unsigned long long st_pretokens, st_hits, st_warp, st_block, st_big, st_cut;

@@ -14,6 +14,7 @@ __global__ void init_kernel(Job J) {
         c->n_def = 0;
         c->ticket = 0;
         c->ticket2 = 0;
+        c->tile_ticket = 0;
         c->total_ids = 0;
         c->long_used = 0;
         c->st_pretokens = c->st_hits = c->st_warp = c->st_block = c->st_big = c->st_cut = 0;
@@ -545,7 +546,7 @@ __global__ void __launch_bounds__(NT, 1) small_kernel(const __grid_constant__ De
     if (PFX)
         for (uint32_t t = tid; t <= J.ntiles; t += NT) slot_docs(J, const_cast<unsigned long long*>(J.slot_off), t);
     __syncthreads();
-    tile_body<PFX>(M, J, sm, tid >> 5, WPB);
+    tile_body<PFX, false>(M, J, sm, tid >> 5, WPB);
     __syncthreads();
     const bool give_up = J.ctr->n_def != 0 || (J.ctr->flags & ~(unsigned)FLAG_NUL) != 0;
     if (!give_up) {

@@ -235,7 +235,9 @@ __device__ __forceinline__ void rare_round(const DevModel& M, const Job& J, Tile
 
 // PFX: the model has a prefix (first pretoken of a document keyed apart and merged with the prefix symbols; staging
 // slots of uneven size read from J.slot_off); without one the slot of a tile is tile * stride.
-template <bool PFX>
+// DYN: tiles are handed out by a ticket counter (the ticket of the next tile is asked for while the current one is in
+// work), so that warps on faster SMs take more of them; otherwise warp gw takes tiles gw, gw + nw, ...
+template <bool PFX, bool DYN>
 __device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileSm& sm, const uint32_t gw, const uint32_t nw) {
     const int tid = threadIdx.x, warp = tid >> 5;
     int lane;  // read once from the special register (kept from being recomputed from %tid inside the loops)
@@ -269,7 +271,14 @@ __device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileS
     }
     __syncwarp();
 
-    for (uint32_t tile = gw; tile < J.ntiles; tile += nw) {
+    uint32_t tile = gw;
+    if (DYN) {
+        if (lane == 0) tile = atomicAdd(&J.ctr->tile_ticket, 1u);
+        tile = __shfl_sync(FULL, tile, 0);
+    }
+    while (tile < J.ntiles) {
+        uint32_t next_tile = tile + nw;
+        if (DYN && lane == 0) next_tile = atomicAdd(&J.ctr->tile_ticket, 1u);  // answered long before the tile is done
         unsigned long long slot_o = 0;
         if (PFX) slot_o = __ldg(J.slot_off + tile);  // asked for early: used only after the classifier
         const long long g0 = (long long)tile * OWN - BACK;  // global position of span index 0
@@ -474,6 +483,7 @@ __device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileS
             if (def_head != NODOC) J.def_first[tile] = def_head;
             ws.st_pre += n;
         }
+        tile = DYN ? __shfl_sync(FULL, next_tile, 0) : next_tile;
     }
     // ---- the misses still queued ----
     __syncwarp();
@@ -501,7 +511,11 @@ template <bool PFX>
 __global__ void __launch_bounds__(NT, HUT_TILE_CTAS) tile_kernel(const __grid_constant__ DevModel M,
                                                                  const __grid_constant__ Job J) {
     __shared__ TileSm sm;
-    tile_body<PFX>(M, J, sm, blockIdx.x * WPB + (threadIdx.x >> 5), gridDim.x * WPB);
+#ifdef HUT_STATIC_TILES
+    tile_body<PFX, false>(M, J, sm, blockIdx.x * WPB + (threadIdx.x >> 5), gridDim.x * WPB);
+#else
+    tile_body<PFX, true>(M, J, sm, blockIdx.x * WPB + (threadIdx.x >> 5), gridDim.x * WPB);
+#endif
 }
 
 }  // namespace hut
