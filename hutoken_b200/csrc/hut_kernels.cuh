@@ -514,7 +514,12 @@ __device__ __forceinline__ void cache_insert(const Job& J, const uint32_t x[4], 
             atomicExch(&s->w[0], w[0]);
             return;
         }
-        if (old == k0 && ld_volatile_u64(&s->k1) == k1) return;  // already there (or being written)
+        if (old == k0 && ld_volatile_u64(&s->k1) == k1) {  // already there (or being written)
+#ifdef HUT_EXP_DUPCOUNT  // experiment: merges whose result another warp had inserted meanwhile, reported as big_merges
+            atomicAdd(&J.ctr->st_big, 1ull);
+#endif
+            return;
+        }
         i = (i + 1) & mask;
     }
 }
