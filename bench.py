@@ -365,6 +365,7 @@ def run_ours(args):
     import torch
     import torch.distributed as dist
     import synth
+    import ctypes as C
     from hutoken_b200 import capi
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -498,6 +499,29 @@ def run_ours(args):
             last = int(ids_h[-1]) if len(ids_h) else 0  # the host reads the result  # noqa: F841
         barrier()
         e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+        # the inverse through the host-buffer call: the ids just returned (pinned host memory) -> text in pinned host
+        # memory, H2D of the ids and D2H of the text inside the timed region (hut_decode_batch streams document chunks)
+        e2e_dec = None
+        if not args.no_decode and len(ids_h):
+            try:
+                nd_h = len(tok_h) - 1
+                res_t = capi._TextResult()
+                call = lambda: eng._check(eng._lib.hut_decode_batch(eng._h, ids_h.ctypes.data, tok_h.ctypes.data, nd_h,  # noqa: E731
+                                                                    C.byref(res_t)))
+                call()
+                t0 = time.perf_counter()
+                reps = max(1, min(args.steps, 3))
+                for _ in range(reps):
+                    call()
+                dec_ms = (time.perf_counter() - t0) * 1e3 / reps
+                txt = np.ctypeslib.as_array(res_t.text, shape=(int(res_t.n_bytes),))
+                same = bool(int(res_t.n_bytes) == nbytes and np.array_equal(txt, data[:nbytes]))
+                e2e_dec = {"value": int(res_t.n_bytes) / (dec_ms * 1e-3) / 1e6, "unit": "decoded MB/s", "ms_per_call": dec_ms,
+                           "h2d_bytes": int(4 * len(ids_h) + 8 * (nd_h + 1)), "d2h_bytes": int(res_t.n_bytes) + 8 * (nd_h + 1),
+                           "round_trip_equals_input": same, "path": eng.decode_stats()["path"],
+                           "api": "hut_decode_batch (ids in pinned host memory -> text in pinned host memory)"}
+            except Exception as ex:  # the decode leg must never take the encode numbers down with it
+                e2e_dec = {"error": str(ex)[:200]}
 
     # ---- decode leg: the ids just produced, resident on the device, back to text ----
     def decode_once(eng_x, lg, tok_ptr, nd, steps):
@@ -665,6 +689,8 @@ def run_ours(args):
                            "d2h_bytes_per_step": int(4 * n_ids + 8 * (ndocs + 1)),
                            "ms_per_step": e2e_ms_max,
                            "api": "hut_encode_batch (host buffers in pinned memory -> ids in pinned memory)"}
+            if e2e_dec is not None:
+                line["e2e"]["decode"] = e2e_dec
         if not args.no_cpu_baseline and world >= 1:
             try:
                 if _ALL_CPUS:

@@ -45,6 +45,16 @@ struct hut_decstate {
     DecSmallHdr* ds_hdr;
     volatile unsigned int* ds_done;
     unsigned int ds_seq;
+    /* large host batches: document chunks streamed through two sets of input buffers (decode_chunked) */
+    int32_t* c_ids[2];
+    size_t c_ids_cap[2];
+    unsigned long long* c_tok[2];
+    size_t c_tok_cap[2];
+    unsigned long long* h_ctok[2]; /* pinned staging of a chunk's rebased offsets */
+    size_t h_ctok_cap[2];
+    cudaEvent_t ev_up[2];
+    float sum_ms;              /* kernel time / launches of the last call (all its chunks) */
+    unsigned sum_launches;
     unsigned char* na_scratch; /* device address of g_noalloc_scratch on this context's decode device */
     int token_wise;  /* the per-token tables exist and HUTOKEN_B200_DECODE=general is not set */
     int last_path;   /* 1: token-wise kernels, 2: general kernels */
@@ -73,6 +83,12 @@ static void dec_free(hut_decstate* s) {
     cudaFreeHost(s->ds_hdr);
     cudaFreeHost((void*)s->ds_done);
     cudaFreeHost(s->h_text_off);
+    for (int b = 0; b < 2; ++b) {
+        cudaFree(s->c_ids[b]);
+        cudaFree(s->c_tok[b]);
+        cudaFreeHost(s->h_ctok[b]);
+        if (s->ev_up[b]) cudaEventDestroy(s->ev_up[b]);
+    }
     if (s->ev[0]) cudaEventDestroy(s->ev[0]);
     if (s->ev[1]) cudaEventDestroy(s->ev[1]);
     free(s);
@@ -355,6 +371,110 @@ static int decode_small(hut_ctx* ctx, const int32_t* ids, const uint64_t* tok_of
     return HUT_STATUS_OK;
 }
 
+/* A large host batch goes through the device in chunks of whole documents: the ids of chunk k + 1 are uploaded (copy
+ * stream, second set of input buffers) while chunk k is decoded and its text downloaded (main stream), so the link is
+ * busy in both directions at once; the kernels (2 ms per GiB of text) disappear behind the copies.  Documents are
+ * decoded independently of each other (core.c:513-581 is called per document), so cutting between them changes nothing. */
+static int decode_chunked(hut_ctx* ctx, const int32_t* ids, const uint64_t* tok_offsets, uint64_t n_docs,
+                          unsigned long long chunk_ids, hut_text_result* result) {
+    hut_decstate* s = ctx->dec;
+    hut_dev* d = &ctx->dev[0];
+    cudaStream_t st = d->stream, sin = d->s_in;
+    std::vector<uint64_t> cut;  /* chunk c = documents [cut[c], cut[c + 1]) */
+    cut.push_back(0);
+    for (uint64_t i = 0; i < n_docs;) {
+        uint64_t j = i + 1;
+        while (j < n_docs && tok_offsets[j + 1] - tok_offsets[i] <= chunk_ids) ++j;
+        cut.push_back(j);
+        i = j;
+    }
+    const size_t nch = cut.size() - 1;
+    size_t max_ids = 0, max_docs = 0;
+    for (size_t c = 0; c < nch; ++c) {
+        const size_t ni = (size_t)(tok_offsets[cut[c + 1]] - tok_offsets[cut[c]]), nd = (size_t)(cut[c + 1] - cut[c]);
+        max_ids = ni > max_ids ? ni : max_ids;
+        max_docs = nd > max_docs ? nd : max_docs;
+    }
+    for (int b = 0; b < 2; ++b) {
+        CU(ctx, grow(&s->c_ids[b], &s->c_ids_cap[b], max_ids + 1));
+        CU(ctx, grow(&s->c_tok[b], &s->c_tok_cap[b], max_docs + 1));
+        CU(ctx, grow_host(&s->h_ctok[b], &s->h_ctok_cap[b], max_docs + 1, false));
+        if (!s->ev_up[b]) CU(ctx, cudaEventCreateWithFlags(&s->ev_up[b], cudaEventDisableTiming));
+    }
+    CU(ctx, grow_host(&s->h_text_off, &s->h_text_off_cap, (size_t)n_docs + 1, false));
+    auto upload = [&](size_t c) -> int {  /* the buffers of chunk c - 2 are free: dec_run(c - 2) has synchronised */
+        const int b = (int)(c & 1);
+        const uint64_t lo = cut[c], hi = cut[c + 1], base = tok_offsets[lo];
+        for (uint64_t i = lo; i <= hi; ++i) s->h_ctok[b][i - lo] = tok_offsets[i] - base;
+        CU(ctx, cudaMemcpyAsync(s->c_tok[b], s->h_ctok[b], (size_t)(hi - lo + 1) * sizeof(unsigned long long),
+                                cudaMemcpyHostToDevice, sin));
+        if (tok_offsets[hi] > base)
+            CU(ctx, cudaMemcpyAsync(s->c_ids[b], ids + base, (size_t)(tok_offsets[hi] - base) * sizeof(int32_t),
+                                    cudaMemcpyHostToDevice, sin));
+        CU(ctx, cudaEventRecord(s->ev_up[b], sin));
+        return HUT_STATUS_OK;
+    };
+    int rc = upload(0);
+    if (rc != HUT_STATUS_OK) return rc;
+    std::vector<unsigned long long> tbase(nch + 1, 0);
+    float ms_sum = 0;
+    unsigned launches = 0;
+    int path = 1;
+    for (size_t c = 0; c < nch; ++c) {
+        const int b = (int)(c & 1);
+        const uint64_t lo = cut[c], hi = cut[c + 1];
+        if (c + 1 < nch) {
+            /* h_ctok / c_ids of the other set were last read by chunk c - 1, whose dec_run has synchronised the main stream;
+             * its upload finished before that */
+            rc = upload(c + 1);
+            if (rc != HUT_STATUS_OK) return rc;
+        }
+        CU(ctx, cudaStreamWaitEvent(st, s->ev_up[b], 0));
+        unsigned long long n_text = 0;
+        rc = dec_run(ctx, s->c_ids[b], tok_offsets[hi] - tok_offsets[lo], s->c_tok[b], hi - lo, &n_text, st);
+        if (rc != HUT_STATUS_OK) {
+            cudaStreamSynchronize(sin);
+            return rc;
+        }
+        launches += s->last_launches;
+        if (s->last_path == 2) path = 2;
+        const unsigned long long need = tbase[c] + n_text + 1;
+        if (need > s->h_text_cap) {
+            /* room for the whole batch from the bytes per id seen so far (+ 1/8), at least what this chunk needs */
+            const unsigned long long done_ids = tok_offsets[hi] - tok_offsets[0], all_ids = tok_offsets[n_docs] - tok_offsets[0];
+            unsigned long long est = done_ids ? (unsigned long long)((double)(tbase[c] + n_text) / (double)done_ids * (double)all_ids) : need;
+            est += est / 8 + 4096;
+            CU(ctx, cudaStreamSynchronize(st)); /* earlier chunks' text is still on its way into the old buffer */
+            CU(ctx, grow_host(&s->h_text, &s->h_text_cap, (size_t)(est > need ? est : need), true));
+        }
+        if (n_text) CU(ctx, cudaMemcpyAsync(s->h_text + tbase[c], s->d_text, (size_t)n_text, cudaMemcpyDeviceToHost, st));
+        /* chunk-local text offsets of the chunk's documents (the chunk's end is the next one's start) */
+        CU(ctx, cudaMemcpyAsync(s->h_text_off + lo, s->d_text_off, (size_t)(hi - lo) * sizeof(unsigned long long),
+                                cudaMemcpyDeviceToHost, st));
+        tbase[c + 1] = tbase[c] + n_text;
+        /* the events of dec_run are re-recorded by the next chunk: read this chunk's kernel time once it is done.  The
+         * next dec_run synchronises the stream anyway, so this costs no overlap: the upload of chunk c + 1 is in flight. */
+        CU(ctx, cudaEventSynchronize(s->ev[1]));
+        float ms = 0;
+        cudaEventElapsedTime(&ms, s->ev[0], s->ev[1]);
+        ms_sum += ms;
+    }
+    CU(ctx, cudaStreamSynchronize(st));
+    for (size_t c = 1; c < nch; ++c)
+        for (uint64_t i = cut[c]; i < cut[c + 1]; ++i) s->h_text_off[i] += tbase[c];
+    s->h_text_off[n_docs] = tbase[nch];
+    if (!s->h_text) CU(ctx, grow_host(&s->h_text, &s->h_text_cap, 16, false));
+    s->h_text[tbase[nch]] = 0;
+    s->last_ms = ms_sum;
+    s->last_launches = launches;
+    s->last_path = path;
+    result->text = s->h_text;
+    result->text_offsets = (const uint64_t*)s->h_text_off;
+    result->n_bytes = tbase[nch];
+    result->n_docs = n_docs;
+    return HUT_STATUS_OK;
+}
+
 extern "C" int hut_decode_batch(hut_ctx* ctx, const int32_t* ids, const uint64_t* tok_offsets, uint64_t n_docs,
                                 hut_text_result* result) {
     if (!ctx) return HUT_STATUS_STATE;
@@ -372,6 +492,14 @@ extern "C" int hut_decode_batch(hut_ctx* ctx, const int32_t* ids, const uint64_t
         !getenv("HUTOKEN_B200_NO_SMALL")) {
         rc = decode_small(ctx, ids, tok_offsets, n_docs, result);
         if (rc != HUT_SMALL_RETRY) return rc;
+    }
+    {
+        /* ids per chunk: hut_options.chunk_mb of int32 ids (default 32 MiB); a batch of up to one and a half chunks goes in one piece */
+        unsigned long long chunk_ids = ((unsigned long long)(ctx->opt.chunk_mb ? ctx->opt.chunk_mb : 32u) << 20) / sizeof(int32_t);
+        if (getenv("HUTOKEN_B200_DECODE_CHUNK_IDS")) chunk_ids = strtoull(getenv("HUTOKEN_B200_DECODE_CHUNK_IDS"), nullptr, 10);  /* tests */
+        if (chunk_ids && n_docs > 1 && n_ids > chunk_ids + chunk_ids / 2) {
+            return decode_chunked(ctx, ids, tok_offsets, n_docs, chunk_ids, result);
+        }
     }
     cudaStream_t st = d->stream;
     CU(ctx, grow(&s->d_ids, &s->d_ids_cap, (size_t)n_ids + 1));

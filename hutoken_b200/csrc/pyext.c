@@ -120,11 +120,33 @@ static PyObject* p_initialize(PyObject* self, PyObject* args, PyObject* kwargs) 
     Py_RETURN_NONE;
 }
 
+/* The reference builds one PyLong per id (lib.c:840-868); a token id is one of at most 2^21 values and most of a
+ * result repeats a few thousand of them, so each value's int object is created once (on first use, under the GIL)
+ * and handed out again with a new reference afterwards: the lists hold ordinary ints equal to the reference's, built
+ * several times faster (bench.py `latency.batch_encode_list_api`). */
+#define ID_OBJ_MAX (1u << 21)
+static PyObject** g_id_obj; /* [ID_OBJ_MAX], NULL until an id is first seen; lives as long as the module */
+
+static inline PyObject* id_object(int32_t id) {
+    if ((uint32_t)id < ID_OBJ_MAX && g_id_obj) {
+        PyObject* v = g_id_obj[id];
+        if (!v) {
+            v = PyLong_FromLong(id);
+            if (!v) return NULL;
+            g_id_obj[id] = v; /* the table keeps its own reference */
+        }
+        Py_INCREF(v);
+        return v;
+    }
+    return PyLong_FromLong(id); /* -1 (unknown symbol), ids beyond the table, or no table */
+}
+
 static PyObject* ids_to_list(const int32_t* ids, uint64_t n) {
     PyObject* list = PyList_New((Py_ssize_t)n);
     if (!list) return PyErr_NoMemory();
+    if (!g_id_obj) g_id_obj = (PyObject**)calloc(ID_OBJ_MAX, sizeof(PyObject*)); /* pages touched only where ids occur */
     for (uint64_t i = 0; i < n; ++i) {
-        PyObject* v = PyLong_FromLong(ids[i]);
+        PyObject* v = id_object(ids[i]);
         if (!v) {
             Py_DECREF(list);
             return PyErr_NoMemory();

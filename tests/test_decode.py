@@ -212,6 +212,37 @@ def test_gpu_decode_corpus_round_trip(name):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("name", MODELS)
+def test_gpu_decode_streamed_chunks(name):
+    """hut_decode_batch streams a large host batch through the device in chunks of whole documents: forced here with
+    tiny chunks (a few hundred ids), the text and offsets equal those of the same call in one piece.  The batch holds
+    empty documents, documents larger than a chunk, and a non-zero first offset."""
+    from common import engine_for
+    eng = engine_for(name)
+    data, offs = synth.corpus(67, 1 << 20, special_every=500)
+    ids, tok = eng.encode_packed(data, offs)
+    keep = ids >= 0
+    cum = np.concatenate([[0], np.cumsum(keep)]).astype(np.uint64)
+    ids2, tok2 = ids[keep], cum[tok.astype(np.int64)]
+    nd = len(tok2) - 1
+    # empty documents sprinkled in (repeated offsets); the batch starts at document 3 (first offset > 0)
+    tok3 = np.sort(np.concatenate([tok2[3:], tok2[10:nd:7], tok2[-1:]])).astype(np.uint64)
+    whole_text, whole_off = eng.decode_packed(ids2, tok3)
+    one_piece = eng.decode_stats()
+    assert one_piece["path"] == "token-wise"
+    for chunk in ("300", "5000", "100000"):
+        os.environ["HUTOKEN_B200_DECODE_CHUNK_IDS"] = chunk
+        try:
+            text, toff = eng.decode_packed(ids2, tok3)
+        finally:
+            del os.environ["HUTOKEN_B200_DECODE_CHUNK_IDS"]
+        assert np.array_equal(toff, whole_off), (name, chunk)
+        assert text.tobytes() == whole_text.tobytes(), (name, chunk)
+        assert eng.decode_stats()["kernel_launches"] > one_piece["kernel_launches"]  # several chunks ran
+    eng.close()
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("byte_mode", [True, False])
 def test_gpu_decode_fuzz_models(byte_mode):
     from hutoken_b200 import capi
