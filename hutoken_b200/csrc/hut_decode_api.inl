@@ -52,9 +52,11 @@ struct hut_decstate {
     size_t c_tok_cap[2];
     unsigned long long* h_ctok[2]; /* pinned staging of a chunk's rebased offsets */
     size_t h_ctok_cap[2];
-    cudaEvent_t ev_up[2];
-    float sum_ms;              /* kernel time / launches of the last call (all its chunks) */
-    unsigned sum_launches;
+    cudaEvent_t ev_up[2], ev_k[2], ev_dl[2]; /* upload done / kernels done / download done, per buffer set */
+    uint8_t* x_text;           /* second set of output buffers: odd chunks decode into these while the even chunk's */
+    size_t x_text_cap;         /* text is still on its way to the host */
+    unsigned long long* x_text_off;
+    size_t x_text_off_cap;
     unsigned char* na_scratch; /* device address of g_noalloc_scratch on this context's decode device */
     int token_wise;  /* the per-token tables exist and HUTOKEN_B200_DECODE=general is not set */
     int last_path;   /* 1: token-wise kernels, 2: general kernels */
@@ -88,7 +90,11 @@ static void dec_free(hut_decstate* s) {
         cudaFree(s->c_tok[b]);
         cudaFreeHost(s->h_ctok[b]);
         if (s->ev_up[b]) cudaEventDestroy(s->ev_up[b]);
+        if (s->ev_k[b]) cudaEventDestroy(s->ev_k[b]);
+        if (s->ev_dl[b]) cudaEventDestroy(s->ev_dl[b]);
     }
+    cudaFree(s->x_text);
+    cudaFree(s->x_text_off);
     if (s->ev[0]) cudaEventDestroy(s->ev[0]);
     if (s->ev[1]) cudaEventDestroy(s->ev[1]);
     free(s);
@@ -379,7 +385,7 @@ static int decode_chunked(hut_ctx* ctx, const int32_t* ids, const uint64_t* tok_
                           unsigned long long chunk_ids, hut_text_result* result) {
     hut_decstate* s = ctx->dec;
     hut_dev* d = &ctx->dev[0];
-    cudaStream_t st = d->stream, sin = d->s_in;
+    cudaStream_t st = d->stream, sin = d->s_in, sout = d->s_out;
     std::vector<uint64_t> cut;  /* chunk c = documents [cut[c], cut[c + 1]) */
     cut.push_back(0);
     for (uint64_t i = 0; i < n_docs;) {
@@ -400,7 +406,15 @@ static int decode_chunked(hut_ctx* ctx, const int32_t* ids, const uint64_t* tok_
         CU(ctx, grow(&s->c_tok[b], &s->c_tok_cap[b], max_docs + 1));
         CU(ctx, grow_host(&s->h_ctok[b], &s->h_ctok_cap[b], max_docs + 1, false));
         if (!s->ev_up[b]) CU(ctx, cudaEventCreateWithFlags(&s->ev_up[b], cudaEventDisableTiming));
+        if (!s->ev_k[b]) CU(ctx, cudaEventCreateWithFlags(&s->ev_k[b], cudaEventDisableTiming));
+        if (!s->ev_dl[b]) CU(ctx, cudaEventCreateWithFlags(&s->ev_dl[b], cudaEventDisableTiming));
     }
+    auto swap_out = [&]() {  /* odd chunks use the second set of output buffers */
+        std::swap(s->d_text, s->x_text);
+        std::swap(s->d_text_cap, s->x_text_cap);
+        std::swap(s->d_text_off, s->x_text_off);
+        std::swap(s->d_text_off_cap, s->x_text_off_cap);
+    };
     CU(ctx, grow_host(&s->h_text_off, &s->h_text_off_cap, (size_t)n_docs + 1, false));
     auto upload = [&](size_t c) -> int {  /* the buffers of chunk c - 2 are free: dec_run(c - 2) has synchronised */
         const int b = (int)(c & 1);
@@ -430,12 +444,19 @@ static int decode_chunked(hut_ctx* ctx, const int32_t* ids, const uint64_t* tok_
             if (rc != HUT_STATUS_OK) return rc;
         }
         CU(ctx, cudaStreamWaitEvent(st, s->ev_up[b], 0));
+        if (c >= 2) CU(ctx, cudaStreamWaitEvent(st, s->ev_dl[b], 0)); /* the text of chunk c - 2 has left this output set */
         unsigned long long n_text = 0;
+        if (b) swap_out();
         rc = dec_run(ctx, s->c_ids[b], tok_offsets[hi] - tok_offsets[lo], s->c_tok[b], hi - lo, &n_text, st);
+        const uint8_t* const o_text = s->d_text;
+        const unsigned long long* const o_off = s->d_text_off;
+        if (b) swap_out();
         if (rc != HUT_STATUS_OK) {
             cudaStreamSynchronize(sin);
+            cudaStreamSynchronize(sout);
             return rc;
         }
+        CU(ctx, cudaEventRecord(s->ev_k[b], st));
         launches += s->last_launches;
         if (s->last_path == 2) path = 2;
         const unsigned long long need = tbase[c] + n_text + 1;
@@ -444,21 +465,25 @@ static int decode_chunked(hut_ctx* ctx, const int32_t* ids, const uint64_t* tok_
             const unsigned long long done_ids = tok_offsets[hi] - tok_offsets[0], all_ids = tok_offsets[n_docs] - tok_offsets[0];
             unsigned long long est = done_ids ? (unsigned long long)((double)(tbase[c] + n_text) / (double)done_ids * (double)all_ids) : need;
             est += est / 8 + 4096;
-            CU(ctx, cudaStreamSynchronize(st)); /* earlier chunks' text is still on its way into the old buffer */
+            CU(ctx, cudaStreamSynchronize(sout)); /* earlier chunks' text is still on its way into the old buffer */
             CU(ctx, grow_host(&s->h_text, &s->h_text_cap, (size_t)(est > need ? est : need), true));
         }
-        if (n_text) CU(ctx, cudaMemcpyAsync(s->h_text + tbase[c], s->d_text, (size_t)n_text, cudaMemcpyDeviceToHost, st));
+        /* download on its own stream: the next chunk's kernels (other output set) do not wait for it */
+        CU(ctx, cudaStreamWaitEvent(sout, s->ev_k[b], 0));
+        if (n_text) CU(ctx, cudaMemcpyAsync(s->h_text + tbase[c], o_text, (size_t)n_text, cudaMemcpyDeviceToHost, sout));
         /* chunk-local text offsets of the chunk's documents (the chunk's end is the next one's start) */
-        CU(ctx, cudaMemcpyAsync(s->h_text_off + lo, s->d_text_off, (size_t)(hi - lo) * sizeof(unsigned long long),
-                                cudaMemcpyDeviceToHost, st));
+        CU(ctx, cudaMemcpyAsync(s->h_text_off + lo, o_off, (size_t)(hi - lo) * sizeof(unsigned long long),
+                                cudaMemcpyDeviceToHost, sout));
+        CU(ctx, cudaEventRecord(s->ev_dl[b], sout));
         tbase[c + 1] = tbase[c] + n_text;
-        /* the events of dec_run are re-recorded by the next chunk: read this chunk's kernel time once it is done.  The
-         * next dec_run synchronises the stream anyway, so this costs no overlap: the upload of chunk c + 1 is in flight. */
+        /* the events of dec_run are re-recorded by the next chunk: read this chunk's kernel time once it is done (the
+         * next dec_run synchronises the main stream anyway; the copies of both directions are in flight meanwhile) */
         CU(ctx, cudaEventSynchronize(s->ev[1]));
         float ms = 0;
         cudaEventElapsedTime(&ms, s->ev[0], s->ev[1]);
         ms_sum += ms;
     }
+    CU(ctx, cudaStreamSynchronize(sout));
     CU(ctx, cudaStreamSynchronize(st));
     for (size_t c = 1; c < nch; ++c)
         for (uint64_t i = cut[c]; i < cut[c + 1]; ++i) s->h_text_off[i] += tbase[c];

@@ -239,7 +239,6 @@ def test_gpu_decode_streamed_chunks(name):
         assert np.array_equal(toff, whole_off), (name, chunk)
         assert text.tobytes() == whole_text.tobytes(), (name, chunk)
         assert eng.decode_stats()["kernel_launches"] > one_piece["kernel_launches"]  # several chunks ran
-    eng.close()
 
 
 @pytest.mark.gpu
