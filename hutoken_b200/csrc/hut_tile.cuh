@@ -10,6 +10,9 @@
 
 namespace hut {
 
+#define HUT_RARE(x) __builtin_expect(!!(x), 0)    // keeps the code behind it out of the hot path's cache lines
+#define HUT_USUAL(x) __builtin_expect(!!(x), 1)
+
 // Cache misses are merged 32 at a time, one per lane, and a batch takes as long as its longest pretoken (the merge
 // loop is quadratic in the symbols).  They therefore wait in one queue per length class, so that the many short
 // ones (numbers, short rare words) are not held up by a long word in every batch.
@@ -347,7 +350,7 @@ __device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileS
             uint32_t px = __shfl_up_sync(FULL, hut_bs_pack_prev(&loc, &mid), 1);
             if (lane == 0) px = 0;   // the look-back chunk's own starts are not used
             hut_bs_starts(&loc, &mid, px, &ST, &NU);
-            if (__any_sync(FULL, mid.EX != 0)) generic_chunk(ws.text, ws.dsm, lane, &ST, &NU);
+            if (HUT_RARE(__any_sync(FULL, mid.EX != 0))) generic_chunk(ws.text, ws.dsm, lane, &ST, &NU);
         }
         uint32_t bnd = ST | NU;
         if (lane == 31) bnd &= (1u << (TRUST - 31 * CHUNK)) - 1u;
@@ -356,7 +359,7 @@ __device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileS
         {
             const long long rem = (long long)J.nbytes - (g0 + lane * CHUNK);  // text bytes from this chunk's start on
             const uint32_t valid = rem >= 32 ? FULL : (rem <= 0 ? 0u : ((1u << rem) - 1u));
-            if (lane >= 1 && lane <= 30 && (NU & valid)) set_flag(J, FLAG_NUL);  // a NUL inside the text
+            if (HUT_RARE(lane >= 1 && lane <= 30 && (NU & valid))) set_flag(J, FLAG_NUL);  // a NUL inside the text
             const uint32_t keep = rem >= 31 ? FULL : (rem < 0 ? 0u : ((2u << rem) - 1u));
             bnd &= keep;
         }
@@ -419,7 +422,7 @@ __device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileS
             uint4 sa = make_uint4(0u, 0u, 0u, 0u), sb = make_uint4(0u, 0u, 0u, 0u);
             if (active && (uint32_t)len <= probe_len) ld_slot256(J.cache + slot_i, sa, sb);
             bool hit = sa.x == key[0] && sa.y == key[1] && sa.z == key[2] && sa.w == key[3];
-            if (!hit && (sa.x | sa.y) != 0u) {       // the slot holds another pretoken: walk on (few lanes, few steps)
+            if (HUT_RARE(!hit && (sa.x | sa.y) != 0u)) {       // the slot holds another pretoken: walk on (few lanes, few steps)
                 uint32_t i = slot_i;
 #pragma unroll 1
                 for (int p = 1; p < CACHE_PROBES; ++p) {
@@ -431,7 +434,7 @@ __device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileS
                 }
             }
             uint32_t c = hit ? val_count(sb.x) : 0u;  // count 0: the value is still being written -> a miss
-            if (!__any_sync(FULL, active && c == 0u)) {
+            if (HUT_USUAL(!__any_sync(FULL, active && c == 0u))) {
                 // ---- every pretoken of the round was answered by the cache: counts are 1..5, three ballots scan them ----
                 const uint32_t m0 = __ballot_sync(FULL, (c & 1u) != 0u), m1 = __ballot_sync(FULL, (c & 2u) != 0u),
                                m2 = __ballot_sync(FULL, (c & 4u) != 0u);
@@ -439,13 +442,13 @@ __device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileS
                 const uint32_t off = run + incl - c;
                 const uint32_t w[4] = {sb.x, sb.y, sb.z, sb.w};
                 if (c) put_hit_ids(slot + off, c, w);
-                if (tile_docs && active && dsb) doc_offsets_at(J, (unsigned long long)(g0 + s), dfirst, off);
+                if (HUT_RARE(tile_docs && active && dsb)) doc_offsets_at(J, (unsigned long long)(g0 + s), dfirst, off);
                 run += __shfl_sync(FULL, incl, 31);
                 continue;
             }
             // ---- some pretokens were not answered.  Pretokens of 16..31 bytes ask the second cache (32-byte keys) first ----
             uint32_t w[4] = {sb.x, sb.y, sb.z, sb.w};
-            if (active && !keyed && len <= CACHE2_KEY_MAX && M.cache_ok) {
+            if (HUT_RARE(active && !keyed && len <= CACHE2_KEY_MAX && M.cache_ok)) {
                 uint32_t k32[8];
                 build_key32(ws.text, sm.kmask32, s, len, PFX ? dsb : 0u, k32);
                 hit = cache2_lookup(J, k32, w);
@@ -472,7 +475,7 @@ __device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileS
                 const uint32_t off = run + inc - cc;     // position of this lane's ids (or room) in the tile's slot
                 if (c) put_hit_ids(slot + off, c, w);
                 if (__any_sync(FULL, state != 0)) rare_round(M, J, sm, ws, tile, s, e, first, cc, off, state);
-                if (tile_docs && active && dsb) doc_offsets_at(J, (unsigned long long)(g0 + s), dfirst, off);
+                if (HUT_RARE(tile_docs && active && dsb)) doc_offsets_at(J, (unsigned long long)(g0 + s), dfirst, off);
                 run += round_total;
             }
         }
