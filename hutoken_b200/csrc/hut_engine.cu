@@ -186,6 +186,9 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     dm.cache_ok = (m->max_value < (1 << 20)) ? 1 : 0;  // ids are packed as signed 21-bit fields
     dm.kmax = m->max_sym_per_char ? m->max_sym_per_char : 1;
     dm.miss_len_max = MAXW;
+    // a queued miss packs its position in the tile's staging slot into 18 bits (hut_tile.cuh q_pack): a model whose slots
+    // are larger leaves every miss to the long-path kernels
+    if (992ull * dm.kmax + 960ull * (m->n_prefix_syms + m->n_prefix_alone + 1) >= (1ull << 18)) dm.miss_len_max = 0;
     dm.first_extra = m->has_prefix ? (m->n_prefix_syms > m->n_prefix_alone ? m->n_prefix_syms : m->n_prefix_alone) : 0u;
     CU(ctx, upload(d, m->sym_off, 257, &dm.sym_off));
     CU(ctx, upload(d, m->sym_pool, m->sym_off[256], &dm.sym_pool));
@@ -223,6 +226,11 @@ static int dev_init(hut_ctx* ctx, hut_dev* d, int device) {
     CU(ctx, cudaMemset(d->cache2, 0, sizeof(CacheSlot2) << d->cache2_bits));
     CU(ctx, cudaMalloc(&d->cut, sizeof(CutRanges)));
 
+    if (getenv("HUTOKEN_B200_CARVEOUT")) {  // experiment: shared-memory carve-out of tile_kernel in percent of the maximum
+        const int pc = atoi(getenv("HUTOKEN_B200_CARVEOUT"));
+        CU(ctx, cudaFuncSetAttribute(tile_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, pc));
+        CU(ctx, cudaFuncSetAttribute(tile_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, pc));
+    }
     int per_sm = 0, sms = 0;
     if (m->has_prefix) CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile_kernel<true>, NT, 0));
     else CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tile_kernel<false>, NT, 0));
@@ -410,7 +418,8 @@ static int launch_shard(hut_ctx* ctx, hut_dev* d, hut_flight* f, const uint8_t* 
     if (n_docs >= 0xFFFFFFF0ull) return set_err(ctx, HUT_STATUS_ARG, "%s", "too many documents in one shard");
     if ((uintptr_t)d_bytes & 15) return set_err(ctx, HUT_STATUS_ARG, "%s", "device text buffer must be 16-byte aligned");
     const uint64_t ntiles64 = (n_bytes + OWN - 1) / OWN;
-    if (ntiles64 >= 0x7FFFFFF0ull) return set_err(ctx, HUT_STATUS_ARG, "%s", "shard too large (max 2 TB)");
+    if (ntiles64 >= 0x7FFFFFF0ull || n_bytes >= (1ull << 38))  // byte positions of queued misses are packed into 38 bits
+        return set_err(ctx, HUT_STATUS_ARG, "%s", "shard too large (max 256 GiB per device and call)");
     const uint32_t ntiles = (uint32_t)ntiles64;
     if (ntiles == 0) {
         CU(ctx, cudaMemsetAsync(d_tok_offsets, 0, (n_docs + 1) * sizeof(uint64_t), st));

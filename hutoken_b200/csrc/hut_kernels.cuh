@@ -415,17 +415,18 @@ __device__ __forceinline__ bool cache_lookup_from(const Job& J, const uint32_t x
 }
 
 // ---- second cache: keys of 16..31 text bytes ----
-__device__ __forceinline__ void build_key32(const uint8_t* text, const uint4* kmask32, int s, int len, uint32_t first,
-                                            uint32_t x[8]) {
+__device__ __forceinline__ void build_key32(const uint8_t* text, int s, int len, uint32_t first, uint32_t x[8]) {
     const uint32_t* w = reinterpret_cast<const uint32_t*>(text + (s & ~3));
     const uint32_t sh = (uint32_t)(s & 3) * 8u;
     uint32_t r[9];
 #pragma unroll
     for (int i = 0; i < 9; ++i) r[i] = w[i];
-    const uint4 m0 = kmask32[2 * len], m1 = kmask32[2 * len + 1];
-    const uint32_t m[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
 #pragma unroll
-    for (int i = 0; i < 8; ++i) x[i] = __funnelshift_r(r[i], r[i + 1], sh) & m[i];
+    for (int i = 0; i < 8; ++i) {  // byte masks worked out here (rare path): no table in shared memory
+        const int rem = len - 4 * i;
+        const uint32_t m = rem >= 4 ? 0xFFFFFFFFu : (rem <= 0 ? 0u : ((1u << (8 * rem)) - 1u));
+        x[i] = __funnelshift_r(r[i], r[i + 1], sh) & m;
+    }
     x[7] |= (0x80u | (first << 5) | (uint32_t)len) << 24;
 }
 

@@ -30,7 +30,7 @@ struct __align__(16) WarpSm {
     uint8_t text[TEXTB];        // span bytes: [tile_start - 32, tile_start + 992 + 16), then zero padding
     uint32_t dsm[CHUNK + 4];    // per chunk: document starts
     uint16_t pstart[SPAN + 8];  // span positions of the boundaries in chunks 1..31 (31 = halo), then the end sentinel
-    uint4 q[MISS_CLASSES][64];  // cache misses waiting for a full batch, by length class: pos_off (x, y), meta (z), tile (w)
+    unsigned long long q[MISS_CLASSES][64];  // cache misses waiting for a full batch (by length class), one word each: see q_pack
     unsigned long long mbar;
     // what only the rounds with cache misses / long pretokens touch lives here, not in registers (warp-uniform values,
     // written by lane 0 or by all lanes alike)
@@ -44,7 +44,6 @@ struct __align__(16) WarpSm {
 
 struct TileSm {
     uint4 kmask[16];            // kmask[len]: byte masks of a 16-byte key holding len text bytes
-    uint4 kmask32[64];          // kmask32[2 * len], [2 * len + 1]: the same for the 32-byte keys of the second cache
     uint32_t byte1[256];
     WarpSm w[WPB];
 };
@@ -116,26 +115,29 @@ __device__ __forceinline__ void defer_push(const Job& J, uint32_t tile, unsigned
     tail = idx;
 }
 
+// A queued miss in one word: byte position (38 bits: 256 GiB per shard), position of its room in the tile's staging
+// slot (18 bits), length in bytes (6 bits), "first pretoken of its document" (1 bit).  Its tile is position / OWN, its
+// room the worst case tile_kernel reserved: one id per symbol (+ the prefix ids of a first pretoken).
+__device__ __forceinline__ unsigned long long q_pack(unsigned long long pos, uint32_t loff, uint32_t len, uint32_t first) {
+    return pos | ((unsigned long long)loff << 38) | ((unsigned long long)len << 56) | ((unsigned long long)first << 62);
+}
+
 // merges the first n (<= 32) queued cache misses, one per lane (merge_entry).  The room a pretoken of another tile
 // did not use is subtracted from that tile's count here; for the tile in progress it is returned (warp sum).
-#ifdef HUT_BATCH_NOINLINE
-__device__ __noinline__ uint32_t run_batch(const DevModel& M, const Job& J, const uint32_t* byte1, const uint4* q,
-#else
-__device__ __forceinline__ uint32_t run_batch(const DevModel& M, const Job& J, const uint32_t* byte1, const uint4* q,
-#endif
+__device__ __forceinline__ uint32_t run_batch(const DevModel& M, const Job& J, const uint32_t* byte1, const unsigned long long* q,
                                            uint32_t n, uint32_t cur_tile) {
     const uint32_t lane = threadIdx.x & 31;
     uint32_t slack = 0;
     if (lane < n) {
-        const uint4 E = q[lane];
-        const unsigned long long pos_off = E.x | ((unsigned long long)E.y << 32);
-        const unsigned long long pos = pos_off & ((1ull << 40) - 1);
-        const uint32_t loff = (uint32_t)(pos_off >> 40);
-        const uint32_t len = E.z & 0xFFu, first = (E.z >> 8) & 1u, room = E.z >> 16;
-        slack = merge_entry<MISS_SMALL>(M, J, byte1, pos, len, first, room,
-                                        stage_slot(J, E.w) + loff);
-        if (slack && E.w != cur_tile) {
-            atomicSub(&J.tot[E.w], slack);
+        const unsigned long long E = q[lane];
+        const unsigned long long pos = E & ((1ull << 38) - 1);
+        const uint32_t loff = (uint32_t)(E >> 38) & 0x3FFFFu;
+        const uint32_t len = (uint32_t)(E >> 56) & 63u, first = (uint32_t)(E >> 62) & 1u;
+        const uint32_t room = len * M.kmax + (first ? M.first_extra : 0u);
+        const uint32_t tile = (uint32_t)(pos / (unsigned long long)OWN);
+        slack = merge_entry<MISS_SMALL>(M, J, byte1, pos, len, first, room, stage_slot(J, tile) + loff);
+        if (slack && tile != cur_tile) {
+            atomicSub(&J.tot[tile], slack);
             slack = 0;
         }
     }
@@ -179,23 +181,22 @@ __device__ __forceinline__ void rare_round(const DevModel& M, const Job& J, Tile
         // unused of its room stays behind as HOLEs, which compact_kernel drops ----
         if (__any_sync(FULL, state == 2)) {
             uint32_t slack = 0, nb = 0;
-            const unsigned long long po = (unsigned long long)(g0 + s) | ((unsigned long long)off << 40);
+            const unsigned long long po = q_pack((unsigned long long)(g0 + s), off, (uint32_t)len, first);
             const uint32_t mycls = (MISS_CLASSES > 1 && len > MISS_SHORT) ? 1u : 0u;
 #pragma unroll 1
             for (uint32_t cls = 0; cls < (uint32_t)MISS_CLASSES; ++cls) {  // one copy of the merge code for all classes
                 const uint32_t m2 = __ballot_sync(FULL, state == 2 && mycls == cls);
                 if (!m2) continue;
-                uint4* const q = ws.q[cls];
+                unsigned long long* const q = ws.q[cls];
                 uint32_t qn = ws.qn[cls];
                 if (state == 2 && mycls == cls)
-                    q[qn + __popc(m2 & lt_mask)] = make_uint4((uint32_t)po, (uint32_t)(po >> 32),
-                                                              (uint32_t)len | (first << 8) | (c << 16), tile);
+                    q[qn + __popc(m2 & lt_mask)] = po;
                 qn += __popc(m2);
                 __syncwarp();
                 while (qn >= 32) {
                     slack += run_batch(M, J, sm.byte1, q, 32, tile);
                     nb += 32;
-                    uint4 t = make_uint4(0, 0, 0, 0);
+                    unsigned long long t = 0;
                     if (lane + 32 < qn) t = q[lane + 32];
                     __syncwarp();
                     if (lane + 32 < qn) q[lane] = t;
@@ -253,11 +254,6 @@ __device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileS
     if (tid < 16) {
         auto wm = [&](int rem) -> uint32_t { return rem >= 4 ? 0xFFFFFFFFu : (rem <= 0 ? 0u : ((1u << (8 * rem)) - 1u)); };
         sm.kmask[tid] = make_uint4(wm(tid), wm(tid - 4), wm(tid - 8), wm(tid - 12));
-    }
-    if (tid < 64) {
-        const int len = tid >> 1, o = (tid & 1) * 16;
-        auto wm = [&](int rem) -> uint32_t { return rem >= 4 ? 0xFFFFFFFFu : (rem <= 0 ? 0u : ((1u << (8 * rem)) - 1u)); };
-        sm.kmask32[tid] = make_uint4(wm(len - o), wm(len - o - 4), wm(len - o - 8), wm(len - o - 12));
     }
     if (lane == 0) {
         mbar_init(&ws.mbar, 1);
@@ -450,7 +446,7 @@ __device__ __forceinline__ void tile_body(const DevModel& M, const Job& J, TileS
             uint32_t w[4] = {sb.x, sb.y, sb.z, sb.w};
             if (HUT_RARE(active && !keyed && len <= CACHE2_KEY_MAX && M.cache_ok)) {
                 uint32_t k32[8];
-                build_key32(ws.text, sm.kmask32, s, len, PFX ? dsb : 0u, k32);
+                build_key32(ws.text, s, len, PFX ? dsb : 0u, k32);
                 hit = cache2_lookup(J, k32, w);
                 c = hit ? val_count(w[0]) : 0u;
             }
