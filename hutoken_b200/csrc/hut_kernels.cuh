@@ -629,11 +629,14 @@ __device__ __forceinline__ uint32_t merge_entry(const DevModel& M, const Job& J,
     }
     // KEY[k] = rank of the pair starting at position k in bits 6.., k below (ranks are dense, < 2^21: hut_model.c), all
     // ones if the pair does not merge: the minimum over KEY is the reference's next merge, leftmost among equal ranks
+    // with distinct values a unit's rank is the unit itself (rank_of_unit): the key then holds the merged unit, and the
+    // array of merged units is neither written nor read (a third less local memory in the SM's L1)
+    const bool dv = M.distinct_values != 0;
     auto keyof = [&](uint32_t mg, uint32_t k) -> uint32_t { return mg == NONE ? 0xFFFFFFFFu : ((rank_of_unit(M, mg) << 6) | k); };
 #pragma unroll 1
     for (uint32_t k = 0; k < m0; ++k) {
         const uint32_t mg = k + 1 < m0 ? pair_probe(M, U[k], U[k + 1]) : NONE;
-        MG[k] = mg;
+        if (!dv) MG[k] = mg;
         KEY[k] = keyof(mg, k);
     }
 #pragma unroll 1
@@ -647,11 +650,11 @@ __device__ __forceinline__ uint32_t merge_entry(const DevModel& M, const Job& J,
             bk = min(min(bk, v.x), min(min(v.y, v.z), v.w));
         }
         if (bk == 0xFFFFFFFFu) break;
-        const uint32_t j = bk & 63u, mu = MG[j];
+        const uint32_t j = bk & 63u, mu = dv ? (bk >> 6) : MG[j];
         const uint32_t r = j + 1 + (uint32_t)(al_ffs(alive >> (j + 1)) - 1);  // right partner of j
         alive &= ~((AL)1 << r);
         U[j] = mu;
-        MG[r] = NONE;
+        if (!dv) MG[r] = NONE;
         KEY[r] = 0xFFFFFFFFu;
         const AL below = alive & (((AL)1 << j) - (AL)1), above = r + 1 < (uint32_t)(8 * sizeof(AL)) ? (alive >> (r + 1)) : (AL)0;
         const int l = below ? al_top(below) : -1;
@@ -660,10 +663,10 @@ __device__ __forceinline__ uint32_t merge_entry(const DevModel& M, const Job& J,
         uint32_t ml, mr;
         pair_probe2(M, ul, mu, ur, &ml, &mr);
         if (l >= 0) {
-            MG[l] = ml;
+            if (!dv) MG[l] = ml;
             KEY[l] = keyof(ml, (uint32_t)l);
         }
-        MG[j] = mr;  // NONE when j is the last symbol now
+        if (!dv) MG[j] = mr;  // NONE when j is the last symbol now
         KEY[j] = keyof(mr, j);
     }
     // ---- ids into the reserved room, HOLEs behind them ----
