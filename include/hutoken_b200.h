@@ -53,7 +53,8 @@ typedef struct hut_options {
     uint32_t big_slots;        /* working areas (= CTAs of huge_kernel) for pretokens of more than 4160 symbols; 0 = default
                                   (8; 2 when max_pretoken > 64 MiB).  Allocated when the first such pretoken shows up. */
     uint32_t chunk_mb;         /* hut_encode_batch streams the batch through the devices in chunks of about this many
-                                  MiB so that upload, kernels and download overlap; 0 = default (32) */
+                                  MiB so that upload, kernels and download overlap; 0 = default (32).  hut_decode_batch
+                                  does the same with chunks of whole documents holding about this many MiB of ids. */
 } hut_options;
 
 /* Replaces p_initialize (lib.c:185-666) + initialize_context (lib.c:128-183): loads the files, derives the
@@ -110,7 +111,9 @@ typedef struct hut_text_result {
  * reference's message "Element must be non-negative and less than vocab size." (core.c:522-530).  The text may
  * contain 0x00 bytes (a replacement standing for byte 0); the reference's binding cuts each string there
  * (PyUnicode_FromString, lib.c:946,1066) and so does ours.  The result lives in pinned host memory owned by the
- * context until the next decode call.  Runs on the context's first device. */
+ * context until the next decode call.  Runs on the context's first device; a batch of more than one and a half
+ * chunks (hut_options.chunk_mb) is streamed through it in chunks of whole documents, ids going up while text comes
+ * down. */
 int hut_decode_batch(hut_ctx* ctx, const int32_t* ids, const uint64_t* tok_offsets, uint64_t n_docs,
                      hut_text_result* result);
 
