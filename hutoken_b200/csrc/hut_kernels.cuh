@@ -14,7 +14,8 @@
  *                   (merge_entry)                       <- bpe_encode_arena_string (core.c:66-209), MinPQ (queue.c),
  *                                                          get_pair_rank_from_strings (core.c:700-722), hashmap.c
  *                   ids -> the tile's slot of the staging buffer, in order; per-tile counts
- *   long_kernel     pretokens of 33 .. 4160 symbols: one CTA each, tournament tree over (rank, position)
+ *   mid_kernel      deferred pretokens of up to 1024 / 4096 symbols: one warp each, arrays in shared memory
+ *   long_kernel     the rest up to 4160 symbols: one CTA each, tournament tree over (rank, position)
  *   huge_kernel     longer ones: cooperative rounds (all pairs of the minimum rank at once, checked per round)
  *   scan kernels    exclusive scan of the per-tile id counts      <- IntVector growth (vector.c:41-55)
  *   compact_kernel  staging slots -> dense int32 ids, coalesced   <- list building (lib.c:699-715, 810-860)
