@@ -519,6 +519,7 @@ def run_ours(args):
                 e2e_dec = {"value": int(res_t.n_bytes) / (dec_ms * 1e-3) / 1e6, "unit": "decoded MB/s", "ms_per_call": dec_ms,
                            "h2d_bytes": int(4 * len(ids_h) + 8 * (nd_h + 1)), "d2h_bytes": int(res_t.n_bytes) + 8 * (nd_h + 1),
                            "round_trip_equals_input": same, "path": eng.decode_stats()["path"],
+                           "scope": "rank 0's own shard (not summed over ranks; at N > 1 all ranks share the host link)",
                            "api": "hut_decode_batch (ids in pinned host memory -> text in pinned host memory)"}
             except Exception as ex:  # the decode leg must never take the encode numbers down with it
                 e2e_dec = {"error": str(ex)[:200]}
