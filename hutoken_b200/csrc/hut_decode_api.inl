@@ -1,10 +1,12 @@
 /* hut_decode_batch / hut_decode_device: host orchestration of the decode kernels (hut_decode.cuh).
- * Included at the end of hut_engine.cu (needs hut_ctx / hut_dev).  Device 0 of the context does the work: decode is
- * a per-document gather + scan, and ranks of a multi-GPU job each decode their own documents. */
+ * Included at the end of hut_engine.cu (needs hut_ctx / hut_dev).  Device 0 of the context does the work of the
+ * device-resident calls and of small host batches; a large host batch is streamed in document chunks dealt round-robin
+ * to all devices of the context (decode_chunked), each of which holds its own decode tables. */
 
 struct hut_decstate {
     DecModel dm;
     int ready;
+    int dev;  // index into ctx->dev of the device this state lives on
     int32_t* d_ids;
     size_t d_ids_cap;
     unsigned long long* d_tok;
@@ -106,13 +108,14 @@ static int dec_init_token_tables(hut_ctx* ctx, hut_decstate* s);
 /* decode-side device state, created by the first hut_decode_* call.  A failure half way leaves nothing behind: the
  * tables uploaded so far are released (they are the newest entries of the device's allocation list) and the next call
  * starts again from scratch. */
-static int dec_init(hut_ctx* ctx) {
-    if (ctx->dec && ctx->dec->ready) return HUT_STATUS_OK;
-    hut_dev* d = &ctx->dev[0];
+static int dec_init_on(hut_ctx* ctx, hut_decstate** slot, int dev) {
+    if (*slot && (*slot)->ready) return HUT_STATUS_OK;
+    hut_dev* d = &ctx->dev[dev];
     CU(ctx, cudaSetDevice(d->device));
-    if (!ctx->dec) ctx->dec = (hut_decstate*)calloc(1, sizeof(hut_decstate));
-    if (!ctx->dec) return set_err(ctx, HUT_STATUS_MEMORY, "%s", "out of memory");
-    hut_decstate* s = ctx->dec;
+    if (!*slot) *slot = (hut_decstate*)calloc(1, sizeof(hut_decstate));
+    if (!*slot) return set_err(ctx, HUT_STATUS_MEMORY, "%s", "out of memory");
+    hut_decstate* s = *slot;
+    s->dev = dev;
     const int first = d->nalloc;
     const int rc = dec_init_tables(ctx, s);
     if (rc != HUT_STATUS_OK) {
@@ -121,14 +124,16 @@ static int dec_init(hut_ctx* ctx) {
         if (s->ev[0]) cudaEventDestroy(s->ev[0]);
         if (s->ev[1]) cudaEventDestroy(s->ev[1]);
         memset(s, 0, sizeof *s);
+        s->dev = dev;
     }
     return rc;
 }
+static int dec_init(hut_ctx* ctx) { return dec_init_on(ctx, &ctx->dec, 0); }
 
 /* Decoded bytes of every token (hut_decode.cuh, token-wise path): lengths and flags first, offsets by a host scan,
  * then the bytes; the 16-byte slots and the one-byte lengths are put together on the host. */
-static int dec_init_token_tables(hut_ctx* ctx, hut_decstate* s) {
-    hut_dev* d = &ctx->dev[0];
+static int dec_init_token_tables(hut_ctx* ctx, hut_decstate* s) {  // on device s->dev (current)
+    hut_dev* d = &ctx->dev[s->dev];
     DecModel& D = s->dm;
     const uint32_t V = D.vocab_lines;
     uint8_t* kids = nullptr;
@@ -176,7 +181,7 @@ static int dec_init_token_tables(hut_ctx* ctx, hut_decstate* s) {
 }
 
 static int dec_init_tables(hut_ctx* ctx, hut_decstate* s) {
-    hut_dev* d = &ctx->dev[0];
+    hut_dev* d = &ctx->dev[s->dev];
     const hut_model* m = ctx->model;
     DecModel& D = s->dm;
     CU(ctx, upload(d, m->dec_off, (size_t)m->vocab_lines + 1, &D.dec_off));
@@ -220,10 +225,9 @@ static int dec_scan(hut_ctx* ctx, hut_decstate* s, const uint32_t* in, unsigned 
 
 /* ids + tok_off resident on device 0 -> packed text + text_off on the device (buffers owned by the context).
  * *n_text receives the text length.  Synchronises the stream twice (raw length, text length). */
-static int dec_run(hut_ctx* ctx, const int32_t* d_ids, unsigned long long n_ids, const unsigned long long* d_tok,
-                   unsigned long long n_docs, unsigned long long* n_text, cudaStream_t st) {
-    hut_decstate* s = ctx->dec;
-    hut_dev* d = &ctx->dev[0];
+static int dec_run(hut_ctx* ctx, hut_decstate* s, const int32_t* d_ids, unsigned long long n_ids,
+                   const unsigned long long* d_tok, unsigned long long n_docs, unsigned long long* n_text, cudaStream_t st) {
+    hut_dev* d = &ctx->dev[s->dev];
     const DecModel& D = s->dm;
     s->last_launches = 0;
     const unsigned long long nsub = (n_ids + DEC_SUB - 1) / DEC_SUB;
@@ -377,15 +381,24 @@ static int decode_small(hut_ctx* ctx, const int32_t* ids, const uint64_t* tok_of
     return HUT_STATUS_OK;
 }
 
-/* A large host batch goes through the device in chunks of whole documents: the ids of chunk k + 1 are uploaded (copy
- * stream, second set of input buffers) while chunk k is decoded and its text downloaded (main stream), so the link is
- * busy in both directions at once; the kernels (2 ms per GiB of text) disappear behind the copies.  Documents are
- * decoded independently of each other (core.c:513-581 is called per document), so cutting between them changes nothing. */
+/* A large host batch goes through the devices in chunks of whole documents, chunk c on device c mod ndev: the ids of a
+ * device's next chunk are uploaded (its copy-in stream, second set of input buffers) while its current chunk is decoded
+ * (main stream) and the text of the one before leaves (copy-out stream, second set of output buffers), so the link is
+ * busy in both directions at once and the kernels (2 ms per GiB of text) disappear behind the copies.  Documents are
+ * decoded independently of each other (core.c:513-581 is called per document), so cutting between them changes nothing.
+ * The host visits the chunks in order (a chunk's place in the text is known once the chunks before it have reported their
+ * lengths); what it has queued on the other devices runs meanwhile. */
 static int decode_chunked(hut_ctx* ctx, const int32_t* ids, const uint64_t* tok_offsets, uint64_t n_docs,
                           unsigned long long chunk_ids, hut_text_result* result) {
-    hut_decstate* s = ctx->dec;
-    hut_dev* d = &ctx->dev[0];
-    cudaStream_t st = d->stream, sin = d->s_in, sout = d->s_out;
+    const int ndev = ctx->ndev;
+    hut_decstate* S[MAX_DEV];
+    S[0] = ctx->dec;
+    for (int i = 1; i < ndev; ++i) {
+        int rc = dec_init_on(ctx, &ctx->dec_x[i], i);
+        if (rc != HUT_STATUS_OK) return rc;
+        S[i] = ctx->dec_x[i];
+    }
+    hut_decstate* const s0 = ctx->dec;  /* owner of the pinned result */
     std::vector<uint64_t> cut;  /* chunk c = documents [cut[c], cut[c + 1]) */
     cut.push_back(0);
     for (uint64_t i = 0; i < n_docs;) {
@@ -401,23 +414,37 @@ static int decode_chunked(hut_ctx* ctx, const int32_t* ids, const uint64_t* tok_
         max_ids = ni > max_ids ? ni : max_ids;
         max_docs = nd > max_docs ? nd : max_docs;
     }
-    for (int b = 0; b < 2; ++b) {
-        CU(ctx, grow(&s->c_ids[b], &s->c_ids_cap[b], max_ids + 1));
-        CU(ctx, grow(&s->c_tok[b], &s->c_tok_cap[b], max_docs + 1));
-        CU(ctx, grow_host(&s->h_ctok[b], &s->h_ctok_cap[b], max_docs + 1, false));
-        if (!s->ev_up[b]) CU(ctx, cudaEventCreateWithFlags(&s->ev_up[b], cudaEventDisableTiming));
-        if (!s->ev_k[b]) CU(ctx, cudaEventCreateWithFlags(&s->ev_k[b], cudaEventDisableTiming));
-        if (!s->ev_dl[b]) CU(ctx, cudaEventCreateWithFlags(&s->ev_dl[b], cudaEventDisableTiming));
+    for (int i = 0; i < ndev && (size_t)i < nch; ++i) {
+        hut_decstate* s = S[i];
+        CU(ctx, cudaSetDevice(ctx->dev[i].device));
+        for (int b = 0; b < 2; ++b) {
+            CU(ctx, grow(&s->c_ids[b], &s->c_ids_cap[b], max_ids + 1));
+            CU(ctx, grow(&s->c_tok[b], &s->c_tok_cap[b], max_docs + 1));
+            CU(ctx, grow_host(&s->h_ctok[b], &s->h_ctok_cap[b], max_docs + 1, false));
+            if (!s->ev_up[b]) CU(ctx, cudaEventCreateWithFlags(&s->ev_up[b], cudaEventDisableTiming));
+            if (!s->ev_k[b]) CU(ctx, cudaEventCreateWithFlags(&s->ev_k[b], cudaEventDisableTiming));
+            if (!s->ev_dl[b]) CU(ctx, cudaEventCreateWithFlags(&s->ev_dl[b], cudaEventDisableTiming));
+        }
     }
-    auto swap_out = [&]() {  /* odd chunks use the second set of output buffers */
-        std::swap(s->d_text, s->x_text);
-        std::swap(s->d_text_cap, s->x_text_cap);
-        std::swap(s->d_text_off, s->x_text_off);
-        std::swap(s->d_text_off_cap, s->x_text_off_cap);
+    CU(ctx, grow_host(&s0->h_text_off, &s0->h_text_off_cap, (size_t)n_docs + 1, false));
+    auto sync_all = [&](bool out_only) -> int {
+        for (int i = 0; i < ndev; ++i) {
+            CU(ctx, cudaSetDevice(ctx->dev[i].device));
+            CU(ctx, cudaStreamSynchronize(ctx->dev[i].s_out));
+            if (!out_only) {
+                CU(ctx, cudaStreamSynchronize(ctx->dev[i].s_in));
+                CU(ctx, cudaStreamSynchronize(ctx->dev[i].stream));
+            }
+        }
+        return HUT_STATUS_OK;
     };
-    CU(ctx, grow_host(&s->h_text_off, &s->h_text_off_cap, (size_t)n_docs + 1, false));
-    auto upload = [&](size_t c) -> int {  /* the buffers of chunk c - 2 are free: dec_run(c - 2) has synchronised */
-        const int b = (int)(c & 1);
+    /* chunk c uses buffer set (c / ndev) & 1 of device c % ndev; the set's previous user is chunk c - 2 * ndev, whose
+     * kernels the host has waited for (end of its visit) */
+    auto upload = [&](size_t c) -> int {
+        const int dv = (int)(c % (size_t)ndev), b = (int)((c / (size_t)ndev) & 1);
+        hut_decstate* s = S[dv];
+        CU(ctx, cudaSetDevice(ctx->dev[dv].device));
+        cudaStream_t sin = ctx->dev[dv].s_in;
         const uint64_t lo = cut[c], hi = cut[c + 1], base = tok_offsets[lo];
         for (uint64_t i = lo; i <= hi; ++i) s->h_ctok[b][i - lo] = tok_offsets[i] - base;
         CU(ctx, cudaMemcpyAsync(s->c_tok[b], s->h_ctok[b], (size_t)(hi - lo + 1) * sizeof(unsigned long long),
@@ -428,73 +455,86 @@ static int decode_chunked(hut_ctx* ctx, const int32_t* ids, const uint64_t* tok_
         CU(ctx, cudaEventRecord(s->ev_up[b], sin));
         return HUT_STATUS_OK;
     };
-    int rc = upload(0);
-    if (rc != HUT_STATUS_OK) return rc;
+    int rc = HUT_STATUS_OK;
+    for (size_t c = 0; c < nch && c < (size_t)ndev; ++c) {
+        rc = upload(c);
+        if (rc != HUT_STATUS_OK) return rc;
+    }
     std::vector<unsigned long long> tbase(nch + 1, 0);
     float ms_sum = 0;
     unsigned launches = 0;
     int path = 1;
     for (size_t c = 0; c < nch; ++c) {
-        const int b = (int)(c & 1);
+        const int dv = (int)(c % (size_t)ndev), b = (int)((c / (size_t)ndev) & 1);
+        hut_decstate* s = S[dv];
+        hut_dev* d = &ctx->dev[dv];
+        cudaStream_t st = d->stream, sout = d->s_out;
         const uint64_t lo = cut[c], hi = cut[c + 1];
-        if (c + 1 < nch) {
-            /* h_ctok / c_ids of the other set were last read by chunk c - 1, whose dec_run has synchronised the main stream;
-             * its upload finished before that */
-            rc = upload(c + 1);
-            if (rc != HUT_STATUS_OK) return rc;
+        if (c + (size_t)ndev < nch) {  /* this device's next chunk: on its way while this one is decoded */
+            rc = upload(c + (size_t)ndev);
+            if (rc != HUT_STATUS_OK) break;
         }
+        CU(ctx, cudaSetDevice(d->device));
         CU(ctx, cudaStreamWaitEvent(st, s->ev_up[b], 0));
-        if (c >= 2) CU(ctx, cudaStreamWaitEvent(st, s->ev_dl[b], 0)); /* the text of chunk c - 2 has left this output set */
+        if (c >= 2 * (size_t)ndev) CU(ctx, cudaStreamWaitEvent(st, s->ev_dl[b], 0)); /* this output set's last text has left */
+        auto swap_out = [&]() {  /* odd visits of a device use its second set of output buffers */
+            std::swap(s->d_text, s->x_text);
+            std::swap(s->d_text_cap, s->x_text_cap);
+            std::swap(s->d_text_off, s->x_text_off);
+            std::swap(s->d_text_off_cap, s->x_text_off_cap);
+        };
         unsigned long long n_text = 0;
         if (b) swap_out();
-        rc = dec_run(ctx, s->c_ids[b], tok_offsets[hi] - tok_offsets[lo], s->c_tok[b], hi - lo, &n_text, st);
+        rc = dec_run(ctx, s, s->c_ids[b], tok_offsets[hi] - tok_offsets[lo], s->c_tok[b], hi - lo, &n_text, st);
         const uint8_t* const o_text = s->d_text;
         const unsigned long long* const o_off = s->d_text_off;
         if (b) swap_out();
-        if (rc != HUT_STATUS_OK) {
-            cudaStreamSynchronize(sin);
-            cudaStreamSynchronize(sout);
-            return rc;
-        }
+        if (rc != HUT_STATUS_OK) break;
         CU(ctx, cudaEventRecord(s->ev_k[b], st));
         launches += s->last_launches;
         if (s->last_path == 2) path = 2;
         const unsigned long long need = tbase[c] + n_text + 1;
-        if (need > s->h_text_cap) {
+        if (need > s0->h_text_cap) {
             /* room for the whole batch from the bytes per id seen so far (+ 1/8), at least what this chunk needs */
             const unsigned long long done_ids = tok_offsets[hi] - tok_offsets[0], all_ids = tok_offsets[n_docs] - tok_offsets[0];
             unsigned long long est = done_ids ? (unsigned long long)((double)(tbase[c] + n_text) / (double)done_ids * (double)all_ids) : need;
             est += est / 8 + 4096;
-            CU(ctx, cudaStreamSynchronize(sout)); /* earlier chunks' text is still on its way into the old buffer */
-            CU(ctx, grow_host(&s->h_text, &s->h_text_cap, (size_t)(est > need ? est : need), true));
+            rc = sync_all(true); /* earlier chunks' text is still on its way into the old buffer */
+            if (rc != HUT_STATUS_OK) break;
+            CU(ctx, cudaSetDevice(d->device));
+            CU(ctx, grow_host(&s0->h_text, &s0->h_text_cap, (size_t)(est > need ? est : need), true));
         }
-        /* download on its own stream: the next chunk's kernels (other output set) do not wait for it */
+        /* download on the device's copy-out stream: its next chunk's kernels (other output set) do not wait for it */
         CU(ctx, cudaStreamWaitEvent(sout, s->ev_k[b], 0));
-        if (n_text) CU(ctx, cudaMemcpyAsync(s->h_text + tbase[c], o_text, (size_t)n_text, cudaMemcpyDeviceToHost, sout));
+        if (n_text) CU(ctx, cudaMemcpyAsync(s0->h_text + tbase[c], o_text, (size_t)n_text, cudaMemcpyDeviceToHost, sout));
         /* chunk-local text offsets of the chunk's documents (the chunk's end is the next one's start) */
-        CU(ctx, cudaMemcpyAsync(s->h_text_off + lo, o_off, (size_t)(hi - lo) * sizeof(unsigned long long),
+        CU(ctx, cudaMemcpyAsync(s0->h_text_off + lo, o_off, (size_t)(hi - lo) * sizeof(unsigned long long),
                                 cudaMemcpyDeviceToHost, sout));
         CU(ctx, cudaEventRecord(s->ev_dl[b], sout));
         tbase[c + 1] = tbase[c] + n_text;
-        /* the events of dec_run are re-recorded by the next chunk: read this chunk's kernel time once it is done (the
-         * next dec_run synchronises the main stream anyway; the copies of both directions are in flight meanwhile) */
+        /* the events of dec_run are re-recorded by the device's next chunk: read this chunk's kernel time once it is done
+         * (the copies of both directions, and the other devices, carry on meanwhile) */
         CU(ctx, cudaEventSynchronize(s->ev[1]));
         float ms = 0;
         cudaEventElapsedTime(&ms, s->ev[0], s->ev[1]);
         ms_sum += ms;
     }
-    CU(ctx, cudaStreamSynchronize(sout));
-    CU(ctx, cudaStreamSynchronize(st));
+    {
+        const int rc2 = sync_all(false);
+        if (rc == HUT_STATUS_OK) rc = rc2;
+    }
+    CU(ctx, cudaSetDevice(ctx->dev[0].device));
+    if (rc != HUT_STATUS_OK) return rc;
     for (size_t c = 1; c < nch; ++c)
-        for (uint64_t i = cut[c]; i < cut[c + 1]; ++i) s->h_text_off[i] += tbase[c];
-    s->h_text_off[n_docs] = tbase[nch];
-    if (!s->h_text) CU(ctx, grow_host(&s->h_text, &s->h_text_cap, 16, false));
-    s->h_text[tbase[nch]] = 0;
-    s->last_ms = ms_sum;
-    s->last_launches = launches;
-    s->last_path = path;
-    result->text = s->h_text;
-    result->text_offsets = (const uint64_t*)s->h_text_off;
+        for (uint64_t i = cut[c]; i < cut[c + 1]; ++i) s0->h_text_off[i] += tbase[c];
+    s0->h_text_off[n_docs] = tbase[nch];
+    if (!s0->h_text) CU(ctx, grow_host(&s0->h_text, &s0->h_text_cap, 16, false));
+    s0->h_text[tbase[nch]] = 0;
+    s0->last_ms = ms_sum;
+    s0->last_launches = launches;
+    s0->last_path = path;
+    result->text = s0->h_text;
+    result->text_offsets = (const uint64_t*)s0->h_text_off;
     result->n_bytes = tbase[nch];
     result->n_docs = n_docs;
     return HUT_STATUS_OK;
@@ -537,7 +577,7 @@ extern "C" int hut_decode_batch(hut_ctx* ctx, const int32_t* ids, const uint64_t
     if (n_ids) CU(ctx, cudaMemcpyAsync(s->d_ids, ids + base, (size_t)n_ids * sizeof(int32_t), cudaMemcpyHostToDevice, st));
     CU(ctx, cudaStreamSynchronize(st)); /* h_text_off is reused below */
     unsigned long long n_text = 0;
-    rc = dec_run(ctx, s->d_ids, n_ids, s->d_tok, n_docs, &n_text, st);
+    rc = dec_run(ctx, s, s->d_ids, n_ids, s->d_tok, n_docs, &n_text, st);
     if (rc != HUT_STATUS_OK) return rc;
     CU(ctx, grow_host(&s->h_text, &s->h_text_cap, (size_t)n_text + 1, false));
     if (n_text) CU(ctx, cudaMemcpyAsync(s->h_text, s->d_text, (size_t)n_text, cudaMemcpyDeviceToHost, st));
@@ -563,7 +603,7 @@ extern "C" int hut_decode_device(hut_ctx* ctx, const int32_t* d_ids, uint64_t n_
     CU(ctx, cudaSetDevice(d->device));
     cudaStream_t st = stream ? (cudaStream_t)stream : d->stream;
     unsigned long long n_text = 0;
-    rc = dec_run(ctx, d_ids, n_ids, (const unsigned long long*)d_tok_offsets, n_docs, &n_text, st);
+    rc = dec_run(ctx, ctx->dec, d_ids, n_ids, (const unsigned long long*)d_tok_offsets, n_docs, &n_text, st);
     if (rc != HUT_STATUS_OK) return rc;
     CU(ctx, cudaStreamSynchronize(st));
     cudaEventElapsedTime(&ctx->dec->last_ms, ctx->dec->ev[0], ctx->dec->ev[1]);

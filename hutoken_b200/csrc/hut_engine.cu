@@ -100,7 +100,8 @@ static void dec_free(hut_decstate* s);
 
 struct hut_ctx {
     hut_model* model;
-    hut_decstate* dec;  // decode-side device state, created by the first hut_decode_* call
+    hut_decstate* dec;  // decode-side state of the first device, created by the first hut_decode_* call
+    hut_decstate* dec_x[MAX_DEV];  // ... of the other devices (index = device index; [0] unused): streamed host batches only
     int ndev;
     hut_dev dev[MAX_DEV];
     hut_options opt;
@@ -360,6 +361,7 @@ extern "C" void hut_destroy(hut_ctx* ctx) {
     if (!ctx) return;
     if (ctx->ndev) cudaSetDevice(ctx->dev[0].device);
     dec_free(ctx->dec);
+    for (int i = 1; i < MAX_DEV; ++i) dec_free(ctx->dec_x[i]);
     for (int i = 0; i < ctx->ndev; ++i) dev_free(&ctx->dev[i]);
     cudaFreeHost(ctx->h_ids);
     cudaFreeHost(ctx->h_tok);

@@ -111,9 +111,9 @@ typedef struct hut_text_result {
  * reference's message "Element must be non-negative and less than vocab size." (core.c:522-530).  The text may
  * contain 0x00 bytes (a replacement standing for byte 0); the reference's binding cuts each string there
  * (PyUnicode_FromString, lib.c:946,1066) and so does ours.  The result lives in pinned host memory owned by the
- * context until the next decode call.  Runs on the context's first device; a batch of more than one and a half
- * chunks (hut_options.chunk_mb) is streamed through it in chunks of whole documents, ids going up while text comes
- * down. */
+ * context until the next decode call.  A batch of up to one and a half chunks (hut_options.chunk_mb) runs on the
+ * context's first device in one piece; a larger one is streamed in chunks of whole documents, dealt round-robin to
+ * all devices of the context, ids going up while text comes down. */
 int hut_decode_batch(hut_ctx* ctx, const int32_t* ids, const uint64_t* tok_offsets, uint64_t n_docs,
                      hut_text_result* result);
 

@@ -242,6 +242,36 @@ def test_gpu_decode_streamed_chunks(name):
 
 
 @pytest.mark.gpu
+def test_gpu_decode_streamed_over_devices():
+    """A context over all distinct GPUs of the box deals the chunks of a streamed hut_decode_batch round-robin to its
+    devices (every device holds its own decode tables): text and offsets equal those of a one-device context.  The
+    same context, same forced chunk size, with one device listed twice and three times runs on any box; the distinct
+    devices need >= 2 GPUs."""
+    import torch
+    from common import engine_for
+    n = torch.cuda.device_count()
+    name = "llama_small"
+    one = engine_for(name)
+    data, offs = synth.corpus(71, 2 << 20, special_every=400)
+    ids, tok = one.encode_packed(data, offs)
+    keep = ids >= 0
+    cum = np.concatenate([[0], np.cumsum(keep)]).astype(np.uint64)
+    ids2, tok2 = ids[keep], cum[tok.astype(np.int64)]
+    want_text, want_off = one.decode_packed(ids2, tok2)
+    lists = [(0, 0), (0, 0, 0)] + ([tuple(range(n))] if n >= 2 else [])
+    for devices in lists:
+        eng = engine_for(name, devices=devices)
+        for chunk in ("700", "20000"):
+            os.environ["HUTOKEN_B200_DECODE_CHUNK_IDS"] = chunk
+            try:
+                text, toff = eng.decode_packed(ids2, tok2)
+            finally:
+                del os.environ["HUTOKEN_B200_DECODE_CHUNK_IDS"]
+            assert np.array_equal(toff, want_off), (devices, chunk)
+            assert text.tobytes() == want_text.tobytes(), (devices, chunk)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("byte_mode", [True, False])
 def test_gpu_decode_fuzz_models(byte_mode):
     from hutoken_b200 import capi
