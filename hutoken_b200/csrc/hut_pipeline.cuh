@@ -334,7 +334,10 @@ __global__ void __launch_bounds__(1024) scan2_kernel(Job J) {
         if (tid == 1023) carry_s = excl + v;
         __syncthreads();
     }
-    if (tid == 0) J.ctr->total_ids = carry_s;
+    if (tid == 0) {
+        J.ctr->total_ids = carry_s;
+        J.ctr->tile_ticket = 0;  // tile_kernel is done with it: compact_kernel hands its tiles out the same way
+    }
 }
 
 __device__ __forceinline__ unsigned long long tile_base(const Job& J, unsigned long long t) {
@@ -445,20 +448,21 @@ __device__ __forceinline__ void compact_tile_holes(const Job& J, uint32_t tile, 
 
 // staging slots -> dense ids (warp per tile); drops the HOLEs left by deferred cache misses and splices in the ids
 // of the pretokens long_kernel merged
-__device__ __forceinline__ void compact_tiles(const Job& J, const uint32_t gw, const uint32_t nw) {
-    const uint32_t lane = threadIdx.x & 31;
-    for (uint32_t tile = gw; tile < J.ntiles; tile += nw) {
+// staging slot of one tile -> dense ids (warp); drops the HOLEs left by deferred cache misses and splices in the ids of
+// the pretokens the long-path kernels merged
+__device__ __forceinline__ void compact_one_tile(const Job& J, const uint32_t tile, const uint32_t lane) {
+    {
         const uint32_t c = J.cnt[tile];
         const uint32_t ns = c & CNT_MASK;
         unsigned long long o = tile_base(J, tile);
         const int32_t* src = stage_slot(J, tile);
         if (!(c & (CNT_CHAIN | CNT_HOLES))) {
             copy_ids(J, src, o, ns);
-            continue;
+            return;
         }
         if (!(c & CNT_CHAIN)) {
             compact_tile_holes(J, tile, src, o, ns);
-            continue;
+            return;
         }
         uint32_t prev = 0;
         for (uint32_t idx = J.def_first[tile]; idx != NODOC;) {
@@ -485,8 +489,41 @@ __device__ __forceinline__ void compact_tiles(const Job& J, const uint32_t gw, c
     }
 }
 
+
+// DYN: groups of COMPACT_GROUP consecutive tiles are handed out by the ticket counter (one atomic per group: a ticket per
+// tile, 1.1 M atomics on one address inside half a millisecond, serialises in L2 -- measured)
+constexpr uint32_t COMPACT_GROUP = 8;
+template <bool DYN>
+__device__ __forceinline__ void compact_tiles(const Job& J, const uint32_t gw, const uint32_t nw) {
+    const uint32_t lane = threadIdx.x & 31;
+    uint32_t tile = gw, next_base = 0;
+    if (DYN) {
+        if (lane == 0) tile = atomicAdd(&J.ctr->tile_ticket, COMPACT_GROUP);
+        tile = __shfl_sync(0xFFFFFFFFu, tile, 0);
+        if (lane == 0) next_base = atomicAdd(&J.ctr->tile_ticket, COMPACT_GROUP);
+    }
+    for (; tile < J.ntiles;) {
+        const uint32_t this_tile = tile;
+        if (DYN) {  // next tile: the following one of the group, or the first of the group asked for a group ago
+            if (((tile + 1u) % COMPACT_GROUP) != 0u) {
+                tile = tile + 1u;
+            } else {
+                tile = __shfl_sync(0xFFFFFFFFu, next_base, 0);
+                if (lane == 0) next_base = atomicAdd(&J.ctr->tile_ticket, COMPACT_GROUP);
+            }
+        } else {
+            tile += nw;
+        }
+        compact_one_tile(J, this_tile, lane);
+    }
+}
+
 __global__ void __launch_bounds__(256, 8) compact_kernel(const Job J) {
-    compact_tiles(J, blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), gridDim.x * (blockDim.x >> 5));
+#ifdef HUT_STATIC_TILES
+    compact_tiles<false>(J, blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), gridDim.x * (blockDim.x >> 5));
+#else
+    compact_tiles<true>(J, blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), gridDim.x * (blockDim.x >> 5));
+#endif
 }
 
 // tile-local document offsets -> global ones
@@ -561,7 +598,7 @@ __global__ void __launch_bounds__(NT, 1) small_kernel(const __grid_constant__ De
             J.ctr->total_ids = run;
         }
         __syncthreads();
-        compact_tiles(J, tid >> 5, WPB);
+        compact_tiles<false>(J, tid >> 5, WPB);
         for (unsigned long long d = tid; d <= J.ndocs; d += NT) fixdoc_doc(J, d);
     }
     __syncthreads();
