@@ -492,7 +492,10 @@ __device__ __forceinline__ void compact_one_tile(const Job& J, const uint32_t ti
 
 // DYN: groups of COMPACT_GROUP consecutive tiles are handed out by the ticket counter (one atomic per group: a ticket per
 // tile, 1.1 M atomics on one address inside half a millisecond, serialises in L2 -- measured)
-constexpr uint32_t COMPACT_GROUP = 8;
+#ifndef HUT_COMPACT_GROUP
+#define HUT_COMPACT_GROUP 8
+#endif
+constexpr uint32_t COMPACT_GROUP = HUT_COMPACT_GROUP;
 template <bool DYN>
 __device__ __forceinline__ void compact_tiles(const Job& J, const uint32_t gw, const uint32_t nw) {
     const uint32_t lane = threadIdx.x & 31;
